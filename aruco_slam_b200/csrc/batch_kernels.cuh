@@ -1,0 +1,363 @@
+// Batched engine: many independent small filters (BASELINE configs C2 / C5), one CTA per
+// sequence, the whole filter — state, covariance (packed lower triangle), id table —
+// resident in shared memory for all frames of a run; observations are read once from HBM.
+//
+// Per frame (EKF.observe, extended_kalman_filter.py:58-82):
+//   association of ids on the device (first-seen order, EKF:75-78, bit-exact integers),
+//   augmentation (EKF:239-290), predict (EKF:95-105), then the update (EKF:107-156)
+//   processed in chunks of CK markers: with R = r I block-diagonal and H evaluated once
+//   at the pre-update state, chunk-sequential conditioning with the innovation corrected
+//   by H delta is algebraically the batch update (DESIGN.md "chunked update").
+//   Each chunk: G = H P, S = G H^T + R, blocked Cholesky (3x3 / 7x7 diagonal blocks
+//   factored redundantly in registers), V = L^-1 G, delta += V^T y, P -= V^T V.
+#pragma once
+#include <cstdint>
+
+#include "../../include/aruco_slam_b200.h"
+#include "model.cuh"
+
+namespace asb {
+
+struct BatchParams {
+    double* states;        // n_seq x state_stride
+    double* covs;          // n_seq x cov_stride, packed lower triangle, row-major
+    int* nlm;              // n_seq
+    int* lm_ids;           // n_seq x max_lm, ids in index order
+    int* status;           // n_seq
+    const int* ids;        // packed observations
+    const double* poses;   // packed (.,6)
+    const long long* offsets;  // n_seq * n_frames + 1
+    long long state_stride, cov_stride;
+    int n_seq, n_frames, t0, t1, max_lm, max_obs, as_written, p_in_smem;
+    Noise nz;
+};
+
+__device__ __forceinline__ int tri(int i) { return (i * (i + 1)) >> 1; }
+// symmetric access into the packed lower triangle
+__device__ __forceinline__ double psym(const double* P, int i, int j) {
+    return j <= i ? P[tri(i) + j] : P[tri(j) + i];
+}
+
+template <int KIND, int CK, int NT>
+__global__ void __launch_bounds__(NT)
+k_batch(BatchParams p) {
+    constexpr int D = Dims<KIND>::D, R = Dims<KIND>::R, W = CAM + D, NB = R;
+    constexpr int MC = R * CK;           // max rows per chunk
+    constexpr int LDS_S = (MC + 1) | 1;  // leading dim of S (+ appended nu row)
+    extern __shared__ __align__(16) unsigned char smraw[];
+    const int tid = threadIdx.x;
+    const int ncap = CAM + D * p.max_lm;
+    const int npad = (ncap + 3) & ~3;
+
+    // ---- shared memory carve-up -----------------------------------------------------
+    double* s_state = reinterpret_cast<double*>(smraw);       // ncap
+    double* s_delta = s_state + npad;                         // ncap
+    double* s_G = s_delta + npad;                             // MC x npad
+    double* s_blk = s_G + (size_t)MC * npad;                  // CK x R x W
+    double* s_nu = s_blk + CK * R * W;                        // MC
+    double* s_S = s_nu + ((MC + 3) & ~3);                     // (MC+1) x LDS_S
+    double* s_dinv = s_S + (MC + 1) * LDS_S;                  // MC
+    double* s_pose = s_dinv + ((MC + 3) & ~3);                // max_obs x 6
+    int* s_ids = reinterpret_cast<int*>(s_pose + (size_t)p.max_obs * 6);   // max_obs
+    int* s_idx = s_ids + p.max_obs;                           // max_obs
+    int* s_new = s_idx + p.max_obs;                           // max_obs
+    int* s_tab = s_new + p.max_obs;                           // max_lm
+    int* s_misc = s_tab + p.max_lm;                           // [0]=nlm [1]=bad
+    double* s_P = reinterpret_cast<double*>(
+        (reinterpret_cast<uintptr_t>(s_misc + 4) + 15) & ~uintptr_t(15));  // packed, if it fits
+
+    for (int seq = blockIdx.x; seq < p.n_seq; seq += gridDim.x) {
+        double* g_state = p.states + (long long)seq * p.state_stride;
+        double* g_P = p.covs + (long long)seq * p.cov_stride;
+        int* g_tab = p.lm_ids + (long long)seq * p.max_lm;
+        double* P = p.p_in_smem ? s_P : g_P;
+        int nlm = p.nlm[seq];
+        int n = CAM + D * nlm;
+        for (int i = tid; i < n; i += NT) s_state[i] = g_state[i];
+        for (int i = tid; i < nlm; i += NT) s_tab[i] = g_tab[i];
+        if (p.p_in_smem)
+            for (int i = tid; i < tri(n); i += NT) s_P[i] = g_P[i];
+        if (tid == 0) s_misc[1] = 0;
+        __syncthreads();
+
+        for (int t = p.t0; t < p.t1; ++t) {
+            const long long ob = p.offsets[(long long)seq * p.n_frames + t];
+            const int k = (int)(p.offsets[(long long)seq * p.n_frames + t + 1] - ob);
+            if (k == 0) continue;  // no detection: no predict either (base_filter.py:197-204)
+            if (k > p.max_obs) {
+                if (tid == 0) s_misc[1] = ASB_ERR_CAPACITY;
+                break;
+            }
+            // ---- load the frame, associate ids ---------------------------------------
+            for (int o = tid; o < k; o += NT) s_ids[o] = p.ids[ob + o];
+            for (int e = tid; e < 6 * k; e += NT) s_pose[e] = p.poses[6 * ob + e];
+            __syncthreads();
+            for (int o = tid; o < k; o += NT) {
+                const int id = s_ids[o];
+                int found = -1;
+                for (int i = 0; i < nlm; ++i)
+                    if (s_tab[i] == id) { found = i; break; }
+                s_idx[o] = found;
+                s_new[o] = 0;
+            }
+            __syncthreads();
+            if (tid == 0) {  // unseen ids, in frame order; duplicates bind to the first
+                int cur = nlm;
+                for (int o = 0; o < k; ++o) {
+                    if (s_idx[o] >= 0) continue;
+                    const int id = s_ids[o];
+                    int found = -1;
+                    for (int i = nlm; i < cur; ++i)
+                        if (s_tab[i] == id) { found = i; break; }
+                    if (found < 0) {
+                        if (cur >= p.max_lm) { s_misc[1] = ASB_ERR_CAPACITY; found = 0; }
+                        else { s_tab[cur] = id; found = cur++; s_new[o] = 1; }
+                    }
+                    s_idx[o] = found;
+                }
+                s_misc[0] = cur;
+            }
+            __syncthreads();
+            const int nlm1 = s_misc[0];
+            if (s_misc[1] == ASB_ERR_CAPACITY) break;
+            const int n1 = CAM + D * nlm1;
+            // ---- augmentation: new landmark states, block-diagonal covariance growth -
+            if (nlm1 > nlm) {
+                for (int o = tid; o < k; o += NT) {
+                    if (!s_new[o]) continue;
+                    double lm[D];
+                    new_landmark<KIND>(s_state, s_pose + 6 * o, lm);
+#pragma unroll
+                    for (int c = 0; c < D; ++c) s_state[CAM + D * s_idx[o] + c] = lm[c];
+                }
+                for (int e = tri(n) + tid; e < tri(n1); e += NT) P[e] = 0.0;
+                __syncthreads();
+                for (int i = n + tid; i < n1; i += NT) P[tri(i) + i] = p.nz.init_lm;
+                __syncthreads();
+            }
+            nlm = nlm1;
+            n = n1;
+            // ---- predict: P += diag(Q); delta = 0 -------------------------------------
+            for (int i = tid; i < n; i += NT) {
+                P[tri(i) + i] += process_noise(p.nz, i);
+                s_delta[i] = 0.0;
+            }
+            __syncthreads();
+
+            // ---- update, CK markers at a time -----------------------------------------
+            for (int c0 = 0; c0 < k; c0 += CK) {
+                const int kc = min(CK, k - c0);
+                const int mc = R * kc;
+                // measurement model at the pre-update state; nu' = nu - H delta
+                for (int o = tid; o < kc; o += NT) {
+                    double lm[D], lnu[R];
+                    const int li = CAM + D * s_idx[c0 + o];
+#pragma unroll
+                    for (int c = 0; c < D; ++c) lm[c] = s_state[li + c];
+                    double* blk = s_blk + o * R * W;
+                    observation_model<KIND>(s_state, lm, s_pose + 6 * (c0 + o), lnu, blk);
+                    if (c0 > 0) {
+#pragma unroll
+                        for (int r = 0; r < R; ++r) {
+                            double s = lnu[r];
+                            for (int c = 0; c < CAM; ++c) s -= blk[r * W + c] * s_delta[c];
+                            for (int c = 0; c < D; ++c) s -= blk[r * W + CAM + c] * s_delta[li + c];
+                            lnu[r] = s;
+                        }
+                    }
+#pragma unroll
+                    for (int r = 0; r < R; ++r) s_nu[R * o + r] = lnu[r];
+                }
+                __syncthreads();
+                // G = H P  (mc x n)
+                for (int e = tid; e < kc * n; e += NT) {
+                    const int o = e / n, j = e - o * n;
+                    const double* blk = s_blk + o * R * W;
+                    const int li = CAM + D * s_idx[c0 + o];
+                    double acc[R];
+#pragma unroll
+                    for (int r = 0; r < R; ++r) acc[r] = 0.0;
+#pragma unroll
+                    for (int c = 0; c < CAM; ++c) {
+                        const double pv = psym(P, c, j);
+#pragma unroll
+                        for (int r = 0; r < R; ++r) acc[r] += blk[r * W + c] * pv;
+                    }
+#pragma unroll
+                    for (int c = 0; c < D; ++c) {
+                        const double pv = psym(P, li + c, j);
+#pragma unroll
+                        for (int r = 0; r < R; ++r) acc[r] += blk[r * W + CAM + c] * pv;
+                    }
+#pragma unroll
+                    for (int r = 0; r < R; ++r) s_G[(R * o + r) * npad + j] = acc[r];
+                }
+                __syncthreads();
+                // S = G H^T + R (lower) with nu appended as row mc
+                for (int e = tid; e < (mc + 1) * mc; e += NT) {
+                    const int a = e / mc, b = e - a * mc;
+                    if (a < mc && b > a) continue;
+                    double s;
+                    if (a < mc) {
+                        const int o2 = b / R, ib = b - o2 * R;
+                        const double* hb = s_blk + o2 * R * W + ib * W;
+                        const double* g = s_G + a * npad;
+                        const int li = CAM + D * s_idx[c0 + o2];
+                        s = (a == b) ? p.nz.r : 0.0;
+#pragma unroll
+                        for (int c = 0; c < CAM; ++c) s += g[c] * hb[c];
+#pragma unroll
+                        for (int c = 0; c < D; ++c) s += g[li + c] * hb[CAM + c];
+                    } else {
+                        s = s_nu[b];
+                    }
+                    s_S[a * LDS_S + b] = s;
+                }
+                __syncthreads();
+                // blocked Cholesky, NB = rows per marker
+                bool bad = false;
+                for (int jb = 0; jb < mc; jb += NB) {
+                    double dblk[NB][NB], dinv[NB];
+#pragma unroll
+                    for (int r = 0; r < NB; ++r)
+#pragma unroll
+                        for (int c = 0; c <= r; ++c) dblk[r][c] = s_S[(jb + r) * LDS_S + jb + c];
+#pragma unroll
+                    for (int c = 0; c < NB; ++c) {
+                        double pv = dblk[c][c];
+#pragma unroll
+                        for (int q = 0; q < c; ++q) pv -= dblk[c][q] * dblk[c][q];
+                        if (!(pv > 0.0) || !(pv < 1e300)) bad = true;
+                        const double rs = rsqrt(pv);
+                        dinv[c] = rs;
+                        dblk[c][c] = pv * rs;
+#pragma unroll
+                        for (int r = c + 1; r < NB; ++r) {
+                            double v = dblk[r][c];
+#pragma unroll
+                            for (int q = 0; q < c; ++q) v -= dblk[r][q] * dblk[c][q];
+                            dblk[r][c] = v * rs;
+                        }
+                    }
+                    for (int i = jb + NB + tid; i <= mc; i += NT) {
+                        double x[NB];
+#pragma unroll
+                        for (int c = 0; c < NB; ++c) {
+                            double v = s_S[i * LDS_S + jb + c];
+#pragma unroll
+                            for (int q = 0; q < c; ++q) v -= x[q] * dblk[c][q];
+                            x[c] = v * dinv[c];
+                        }
+#pragma unroll
+                        for (int c = 0; c < NB; ++c) s_S[i * LDS_S + jb + c] = x[c];
+                    }
+#pragma unroll
+                    for (int r = 0; r < NB; ++r) {
+                        if (tid == r) {
+#pragma unroll
+                            for (int c = 0; c <= r; ++c) s_S[(jb + r) * LDS_S + jb + c] = dblk[r][c];
+                            s_dinv[jb + r] = dinv[r];
+                        }
+                    }
+                    __syncthreads();
+                    const int t0 = jb + NB, rem = mc - t0;
+                    if (rem > 0) {
+                        for (int e = tid; e < (rem + 1) * rem; e += NT) {
+                            const int i = t0 + e / rem, kk = t0 + e % rem;
+                            if (i < mc && kk > i) continue;
+                            double s = s_S[i * LDS_S + kk];
+#pragma unroll
+                            for (int c = 0; c < NB; ++c) s -= s_S[i * LDS_S + jb + c] * s_S[kk * LDS_S + jb + c];
+                            s_S[i * LDS_S + kk] = s;
+                        }
+                    }
+                    __syncthreads();
+                }
+                if (bad && tid == 0) s_misc[1] = ASB_ERR_NOT_SPD;
+                // V = L^-1 G (in place), delta += V^T y   (y = appended row of S)
+                for (int j = tid; j < n; j += NT) {
+                    double dsum = 0.0;
+                    for (int a = 0; a < mc; ++a) {
+                        double v = s_G[a * npad + j];
+                        const double* la = s_S + a * LDS_S;
+                        for (int b = 0; b < a; ++b) v -= la[b] * s_G[b * npad + j];
+                        v *= s_dinv[a];
+                        s_G[a * npad + j] = v;
+                        dsum += v * s_S[mc * LDS_S + a];
+                    }
+                    s_delta[j] += dsum;
+                }
+                __syncthreads();
+                // P -= V^T V on the packed lower triangle, 4x4 register blocks
+                {
+                    const int nb = (n + 3) >> 2;
+                    const int nblk = (nb * (nb + 1)) >> 1;
+                    for (int blk_id = tid; blk_id < nblk; blk_id += NT) {
+                        int bi = (int)((sqrtf(8.0f * blk_id + 1.0f) - 1.0f) * 0.5f);
+                        while (tri(bi + 1) <= blk_id) ++bi;
+                        while (tri(bi) > blk_id) --bi;
+                        const int bj = blk_id - tri(bi);
+                        const int i0 = 4 * bi, j0 = 4 * bj;
+                        double acc[4][4];
+#pragma unroll
+                        for (int r = 0; r < 4; ++r)
+#pragma unroll
+                            for (int c = 0; c < 4; ++c) acc[r][c] = 0.0;
+                        for (int a = 0; a < mc; ++a) {
+                            const double* g = s_G + a * npad;
+                            const double2 xa = *reinterpret_cast<const double2*>(g + i0);
+                            const double2 xb = *reinterpret_cast<const double2*>(g + i0 + 2);
+                            const double2 ya = *reinterpret_cast<const double2*>(g + j0);
+                            const double2 yb = *reinterpret_cast<const double2*>(g + j0 + 2);
+                            const double xs[4] = {xa.x, xa.y, xb.x, xb.y};
+                            const double ys[4] = {ya.x, ya.y, yb.x, yb.y};
+#pragma unroll
+                            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                                for (int c = 0; c < 4; ++c) acc[r][c] += xs[r] * ys[c];
+                        }
+#pragma unroll
+                        for (int r = 0; r < 4; ++r) {
+                            const int i = i0 + r;
+                            if (i >= n) break;
+                            double* row = P + tri(i);
+#pragma unroll
+                            for (int c = 0; c < 4; ++c) {
+                                const int j = j0 + c;
+                                if (j <= i) row[j] -= acc[r][c];
+                            }
+                        }
+                    }
+                }
+                __syncthreads();
+            }  // chunks
+
+            // ---- state update + quaternion reset --------------------------------------
+            if (tid == 0) camera_reset(s_state, s_delta, p.as_written);
+            for (int l = tid; l < nlm; l += NT)
+                landmark_update<KIND>(s_state + CAM + D * l, s_delta + CAM + D * l);
+            __syncthreads();
+        }  // frames
+
+        // ---- write back -----------------------------------------------------------------
+        for (int i = tid; i < n; i += NT) g_state[i] = s_state[i];
+        for (int i = tid; i < nlm; i += NT) g_tab[i] = s_tab[i];
+        if (p.p_in_smem)
+            for (int i = tid; i < tri(n); i += NT) g_P[i] = s_P[i];
+        if (tid == 0) {
+            p.nlm[seq] = nlm;
+            if (s_misc[1] != 0) p.status[seq] = s_misc[1];
+        }
+        __syncthreads();
+    }
+}
+
+// Expand one packed covariance into a dense row-major n x n matrix.
+__global__ void k_unpack(const double* __restrict__ packed, int n, double* __restrict__ dense) {
+    const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= (long long)n * n) return;
+    const int i = (int)(e / n), j = (int)(e % n);
+    dense[e] = psym(packed, i, j);
+}
+
+}  // namespace asb

@@ -1,0 +1,193 @@
+// Library-level entry points of the C ABI and the measurement helpers
+// (asb_fp64_peak, asb_copy_bandwidth) used by bench.py for the roofline denominators that
+// MEASURED_PEAKS.json does not carry (FP64 pipe peak).
+#include <mma.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "common.cuh"
+
+namespace asb {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+}
+const char* get_error() { return g_err; }
+
+// ---- FP64 FMA pipe: 16 independent chains per thread ------------------------------------
+__global__ void __launch_bounds__(256) k_dfma_peak(double* out, int iters, double seed) {
+    double a[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) a[i] = seed + i + threadIdx.x;
+    const double x = 1.0000001, y = 1e-9;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) a[i] = fma(a[i], x, y);
+    }
+    double s = 0;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) s += a[i];
+    if (s == 123.456) out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+// ---- FP64 tensor path: mma.sync.m8n8k4.f64 (DMMA), 8 independent accumulator tiles -----
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+}
+
+__global__ void __launch_bounds__(256) k_dmma_peak(double* out, int iters, double seed) {
+    double c[8][2];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) c[i][0] = c[i][1] = seed + i;
+    const double a = 1e-3 + threadIdx.x * 1e-6, b = 1e-3;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) dmma884(c[i][0], c[i][1], a, b);
+    }
+    double s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += c[i][0] + c[i][1];
+    if (s == 123.456) out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+// both pipes in one kernel: even warps DFMA, odd warps DMMA
+__global__ void __launch_bounds__(256) k_mixed_peak(double* out, int iters, double seed) {
+    const int warp = threadIdx.x >> 5;
+    double s = 0;
+    if (warp & 1) {
+        double c[8][2];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) c[i][0] = c[i][1] = seed + i;
+        const double a = 1e-3 + threadIdx.x * 1e-6, b = 1e-3;
+        for (int it = 0; it < iters; ++it) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) dmma884(c[i][0], c[i][1], a, b);
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s += c[i][0] + c[i][1];
+    } else {
+        double a[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) a[i] = seed + i + threadIdx.x;
+        const double x = 1.0000001, y = 1e-9;
+        for (int it = 0; it < iters; ++it) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) a[i] = fma(a[i], x, y);
+        }
+#pragma unroll
+        for (int i = 0; i < 16; ++i) s += a[i];
+    }
+    if (s == 123.456) out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+__global__ void k_copy(const double2* __restrict__ src, double2* __restrict__ dst, long long n) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+        __stcs(dst + i, __ldcs(src + i));
+}
+
+}  // namespace asb
+
+using namespace asb;
+
+extern "C" {
+
+int asb_abi_version(void) { return ASB_ABI_VERSION; }
+
+const char* asb_last_error(void) { return get_error(); }
+
+int asb_device_count(int* count) {
+    if (!count) return fail(ASB_ERR_BAD_ARG, "count is NULL");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) {
+        *count = 0;
+        return fail(ASB_ERR_CUDA, "cudaGetDeviceCount: %s", cudaGetErrorString(e));
+    }
+    *count = n;
+    return ASB_OK;
+}
+
+int asb_default_noise(int kind, asb_noise* out) {
+    if (!out || (kind != ASB_KIND_EKF && kind != ASB_KIND_ROT)) return fail(ASB_ERR_BAD_ARG, "bad kind/out");
+    Noise n = default_noise(kind);
+    out->init_cam = n.init_cam; out->init_lm = n.init_lm; out->r = n.r;
+    out->q_cam = n.q_cam; out->q_err = n.q_err; out->q_lm = n.q_lm;
+    return ASB_OK;
+}
+
+int asb_fp64_peak(int device, int which, double* tflops) {
+    if (!tflops || which < 0 || which > 2) return fail(ASB_ERR_BAD_ARG, "bad which/tflops");
+    ASB_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    ASB_CUDA(cudaGetDeviceProperties(&prop, device));
+    const int grid = prop.multiProcessorCount * 8, block = 256, iters = 20000;
+    double* out = nullptr;
+    ASB_CUDA(cudaMalloc(&out, (size_t)grid * block * sizeof(double)));
+    cudaEvent_t e0, e1;
+    ASB_CUDA(cudaEventCreate(&e0));
+    ASB_CUDA(cudaEventCreate(&e1));
+    double best = 0;
+    for (int rep = 0; rep < 4; ++rep) {
+        ASB_CUDA(cudaEventRecord(e0));
+        if (which == 0) k_dfma_peak<<<grid, block>>>(out, iters, 1.0);
+        else if (which == 1) k_dmma_peak<<<grid, block>>>(out, iters, 1.0);
+        else k_mixed_peak<<<grid, block>>>(out, iters, 1.0);
+        ASB_CUDA(cudaEventRecord(e1));
+        ASB_CUDA(cudaEventSynchronize(e1));
+        float ms = 0;
+        ASB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        const double threads = (double)grid * block, warps = threads / 32;
+        double flop;
+        if (which == 0) flop = threads * iters * 16.0 * 2.0;
+        else if (which == 1) flop = warps * iters * 8.0 * (8 * 8 * 4 * 2.0);
+        else flop = 0.5 * threads * iters * 16.0 * 2.0 + 0.5 * warps * iters * 8.0 * (8 * 8 * 4 * 2.0);
+        best = std::max(best, flop / (ms * 1e-3) / 1e12);
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(out);
+    *tflops = best;
+    return ASB_OK;
+}
+
+int asb_copy_bandwidth(int device, int64_t bytes, double* gbs) {
+    if (!gbs || bytes < (1 << 20)) return fail(ASB_ERR_BAD_ARG, "bad bytes/gbs");
+    ASB_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    ASB_CUDA(cudaGetDeviceProperties(&prop, device));
+    double2 *a = nullptr, *b = nullptr;
+    const long long n = bytes / sizeof(double2);
+    ASB_CUDA(cudaMalloc(&a, n * sizeof(double2)));
+    ASB_CUDA(cudaMalloc(&b, n * sizeof(double2)));
+    ASB_CUDA(cudaMemset(a, 0, n * sizeof(double2)));
+    cudaEvent_t e0, e1;
+    ASB_CUDA(cudaEventCreate(&e0));
+    ASB_CUDA(cudaEventCreate(&e1));
+    double best = 0;
+    for (int rep = 0; rep < 6; ++rep) {
+        ASB_CUDA(cudaEventRecord(e0));
+        k_copy<<<prop.multiProcessorCount * 16, 512>>>(a, b, n);
+        ASB_CUDA(cudaEventRecord(e1));
+        ASB_CUDA(cudaEventSynchronize(e1));
+        float ms = 0;
+        ASB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        best = std::max(best, 2.0 * n * sizeof(double2) / (ms * 1e-3) / 1e9);
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(a);
+    cudaFree(b);
+    *gbs = best;
+    return ASB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,291 @@
+// Batched engine host side + C ABI ("batched independent filters" section of
+// include/aruco_slam_b200.h).  See batch_kernels.cuh for the kernel.
+#include <algorithm>
+#include <cstdlib>
+#include <new>
+#include <vector>
+
+#include "batch_kernels.cuh"
+#include "common.cuh"
+
+using namespace asb;
+
+namespace {
+constexpr uint32_t BATCH_MAGIC = 0x41534242;  // "ASBB"
+}
+
+struct asb_batch {
+    uint32_t magic = BATCH_MAGIC;
+    int kind = 0, quat_mode = 0, device = 0, D = 3, R = 3;
+    Noise nz{};
+    int n_seq = 0, max_lm = 0, max_obs = 0, ncap = 0;
+    long long state_stride = 0, cov_stride = 0;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    double *d_states = nullptr, *d_covs = nullptr, *d_poses = nullptr, *d_dense = nullptr;
+    int *d_nlm = nullptr, *d_tab = nullptr, *d_status = nullptr, *d_ids = nullptr;
+    long long* d_off = nullptr;
+    int n_frames = 0;
+    long long n_obs = 0;
+    int sm_count = 0, smem_optin = 0;
+    int ck = 4;       // markers per chunk (ASB_BATCH_CK)
+    int threads = 128;
+};
+
+static int check(asb_batch* b) {
+    if (!b || b->magic != BATCH_MAGIC) return fail(ASB_ERR_BAD_HANDLE, "bad asb_batch handle");
+    return ASB_OK;
+}
+#define ASB_CHECK_BATCH(b)              \
+    do {                                \
+        int _rc = check(b);             \
+        if (_rc != ASB_OK) return _rc;  \
+        cudaSetDevice((b)->device);     \
+    } while (0)
+
+template <typename T>
+static cudaError_t dmalloc(T** p, size_t count) {
+    return cudaMalloc(reinterpret_cast<void**>(p), std::max<size_t>(count, 1) * sizeof(T));
+}
+
+// shared-memory bytes of k_batch excluding the packed covariance (same carve-up as the kernel)
+static size_t batch_smem_base(int D, int R, int CK, int max_lm, int max_obs) {
+    const int W = CAM + D, MC = R * CK, LDS_S = (MC + 1) | 1;
+    const int ncap = CAM + D * max_lm, npad = (ncap + 3) & ~3;
+    size_t dbl = (size_t)npad * 2 + (size_t)MC * npad + (size_t)CK * R * W + ((MC + 3) & ~3) +
+                 (size_t)(MC + 1) * LDS_S + ((MC + 3) & ~3) + (size_t)max_obs * 6;
+    size_t ints = (size_t)max_obs * 3 + max_lm + 4;
+    return dbl * 8 + ints * 4 + 16;
+}
+
+template <int KIND, int CK, int NT>
+static int launch_batch(asb_batch* b, const BatchParams& p, size_t smem, int grid) {
+    auto kern = k_batch<KIND, CK, NT>;
+    ASB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<grid, NT, smem, b->stream>>>(p);
+    ASB_CUDA(cudaGetLastError());
+    return ASB_OK;
+}
+
+template <int KIND, int CK>
+static int launch_batch_nt(asb_batch* b, const BatchParams& p, size_t smem, int grid) {
+    if (b->threads >= 256) return launch_batch<KIND, CK, 256>(b, p, smem, grid);
+    return launch_batch<KIND, CK, 128>(b, p, smem, grid);
+}
+
+extern "C" {
+
+int asb_batch_create(int kind, int quat_mode, const double pose0[10], const asb_noise* cfg, int n_seq,
+                     int max_landmarks, int max_obs_per_frame, int device, asb_batch** out) {
+    if (!out) return fail(ASB_ERR_BAD_ARG, "out is NULL");
+    *out = nullptr;
+    if (kind != ASB_KIND_EKF && kind != ASB_KIND_ROT) return fail(ASB_ERR_BAD_ARG, "kind %d", kind);
+    if (quat_mode != ASB_QUAT_AS_WRITTEN && quat_mode != ASB_QUAT_SCALAR_FIRST)
+        return fail(ASB_ERR_BAD_ARG, "quat_mode %d", quat_mode);
+    if (n_seq < 1 || max_landmarks < 1 || max_obs_per_frame < 1) return fail(ASB_ERR_BAD_ARG, "bad sizes");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(ASB_ERR_CUDA, "no CUDA device: this library has no CPU fallback");
+    if (device < 0 || device >= ndev) return fail(ASB_ERR_BAD_ARG, "device %d of %d", device, ndev);
+    ASB_CUDA(cudaSetDevice(device));
+    asb_batch* b = new (std::nothrow) asb_batch();
+    if (!b) return fail(ASB_ERR_BAD_ARG, "out of host memory");
+    b->kind = kind; b->quat_mode = quat_mode; b->device = device;
+    b->D = kind == ASB_KIND_EKF ? 3 : 10;
+    b->R = kind == ASB_KIND_EKF ? 3 : 7;
+    b->nz = to_noise(kind, cfg);
+    b->n_seq = n_seq; b->max_lm = max_landmarks; b->max_obs = max_obs_per_frame;
+    b->ncap = CAM + b->D * max_landmarks;
+    b->state_stride = round_up(b->ncap, 4);
+    b->cov_stride = ((long long)b->ncap * (b->ncap + 1) / 2 + 3) & ~3LL;
+    cudaDeviceProp prop;
+    ASB_CUDA(cudaGetDeviceProperties(&prop, device));
+    b->sm_count = prop.multiProcessorCount;
+    b->smem_optin = (int)prop.sharedMemPerBlockOptin;
+    if (const char* e = std::getenv("ASB_BATCH_CK")) b->ck = std::atoi(e);
+    if (b->ck != 2 && b->ck != 4 && b->ck != 8) b->ck = 4;
+    if (const char* e = std::getenv("ASB_BATCH_THREADS")) b->threads = std::atoi(e);
+    else b->threads = b->ncap > 150 ? 256 : 128;
+    ASB_CUDA(cudaStreamCreateWithFlags(&b->own_stream, cudaStreamNonBlocking));
+    b->stream = b->own_stream;
+    ASB_CUDA(dmalloc(&b->d_states, (size_t)n_seq * b->state_stride));
+    ASB_CUDA(dmalloc(&b->d_covs, (size_t)n_seq * b->cov_stride));
+    ASB_CUDA(dmalloc(&b->d_nlm, (size_t)n_seq));
+    ASB_CUDA(dmalloc(&b->d_tab, (size_t)n_seq * max_landmarks));
+    ASB_CUDA(dmalloc(&b->d_status, (size_t)n_seq));
+    ASB_CUDA(dmalloc(&b->d_dense, (size_t)b->ncap * b->ncap));
+    ASB_CUDA(cudaMemset(b->d_nlm, 0, (size_t)n_seq * sizeof(int)));
+    ASB_CUDA(cudaMemset(b->d_status, 0, (size_t)n_seq * sizeof(int)));
+    ASB_CUDA(cudaMemset(b->d_tab, 0, (size_t)n_seq * max_landmarks * sizeof(int)));
+    ASB_CUDA(cudaMemset(b->d_covs, 0, (size_t)n_seq * b->cov_stride * sizeof(double)));
+    // every sequence starts at pose0 with P = init_cam * I10 (EKF:46-48)
+    std::vector<double> st((size_t)n_seq * b->state_stride, 0.0);
+    const double pose_default[CAM] = {0, 0, 0, 1, 0, 0, 0, 0, 0, 0};
+    const double* ps = pose0 ? pose0 : pose_default;
+    for (int s = 0; s < n_seq; ++s) std::copy(ps, ps + CAM, st.begin() + (size_t)s * b->state_stride);
+    ASB_CUDA(cudaMemcpy(b->d_states, st.data(), st.size() * sizeof(double), cudaMemcpyHostToDevice));
+    std::vector<double> p0(CAM * (CAM + 1) / 2, 0.0);
+    for (int i = 0; i < CAM; ++i) p0[i * (i + 1) / 2 + i] = b->nz.init_cam;
+    for (int s = 0; s < n_seq; ++s)
+        ASB_CUDA(cudaMemcpyAsync(b->d_covs + (size_t)s * b->cov_stride, p0.data(), p0.size() * sizeof(double),
+                                 cudaMemcpyHostToDevice, b->stream));
+    ASB_CUDA(cudaStreamSynchronize(b->stream));
+    *out = b;
+    return ASB_OK;
+}
+
+int asb_batch_destroy(asb_batch* b) {
+    ASB_CHECK_BATCH(b);
+    cudaStreamSynchronize(b->stream);
+    cudaFree(b->d_states); cudaFree(b->d_covs); cudaFree(b->d_nlm); cudaFree(b->d_tab);
+    cudaFree(b->d_status); cudaFree(b->d_ids); cudaFree(b->d_poses); cudaFree(b->d_off);
+    cudaFree(b->d_dense);
+    cudaStreamDestroy(b->own_stream);
+    b->magic = 0;
+    delete b;
+    return ASB_OK;
+}
+
+int asb_batch_set_stream(asb_batch* b, void* cuda_stream) {
+    ASB_CHECK_BATCH(b);
+    ASB_CUDA(cudaStreamSynchronize(b->stream));
+    b->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : b->own_stream;
+    return ASB_OK;
+}
+
+int asb_batch_synchronize(asb_batch* b) {
+    ASB_CHECK_BATCH(b);
+    ASB_CUDA(cudaStreamSynchronize(b->stream));
+    return ASB_OK;
+}
+
+int asb_batch_upload(asb_batch* b, const int32_t* ids, const double* poses, const int64_t* offsets,
+                     int n_frames) {
+    ASB_CHECK_BATCH(b);
+    if (!ids || !poses || !offsets || n_frames < 1) return fail(ASB_ERR_BAD_ARG, "bad stream");
+    const long long nrec = (long long)b->n_seq * n_frames;
+    const long long total = offsets[nrec];
+    if (total > b->n_obs || !b->d_ids) {
+        ASB_CUDA(cudaStreamSynchronize(b->stream));
+        cudaFree(b->d_ids); cudaFree(b->d_poses);
+        b->d_ids = nullptr; b->d_poses = nullptr;
+        ASB_CUDA(dmalloc(&b->d_ids, (size_t)total));
+        ASB_CUDA(dmalloc(&b->d_poses, (size_t)total * 6));
+        b->n_obs = total;
+    }
+    if (n_frames != b->n_frames || !b->d_off) {
+        ASB_CUDA(cudaStreamSynchronize(b->stream));
+        cudaFree(b->d_off);
+        b->d_off = nullptr;
+        ASB_CUDA(dmalloc(&b->d_off, (size_t)nrec + 1));
+        b->n_frames = n_frames;
+    }
+    static_assert(sizeof(long long) == sizeof(int64_t), "offset width");
+    ASB_CUDA(cudaMemcpyAsync(b->d_ids, ids, (size_t)total * sizeof(int), cudaMemcpyHostToDevice, b->stream));
+    ASB_CUDA(cudaMemcpyAsync(b->d_poses, poses, (size_t)total * 6 * sizeof(double), cudaMemcpyHostToDevice, b->stream));
+    ASB_CUDA(cudaMemcpyAsync(b->d_off, offsets, (size_t)(nrec + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, b->stream));
+    return ASB_OK;
+}
+
+int asb_batch_run(asb_batch* b, int t0, int t1) {
+    ASB_CHECK_BATCH(b);
+    if (!b->d_off) return fail(ASB_ERR_NO_STREAM, "batch_run before batch_upload");
+    if (t0 < 0 || t1 < t0 || t1 > b->n_frames) return fail(ASB_ERR_BAD_ARG, "bad frame range [%d,%d)", t0, t1);
+    BatchParams p;
+    p.states = b->d_states; p.covs = b->d_covs; p.nlm = b->d_nlm; p.lm_ids = b->d_tab; p.status = b->d_status;
+    p.ids = b->d_ids; p.poses = b->d_poses; p.offsets = b->d_off;
+    p.state_stride = b->state_stride; p.cov_stride = b->cov_stride;
+    p.n_seq = b->n_seq; p.n_frames = b->n_frames; p.t0 = t0; p.t1 = t1;
+    p.max_lm = b->max_lm; p.max_obs = b->max_obs;
+    p.as_written = (b->kind == ASB_KIND_EKF && b->quat_mode == ASB_QUAT_AS_WRITTEN) ? 1 : 0;
+    p.nz = b->nz;
+    const size_t base = batch_smem_base(b->D, b->R, b->ck, b->max_lm, b->max_obs);
+    const size_t pbytes = (size_t)b->cov_stride * sizeof(double);
+    p.p_in_smem = (base + pbytes <= (size_t)b->smem_optin) ? 1 : 0;
+    const size_t smem = base + (p.p_in_smem ? pbytes : 0);
+    if (smem > (size_t)b->smem_optin)
+        return fail(ASB_ERR_CAPACITY, "batched filter needs %zu B shared memory > %d", smem, b->smem_optin);
+    const int per_sm = std::max(1, std::min(8, (int)((size_t)(b->smem_optin + 1024) / (smem + 1024))));
+    const int grid = std::min(b->n_seq, b->sm_count * per_sm);
+#define ASB_DISPATCH(KIND)                                                     \
+    switch (b->ck) {                                                           \
+        case 2: return launch_batch_nt<KIND, 2>(b, p, smem, grid);             \
+        case 8: return launch_batch_nt<KIND, 8>(b, p, smem, grid);             \
+        default: return launch_batch_nt<KIND, 4>(b, p, smem, grid);            \
+    }
+    if (b->kind == ASB_KIND_EKF) { ASB_DISPATCH(0) }
+    ASB_DISPATCH(1)
+#undef ASB_DISPATCH
+}
+
+int asb_batch_get_dims(asb_batch* b, int seq, int* n_landmarks, int* n_state) {
+    ASB_CHECK_BATCH(b);
+    if (seq < 0 || seq >= b->n_seq) return fail(ASB_ERR_BAD_ARG, "seq %d", seq);
+    ASB_CUDA(cudaStreamSynchronize(b->stream));
+    int nlm = 0;
+    ASB_CUDA(cudaMemcpy(&nlm, b->d_nlm + seq, sizeof(int), cudaMemcpyDeviceToHost));
+    if (n_landmarks) *n_landmarks = nlm;
+    if (n_state) *n_state = CAM + b->D * nlm;
+    return ASB_OK;
+}
+
+static int seq_status(asb_batch* b, int seq) {
+    int st = 0;
+    ASB_CUDA(cudaMemcpy(&st, b->d_status + seq, sizeof(int), cudaMemcpyDeviceToHost));
+    if (st != 0) return fail(st, "sequence %d: %s", seq, st == ASB_ERR_NOT_SPD ? "S not positive definite" : "capacity exceeded");
+    return ASB_OK;
+}
+
+int asb_batch_get_state(asb_batch* b, int seq, double* out, int n_state) {
+    ASB_CHECK_BATCH(b);
+    int nlm, n;
+    int rc = asb_batch_get_dims(b, seq, &nlm, &n);
+    if (rc != ASB_OK) return rc;
+    if (!out || n_state != n) return fail(ASB_ERR_BAD_ARG, "n_state %d != %d", n_state, n);
+    ASB_CUDA(cudaMemcpy(out, b->d_states + (size_t)seq * b->state_stride, n * sizeof(double), cudaMemcpyDeviceToHost));
+    return seq_status(b, seq);
+}
+
+int asb_batch_get_cov(asb_batch* b, int seq, double* out, int n_state) {
+    ASB_CHECK_BATCH(b);
+    int nlm, n;
+    int rc = asb_batch_get_dims(b, seq, &nlm, &n);
+    if (rc != ASB_OK) return rc;
+    if (!out || n_state != n) return fail(ASB_ERR_BAD_ARG, "n_state %d != %d", n_state, n);
+    const long long cnt = (long long)n * n;
+    k_unpack<<<(unsigned)((cnt + 255) / 256), 256, 0, b->stream>>>(b->d_covs + (size_t)seq * b->cov_stride, n, b->d_dense);
+    ASB_CUDA(cudaGetLastError());
+    ASB_CUDA(cudaStreamSynchronize(b->stream));
+    ASB_CUDA(cudaMemcpy(out, b->d_dense, cnt * sizeof(double), cudaMemcpyDeviceToHost));
+    return seq_status(b, seq);
+}
+
+int asb_batch_get_landmark_ids(asb_batch* b, int seq, int32_t* ids, int capacity) {
+    ASB_CHECK_BATCH(b);
+    int nlm, n;
+    int rc = asb_batch_get_dims(b, seq, &nlm, &n);
+    if (rc != ASB_OK) return rc;
+    if (!ids || capacity < nlm) return fail(ASB_ERR_BAD_ARG, "capacity %d < %d", capacity, nlm);
+    ASB_CUDA(cudaMemcpy(ids, b->d_tab + (size_t)seq * b->max_lm, nlm * sizeof(int), cudaMemcpyDeviceToHost));
+    return ASB_OK;
+}
+
+int asb_batch_get_cameras(asb_batch* b, double* out, int32_t* status) {
+    ASB_CHECK_BATCH(b);
+    if (!out) return fail(ASB_ERR_BAD_ARG, "out is NULL");
+    ASB_CUDA(cudaStreamSynchronize(b->stream));
+    ASB_CUDA(cudaMemcpy2D(out, CAM * sizeof(double), b->d_states, (size_t)b->state_stride * sizeof(double),
+                          CAM * sizeof(double), b->n_seq, cudaMemcpyDeviceToHost));
+    if (status) ASB_CUDA(cudaMemcpy(status, b->d_status, (size_t)b->n_seq * sizeof(int), cudaMemcpyDeviceToHost));
+    return ASB_OK;
+}
+
+int asb_batch_device_views(asb_batch* b, void** d_states, void** d_covs, int* state_stride, int* cov_ld) {
+    ASB_CHECK_BATCH(b);
+    if (d_states) *d_states = b->d_states;
+    if (d_covs) *d_covs = b->d_covs;
+    if (state_stride) *state_stride = (int)b->state_stride;
+    if (cov_ld) *cov_ld = (int)b->cov_stride;  // packed lower triangle: doubles per sequence
+    return ASB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,507 @@
+// Single-filter engine + its C ABI (include/aruco_slam_b200.h, "single filter" section).
+// Host side: id -> index association (dict semantics of EKF:75-78 / EKF:253-254), staging
+// of one frame's observations, and the per-frame launch sequence documented in
+// single_kernels.cuh.  All arithmetic runs in the CUDA kernels; there is no CPU fallback.
+#include <algorithm>
+#include <cmath>
+#include <new>
+#include <unordered_map>
+#include <vector>
+
+#include "common.cuh"
+#include "single_kernels.cuh"
+
+using namespace asb;
+
+namespace {
+constexpr uint32_t FILTER_MAGIC = 0x41534246;  // "ASBF"
+constexpr int N_SLOTS = 8;                     // staging ring depth
+
+struct FrameRec {  // one frame of a device-resident stream
+    int64_t off;
+    int k, n0, n1;
+    std::vector<int32_t> new_ids;
+};
+}  // namespace
+
+struct asb_filter {
+    uint32_t magic = FILTER_MAGIC;
+    int kind = 0, quat_mode = 0, device = 0;
+    int D = 3, R = 3, W = 13;
+    Noise nz{};
+    int cap_lm = 0, ncap = 0, ld = 0, max_obs = 0, kc_max = 0;
+    int nlm = 0;
+    std::unordered_map<int32_t, int> map;
+    std::vector<int32_t> id_order;
+
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    double *d_state = nullptr, *d_P = nullptr, *d_G = nullptr, *d_blocks = nullptr, *d_nu = nullptr;
+    double *d_L = nullptr, *d_invd = nullptr, *d_y = nullptr, *d_dx = nullptr, *d_unc = nullptr;
+    int* d_status = nullptr;
+    // staging ring (host pinned + device)
+    int* h_idx = nullptr; double* h_pose = nullptr; unsigned char* h_new = nullptr;
+    int* d_idx = nullptr; double* d_pose = nullptr; unsigned char* d_new = nullptr;
+    cudaEvent_t slot_ev[N_SLOTS]{};
+    int slot = 0;
+    int last_k = 0;
+    const int* last_idx = nullptr;
+    // resident stream
+    int* s_idx = nullptr; double* s_pose = nullptr; unsigned char* s_new = nullptr;
+    std::vector<FrameRec> frames;
+    int next_frame = 0;
+    int sweep_grid = 0;
+
+    int n_state() const { return CAM + D * nlm; }
+};
+
+static int check(asb_filter* f) {
+    if (!f || f->magic != FILTER_MAGIC) return fail(ASB_ERR_BAD_HANDLE, "bad asb_filter handle");
+    return ASB_OK;
+}
+
+#define ASB_CHECK_HANDLE(f)             \
+    do {                                \
+        int _rc = check(f);             \
+        if (_rc != ASB_OK) return _rc;  \
+        cudaSetDevice((f)->device);     \
+    } while (0)
+
+template <typename T>
+static cudaError_t dmalloc(T** p, size_t count) {
+    return cudaMalloc(reinterpret_cast<void**>(p), count * sizeof(T));
+}
+
+// ---------------------------------------------------------------------------------------
+// launch sequence for one frame whose observations are at (idx, pose, isnew) on the device
+// ---------------------------------------------------------------------------------------
+template <int KIND>
+static int launch_frame(asb_filter* f, const int* idx, const double* pose, const unsigned char* isnew,
+                        int k, int n0, int n1, bool do_predict, bool do_update) {
+    constexpr int D = Dims<KIND>::D, R = Dims<KIND>::R, W = CAM + D;
+    cudaStream_t st = f->stream;
+    const int ld = f->ld;
+    {
+        long long work = (long long)n0 + (long long)(n1 - n0) * (n1 + n0);
+        int grid = (int)std::min<long long>(1 + work / 1024, 592);
+        k_prep<KIND><<<grid, 256, 0, st>>>(f->d_state, f->d_P, ld, n0, n1, f->nz, idx, pose, isnew, k,
+                                           f->d_blocks, f->d_nu, do_predict ? 1 : 0);
+    }
+    if (do_update && k > 0) {
+        const int nI = (n1 + SW_TI - 1) / SW_TI;
+        const int ntiles = nI * (nI + 1);
+        for (int c0 = 0; c0 < k; c0 += f->kc_max) {
+            const int kc = std::min(f->kc_max, k - c0);
+            const int m = R * kc, m4 = round_up(m, 4);
+            const bool last = c0 + kc >= k;
+            dim3 gg((ld + 127) / 128, (kc + GATHER_OBS - 1) / GATHER_OBS);
+            k_gather<KIND><<<gg, 128, 0, st>>>(f->d_P, ld, n1, idx + c0, f->d_blocks + (size_t)c0 * R * W,
+                                               kc, m4, f->d_G);
+            const int lds = (m + 1) | 1;
+            const size_t sm_chol = (size_t)(m + 1) * lds * sizeof(double);
+            k_chol<KIND><<<1, 256, sm_chol, st>>>(f->d_G, ld, idx + c0, f->d_blocks + (size_t)c0 * R * W,
+                                                  f->d_nu + (size_t)R * c0, kc, m4, f->nz.r, f->d_dx,
+                                                  c0 > 0 ? 1 : 0, f->d_L, f->d_invd, f->d_y, f->d_status);
+            const size_t sm_solve = ((size_t)m4 * m4 + (size_t)m4 * SOLVE_COLS + 2 * m4) * sizeof(double);
+            k_solve<<<(ld + SOLVE_COLS - 1) / SOLVE_COLS, SOLVE_COLS, sm_solve, st>>>(
+                f->d_G, ld, n1, m4, f->d_L, f->d_invd, f->d_y, f->d_dx, c0 > 0 ? 1 : 0);
+            if (last)
+                k_apply<KIND><<<(std::max(f->nlm, 1) + 127) / 128, 128, 0, st>>>(
+                    f->d_state, f->d_dx, f->nlm, (KIND == 0 && f->quat_mode == ASB_QUAT_AS_WRITTEN) ? 1 : 0);
+            const size_t sm_sweep = (size_t)m4 * (SW_TI + SW_TJ) * sizeof(double);
+            const int grid = std::min(ntiles, f->sweep_grid * (sm_sweep <= 100 * 1024 ? 2 : 1));
+            k_sweep<<<grid, SW_THREADS, sm_sweep, st>>>(f->d_P, ld, n1, f->d_G, m4, ntiles);
+        }
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(ASB_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(e));
+    return ASB_OK;
+}
+
+static int launch_frame_dyn(asb_filter* f, const int* idx, const double* pose, const unsigned char* isnew,
+                            int k, int n0, int n1, bool do_predict, bool do_update) {
+    return f->kind == ASB_KIND_EKF ? launch_frame<0>(f, idx, pose, isnew, k, n0, n1, do_predict, do_update)
+                                   : launch_frame<1>(f, idx, pose, isnew, k, n0, n1, do_predict, do_update);
+}
+
+// Stage k observations into the next ring slot and copy them to the device (async).
+static int stage(asb_filter* f, const std::vector<int>& idx, const double* poses,
+                 const std::vector<unsigned char>& isnew, int k, int** d_idx, double** d_pose,
+                 unsigned char** d_new) {
+    const int s = f->slot;
+    f->slot = (f->slot + 1) % N_SLOTS;
+    ASB_CUDA(cudaEventSynchronize(f->slot_ev[s]));
+    const size_t o = (size_t)s * f->max_obs;
+    std::memcpy(f->h_idx + o, idx.data(), k * sizeof(int));
+    std::memcpy(f->h_pose + 6 * o, poses, (size_t)k * 6 * sizeof(double));
+    std::memcpy(f->h_new + o, isnew.data(), k);
+    ASB_CUDA(cudaMemcpyAsync(f->d_idx + o, f->h_idx + o, k * sizeof(int), cudaMemcpyHostToDevice, f->stream));
+    ASB_CUDA(cudaMemcpyAsync(f->d_pose + 6 * o, f->h_pose + 6 * o, (size_t)k * 6 * sizeof(double),
+                             cudaMemcpyHostToDevice, f->stream));
+    ASB_CUDA(cudaMemcpyAsync(f->d_new + o, f->h_new + o, k, cudaMemcpyHostToDevice, f->stream));
+    ASB_CUDA(cudaEventRecord(f->slot_ev[s], f->stream));
+    *d_idx = f->d_idx + o;
+    *d_pose = f->d_pose + 6 * o;
+    *d_new = f->d_new + o;
+    return ASB_OK;
+}
+
+static int poll_status(asb_filter* f) {
+    int st = 0;
+    ASB_CUDA(cudaMemcpyAsync(&st, f->d_status, sizeof(int), cudaMemcpyDeviceToHost, f->stream));
+    ASB_CUDA(cudaStreamSynchronize(f->stream));
+    if (st != 0) {
+        ASB_CUDA(cudaMemsetAsync(f->d_status, 0, sizeof(int), f->stream));
+        return fail(st, "innovation covariance S was not positive definite / finite");
+    }
+    return ASB_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------
+extern "C" {
+
+int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb_noise* cfg,
+                      int max_landmarks, int device, asb_filter** out) {
+    if (!out) return fail(ASB_ERR_BAD_ARG, "out is NULL");
+    *out = nullptr;
+    if (kind != ASB_KIND_EKF && kind != ASB_KIND_ROT) return fail(ASB_ERR_BAD_ARG, "kind %d", kind);
+    if (quat_mode != ASB_QUAT_AS_WRITTEN && quat_mode != ASB_QUAT_SCALAR_FIRST)
+        return fail(ASB_ERR_BAD_ARG, "quat_mode %d", quat_mode);
+    if (max_landmarks < 1) return fail(ASB_ERR_BAD_ARG, "max_landmarks %d", max_landmarks);
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(ASB_ERR_CUDA, "no CUDA device: this library has no CPU fallback");
+    if (device < 0 || device >= ndev) return fail(ASB_ERR_BAD_ARG, "device %d of %d", device, ndev);
+    ASB_CUDA(cudaSetDevice(device));
+    asb_filter* f = new (std::nothrow) asb_filter();
+    if (!f) return fail(ASB_ERR_BAD_ARG, "out of host memory");
+    f->kind = kind;
+    f->quat_mode = quat_mode;
+    f->device = device;
+    f->D = kind == ASB_KIND_EKF ? 3 : 10;
+    f->R = kind == ASB_KIND_EKF ? 3 : 7;
+    f->W = CAM + f->D;
+    f->nz = to_noise(kind, cfg);
+    f->cap_lm = max_landmarks;
+    f->ncap = CAM + f->D * max_landmarks;
+    f->ld = round_up(f->ncap, PAD);
+    f->max_obs = std::max(64, std::min(max_landmarks * 2, 4096));
+    f->kc_max = (M_MAX - 2) / f->R;  // rows per chunk: R*kc rounded up to 4 must be <= M_MAX
+    cudaDeviceProp prop;
+    ASB_CUDA(cudaGetDeviceProperties(&prop, device));
+    f->sweep_grid = prop.multiProcessorCount;
+    ASB_CUDA(cudaStreamCreateWithFlags(&f->own_stream, cudaStreamNonBlocking));
+    f->stream = f->own_stream;
+    const size_t ld = f->ld;
+    ASB_CUDA(dmalloc(&f->d_state, ld));
+    ASB_CUDA(dmalloc(&f->d_P, ld * ld));
+    ASB_CUDA(dmalloc(&f->d_G, (size_t)M_MAX * ld));
+    ASB_CUDA(dmalloc(&f->d_blocks, (size_t)f->max_obs * f->R * f->W));
+    ASB_CUDA(dmalloc(&f->d_nu, (size_t)f->max_obs * f->R));
+    ASB_CUDA(dmalloc(&f->d_L, (size_t)M_MAX * M_MAX));
+    ASB_CUDA(dmalloc(&f->d_invd, (size_t)M_MAX));
+    ASB_CUDA(dmalloc(&f->d_y, (size_t)M_MAX));
+    ASB_CUDA(dmalloc(&f->d_dx, ld));
+    ASB_CUDA(dmalloc(&f->d_unc, 16));
+    ASB_CUDA(dmalloc(&f->d_status, 1));
+    ASB_CUDA(dmalloc(&f->d_idx, (size_t)N_SLOTS * f->max_obs));
+    ASB_CUDA(dmalloc(&f->d_pose, (size_t)N_SLOTS * f->max_obs * 6));
+    ASB_CUDA(dmalloc(&f->d_new, (size_t)N_SLOTS * f->max_obs));
+    ASB_CUDA(cudaMallocHost(&f->h_idx, (size_t)N_SLOTS * f->max_obs * sizeof(int)));
+    ASB_CUDA(cudaMallocHost(&f->h_pose, (size_t)N_SLOTS * f->max_obs * 6 * sizeof(double)));
+    ASB_CUDA(cudaMallocHost(&f->h_new, (size_t)N_SLOTS * f->max_obs));
+    for (auto& e : f->slot_ev) ASB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    ASB_CUDA(cudaMemsetAsync(f->d_P, 0, ld * ld * sizeof(double), f->stream));
+    ASB_CUDA(cudaMemsetAsync(f->d_G, 0, (size_t)M_MAX * ld * sizeof(double), f->stream));
+    ASB_CUDA(cudaMemsetAsync(f->d_state, 0, ld * sizeof(double), f->stream));
+    ASB_CUDA(cudaMemsetAsync(f->d_dx, 0, ld * sizeof(double), f->stream));
+    ASB_CUDA(cudaMemsetAsync(f->d_status, 0, sizeof(int), f->stream));
+    // state = pose0; P = init_cam * I10  (EKF:46-48)
+    std::vector<double> p0(CAM * f->ld, 0.0);
+    for (int i = 0; i < CAM; ++i) p0[(size_t)i * f->ld + i] = f->nz.init_cam;
+    ASB_CUDA(cudaMemcpyAsync(f->d_P, p0.data(), p0.size() * sizeof(double), cudaMemcpyHostToDevice, f->stream));
+    double pose_default[CAM] = {0, 0, 0, 1, 0, 0, 0, 0, 0, 0};
+    ASB_CUDA(cudaMemcpyAsync(f->d_state, pose0 ? pose0 : pose_default, CAM * sizeof(double),
+                             cudaMemcpyHostToDevice, f->stream));
+    ASB_CUDA(cudaStreamSynchronize(f->stream));
+    // opt in to large dynamic shared memory
+    const int big = 200 * 1024;
+    ASB_CUDA(cudaFuncSetAttribute(k_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    ASB_CUDA(cudaFuncSetAttribute(k_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    ASB_CUDA(cudaFuncSetAttribute(k_chol<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    ASB_CUDA(cudaFuncSetAttribute(k_chol<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    *out = f;
+    return ASB_OK;
+}
+
+int asb_filter_destroy(asb_filter* f) {
+    ASB_CHECK_HANDLE(f);
+    cudaStreamSynchronize(f->stream);
+    cudaFree(f->d_state); cudaFree(f->d_P); cudaFree(f->d_G); cudaFree(f->d_blocks); cudaFree(f->d_nu);
+    cudaFree(f->d_L); cudaFree(f->d_invd); cudaFree(f->d_y); cudaFree(f->d_dx); cudaFree(f->d_unc);
+    cudaFree(f->d_status); cudaFree(f->d_idx); cudaFree(f->d_pose); cudaFree(f->d_new);
+    cudaFree(f->s_idx); cudaFree(f->s_pose); cudaFree(f->s_new);
+    cudaFreeHost(f->h_idx); cudaFreeHost(f->h_pose); cudaFreeHost(f->h_new);
+    for (auto& e : f->slot_ev) cudaEventDestroy(e);
+    cudaStreamDestroy(f->own_stream);
+    f->magic = 0;
+    delete f;
+    return ASB_OK;
+}
+
+int asb_filter_set_stream(asb_filter* f, void* cuda_stream) {
+    ASB_CHECK_HANDLE(f);
+    ASB_CUDA(cudaStreamSynchronize(f->stream));
+    f->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : f->own_stream;
+    return ASB_OK;
+}
+
+int asb_filter_synchronize(asb_filter* f) {
+    ASB_CHECK_HANDLE(f);
+    return poll_status(f);
+}
+
+static int observe_impl(asb_filter* f, const int32_t* ids, const double* poses, int k, bool add_new,
+                        bool do_predict) {
+    if (k < 0 || (k > 0 && (!ids || !poses))) return fail(ASB_ERR_BAD_ARG, "bad ids/poses/k");
+    if (k > f->max_obs) return fail(ASB_ERR_CAPACITY, "%d observations > per-frame capacity %d", k, f->max_obs);
+    std::vector<int> idx(k);
+    std::vector<unsigned char> isnew(k, 0);
+    const int n0 = f->n_state();
+    if (add_new) {
+        int fresh = 0;
+        {
+            std::unordered_map<int32_t, int> seen;
+            for (int o = 0; o < k; ++o)
+                if (!f->map.count(ids[o]) && !seen.count(ids[o])) { seen[ids[o]] = 1; ++fresh; }
+        }
+        if (f->nlm + fresh > f->cap_lm)
+            return fail(ASB_ERR_CAPACITY, "%d landmarks > max_landmarks %d", f->nlm + fresh, f->cap_lm);
+        for (int o = 0; o < k; ++o) {
+            auto it = f->map.find(ids[o]);
+            if (it == f->map.end()) {
+                idx[o] = f->nlm;
+                isnew[o] = 1;
+                f->map[ids[o]] = f->nlm++;
+                f->id_order.push_back(ids[o]);
+            } else {
+                idx[o] = it->second;
+            }
+        }
+    } else {
+        for (int o = 0; o < k; ++o) {
+            auto it = f->map.find(ids[o]);
+            if (it == f->map.end()) return fail(ASB_ERR_UNKNOWN_ID, "unknown landmark id %d", ids[o]);
+            idx[o] = it->second;
+        }
+    }
+    const int n1 = f->n_state();
+    int* d_idx = nullptr; double* d_pose = nullptr; unsigned char* d_new = nullptr;
+    if (k > 0) {
+        int rc = stage(f, idx, poses, isnew, k, &d_idx, &d_pose, &d_new);
+        if (rc != ASB_OK) return rc;
+    }
+    f->last_k = k;
+    f->last_idx = d_idx;
+    return launch_frame_dyn(f, d_idx, d_pose, d_new, k, n0, n1, do_predict, true);
+}
+
+int asb_observe(asb_filter* f, const int32_t* ids, const double* poses, int k) {
+    ASB_CHECK_HANDLE(f);
+    return observe_impl(f, ids, poses, k, true, true);
+}
+
+int asb_predict(asb_filter* f) {
+    ASB_CHECK_HANDLE(f);
+    const int n = f->n_state();
+    return launch_frame_dyn(f, nullptr, nullptr, nullptr, 0, n, n, true, false);
+}
+
+int asb_update(asb_filter* f, const int32_t* ids, const double* poses, int k) {
+    ASB_CHECK_HANDLE(f);
+    if (k <= 0) return fail(ASB_ERR_BAD_ARG, "update with no observations");
+    return observe_impl(f, ids, poses, k, false, false);
+}
+
+int asb_add_marker(asb_filter* f, int32_t id, const double pose[6], const double* uncertainity) {
+    ASB_CHECK_HANDLE(f);
+    if (!pose) return fail(ASB_ERR_BAD_ARG, "pose is NULL");
+    if (f->nlm + 1 > f->cap_lm) return fail(ASB_ERR_CAPACITY, "max_landmarks %d reached", f->cap_lm);
+    const int n0 = f->n_state();
+    std::vector<int> idx(1, f->nlm);
+    std::vector<unsigned char> isnew(1, 1);
+    f->map[id] = f->nlm++;  // dict assignment: a known id is re-bound (EKF:253)
+    f->id_order.push_back(id);
+    const int n1 = f->n_state();
+    int* d_idx; double* d_pose; unsigned char* d_new;
+    int rc = stage(f, idx, pose, isnew, 1, &d_idx, &d_pose, &d_new);
+    if (rc != ASB_OK) return rc;
+    rc = launch_frame_dyn(f, d_idx, d_pose, d_new, 1, n0, n1, false, false);
+    if (rc != ASB_OK) return rc;
+    if (uncertainity) {
+        ASB_CUDA(cudaStreamSynchronize(f->stream));  // d_unc reuse
+        ASB_CUDA(cudaMemcpyAsync(f->d_unc, uncertainity, f->D * sizeof(double), cudaMemcpyHostToDevice, f->stream));
+        k_set_diag<<<1, 32, 0, f->stream>>>(f->d_P, f->ld, n0, f->D, f->d_unc);
+        ASB_CUDA(cudaStreamSynchronize(f->stream));
+    }
+    return ASB_OK;
+}
+
+int asb_stream_upload(asb_filter* f, const int32_t* ids, const double* poses, const int64_t* offsets,
+                      int n_frames) {
+    ASB_CHECK_HANDLE(f);
+    if (!ids || !poses || !offsets || n_frames < 1) return fail(ASB_ERR_BAD_ARG, "bad stream");
+    const int64_t total = offsets[n_frames];
+    std::vector<int> idx(total);
+    std::vector<unsigned char> isnew(total, 0);
+    std::unordered_map<int32_t, int> sim = f->map;
+    int nlm = f->nlm;
+    f->frames.clear();
+    f->frames.reserve(n_frames);
+    for (int t = 0; t < n_frames; ++t) {
+        FrameRec fr;
+        fr.off = offsets[t];
+        fr.k = (int)(offsets[t + 1] - offsets[t]);
+        if (fr.k > f->max_obs) return fail(ASB_ERR_CAPACITY, "frame %d: %d observations > %d", t, fr.k, f->max_obs);
+        fr.n0 = CAM + f->D * nlm;
+        for (int64_t o = fr.off; o < fr.off + fr.k; ++o) {
+            auto it = sim.find(ids[o]);
+            if (it == sim.end()) {
+                if (nlm + 1 > f->cap_lm) return fail(ASB_ERR_CAPACITY, "stream needs > %d landmarks", f->cap_lm);
+                idx[o] = nlm;
+                isnew[o] = 1;
+                sim[ids[o]] = nlm++;
+                fr.new_ids.push_back(ids[o]);
+            } else {
+                idx[o] = it->second;
+            }
+        }
+        fr.n1 = CAM + f->D * nlm;
+        f->frames.push_back(std::move(fr));
+    }
+    ASB_CUDA(cudaStreamSynchronize(f->stream));
+    cudaFree(f->s_idx); cudaFree(f->s_pose); cudaFree(f->s_new);
+    f->s_idx = nullptr; f->s_pose = nullptr; f->s_new = nullptr;
+    ASB_CUDA(dmalloc(&f->s_idx, (size_t)std::max<int64_t>(total, 1)));
+    ASB_CUDA(dmalloc(&f->s_pose, (size_t)std::max<int64_t>(total, 1) * 6));
+    ASB_CUDA(dmalloc(&f->s_new, (size_t)std::max<int64_t>(total, 1)));
+    ASB_CUDA(cudaMemcpy(f->s_idx, idx.data(), total * sizeof(int), cudaMemcpyHostToDevice));
+    ASB_CUDA(cudaMemcpy(f->s_pose, poses, (size_t)total * 6 * sizeof(double), cudaMemcpyHostToDevice));
+    ASB_CUDA(cudaMemcpy(f->s_new, isnew.data(), total, cudaMemcpyHostToDevice));
+    f->next_frame = 0;
+    return ASB_OK;
+}
+
+int asb_stream_run(asb_filter* f, int t0, int t1) {
+    ASB_CHECK_HANDLE(f);
+    if (f->frames.empty()) return fail(ASB_ERR_NO_STREAM, "stream_run before stream_upload");
+    if (t0 != f->next_frame || t1 < t0 || t1 > (int)f->frames.size())
+        return fail(ASB_ERR_BAD_ARG, "frames must run in order: next is %d, got [%d,%d)", f->next_frame, t0, t1);
+    for (int t = t0; t < t1; ++t) {
+        const FrameRec& fr = f->frames[t];
+        for (int32_t id : fr.new_ids) {
+            f->map[id] = f->nlm++;
+            f->id_order.push_back(id);
+        }
+        f->last_k = fr.k;
+        f->last_idx = f->s_idx + fr.off;
+        if (fr.k == 0) continue;  // BASE:197-204: frames without detections do not predict
+        int rc = launch_frame_dyn(f, f->s_idx + fr.off, f->s_pose + 6 * fr.off, f->s_new + fr.off, fr.k, fr.n0,
+                                  fr.n1, true, true);
+        if (rc != ASB_OK) return rc;
+        f->next_frame = t + 1;
+    }
+    f->next_frame = t1;
+    return ASB_OK;
+}
+
+int asb_get_dims(asb_filter* f, int* n_landmarks, int* n_state) {
+    ASB_CHECK_HANDLE(f);
+    if (n_landmarks) *n_landmarks = f->nlm;
+    if (n_state) *n_state = f->n_state();
+    return ASB_OK;
+}
+
+int asb_get_state(asb_filter* f, double* out, int n_state) {
+    ASB_CHECK_HANDLE(f);
+    if (!out || n_state != f->n_state()) return fail(ASB_ERR_BAD_ARG, "n_state %d != %d", n_state, f->n_state());
+    int rc = poll_status(f);
+    ASB_CUDA(cudaMemcpy(out, f->d_state, n_state * sizeof(double), cudaMemcpyDeviceToHost));
+    return rc;
+}
+
+int asb_set_state(asb_filter* f, const double* in, int n_state) {
+    ASB_CHECK_HANDLE(f);
+    if (!in || n_state != f->n_state()) return fail(ASB_ERR_BAD_ARG, "n_state %d != %d", n_state, f->n_state());
+    ASB_CUDA(cudaStreamSynchronize(f->stream));
+    ASB_CUDA(cudaMemcpy(f->d_state, in, n_state * sizeof(double), cudaMemcpyHostToDevice));
+    return ASB_OK;
+}
+
+int asb_get_cov(asb_filter* f, double* out, int n_state) {
+    ASB_CHECK_HANDLE(f);
+    if (!out || n_state != f->n_state()) return fail(ASB_ERR_BAD_ARG, "n_state %d != %d", n_state, f->n_state());
+    int rc = poll_status(f);
+    ASB_CUDA(cudaMemcpy2D(out, (size_t)n_state * sizeof(double), f->d_P, (size_t)f->ld * sizeof(double),
+                          (size_t)n_state * sizeof(double), n_state, cudaMemcpyDeviceToHost));
+    return rc;
+}
+
+int asb_set_cov(asb_filter* f, const double* in, int n_state) {
+    ASB_CHECK_HANDLE(f);
+    if (!in || n_state != f->n_state()) return fail(ASB_ERR_BAD_ARG, "n_state %d != %d", n_state, f->n_state());
+    ASB_CUDA(cudaStreamSynchronize(f->stream));
+    ASB_CUDA(cudaMemcpy2D(f->d_P, (size_t)f->ld * sizeof(double), in, (size_t)n_state * sizeof(double),
+                          (size_t)n_state * sizeof(double), n_state, cudaMemcpyHostToDevice));
+    return ASB_OK;
+}
+
+int asb_get_cov_diag(asb_filter* f, double* out, int n_state) {
+    ASB_CHECK_HANDLE(f);
+    if (!out || n_state != f->n_state()) return fail(ASB_ERR_BAD_ARG, "n_state %d != %d", n_state, f->n_state());
+    int rc = poll_status(f);
+    ASB_CUDA(cudaMemcpy2D(out, sizeof(double), f->d_P, (size_t)(f->ld + 1) * sizeof(double), sizeof(double),
+                          n_state, cudaMemcpyDeviceToHost));
+    return rc;
+}
+
+int asb_get_landmark_ids(asb_filter* f, int32_t* ids, int capacity) {
+    ASB_CHECK_HANDLE(f);
+    if (!ids || capacity < f->nlm) return fail(ASB_ERR_BAD_ARG, "capacity %d < %d", capacity, f->nlm);
+    std::copy(f->id_order.begin(), f->id_order.end(), ids);
+    return ASB_OK;
+}
+
+int asb_set_landmarks(asb_filter* f, const int32_t* ids, int n) {
+    ASB_CHECK_HANDLE(f);
+    if (n < 0 || (n > 0 && !ids)) return fail(ASB_ERR_BAD_ARG, "bad ids");
+    if (n > f->cap_lm) return fail(ASB_ERR_CAPACITY, "%d landmarks > max_landmarks %d", n, f->cap_lm);
+    f->map.clear();
+    f->id_order.assign(ids, ids + n);
+    for (int i = 0; i < n; ++i) f->map[ids[i]] = i;
+    f->nlm = n;
+    return ASB_OK;
+}
+
+int asb_device_views(asb_filter* f, void** d_state, void** d_cov, int* ld) {
+    ASB_CHECK_HANDLE(f);
+    if (d_state) *d_state = f->d_state;
+    if (d_cov) *d_cov = f->d_P;
+    if (ld) *ld = f->ld;
+    return ASB_OK;
+}
+
+int asb_get_last_update(asb_filter* f, double* nu, double* blocks, double* dx, int* m) {
+    ASB_CHECK_HANDLE(f);
+    ASB_CUDA(cudaStreamSynchronize(f->stream));
+    const int k = f->last_k;
+    if (m) *m = f->R * k;
+    if (nu && k) ASB_CUDA(cudaMemcpy(nu, f->d_nu, (size_t)f->R * k * sizeof(double), cudaMemcpyDeviceToHost));
+    if (blocks && k)
+        ASB_CUDA(cudaMemcpy(blocks, f->d_blocks, (size_t)k * f->R * f->W * sizeof(double), cudaMemcpyDeviceToHost));
+    if (dx) ASB_CUDA(cudaMemcpy(dx, f->d_dx, (size_t)f->n_state() * sizeof(double), cudaMemcpyDeviceToHost));
+    return ASB_OK;
+}
+
+}  // extern "C"

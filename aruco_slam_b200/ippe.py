@@ -1,0 +1,49 @@
+"""Batched square-marker pose estimation (replaces the per-marker
+``cv2.solvePnP(..., flags=cv2.SOLVEPNP_IPPE_SQUARE)`` loop of
+``BaseFilter.estimate_pose_of_markers``, filters/base_filter.py:92-171)."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+
+
+def _corner_array(corners) -> np.ndarray:
+    """Accept what ``detectMarkers`` returns (tuple of (1,4,2) float32) or any
+    array reshapeable to (k,4,2)."""
+    if isinstance(corners, (tuple, list)):
+        if len(corners) == 0:
+            return np.zeros((0, 4, 2), dtype=np.float32)
+        corners = np.stack([np.asarray(c, dtype=np.float32).reshape(4, 2) for c in corners])
+    return np.ascontiguousarray(np.asarray(corners, dtype=np.float32).reshape(-1, 4, 2))
+
+
+def _intrinsics(camera_matrix, dist_coeffs):
+    km = _lib.as_f64(camera_matrix, (9,))
+    dist = np.zeros(5)
+    d = _lib.as_f64(dist_coeffs).reshape(-1)
+    dist[:min(5, d.size)] = d[:5]
+    return km, dist
+
+
+def estimate_pose_of_markers(corners, camera_matrix, dist_coeffs, marker_size: float = 0.16,
+                             device: int = 0) -> np.ndarray:
+    """(k,4,2) float32 corners -> (k,6) float64 ``[tvec, rvec]`` rows (host in, host out)."""
+    c = _corner_array(corners)
+    km, dist = _intrinsics(camera_matrix, dist_coeffs)
+    out = np.empty((c.shape[0], 6), dtype=np.float64)
+    _lib.check(_lib.lib().asb_ippe_square(_lib.fptr(c), c.shape[0], _lib.dptr(km), _lib.dptr(dist),
+                                          float(marker_size), _lib.dptr(out), int(device)))
+    return out
+
+
+def estimate_pose_device(d_corners: int, n: int, camera_matrix, dist_coeffs, marker_size: float,
+                         d_out: int, d_out2: int | None = None, d_err: int | None = None,
+                         stream: int | None = None) -> None:
+    """Device-pointer variant (raw addresses, e.g. ``tensor.data_ptr()``), asynchronous."""
+    km, dist = _intrinsics(camera_matrix, dist_coeffs)
+    _lib.check(_lib.lib().asb_ippe_square_device(
+        C.c_void_p(d_corners), int(n), _lib.dptr(km), _lib.dptr(dist), float(marker_size),
+        C.c_void_p(d_out), C.c_void_p(d_out2 or 0), C.c_void_p(d_err or 0), C.c_void_p(stream or 0)))

@@ -32,6 +32,12 @@ extern "C" {
 
 #define ASB_ABI_VERSION 1
 
+#if defined(__GNUC__)
+#define ASB_API __attribute__((visibility("default")))
+#else
+#define ASB_API
+#endif
+
 typedef enum asb_status {
     ASB_OK = 0,
     ASB_ERR_BAD_HANDLE = -1,
@@ -67,101 +73,101 @@ typedef struct asb_filter asb_filter;   /* one filter, covariance resident in HB
 typedef struct asb_batch asb_batch;     /* many independent filters, one CTA each   */
 
 /* ---- library ----------------------------------------------------------------- */
-int asb_abi_version(void);
-const char* asb_last_error(void);
-int asb_device_count(int* count);
+ASB_API int asb_abi_version(void);
+ASB_API const char* asb_last_error(void);
+ASB_API int asb_device_count(int* count);
 /* Fill a noise struct with the reference constants of `kind`. */
-int asb_default_noise(int kind, asb_noise* out);
+ASB_API int asb_default_noise(int kind, asb_noise* out);
 
 /* ---- single filter: EKF.__init__ (EKF:40-56) / EKF_Rotations.__init__ (ROT:46-64) ---- */
-int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb_noise* cfg,
+ASB_API int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb_noise* cfg,
                       int max_landmarks, int device, asb_filter** out);
-int asb_filter_destroy(asb_filter* f);
+ASB_API int asb_filter_destroy(asb_filter* f);
 /* Run on a caller-owned CUDA stream (cudaStream_t cast to void*); NULL => the handle's own. */
-int asb_filter_set_stream(asb_filter* f, void* cuda_stream);
-int asb_filter_synchronize(asb_filter* f);
+ASB_API int asb_filter_set_stream(asb_filter* f, void* cuda_stream);
+ASB_API int asb_filter_synchronize(asb_filter* f);
 
 /* observe (EKF:58-82, ROT:66-90): add unseen ids in frame order, predict, update.
  * ids (k) int32, poses (k,6) row-major, HOST pointers. Asynchronous on the stream. */
-int asb_observe(asb_filter* f, const int32_t* ids, const double* poses, int k);
+ASB_API int asb_observe(asb_filter* f, const int32_t* ids, const double* poses, int k);
 /* predict (EKF:95-105, ROT:103-113): P += diag(Q); the state is unchanged. */
-int asb_predict(asb_filter* f);
+ASB_API int asb_predict(asb_filter* f);
 /* update (EKF:107-156, ROT:115-181). Unknown id => ASB_ERR_UNKNOWN_ID, nothing changed. */
-int asb_update(asb_filter* f, const int32_t* ids, const double* poses, int k);
+ASB_API int asb_update(asb_filter* f, const int32_t* ids, const double* poses, int k);
 /* add_marker (EKF:239-290, ROT:275-335). `uncertainity` = d diagonal values or NULL
  * (=> init_lm).  Re-adding a known id re-binds the id to a new index, as the reference's
  * dict assignment does. */
-int asb_add_marker(asb_filter* f, int32_t id, const double pose[6], const double* uncertainity);
+ASB_API int asb_add_marker(asb_filter* f, int32_t id, const double pose[6], const double* uncertainity);
 
 /* Device-resident observation stream (bench "value" path: inputs already in HBM).
  * offsets (T+1) int64 prefix sums; ids/poses packed over all frames.  upload associates
  * ids on the host (first-seen order, EKF:75-78) and copies once; run enqueues frames
  * [t0,t1) with no host<->device traffic. */
-int asb_stream_upload(asb_filter* f, const int32_t* ids, const double* poses,
+ASB_API int asb_stream_upload(asb_filter* f, const int32_t* ids, const double* poses,
                       const int64_t* offsets, int n_frames);
-int asb_stream_run(asb_filter* f, int t0, int t1);
+ASB_API int asb_stream_run(asb_filter* f, int t0, int t1);
 
 /* state / uncertainty / landmarks attributes (EKF:46-51), get_poses (EKF:84-89),
  * get_lm_uncertainties (EKF:91-93), get_lm_estimates (EKF:355-357). */
-int asb_get_dims(asb_filter* f, int* n_landmarks, int* n_state);
-int asb_get_state(asb_filter* f, double* out, int n_state);
-int asb_set_state(asb_filter* f, const double* in, int n_state);
-int asb_get_cov(asb_filter* f, double* out, int n_state);            /* N*N row-major */
-int asb_set_cov(asb_filter* f, const double* in, int n_state);
-int asb_get_cov_diag(asb_filter* f, double* out, int n_state);
-int asb_get_landmark_ids(asb_filter* f, int32_t* ids_in_index_order, int capacity);
+ASB_API int asb_get_dims(asb_filter* f, int* n_landmarks, int* n_state);
+ASB_API int asb_get_state(asb_filter* f, double* out, int n_state);
+ASB_API int asb_set_state(asb_filter* f, const double* in, int n_state);
+ASB_API int asb_get_cov(asb_filter* f, double* out, int n_state);            /* N*N row-major */
+ASB_API int asb_set_cov(asb_filter* f, const double* in, int n_state);
+ASB_API int asb_get_cov_diag(asb_filter* f, double* out, int n_state);
+ASB_API int asb_get_landmark_ids(asb_filter* f, int32_t* ids_in_index_order, int capacity);
 /* Replace the id->index map (ids in index order); state/cov are then set with the
  * setters above.  This is the checkpoint / re-synchronisation path (SURVEY §8c ii). */
-int asb_set_landmarks(asb_filter* f, const int32_t* ids_in_index_order, int n);
+ASB_API int asb_set_landmarks(asb_filter* f, const int32_t* ids_in_index_order, int n);
 /* Raw device pointers for zero-copy consumers (torch.from_blob / cupy): state (N),
  * covariance (row-major with leading dimension *ld doubles). */
-int asb_device_views(asb_filter* f, void** d_state, void** d_cov, int* ld);
+ASB_API int asb_device_views(asb_filter* f, void** d_state, void** d_cov, int* ld);
 
 /* Intermediates of the last update(), for parity tests (parse_poses EKF:158-200):
  * nu = z - h (m), blocks = per observation [r x 10 camera block | r x d landmark block]
  * row-major (k * r * (10+d)), dx = K nu (N).  Any pointer may be NULL. */
-int asb_get_last_update(asb_filter* f, double* nu, double* blocks, double* dx, int* m);
+ASB_API int asb_get_last_update(asb_filter* f, double* nu, double* blocks, double* dx, int* m);
 
 /* ---- batched independent filters (BASELINE configs C2 / C5) --------------------- */
-int asb_batch_create(int kind, int quat_mode, const double pose0[10], const asb_noise* cfg,
+ASB_API int asb_batch_create(int kind, int quat_mode, const double pose0[10], const asb_noise* cfg,
                      int n_seq, int max_landmarks, int max_obs_per_frame, int device,
                      asb_batch** out);
-int asb_batch_destroy(asb_batch* b);
-int asb_batch_set_stream(asb_batch* b, void* cuda_stream);
-int asb_batch_synchronize(asb_batch* b);
+ASB_API int asb_batch_destroy(asb_batch* b);
+ASB_API int asb_batch_set_stream(asb_batch* b, void* cuda_stream);
+ASB_API int asb_batch_synchronize(asb_batch* b);
 /* offsets (n_seq*n_frames + 1) int64: frame t of sequence s = rows
  * [offsets[s*n_frames+t], offsets[s*n_frames+t+1]) of ids / poses (HOST pointers). */
-int asb_batch_upload(asb_batch* b, const int32_t* ids, const double* poses,
+ASB_API int asb_batch_upload(asb_batch* b, const int32_t* ids, const double* poses,
                      const int64_t* offsets, int n_frames);
 /* observe() for frames [t0,t1) of every sequence; id association on the device. */
-int asb_batch_run(asb_batch* b, int t0, int t1);
-int asb_batch_get_dims(asb_batch* b, int seq, int* n_landmarks, int* n_state);
-int asb_batch_get_state(asb_batch* b, int seq, double* out, int n_state);
-int asb_batch_get_cov(asb_batch* b, int seq, double* out, int n_state);
-int asb_batch_get_landmark_ids(asb_batch* b, int seq, int32_t* ids_in_index_order, int capacity);
+ASB_API int asb_batch_run(asb_batch* b, int t0, int t1);
+ASB_API int asb_batch_get_dims(asb_batch* b, int seq, int* n_landmarks, int* n_state);
+ASB_API int asb_batch_get_state(asb_batch* b, int seq, double* out, int n_state);
+ASB_API int asb_batch_get_cov(asb_batch* b, int seq, double* out, int n_state);
+ASB_API int asb_batch_get_landmark_ids(asb_batch* b, int seq, int32_t* ids_in_index_order, int capacity);
 /* camera pose (10) of every sequence, (n_seq,10) row-major, + per-sequence status. */
-int asb_batch_get_cameras(asb_batch* b, double* out, int32_t* status_or_null);
-int asb_batch_device_views(asb_batch* b, void** d_states, void** d_covs, int* state_stride,
+ASB_API int asb_batch_get_cameras(asb_batch* b, double* out, int32_t* status_or_null);
+ASB_API int asb_batch_device_views(asb_batch* b, void** d_states, void** d_covs, int* state_stride,
                            int* cov_ld);
 
 /* ---- square-marker pose: estimate_pose_of_markers (BASE:92-171), i.e.
  *      cv2.solvePnP(marker_points, c, K, dist, flags=SOLVEPNP_IPPE_SQUARE) per marker ----
  * corners (n,4,2) float32 pixel corners in the order BASE:112-120 expects; camera_matrix
  * 3x3 row-major; dist_coeffs k1 k2 p1 p2 k3; out (n,6) = [tvec, rvec] rows (BASE:171). */
-int asb_ippe_square(const float* corners, int64_t n, const double camera_matrix[9],
+ASB_API int asb_ippe_square(const float* corners, int64_t n, const double camera_matrix[9],
                     const double dist_coeffs[5], double marker_size, double* out, int device);
 /* Same on DEVICE buffers, asynchronous on `cuda_stream`.  out2_or_null receives the
  * second IPPE solution (n,6) and err_or_null (n,2) the two float reprojection errors. */
-int asb_ippe_square_device(const float* d_corners, int64_t n, const double camera_matrix[9],
+ASB_API int asb_ippe_square_device(const float* d_corners, int64_t n, const double camera_matrix[9],
                            const double dist_coeffs[5], double marker_size, double* d_out,
                            double* d_out2_or_null, float* d_err_or_null, void* cuda_stream);
 
 /* ---- measurement helpers (bench / profiles) -------------------------------------- */
 /* FP64 pipe micro-benchmarks: achieved TFLOP/s of dependent-free DFMA chains and of
  * mma.sync m8n8k4 f64 (DMMA), timed with CUDA events. which: 0 = DFMA, 1 = DMMA, 2 = both. */
-int asb_fp64_peak(int device, int which, double* tflops);
+ASB_API int asb_fp64_peak(int device, int which, double* tflops);
 /* Streaming copy bandwidth (GB/s, read+write bytes) over `bytes` of HBM. */
-int asb_copy_bandwidth(int device, int64_t bytes, double* gbs);
+ASB_API int asb_copy_bandwidth(int device, int64_t bytes, double* gbs);
 
 #ifdef __cplusplus
 }
