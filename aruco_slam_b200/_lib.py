@@ -71,6 +71,7 @@ SIGNATURES = {
     "asb_batch_create": (C.c_int, [C.c_int, C.c_int, _dp, C.POINTER(Noise), C.c_int, C.c_int,
                                    C.c_int, C.c_int, C.POINTER(_vp)]),
     "asb_batch_destroy": (C.c_int, [_vp]),
+    "asb_batch_reset": (C.c_int, [_vp]),
     "asb_batch_set_stream": (C.c_int, [_vp, _vp]),
     "asb_batch_synchronize": (C.c_int, [_vp]),
     "asb_batch_upload": (C.c_int, [_vp, _ip, _dp, _lp, C.c_int]),

@@ -49,6 +49,10 @@ class FilterBatch:
             except Exception:  # interpreter shutdown
                 pass
 
+    def reset(self) -> None:
+        """Back to freshly constructed filters (asynchronous)."""
+        _lib.check(self._lib.asb_batch_reset(self._h))
+
     def set_stream(self, cuda_stream: int | None) -> None:
         _lib.check(self._lib.asb_batch_set_stream(self._h, C.c_void_p(cuda_stream or 0)))
 

@@ -21,7 +21,7 @@ struct asb_batch {
     int n_seq = 0, max_lm = 0, max_obs = 0, ncap = 0;
     long long state_stride = 0, cov_stride = 0;
     cudaStream_t own_stream = nullptr, stream = nullptr;
-    double *d_states = nullptr, *d_covs = nullptr, *d_poses = nullptr, *d_dense = nullptr;
+    double *d_states = nullptr, *d_covs = nullptr, *d_poses = nullptr, *d_dense = nullptr, *d_pose0 = nullptr;
     int *d_nlm = nullptr, *d_tab = nullptr, *d_status = nullptr, *d_ids = nullptr;
     long long* d_off = nullptr;
     int n_frames = 0;
@@ -74,6 +74,14 @@ static int launch_batch_nt(asb_batch* b, const BatchParams& p, size_t smem, int 
 
 extern "C" {
 
+int asb_batch_reset(asb_batch* b) {
+    ASB_CHECK_BATCH(b);
+    k_batch_init<<<b->n_seq, 64, 0, b->stream>>>(b->d_states, b->d_covs, b->d_nlm, b->d_status, b->state_stride,
+                                                 b->cov_stride, b->n_seq, b->d_pose0, b->nz.init_cam);
+    ASB_CUDA(cudaGetLastError());
+    return ASB_OK;
+}
+
 int asb_batch_create(int kind, int quat_mode, const double pose0[10], const asb_noise* cfg, int n_seq,
                      int max_landmarks, int max_obs_per_frame, int device, asb_batch** out) {
     if (!out) return fail(ASB_ERR_BAD_ARG, "out is NULL");
@@ -116,18 +124,13 @@ int asb_batch_create(int kind, int quat_mode, const double pose0[10], const asb_
     ASB_CUDA(cudaMemset(b->d_nlm, 0, (size_t)n_seq * sizeof(int)));
     ASB_CUDA(cudaMemset(b->d_status, 0, (size_t)n_seq * sizeof(int)));
     ASB_CUDA(cudaMemset(b->d_tab, 0, (size_t)n_seq * max_landmarks * sizeof(int)));
-    ASB_CUDA(cudaMemset(b->d_covs, 0, (size_t)n_seq * b->cov_stride * sizeof(double)));
-    // every sequence starts at pose0 with P = init_cam * I10 (EKF:46-48)
-    std::vector<double> st((size_t)n_seq * b->state_stride, 0.0);
     const double pose_default[CAM] = {0, 0, 0, 1, 0, 0, 0, 0, 0, 0};
-    const double* ps = pose0 ? pose0 : pose_default;
-    for (int s = 0; s < n_seq; ++s) std::copy(ps, ps + CAM, st.begin() + (size_t)s * b->state_stride);
-    ASB_CUDA(cudaMemcpy(b->d_states, st.data(), st.size() * sizeof(double), cudaMemcpyHostToDevice));
-    std::vector<double> p0(CAM * (CAM + 1) / 2, 0.0);
-    for (int i = 0; i < CAM; ++i) p0[i * (i + 1) / 2 + i] = b->nz.init_cam;
-    for (int s = 0; s < n_seq; ++s)
-        ASB_CUDA(cudaMemcpyAsync(b->d_covs + (size_t)s * b->cov_stride, p0.data(), p0.size() * sizeof(double),
-                                 cudaMemcpyHostToDevice, b->stream));
+    ASB_CUDA(dmalloc(&b->d_pose0, (size_t)CAM));
+    ASB_CUDA(cudaMemcpy(b->d_pose0, pose0 ? pose0 : pose_default, CAM * sizeof(double), cudaMemcpyHostToDevice));
+    {
+        int rc = asb_batch_reset(b);
+        if (rc != ASB_OK) return rc;
+    }
     ASB_CUDA(cudaStreamSynchronize(b->stream));
     *out = b;
     return ASB_OK;
@@ -138,7 +141,7 @@ int asb_batch_destroy(asb_batch* b) {
     cudaStreamSynchronize(b->stream);
     cudaFree(b->d_states); cudaFree(b->d_covs); cudaFree(b->d_nlm); cudaFree(b->d_tab);
     cudaFree(b->d_status); cudaFree(b->d_ids); cudaFree(b->d_poses); cudaFree(b->d_off);
-    cudaFree(b->d_dense);
+    cudaFree(b->d_dense); cudaFree(b->d_pose0);
     cudaStreamDestroy(b->own_stream);
     b->magic = 0;
     delete b;

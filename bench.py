@@ -1,0 +1,457 @@
+#!/usr/bin/env python
+"""bench.py — MEKF marker-updates/s on B200 (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W            # this framework
+    python bench.py --impl reference --gpus N --steps K ...  # CPU arm (oracle port)
+
+Headline workload (config.workload "C2"): BASELINE.json configs[1] — 4096 independent
+synthetic MEKF sequences x 32 markers x 1000 frames PER GPU (weak scaling: sequences
+shard across ranks with no data-path collective).  One "step" = one pass of the hot path
+(EKF.observe for every frame of every sequence) over that batch from freshly constructed
+filters.  `value` = marker-updates/s with the observations already resident in HBM;
+`e2e` = the same through the public Python API with host buffers (H2D of the step's
+observations from pinned memory + D2H of the resulting camera poses inside the timed
+region).  Extra workloads measured in the same run and reported under "workloads":
+C3 (one EKF, 2000-marker map, N = 6010, the HBM-bound covariance sweep) and C4 (1M-corner
+batched IPPE).  See DESIGN.md §Measurement for the byte/flop accounting.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+METRIC = "mekf_marker_updates_per_sec"
+UNIT = "marker-updates/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--seqs", type=int, default=4096, help="sequences per GPU (C2)")
+    ap.add_argument("--markers", type=int, default=32)
+    ap.add_argument("--frames", type=int, default=1000)
+    ap.add_argument("--p-visible", type=float, default=0.5)
+    ap.add_argument("--unique", type=int, default=64,
+                    help="distinct synthetic sequences generated per rank and tiled to --seqs")
+    ap.add_argument("--kind", default="ekf", choices=["ekf", "rot"])
+    ap.add_argument("--quat-mode", default="as_written", choices=["as_written", "scalar_first"])
+    ap.add_argument("--no-extras", action="store_true", help="skip the C3 / C4 legs")
+    ap.add_argument("--only", default=None, choices=["c3", "c4"],
+                    help="profiling aid: run just that leg and print its JSON")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU baseline budget")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------
+# helpers
+# ------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *exc):
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+            self.thread.join(timeout=2)
+
+    def summary(self):
+        sm, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx = max(mx, float(r[2]))
+                for name, v in zip(names, r[4:8]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except (ValueError, IndexError):
+                continue
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def flops_batch_form(n_state: int, k: int, rows: int, width: int) -> float:
+    """Algorithmic FP64 flops of one frame: P update, gain solve,
+    Cholesky, PH^T, S, dx for m = rows*k measurement rows."""
+    m = rows * k
+    n = n_state
+    return 2.0 * n * n * m + 2.0 * n * m * m + m ** 3 / 3.0 + 2.0 * width * n * m \
+        + 2.0 * width * m * m + 2.0 * n * m
+
+
+def pinned_like(a: np.ndarray):
+    import torch
+    t = torch.empty(a.shape, dtype=torch.from_numpy(np.empty(0, a.dtype)).dtype, pin_memory=True)
+    out = t.numpy()
+    out[...] = a
+    return t, out
+
+
+# ------------------------------------------------------------------------------------------
+# CPU arm: the oracle port of the reference's algorithm on the host cores
+# ------------------------------------------------------------------------------------------
+def _cpu_worker(job):
+    seq, markers, frames, p_vis, kind, quat_mode = job
+    os.environ.setdefault("OMP_NUM_THREADS", "1")
+    from aruco_slam_b200 import synth
+    from oracle import ekf_oracle
+    s = synth.make_stream(seq, markers, frames, p_vis, kind)
+    o = ekf_oracle.make(kind, quat_mode)
+    t0 = time.perf_counter()
+    n = 0
+    for t in range(frames):
+        o.observe([int(i) for i in s.ids[t]], s.poses[t])
+        n += len(s.ids[t])
+    return n, time.perf_counter() - t0
+
+
+def cpu_port_throughput(args, workers: int, frames: int, reps: int = 1):
+    """marker-updates/s of the numpy oracle: `workers` processes, one sequence each."""
+    import multiprocessing as mp
+    jobs = [(s, args.markers, frames, args.p_visible, args.kind, args.quat_mode)
+            for s in range(workers * reps)]
+    t0 = time.perf_counter()
+    if workers == 1:
+        res = [_cpu_worker(j) for j in jobs]
+    else:
+        with mp.get_context("spawn").Pool(workers) as pool:
+            pool.map(_cpu_worker, jobs[:workers])  # warm: imports, page-in
+            t0 = time.perf_counter()
+            res = pool.map(_cpu_worker, jobs)
+    wall = time.perf_counter() - t0
+    total = sum(r[0] for r in res)
+    return total / wall, total, wall
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    workers = max(1, min(cores, 64))
+    frames = 60
+    # size one step to ~10-20 s: oracle runs ~2.5 ms/frame/sequence
+    vals = []
+    for _ in range(args.warmup):
+        pass  # the pool's own warm pass (imports, page-in) is inside cpu_port_throughput
+    t_all = time.perf_counter()
+    for _ in range(max(1, args.steps)):
+        v, total, wall = cpu_port_throughput(args, workers, frames, reps=1)
+        vals.append(v)
+        if time.perf_counter() - t_all > 150:
+            break
+    value = float(np.mean(vals))
+    sample = (f"{workers} sequences x {args.markers} markers x {frames} frames per step, one "
+              f"process per sequence, numpy oracle port of the reference algorithm "
+              f"(dense (I-KH)P as written)")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": len(vals), "warmup": args.warmup, "ms_per_step": 1e3 * wall, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": workers, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args):
+    return {"workload": f"C2: {args.seqs} independent MEKF sequences x {args.markers} markers x "
+                        f"{args.frames} frames per GPU (BASELINE.json configs[1])",
+            "filter": "EKF (filters/extended_kalman_filter.py)" if args.kind == "ekf"
+            else "EKF_Rotations (filters/ekf_with_rotations.py)",
+            "quat_mode": args.quat_mode, "sequences_per_gpu": args.seqs, "markers": args.markers,
+            "frames": args.frames, "p_visible": args.p_visible,
+            "cache": "inputs larger than L2 (3.4 GB of observations per step)"}
+
+
+# ------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------
+def timed(torch, dist, fn, steps):
+    """EXACTLY `steps` calls bracketed by barrier + synchronize; CUDA events on the current
+    stream; max over ranks."""
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms.item())
+
+
+def leg_c3(torch, stream_ptr, hbm_peak):
+    """C3: one EKF with a 2000-marker map (N = 6010, P = 289 MB), 20 markers per frame."""
+    import ctypes as C
+    from aruco_slam_b200 import EKF, _lib, synth
+    km, dist = synth.reference_calibration()
+    timed_frames, warm = 200, 20
+    stream, n_build = synth.make_map_build_stream(2000, 20, warm + timed_frames)
+    f = EKF(np.array([0, 0, 0, 1, 0, 0, 0, 0, 0, 0.0]), camera_matrix=km, dist_coeffs=dist,
+            quat_mode="as_written", max_landmarks=2000)
+    f.set_stream(stream_ptr)
+    ids, poses, off = stream.packed()
+    f.stream_upload(ids, poses, off)
+    f.stream_run(0, n_build + warm)  # untimed map build + warm-up frames
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    f.stream_run(n_build + warm, n_build + warm + timed_frames)
+    e1.record()
+    torch.cuda.synchronize()
+    f.synchronize()
+    ms = e0.elapsed_time(e1)
+    n = 6010
+    per_frame_bytes = 16.0 * n * n  # one read + one write of dense FP64 P
+    ach = per_frame_bytes * timed_frames / (ms * 1e-3) / 1e9
+    # e2e: per-frame observe() with host buffers + camera pose read-back every frame
+    t_frames = 50
+    extra, _ = synth.make_map_build_stream(2000, 20, t_frames, seed=77)
+    nb = 2000 // 20
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for t in range(nb, nb + t_frames):
+        f.observe(extra.ids[t], extra.poses[t])
+        cam, _ = f.get_poses()
+    wall = time.perf_counter() - t0
+    del f
+    return {
+        "workload": "C3: single EKF, 2000-marker map (N=6010, FP64 P 289 MB), 20 markers/frame",
+        "value": 20.0 * timed_frames / (ms * 1e-3), "unit": UNIT, "us_per_frame": 1e3 * ms / timed_frames,
+        "frames": timed_frames, "gpu_launches_per_frame": 6,
+        "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
+                     "frac": ach / hbm_peak, "traffic": None,
+                     "note": "achieved = 16*N^2 B per frame / whole-frame time (all 6 kernels)"},
+        "e2e": {"value": 20.0 * t_frames / wall, "unit": UNIT, "h2d_bytes_per_step": 20 * 52,
+                "d2h_bytes_per_step": 8 * 6010},
+    }
+
+
+def leg_c4(torch, stream_ptr, hbm_peak, fp64_peak):
+    """C4: batched IPPE over 1M corner sets."""
+    from aruco_slam_b200 import estimate_pose_of_markers, synth
+    from aruco_slam_b200.ippe import estimate_pose_device
+    km, dist = synth.reference_calibration()
+    n = 1_000_000
+    base = synth.make_corner_sets(125_000, km, dist, seed=11)
+    corners = np.ascontiguousarray(np.tile(base, (8, 1, 1)))
+    d_c = torch.from_numpy(corners).cuda()
+    d_o = torch.empty((n, 6), dtype=torch.float64, device="cuda")
+    for _ in range(3):
+        estimate_pose_device(d_c.data_ptr(), n, km, dist, 0.16, d_o.data_ptr(), stream=stream_ptr)
+    torch.cuda.synchronize()
+    reps = 10
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        estimate_pose_device(d_c.data_ptr(), n, km, dist, 0.16, d_o.data_ptr(), stream=stream_ptr)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    t0 = time.perf_counter()
+    out = estimate_pose_of_markers(corners, km, dist, 0.16)
+    wall = time.perf_counter() - t0
+    ach = 80.0 * n / (ms * 1e-3) / 1e9
+    return {"workload": "C4: batched IPPE square-marker pose, 1M corner sets", "value": n / (ms * 1e-3),
+            "unit": "poses/s", "ms_per_batch": ms,
+            "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": ach / hbm_peak, "traffic": None,
+                         "note": "80 B per set (32 in + 48 out); the kernel is FP64-pipe bound"},
+            "e2e": {"value": n / wall, "unit": "poses/s", "h2d_bytes_per_step": 32 * n,
+                    "d2h_bytes_per_step": 48 * n}, "finite": bool(np.isfinite(out).all())}
+
+
+def run_b200(args):
+    import torch
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    torch.cuda.set_device(local)
+    if world > 1:
+        import torch.distributed as dist_mod
+        dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local))
+        dist = dist_mod
+    import ctypes as C
+    from aruco_slam_b200 import FilterBatch, _lib, synth
+
+    lib = _lib.lib()
+    hbm_peak, peak_src = measured_peaks()
+    fp64 = C.c_double()
+    _lib.check(lib.asb_fp64_peak(local, 0, C.byref(fp64)))
+    fp64_peak = fp64.value
+    # a non-default stream: the library launches on it and torch.cuda.Event times it
+    side = torch.cuda.Stream()
+    torch.cuda.set_stream(side)
+    stream_ptr = torch.cuda.current_stream().cuda_stream
+    assert stream_ptr != 0
+
+    if args.only:
+        leg = leg_c3(torch, stream_ptr, hbm_peak) if args.only == "c3" else \
+            leg_c4(torch, stream_ptr, hbm_peak, fp64_peak)
+        print(json.dumps(leg), flush=True)
+        return
+
+    # ---- synthetic observations of this rank's shard --------------------------------------
+    t_gen = time.perf_counter()
+    ids, poses, off = synth.make_batch(args.seqs, args.markers, args.frames, args.p_visible, args.kind,
+                                       seq_base=rank * args.unique, unique=args.unique)
+    n_updates = int(off[-1])
+    rows, width, d = (3, 13, 3) if args.kind == "ekf" else (7, 20, 10)
+    n_state = 10 + d * args.markers
+    counts = np.diff(off)
+    flops = float(sum(flops_batch_form(n_state, int(k), rows, width) * c
+                      for k, c in zip(*np.unique(counts, return_counts=True))))
+    gen_s = time.perf_counter() - t_gen
+    keep_i, h_ids = pinned_like(ids)
+    keep_p, h_poses = pinned_like(poses)
+    keep_o, h_off = pinned_like(off)
+
+    batch = FilterBatch(args.kind, args.seqs, args.markers, args.markers, quat_mode=args.quat_mode,
+                        device=local)
+    batch.set_stream(stream_ptr)
+    batch.upload(h_ids, h_poses, h_off)
+    torch.cuda.synchronize()
+
+    def step_resident():
+        batch.reset()
+        batch.run(0, args.frames)
+
+    def step_e2e():
+        batch.upload(h_ids, h_poses, h_off)
+        batch.reset()
+        batch.run(0, args.frames)
+        return batch.cameras()
+
+    for _ in range(args.warmup):
+        step_resident()
+    with ClockSampler(local) as clk:
+        ms = timed(torch, dist, step_resident, args.steps)
+    cams, status = batch.cameras()
+    ok = bool(np.isfinite(cams).all() and not status.any())
+    ms_step = ms / args.steps
+    value = world * n_updates / (ms_step * 1e-3)
+
+    # e2e through the public API with host buffers
+    step_e2e()
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_e2e()
+    torch.cuda.synchronize()
+    wall = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(wall, op=dist.ReduceOp.MAX)
+    e2e_value = world * n_updates * args.steps / float(wall.item())
+    h2d = ids.nbytes + poses.nbytes + off.nbytes
+    d2h = cams.nbytes + status.nbytes
+
+    ach_tf = flops / (ms_step * 1e-3) / 1e12
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64",
+        "data": f"synthetic (SURVEY.md 8d generator; {args.unique} distinct sequences per rank tiled to "
+                f"{args.seqs})",
+        "config": workload_config(args),
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "gpu_launches": 2 * args.steps,
+        "clocks": clk.summary(),
+        "roofline": {"bound": "fp64", "achieved": ach_tf, "peak": fp64_peak, "unit": "TFLOP/s",
+                     "frac": ach_tf / fp64_peak, "traffic": None,
+                     "note": "k_batch keeps each filter in shared memory; HBM traffic is the observation "
+                             "stream only, so the FP64 FMA pipe bounds it. achieved = algorithmic "
+                             "batch-form flops F(N,m,k) of SURVEY.md 8d / time; peak = DFMA peak measured "
+                             "live by asb_fp64_peak",
+                     "hbm_gbs": (h2d + 2 * args.seqs * 8 * (n_state + n_state * (n_state + 1) // 2))
+                     / (ms_step * 1e-3) / 1e9, "hbm_peak": hbm_peak, "hbm_peak_source": peak_src},
+        "valid": ok, "marker_updates_per_step_per_gpu": n_updates, "gen_seconds": gen_s,
+    }
+    del batch
+    if rank == 0 and world == 1:
+        if not args.no_extras:
+            line["workloads"] = {}
+            for name, leg in (("c3", lambda: leg_c3(torch, stream_ptr, hbm_peak)),
+                              ("c4", lambda: leg_c4(torch, stream_ptr, hbm_peak, fp64_peak))):
+                try:
+                    line["workloads"][name] = leg()
+                except Exception as exc:  # keep the headline line even if an extra leg fails
+                    line["workloads"][name] = {"error": repr(exc)}
+        frames = max(20, int(args.cpu_seconds / 2.6e-3 / 1.0))
+        frames = min(frames, args.frames)
+        v, total, wall_cpu = cpu_port_throughput(args, 1, frames)
+        line["cpu_baseline"] = {
+            "value": v, "unit": UNIT, "cores": 1, "kind": "port",
+            "sample": f"1 sequence x {args.markers} markers x {frames} frames of the same workload, "
+                      f"oracle/ekf_oracle.py (numpy restatement of the reference algorithm), "
+                      f"{wall_cpu:.1f} s on {os.cpu_count()} host cores (1 used)"}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -133,6 +133,8 @@ ASB_API int asb_batch_create(int kind, int quat_mode, const double pose0[10], co
                      int n_seq, int max_landmarks, int max_obs_per_frame, int device,
                      asb_batch** out);
 ASB_API int asb_batch_destroy(asb_batch* b);
+/* Back to the constructor's state (pose0, P = init_cam I10, empty maps), asynchronous. */
+ASB_API int asb_batch_reset(asb_batch* b);
 ASB_API int asb_batch_set_stream(asb_batch* b, void* cuda_stream);
 ASB_API int asb_batch_synchronize(asb_batch* b);
 /* offsets (n_seq*n_frames + 1) int64: frame t of sequence s = rows
