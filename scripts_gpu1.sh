@@ -1,3 +1,7 @@
 set -x
-python -m pytest tests -m gpu -q 2>&1 | tail -30
-python bench.py --steps 1 --warmup 1 2>&1 | tail -20
+mkdir -p gpurun_out
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv
+timeout 900 python -m pytest tests -m gpu -q -x 2>&1 | tail -30 > gpurun_out/pytest_gpu.log; tail -5 gpurun_out/pytest_gpu.log
+timeout 900 python bench.py --steps 3 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; tail -c 3000 gpurun_out/bench.json; tail -5 gpurun_out/bench.err
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_c3.csv python bench.py --only c3 > gpurun_out/ncu_c3.log 2>&1
+tail -3 gpurun_out/ncu_c3.log
