@@ -107,9 +107,8 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
             if (last)
                 k_apply<KIND><<<(std::max(f->nlm, 1) + 127) / 128, 128, 0, st>>>(
                     f->d_state, f->d_dx, f->nlm, (KIND == 0 && f->quat_mode == ASB_QUAT_AS_WRITTEN) ? 1 : 0);
-            const size_t sm_sweep = (size_t)m4 * (SW_TI + SW_TJ) * sizeof(double);
-            const int grid = std::min(ntiles, f->sweep_grid * (sm_sweep <= 100 * 1024 ? 2 : 1));
-            k_sweep<<<grid, SW_THREADS, sm_sweep, st>>>(f->d_P, ld, n1, f->d_G, m4, ntiles);
+            const int grid = std::min(ntiles, f->sweep_grid);  // persistent: one CTA per SM
+            k_sweep<<<grid, SW_THREADS, sweep_smem_bytes(m4), st>>>(f->d_P, ld, f->d_G, m4, ntiles);
         }
     }
     cudaError_t e = cudaGetLastError();
@@ -226,7 +225,7 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
                              cudaMemcpyHostToDevice, f->stream));
     ASB_CUDA(cudaStreamSynchronize(f->stream));
     // opt in to large dynamic shared memory
-    const int big = 200 * 1024;
+    const int big = (int)prop.sharedMemPerBlockOptin - 2048;  // static smem (mbarriers) counts too
     ASB_CUDA(cudaFuncSetAttribute(k_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_chol<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));

@@ -22,7 +22,7 @@ constexpr int SW_TI = 128;     // sweep tile rows
 constexpr int SW_TJ = 64;      // sweep tile cols
 constexpr int SW_THREADS = 256;
 constexpr int PAD = 128;       // leading dimension / row padding of P and V (doubles)
-constexpr int M_MAX = 128;     // max (padded) measurement rows per chunk
+constexpr int M_MAX = 96;      // max (padded) measurement rows per chunk (sweep panels: 96 x 268 x 8 B = 206 KB)
 
 // ------------------------------------------------------------------------------------
 // k_prep
@@ -377,103 +377,162 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
         : "memory");
 }
 
+// FP64 tensor-core MMA (SASS: DMMA.8x8x4): D(8x8) += A(8x4) B(4x8).  Lane (g = lane/4,
+// t = lane%4) holds A[g][t], B[t][g] and the accumulator pair C[g][2t], C[g][2t+1].
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+}
+
 // Tile (I, J) covers rows [128 I, 128 I + 128) x cols [64 J, 64 J + 64); the tiles with
 // 64 J <= 128 I + 127 are enumerated t = I (I + 1) + J, J in [0, 2 I + 2).
-// 256 threads = 16 (ti) x 16 (tj); thread micro-tile: rows 8 ti .. 8 ti + 7, columns
-// {2 tj, 2 tj + 1, 32 + 2 tj, 33 + 2 tj}  (16-byte pairs so that the panel reads are
-// bank-conflict free and global accesses are 16-byte vectors).
-__global__ void __launch_bounds__(SW_THREADS, 2)
-k_sweep(double* __restrict__ P, int ld, int n, const double* __restrict__ V, int m4, int ntiles) {
+//
+// Persistent kernel, one CTA per SM, 8 warps = 4 (rows) x 2 (cols); a warp owns a 32 x 32
+// block of the tile as 4 x 4 DMMA accumulator tiles.  Each CTA walks a contiguous chunk of
+// the tile list (row-block major), so the 128-column panel VI stays in shared memory while
+// the 64-column panel VJ is double-buffered: the bulk copies (TMA, SASS UBLKCP) of tile
+// t+1's VJ fly during tile t's MMAs.  The P sub-tile goes global -> registers in the
+// accumulator-fragment layout at the start of the tile and is only consumed after the
+// k-loop (out = P - V_I^T V_J), so its HBM latency hides behind the tile's own math; the
+// result is stored to (i, j) and mirrored to (j, i).
+// Panel row strides (SW_LDI, SW_LDJ) are = 4 mod 16 doubles: the fragment loads
+// (address = (4 kk + t) * stride + g) are then bank-conflict free.
+constexpr int SW_LDI = SW_TI + 4;
+constexpr int SW_LDJ = SW_TJ + 4;
+
+__host__ __device__ inline size_t sweep_smem_bytes(int m4) {
+    return (size_t)m4 * (SW_LDI + 2 * SW_LDJ) * sizeof(double);
+}
+
+__global__ void __launch_bounds__(SW_THREADS, 1)
+k_sweep(double* __restrict__ P, int ld, const double* __restrict__ V, int m4, int ntiles) {
     extern __shared__ __align__(128) unsigned char smraw[];
-    double* VI = reinterpret_cast<double*>(smraw);  // m4 x 128
-    double* VJ = VI + (size_t)m4 * SW_TI;           // m4 x 64
-    __shared__ __align__(8) uint64_t bar;
-    const int tid = threadIdx.x;
-    const int tj = tid & 15, ti = tid >> 4;
+    double* VI = reinterpret_cast<double*>(smraw);   // m4 x SW_LDI
+    double* VJ0 = VI + (size_t)m4 * SW_LDI;          // 2 x (m4 x SW_LDJ)
+    __shared__ __align__(8) uint64_t bar[3];         // [0] VI, [1] VJ buf 0, [2] VJ buf 1
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, t4 = lane & 3;
+    const int wi = warp >> 1, wj = warp & 1;
     if (tid == 0) {
-        mbar_init(&bar, 1);
+        mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], 1);
+        mbar_init(&bar[2], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
-    uint32_t phase = 0;
-    for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
-        int I = (int)((sqrt(4.0 * t + 1.0) - 1.0) * 0.5);
-        while ((I + 1) * (I + 2) <= t) ++I;
-        while (I * (I + 1) > t) --I;
-        const int J = t - I * (I + 1);
+    const int t_begin = (int)((long long)ntiles * blockIdx.x / gridDim.x);
+    const int t_end = (int)((long long)ntiles * (blockIdx.x + 1) / gridDim.x);
+    if (t_begin >= t_end) return;
+    int I = (int)((sqrt(4.0 * t_begin + 1.0) - 1.0) * 0.5);
+    while ((I + 1) * (I + 2) <= t_begin) ++I;
+    while (I * (I + 1) > t_begin) --I;
+    int J = t_begin - I * (I + 1);
+
+    auto load_vi = [&](int i0) {  // warp 0
+        if (lane == 0) mbar_expect_tx(&bar[0], (uint32_t)(m4 * SW_TI * sizeof(double)));
+        __syncwarp();
+        for (int a = lane; a < m4; a += 32)
+            bulk_g2s(VI + a * SW_LDI, V + (long long)a * ld + i0, SW_TI * sizeof(double), &bar[0]);
+    };
+    auto load_vj = [&](int buf, int j0) {  // warp 0
+        double* dst = VJ0 + (size_t)buf * m4 * SW_LDJ;
+        if (lane == 0) mbar_expect_tx(&bar[1 + buf], (uint32_t)(m4 * SW_TJ * sizeof(double)));
+        __syncwarp();
+        for (int a = lane; a < m4; a += 32)
+            bulk_g2s(dst + a * SW_LDJ, V + (long long)a * ld + j0, SW_TJ * sizeof(double), &bar[1 + buf]);
+    };
+
+    uint32_t ph_i = 0, ph_j = 0;  // ph_j: bit b = phase of VJ buffer b
+    bool vi_pending = true;
+    if (warp == 0) {
+        load_vi(I * SW_TI);
+        load_vj(0, J * SW_TJ);
+    }
+    int buf = 0;
+    for (int t = t_begin; t < t_end; ++t, buf ^= 1) {
         const int i0 = I * SW_TI, j0 = J * SW_TJ;
-        if (j0 >= n) continue;  // uniform across the CTA
-        // stage the two V panels with bulk copies (one per row of V)
-        if (tid < 32) {
-            if (tid == 0) mbar_expect_tx(&bar, (uint32_t)(m4 * (SW_TI + SW_TJ) * sizeof(double)));
-            __syncwarp();
-            for (int a = tid; a < m4; a += 32) {
-                bulk_g2s(VI + a * SW_TI, V + (long long)a * ld + i0, SW_TI * sizeof(double), &bar);
-                bulk_g2s(VJ + a * SW_TJ, V + (long long)a * ld + j0, SW_TJ * sizeof(double), &bar);
-            }
-        }
-        // P sub-tile -> registers
-        double acc[8][4];
-        const int gi = i0 + 8 * ti, gja = j0 + 2 * tj, gjb = j0 + 32 + 2 * tj;
+        // next tile
+        int In = I, Jn = J + 1;
+        if (Jn == 2 * I + 2) { In = I + 1; Jn = 0; }
+        const bool has_next = t + 1 < t_end;
+        if (warp == 0 && has_next) load_vj(buf ^ 1, Jn * SW_TJ);  // buffer freed by the last __syncthreads
+
+        // P sub-tile -> registers (accumulator-fragment layout)
+        const int ri = i0 + 32 * wi + g, cj = j0 + 32 * wj + 2 * t4;
+        double2 pf[4][4];
 #pragma unroll
-        for (int r = 0; r < 8; ++r) {
-            const double2 a = __ldcs(reinterpret_cast<const double2*>(P + (long long)(gi + r) * ld + gja));
-            const double2 b = __ldcs(reinterpret_cast<const double2*>(P + (long long)(gi + r) * ld + gjb));
-            acc[r][0] = a.x; acc[r][1] = a.y; acc[r][2] = b.x; acc[r][3] = b.y;
-        }
-        mbar_wait(&bar, phase);
-        phase ^= 1;
-        const double* vi = VI + 8 * ti;
-        const double* vja = VJ + 2 * tj;
-#pragma unroll 4
-        for (int a = 0; a < m4; ++a) {
-            const double2 x0 = *reinterpret_cast<const double2*>(vi + a * SW_TI);
-            const double2 x1 = *reinterpret_cast<const double2*>(vi + a * SW_TI + 2);
-            const double2 x2 = *reinterpret_cast<const double2*>(vi + a * SW_TI + 4);
-            const double2 x3 = *reinterpret_cast<const double2*>(vi + a * SW_TI + 6);
-            const double2 ya = *reinterpret_cast<const double2*>(vja + a * SW_TJ);
-            const double2 yb = *reinterpret_cast<const double2*>(vja + a * SW_TJ + 32);
-            const double xs[8] = {x0.x, x0.y, x1.x, x1.y, x2.x, x2.y, x3.x, x3.y};
+        for (int rm = 0; rm < 4; ++rm)
 #pragma unroll
-            for (int r = 0; r < 8; ++r) {
-                acc[r][0] -= xs[r] * ya.x;
-                acc[r][1] -= xs[r] * ya.y;
-                acc[r][2] -= xs[r] * yb.x;
-                acc[r][3] -= xs[r] * yb.y;
-            }
+            for (int rn = 0; rn < 4; ++rn)
+                pf[rm][rn] = *reinterpret_cast<const double2*>(P + (long long)(ri + 8 * rm) * ld + cj + 8 * rn);
+
+        double acc[4][4][2];
+#pragma unroll
+        for (int rm = 0; rm < 4; ++rm)
+#pragma unroll
+            for (int rn = 0; rn < 4; ++rn) acc[rm][rn][0] = acc[rm][rn][1] = 0.0;
+
+        if (vi_pending) {
+            mbar_wait(&bar[0], ph_i);
+            ph_i ^= 1;
+            vi_pending = false;
         }
-        const bool interior = (i0 >= j0 + SW_TJ) && (i0 + SW_TI <= n);  // strictly below diagonal, in range
+        mbar_wait(&bar[1 + buf], (ph_j >> buf) & 1u);
+        ph_j ^= 1u << buf;
+
+        const double* va = VI + t4 * SW_LDI + 32 * wi + g;
+        const double* vb = VJ0 + (size_t)buf * m4 * SW_LDJ + t4 * SW_LDJ + 32 * wj + g;
+#pragma unroll 3
+        for (int kk = 0; kk < m4; kk += 4) {
+            double a[4], b[4];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                a[r] = va[kk * SW_LDI + 8 * r];
+                b[r] = vb[kk * SW_LDJ + 8 * r];
+            }
+#pragma unroll
+            for (int rm = 0; rm < 4; ++rm)
+#pragma unroll
+                for (int rn = 0; rn < 4; ++rn) dmma884(acc[rm][rn][0], acc[rm][rn][1], a[rm], b[rn]);
+        }
+
+        const bool interior = i0 >= j0 + SW_TJ;  // strictly below the diagonal
         if (interior) {
 #pragma unroll
-            for (int r = 0; r < 8; ++r) {
-                double* row = P + (long long)(gi + r) * ld;
-                __stcs(reinterpret_cast<double2*>(row + gja), make_double2(acc[r][0], acc[r][1]));
-                __stcs(reinterpret_cast<double2*>(row + gjb), make_double2(acc[r][2], acc[r][3]));
-            }
-            const int cols[4] = {gja, gja + 1, gjb, gjb + 1};
+            for (int rm = 0; rm < 4; ++rm)
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                double* row = P + (long long)cols[c] * ld + gi;
-#pragma unroll
-                for (int r = 0; r < 8; r += 2)
-                    __stcs(reinterpret_cast<double2*>(row + r), make_double2(acc[r][c], acc[r + 1][c]));
-            }
+                for (int rn = 0; rn < 4; ++rn) {
+                    const double o0 = pf[rm][rn].x - acc[rm][rn][0], o1 = pf[rm][rn].y - acc[rm][rn][1];
+                    const int i = ri + 8 * rm, j = cj + 8 * rn;
+                    *reinterpret_cast<double2*>(P + (long long)i * ld + j) = make_double2(o0, o1);
+                    P[(long long)j * ld + i] = o0;
+                    P[(long long)(j + 1) * ld + i] = o1;
+                }
         } else {
-            const int cols[4] = {gja, gja + 1, gjb, gjb + 1};
 #pragma unroll
-            for (int r = 0; r < 8; ++r) {
-                const int i = gi + r;
+            for (int rm = 0; rm < 4; ++rm)
 #pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    const int j = cols[c];
-                    if (i < n && j < n && i >= j) {
-                        P[(long long)i * ld + j] = acc[r][c];
-                        if (i > j) P[(long long)j * ld + i] = acc[r][c];
+                for (int rn = 0; rn < 4; ++rn) {
+                    const double o[2] = {pf[rm][rn].x - acc[rm][rn][0], pf[rm][rn].y - acc[rm][rn][1]};
+                    const int i = ri + 8 * rm;
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        const int j = cj + 8 * rn + e;
+                        if (i >= j) {
+                            P[(long long)i * ld + j] = o[e];
+                            if (i > j) P[(long long)j * ld + i] = o[e];
+                        }
                     }
                 }
-            }
         }
-        __syncthreads();  // all panel reads done before the next tile's bulk copies land
+        __syncthreads();  // every warp is done with VJ[buf] (and VI) before they are overwritten
+        if (has_next && In != I) {
+            if (warp == 0) load_vi(In * SW_TI);
+            vi_pending = true;
+        }
+        I = In;
+        J = Jn;
     }
 }
 
