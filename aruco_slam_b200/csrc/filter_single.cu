@@ -4,6 +4,7 @@
 // single_kernels.cuh.  All arithmetic runs in the CUDA kernels; there is no CPU fallback.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <new>
 #include <unordered_map>
 #include <vector>
@@ -35,7 +36,7 @@ struct asb_filter {
     std::vector<int32_t> id_order;
 
     cudaStream_t own_stream = nullptr, stream = nullptr;
-    double *d_state = nullptr, *d_P = nullptr, *d_G = nullptr, *d_blocks = nullptr, *d_nu = nullptr;
+    double *d_state = nullptr, *d_P = nullptr, *d_G = nullptr, *d_Vt = nullptr, *d_blocks = nullptr, *d_nu = nullptr;
     double *d_L = nullptr, *d_invd = nullptr, *d_y = nullptr, *d_dx = nullptr, *d_unc = nullptr;
     int* d_status = nullptr;
     // staging ring (host pinned + device)
@@ -49,7 +50,7 @@ struct asb_filter {
     int* s_idx = nullptr; double* s_pose = nullptr; unsigned char* s_new = nullptr;
     std::vector<FrameRec> frames;
     int next_frame = 0;
-    int sweep_grid = 0;
+    int sweep_grid = 0, smem_optin = 0, force_big = 0;
 
     int n_state() const { return CAM + D * nlm; }
 };
@@ -87,8 +88,6 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
                                            f->d_blocks, f->d_nu, do_predict ? 1 : 0);
     }
     if (do_update && k > 0) {
-        const int nI = (n1 + SW_TI - 1) / SW_TI;
-        const int ntiles = nI * (nI + 1);
         for (int c0 = 0; c0 < k; c0 += f->kc_max) {
             const int kc = std::min(f->kc_max, k - c0);
             const int m = R * kc, m4 = round_up(m, 4);
@@ -103,12 +102,23 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
                                                   c0 > 0 ? 1 : 0, f->d_L, f->d_invd, f->d_y, f->d_status);
             const size_t sm_solve = ((size_t)m4 * m4 + (size_t)m4 * SOLVE_COLS + 2 * m4) * sizeof(double);
             k_solve<<<(ld + SOLVE_COLS - 1) / SOLVE_COLS, SOLVE_COLS, sm_solve, st>>>(
-                f->d_G, ld, n1, m4, f->d_L, f->d_invd, f->d_y, f->d_dx, c0 > 0 ? 1 : 0);
+                f->d_G, f->d_Vt, ld, n1, m4, f->d_L, f->d_invd, f->d_y, f->d_dx, c0 > 0 ? 1 : 0);
             if (last)
                 k_apply<KIND><<<(std::max(f->nlm, 1) + 127) / 128, 128, 0, st>>>(
                     f->d_state, f->d_dx, f->nlm, (KIND == 0 && f->quat_mode == ASB_QUAT_AS_WRITTEN) ? 1 : 0);
-            const int grid = std::min(ntiles, f->sweep_grid);  // persistent: one CTA per SM
-            k_sweep<<<grid, SW_THREADS, sweep_smem_bytes(m4), st>>>(f->d_P, ld, f->d_G, m4, ntiles);
+            // persistent sweep: 2 CTAs / SM (64 x 64 tiles) while both fit in shared memory,
+            // else 1 CTA / SM (128 x 64 tiles)
+            if (2 * (SweepDual::smem_bytes(m4) + 1024) <= (size_t)f->smem_optin && !f->force_big) {
+                const int ntiles = SweepDual::num_tiles(n1);
+                const int grid = std::min(ntiles, 2 * f->sweep_grid);
+                k_sweep<SweepDual><<<grid, SweepDual::THREADS, SweepDual::smem_bytes(m4), st>>>(
+                    f->d_P, ld, f->d_Vt, m4, ntiles, 0);
+            } else {
+                const int ntiles = SweepBig::num_tiles(n1);
+                const int grid = std::min(ntiles, f->sweep_grid);
+                k_sweep<SweepBig><<<grid, SweepBig::THREADS, SweepBig::smem_bytes(m4), st>>>(
+                    f->d_P, ld, f->d_Vt, m4, ntiles, 0);
+            }
         }
     }
     cudaError_t e = cudaGetLastError();
@@ -190,12 +200,16 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
     cudaDeviceProp prop;
     ASB_CUDA(cudaGetDeviceProperties(&prop, device));
     f->sweep_grid = prop.multiProcessorCount;
+    f->smem_optin = (int)prop.sharedMemPerBlockOptin;
+    if (const char* e = std::getenv("ASB_SWEEP_BIG")) f->force_big = std::atoi(e);
     ASB_CUDA(cudaStreamCreateWithFlags(&f->own_stream, cudaStreamNonBlocking));
     f->stream = f->own_stream;
     const size_t ld = f->ld;
     ASB_CUDA(dmalloc(&f->d_state, ld));
     ASB_CUDA(dmalloc(&f->d_P, ld * ld));
     ASB_CUDA(dmalloc(&f->d_G, (size_t)M_MAX * ld));
+    ASB_CUDA(dmalloc(&f->d_Vt, (size_t)M_MAX * V_LDB * (ld / V_BLK)));
+    ASB_CUDA(cudaMemsetAsync(f->d_Vt, 0, (size_t)M_MAX * V_LDB * (ld / V_BLK) * sizeof(double), f->stream));
     ASB_CUDA(dmalloc(&f->d_blocks, (size_t)f->max_obs * f->R * f->W));
     ASB_CUDA(dmalloc(&f->d_nu, (size_t)f->max_obs * f->R));
     ASB_CUDA(dmalloc(&f->d_L, (size_t)M_MAX * M_MAX));
@@ -226,7 +240,8 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
     ASB_CUDA(cudaStreamSynchronize(f->stream));
     // opt in to large dynamic shared memory
     const int big = (int)prop.sharedMemPerBlockOptin - 2048;  // static smem (mbarriers) counts too
-    ASB_CUDA(cudaFuncSetAttribute(k_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepBig>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepDual>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_chol<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_chol<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
@@ -237,7 +252,7 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
 int asb_filter_destroy(asb_filter* f) {
     ASB_CHECK_HANDLE(f);
     cudaStreamSynchronize(f->stream);
-    cudaFree(f->d_state); cudaFree(f->d_P); cudaFree(f->d_G); cudaFree(f->d_blocks); cudaFree(f->d_nu);
+    cudaFree(f->d_state); cudaFree(f->d_P); cudaFree(f->d_G); cudaFree(f->d_Vt); cudaFree(f->d_blocks); cudaFree(f->d_nu);
     cudaFree(f->d_L); cudaFree(f->d_invd); cudaFree(f->d_y); cudaFree(f->d_dx); cudaFree(f->d_unc);
     cudaFree(f->d_status); cudaFree(f->d_idx); cudaFree(f->d_pose); cudaFree(f->d_new);
     cudaFree(f->s_idx); cudaFree(f->s_pose); cudaFree(f->s_new);
@@ -488,6 +503,35 @@ int asb_device_views(asb_filter* f, void** d_state, void** d_cov, int* ld) {
     if (d_state) *d_state = f->d_state;
     if (d_cov) *d_cov = f->d_P;
     if (ld) *ld = f->ld;
+    return ASB_OK;
+}
+
+int asb_bench_sweep(asb_filter* f, int m4, int config, int dbg, int reps, double* us_per_launch) {
+    ASB_CHECK_HANDLE(f);
+    if (!us_per_launch || m4 < 4 || m4 > M_MAX || (m4 & 3) || reps < 1) return fail(ASB_ERR_BAD_ARG, "bad args");
+    const int n1 = f->n_state(), ld = f->ld;
+    cudaEvent_t e0, e1;
+    ASB_CUDA(cudaEventCreate(&e0));
+    ASB_CUDA(cudaEventCreate(&e1));
+    for (int rep = -2; rep < reps; ++rep) {
+        if (rep == 0) ASB_CUDA(cudaEventRecord(e0, f->stream));
+        if (config == 1) {
+            const int ntiles = SweepDual::num_tiles(n1);
+            k_sweep<SweepDual><<<std::min(ntiles, 2 * f->sweep_grid), SweepDual::THREADS, SweepDual::smem_bytes(m4),
+                                 f->stream>>>(f->d_P, ld, f->d_Vt, m4, ntiles, dbg);
+        } else {
+            const int ntiles = SweepBig::num_tiles(n1);
+            k_sweep<SweepBig><<<std::min(ntiles, f->sweep_grid), SweepBig::THREADS, SweepBig::smem_bytes(m4),
+                                f->stream>>>(f->d_P, ld, f->d_Vt, m4, ntiles, dbg);
+        }
+    }
+    ASB_CUDA(cudaEventRecord(e1, f->stream));
+    ASB_CUDA(cudaEventSynchronize(e1));
+    float ms = 0;
+    ASB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *us_per_launch = 1e3 * ms / reps;
     return ASB_OK;
 }
 

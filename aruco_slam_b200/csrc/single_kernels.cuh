@@ -15,12 +15,10 @@
 
 #include "../../include/aruco_slam_b200.h"
 #include "model.cuh"
+#include "sweep.cuh"
 
 namespace asb {
 
-constexpr int SW_TI = 128;     // sweep tile rows
-constexpr int SW_TJ = 64;      // sweep tile cols
-constexpr int SW_THREADS = 256;
 constexpr int PAD = 128;       // leading dimension / row padding of P and V (doubles)
 constexpr int M_MAX = 96;      // max (padded) measurement rows per chunk (sweep panels: 96 x 268 x 8 B = 206 KB)
 
@@ -268,15 +266,15 @@ k_chol(const double* __restrict__ G, int ld, const int* __restrict__ idx,
 }
 
 // ------------------------------------------------------------------------------------
-// k_solve: V = L^-1 G in place (blocked forward substitution, 4 rows at a time, one
+// k_solve: V = L^-1 G, written in the tiled panel layout (blocked forward substitution, 4 rows at a time, one
 // thread per column) and dx (+)= V^T y.
 // ------------------------------------------------------------------------------------
 constexpr int SOLVE_COLS = 64;
 
 __global__ void __launch_bounds__(SOLVE_COLS)
-k_solve(double* __restrict__ G, int ld, int n, int m4, const double* __restrict__ Lg,
-        const double* __restrict__ invd, const double* __restrict__ y, double* __restrict__ dx,
-        int accumulate) {
+k_solve(const double* __restrict__ G, double* __restrict__ Vt, int ld, int n, int m4,
+        const double* __restrict__ Lg, const double* __restrict__ invd, const double* __restrict__ y,
+        double* __restrict__ dx, int accumulate) {
     extern __shared__ double sm[];
     double* Ls = sm;                       // m4 x m4
     double* Vs = Ls + m4 * m4;             // m4 x SOLVE_COLS
@@ -306,8 +304,8 @@ k_solve(double* __restrict__ G, int ld, int n, int m4, const double* __restrict_
         v3 = (v3 - l3[a0] * v0 - l3[a0 + 1] * v1 - l3[a0 + 2] * v2) * ds[a0 + 3];
         Vs[(a0 + 0) * SOLVE_COLS + tid] = v0; Vs[(a0 + 1) * SOLVE_COLS + tid] = v1;
         Vs[(a0 + 2) * SOLVE_COLS + tid] = v2; Vs[(a0 + 3) * SOLVE_COLS + tid] = v3;
-        G[(long long)(a0 + 0) * ld + j] = v0; G[(long long)(a0 + 1) * ld + j] = v1;
-        G[(long long)(a0 + 2) * ld + j] = v2; G[(long long)(a0 + 3) * ld + j] = v3;
+        double* vt = Vt + v_index(m4, a0, j);  // tiled panel layout the sweep's bulk copies expect (sweep.cuh)
+        vt[0] = v0; vt[V_LDB] = v1; vt[2 * V_LDB] = v2; vt[3 * V_LDB] = v3;
         acc += v0 * ys[a0] + v1 * ys[a0 + 1] + v2 * ys[a0 + 2] + v3 * ys[a0 + 3];
     }
     if (j < n) dx[j] = accumulate ? dx[j] + acc : acc;
@@ -338,201 +336,6 @@ __global__ void k_apply(double* __restrict__ state, const double* __restrict__ d
         landmark_update<KIND>(lm, d);
 #pragma unroll
         for (int c = 0; c < D; ++c) s[c] = lm[c];
-    }
-}
-
-// ------------------------------------------------------------------------------------
-// k_sweep: P <- P - V^T V on lower-triangle tiles, mirrored into the upper triangle.
-// ------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) {
-    return (uint32_t)__cvta_generic_to_shared(p);
-}
-__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
-                 "r"(bytes)
-                 : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t phase) {
-    asm volatile(
-        "{\n"
-        ".reg .pred P1;\n"
-        "LAB_WAIT:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
-        "@P1 bra DONE;\n"
-        "bra LAB_WAIT;\n"
-        "DONE:\n"
-        "}\n" ::"r"(smem_u32(bar)),
-        "r"(phase)
-        : "memory");
-}
-// TMA bulk copy global -> shared, completion on an mbarrier (SASS: UBLKCP).
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-    asm volatile(
-        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
-            "r"(smem_u32(dst)),
-        "l"(src), "r"(bytes), "r"(smem_u32(bar))
-        : "memory");
-}
-
-// FP64 tensor-core MMA (SASS: DMMA.8x8x4): D(8x8) += A(8x4) B(4x8).  Lane (g = lane/4,
-// t = lane%4) holds A[g][t], B[t][g] and the accumulator pair C[g][2t], C[g][2t+1].
-__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
-    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
-                 : "+d"(c0), "+d"(c1)
-                 : "d"(a), "d"(b));
-}
-
-// Tile (I, J) covers rows [128 I, 128 I + 128) x cols [64 J, 64 J + 64); the tiles with
-// 64 J <= 128 I + 127 are enumerated t = I (I + 1) + J, J in [0, 2 I + 2).
-//
-// Persistent kernel, one CTA per SM, 8 warps = 4 (rows) x 2 (cols); a warp owns a 32 x 32
-// block of the tile as 4 x 4 DMMA accumulator tiles.  Each CTA walks a contiguous chunk of
-// the tile list (row-block major), so the 128-column panel VI stays in shared memory while
-// the 64-column panel VJ is double-buffered: the bulk copies (TMA, SASS UBLKCP) of tile
-// t+1's VJ fly during tile t's MMAs.  The P sub-tile goes global -> registers in the
-// accumulator-fragment layout at the start of the tile and is only consumed after the
-// k-loop (out = P - V_I^T V_J), so its HBM latency hides behind the tile's own math; the
-// result is stored to (i, j) and mirrored to (j, i).
-// Panel row strides (SW_LDI, SW_LDJ) are = 4 mod 16 doubles: the fragment loads
-// (address = (4 kk + t) * stride + g) are then bank-conflict free.
-constexpr int SW_LDI = SW_TI + 4;
-constexpr int SW_LDJ = SW_TJ + 4;
-
-__host__ __device__ inline size_t sweep_smem_bytes(int m4) {
-    return (size_t)m4 * (SW_LDI + 2 * SW_LDJ) * sizeof(double);
-}
-
-__global__ void __launch_bounds__(SW_THREADS, 1)
-k_sweep(double* __restrict__ P, int ld, const double* __restrict__ V, int m4, int ntiles) {
-    extern __shared__ __align__(128) unsigned char smraw[];
-    double* VI = reinterpret_cast<double*>(smraw);   // m4 x SW_LDI
-    double* VJ0 = VI + (size_t)m4 * SW_LDI;          // 2 x (m4 x SW_LDJ)
-    __shared__ __align__(8) uint64_t bar[3];         // [0] VI, [1] VJ buf 0, [2] VJ buf 1
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int g = lane >> 2, t4 = lane & 3;
-    const int wi = warp >> 1, wj = warp & 1;
-    if (tid == 0) {
-        mbar_init(&bar[0], 1);
-        mbar_init(&bar[1], 1);
-        mbar_init(&bar[2], 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncthreads();
-    const int t_begin = (int)((long long)ntiles * blockIdx.x / gridDim.x);
-    const int t_end = (int)((long long)ntiles * (blockIdx.x + 1) / gridDim.x);
-    if (t_begin >= t_end) return;
-    int I = (int)((sqrt(4.0 * t_begin + 1.0) - 1.0) * 0.5);
-    while ((I + 1) * (I + 2) <= t_begin) ++I;
-    while (I * (I + 1) > t_begin) --I;
-    int J = t_begin - I * (I + 1);
-
-    auto load_vi = [&](int i0) {  // warp 0
-        if (lane == 0) mbar_expect_tx(&bar[0], (uint32_t)(m4 * SW_TI * sizeof(double)));
-        __syncwarp();
-        for (int a = lane; a < m4; a += 32)
-            bulk_g2s(VI + a * SW_LDI, V + (long long)a * ld + i0, SW_TI * sizeof(double), &bar[0]);
-    };
-    auto load_vj = [&](int buf, int j0) {  // warp 0
-        double* dst = VJ0 + (size_t)buf * m4 * SW_LDJ;
-        if (lane == 0) mbar_expect_tx(&bar[1 + buf], (uint32_t)(m4 * SW_TJ * sizeof(double)));
-        __syncwarp();
-        for (int a = lane; a < m4; a += 32)
-            bulk_g2s(dst + a * SW_LDJ, V + (long long)a * ld + j0, SW_TJ * sizeof(double), &bar[1 + buf]);
-    };
-
-    uint32_t ph_i = 0, ph_j = 0;  // ph_j: bit b = phase of VJ buffer b
-    bool vi_pending = true;
-    if (warp == 0) {
-        load_vi(I * SW_TI);
-        load_vj(0, J * SW_TJ);
-    }
-    int buf = 0;
-    for (int t = t_begin; t < t_end; ++t, buf ^= 1) {
-        const int i0 = I * SW_TI, j0 = J * SW_TJ;
-        // next tile
-        int In = I, Jn = J + 1;
-        if (Jn == 2 * I + 2) { In = I + 1; Jn = 0; }
-        const bool has_next = t + 1 < t_end;
-        if (warp == 0 && has_next) load_vj(buf ^ 1, Jn * SW_TJ);  // buffer freed by the last __syncthreads
-
-        // P sub-tile -> registers (accumulator-fragment layout)
-        const int ri = i0 + 32 * wi + g, cj = j0 + 32 * wj + 2 * t4;
-        double2 pf[4][4];
-#pragma unroll
-        for (int rm = 0; rm < 4; ++rm)
-#pragma unroll
-            for (int rn = 0; rn < 4; ++rn)
-                pf[rm][rn] = *reinterpret_cast<const double2*>(P + (long long)(ri + 8 * rm) * ld + cj + 8 * rn);
-
-        double acc[4][4][2];
-#pragma unroll
-        for (int rm = 0; rm < 4; ++rm)
-#pragma unroll
-            for (int rn = 0; rn < 4; ++rn) acc[rm][rn][0] = acc[rm][rn][1] = 0.0;
-
-        if (vi_pending) {
-            mbar_wait(&bar[0], ph_i);
-            ph_i ^= 1;
-            vi_pending = false;
-        }
-        mbar_wait(&bar[1 + buf], (ph_j >> buf) & 1u);
-        ph_j ^= 1u << buf;
-
-        const double* va = VI + t4 * SW_LDI + 32 * wi + g;
-        const double* vb = VJ0 + (size_t)buf * m4 * SW_LDJ + t4 * SW_LDJ + 32 * wj + g;
-#pragma unroll 3
-        for (int kk = 0; kk < m4; kk += 4) {
-            double a[4], b[4];
-#pragma unroll
-            for (int r = 0; r < 4; ++r) {
-                a[r] = va[kk * SW_LDI + 8 * r];
-                b[r] = vb[kk * SW_LDJ + 8 * r];
-            }
-#pragma unroll
-            for (int rm = 0; rm < 4; ++rm)
-#pragma unroll
-                for (int rn = 0; rn < 4; ++rn) dmma884(acc[rm][rn][0], acc[rm][rn][1], a[rm], b[rn]);
-        }
-
-        const bool interior = i0 >= j0 + SW_TJ;  // strictly below the diagonal
-        if (interior) {
-#pragma unroll
-            for (int rm = 0; rm < 4; ++rm)
-#pragma unroll
-                for (int rn = 0; rn < 4; ++rn) {
-                    const double o0 = pf[rm][rn].x - acc[rm][rn][0], o1 = pf[rm][rn].y - acc[rm][rn][1];
-                    const int i = ri + 8 * rm, j = cj + 8 * rn;
-                    *reinterpret_cast<double2*>(P + (long long)i * ld + j) = make_double2(o0, o1);
-                    P[(long long)j * ld + i] = o0;
-                    P[(long long)(j + 1) * ld + i] = o1;
-                }
-        } else {
-#pragma unroll
-            for (int rm = 0; rm < 4; ++rm)
-#pragma unroll
-                for (int rn = 0; rn < 4; ++rn) {
-                    const double o[2] = {pf[rm][rn].x - acc[rm][rn][0], pf[rm][rn].y - acc[rm][rn][1]};
-                    const int i = ri + 8 * rm;
-#pragma unroll
-                    for (int e = 0; e < 2; ++e) {
-                        const int j = cj + 8 * rn + e;
-                        if (i >= j) {
-                            P[(long long)i * ld + j] = o[e];
-                            if (i > j) P[(long long)j * ld + i] = o[e];
-                        }
-                    }
-                }
-        }
-        __syncthreads();  // every warp is done with VJ[buf] (and VI) before they are overwritten
-        if (has_next && In != I) {
-            if (warp == 0) load_vi(In * SW_TI);
-            vi_pending = true;
-        }
-        I = In;
-        J = Jn;
     }
 }
 

@@ -168,6 +168,11 @@ ASB_API int asb_ippe_square_device(const float* d_corners, int64_t n, const doub
 /* FP64 pipe micro-benchmarks: achieved TFLOP/s of dependent-free DFMA chains and of
  * mma.sync m8n8k4 f64 (DMMA), timed with CUDA events. which: 0 = DFMA, 1 = DMMA, 2 = both. */
 ASB_API int asb_fp64_peak(int device, int which, double* tflops);
+/* The covariance sweep kernel alone on this filter's current P (state dims as they are),
+ * `reps` back-to-back launches timed with CUDA events.  config 0 = 128x64 tiles 1 CTA/SM,
+ * 1 = 64x64 tiles 2 CTAs/SM.  dbg != 0 disables parts of the kernel (experiments; the
+ * filter's P is garbage afterwards).  V is whatever the last update left in the panel. */
+ASB_API int asb_bench_sweep(asb_filter* f, int m4, int config, int dbg, int reps, double* us_per_launch);
 /* Streaming copy bandwidth (GB/s, read+write bytes) over `bytes` of HBM. */
 ASB_API int asb_copy_bandwidth(int device, int64_t bytes, double* gbs);
 
