@@ -88,6 +88,42 @@ __global__ void __launch_bounds__(256) k_mixed_peak(double* out, int iters, doub
     if (s == 123.456) out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
+// dependent-issue latencies (clocks per op) of one warp: DFMA, rsqrt(double), LDS.64, BAR.SYNC (256 thr)
+__global__ void k_latency(double* out, double seed) {
+    __shared__ double sm[64];
+    const int n = 512;
+    double a = seed, r[4];
+    long long t0, t1;
+    if (threadIdx.x < 64) sm[threadIdx.x] = (double)((threadIdx.x + 1) & 63);
+    __syncthreads();
+    t0 = clock64();
+#pragma unroll 16
+    for (int i = 0; i < n; ++i) a = fma(a, 1.0000001, 1e-9);
+    t1 = clock64();
+    r[0] = (double)(t1 - t0) / n;
+    double b = 1.5 + a * 1e-30;
+    t0 = clock64();
+#pragma unroll 4
+    for (int i = 0; i < 64; ++i) b = rsqrt(b) + 1.0;
+    t1 = clock64();
+    r[1] = (double)(t1 - t0) / 64;
+    int idx = (int)(b * 1e-30);
+    t0 = clock64();
+#pragma unroll 16
+    for (int i = 0; i < n; ++i) idx = (int)sm[idx];
+    t1 = clock64();
+    r[2] = (double)(t1 - t0) / n;
+    t0 = clock64();
+#pragma unroll 16
+    for (int i = 0; i < 64; ++i) __syncthreads();
+    t1 = clock64();
+    r[3] = (double)(t1 - t0) / 64;
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        out[0] = r[0]; out[1] = r[1]; out[2] = r[2]; out[3] = r[3];
+        out[4] = a + b + idx;
+    }
+}
+
 __global__ void k_copy(const double2* __restrict__ src, double2* __restrict__ dst, long long n) {
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
@@ -156,6 +192,20 @@ int asb_fp64_peak(int device, int which, double* tflops) {
     cudaEventDestroy(e1);
     cudaFree(out);
     *tflops = best;
+    return ASB_OK;
+}
+
+int asb_latency_probe(int device, double clocks[4]) {
+    if (!clocks) return fail(ASB_ERR_BAD_ARG, "clocks is NULL");
+    ASB_CUDA(cudaSetDevice(device));
+    double* out = nullptr;
+    ASB_CUDA(cudaMalloc(&out, 8 * sizeof(double)));
+    k_latency<<<1, 256>>>(out, 1.0);
+    k_latency<<<1, 256>>>(out, 1.0);
+    double h[8];
+    ASB_CUDA(cudaMemcpy(h, out, sizeof h, cudaMemcpyDeviceToHost));
+    cudaFree(out);
+    for (int i = 0; i < 4; ++i) clocks[i] = h[i];
     return ASB_OK;
 }
 

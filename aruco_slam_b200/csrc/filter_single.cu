@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include "front.cuh"
 #include "single_kernels.cuh"
 
 using namespace asb;
@@ -36,9 +37,10 @@ struct asb_filter {
     std::vector<int32_t> id_order;
 
     cudaStream_t own_stream = nullptr, stream = nullptr;
-    double *d_state = nullptr, *d_P = nullptr, *d_G = nullptr, *d_Vt = nullptr, *d_blocks = nullptr, *d_nu = nullptr;
-    double *d_L = nullptr, *d_invd = nullptr, *d_y = nullptr, *d_dx = nullptr, *d_unc = nullptr;
+    double *d_state = nullptr, *d_P = nullptr, *d_Vt = nullptr, *d_blocks = nullptr, *d_nu = nullptr;
+    double *d_dx[2] = {nullptr, nullptr}, *dx_last = nullptr, *d_unc = nullptr;
     int* d_status = nullptr;
+    unsigned long long* d_prof = nullptr;
     // staging ring (host pinned + device)
     int* h_idx = nullptr; double* h_pose = nullptr; unsigned char* h_new = nullptr;
     int* d_idx = nullptr; double* d_pose = nullptr; unsigned char* d_new = nullptr;
@@ -75,51 +77,67 @@ static cudaError_t dmalloc(T** p, size_t count) {
 // ---------------------------------------------------------------------------------------
 // launch sequence for one frame whose observations are at (idx, pose, isnew) on the device
 // ---------------------------------------------------------------------------------------
+// persistent sweep: 2 CTAs / SM (64 x 64 tiles) while both fit in shared memory, else
+// 1 CTA / SM (128 x 64 tiles)
+static void launch_sweep(asb_filter* f, int n1, int m4, int dbg, const SweepExtra& ex, int config = -1) {
+    const bool dual = config < 0 ? (2 * (SweepDual::smem_bytes(m4) + 1024) <= (size_t)f->smem_optin && !f->force_big)
+                                 : config == 1;
+    if (dual) {
+        const int ntiles = SweepDual::num_tiles(n1);
+        const int grid = std::min(ntiles, 2 * f->sweep_grid);
+        k_sweep<SweepDual><<<grid, SweepDual::THREADS, SweepDual::smem_bytes(m4), f->stream>>>(
+            f->d_P, f->ld, f->d_Vt, m4, ntiles, dbg, ex);
+    } else {
+        const int ntiles = SweepBig::num_tiles(n1);
+        const int grid = std::min(ntiles, f->sweep_grid);
+        k_sweep<SweepBig><<<grid, SweepBig::THREADS, SweepBig::smem_bytes(m4), f->stream>>>(
+            f->d_P, f->ld, f->d_Vt, m4, ntiles, dbg, ex);
+    }
+}
+
 template <int KIND>
 static int launch_frame(asb_filter* f, const int* idx, const double* pose, const unsigned char* isnew,
                         int k, int n0, int n1, bool do_predict, bool do_update) {
-    constexpr int D = Dims<KIND>::D, R = Dims<KIND>::R, W = CAM + D;
+    constexpr int R = Dims<KIND>::R, W = CAM + Dims<KIND>::D;
     cudaStream_t st = f->stream;
     const int ld = f->ld;
-    {
+    if (!do_update || k == 0) {
+        // predict() / add_marker() on their own: diagonal add, covariance growth, new states
         long long work = (long long)n0 + (long long)(n1 - n0) * (n1 + n0);
         int grid = (int)std::min<long long>(1 + work / 1024, 592);
         k_prep<KIND><<<grid, 256, 0, st>>>(f->d_state, f->d_P, ld, n0, n1, f->nz, idx, pose, isnew, k,
-                                           f->d_blocks, f->d_nu, do_predict ? 1 : 0);
-    }
-    if (do_update && k > 0) {
+                                           do_predict ? 1 : 0);
+    } else {
+        // update: two launches per chunk of <= kc_max markers (k_front, k_sweep)
+        int cur = 0;
         for (int c0 = 0; c0 < k; c0 += f->kc_max) {
             const int kc = std::min(f->kc_max, k - c0);
-            const int m = R * kc, m4 = round_up(m, 4);
-            const bool last = c0 + kc >= k;
-            dim3 gg((ld + 127) / 128, (kc + GATHER_OBS - 1) / GATHER_OBS);
-            k_gather<KIND><<<gg, 128, 0, st>>>(f->d_P, ld, n1, idx + c0, f->d_blocks + (size_t)c0 * R * W,
-                                               kc, m4, f->d_G);
-            const int lds = (m + 1) | 1;
-            const size_t sm_chol = (size_t)(m + 1) * lds * sizeof(double);
-            k_chol<KIND><<<1, 256, sm_chol, st>>>(f->d_G, ld, idx + c0, f->d_blocks + (size_t)c0 * R * W,
-                                                  f->d_nu + (size_t)R * c0, kc, m4, f->nz.r, f->d_dx,
-                                                  c0 > 0 ? 1 : 0, f->d_L, f->d_invd, f->d_y, f->d_status);
-            const size_t sm_solve = ((size_t)m4 * m4 + (size_t)m4 * SOLVE_COLS + 2 * m4) * sizeof(double);
-            k_solve<<<(ld + SOLVE_COLS - 1) / SOLVE_COLS, SOLVE_COLS, sm_solve, st>>>(
-                f->d_G, f->d_Vt, ld, n1, m4, f->d_L, f->d_invd, f->d_y, f->d_dx, c0 > 0 ? 1 : 0);
-            if (last)
-                k_apply<KIND><<<(std::max(f->nlm, 1) + 127) / 128, 128, 0, st>>>(
-                    f->d_state, f->d_dx, f->nlm, (KIND == 0 && f->quat_mode == ASB_QUAT_AS_WRITTEN) ? 1 : 0);
-            // persistent sweep: 2 CTAs / SM (64 x 64 tiles) while both fit in shared memory,
-            // else 1 CTA / SM (128 x 64 tiles)
-            if (2 * (SweepDual::smem_bytes(m4) + 1024) <= (size_t)f->smem_optin && !f->force_big) {
-                const int ntiles = SweepDual::num_tiles(n1);
-                const int grid = std::min(ntiles, 2 * f->sweep_grid);
-                k_sweep<SweepDual><<<grid, SweepDual::THREADS, SweepDual::smem_bytes(m4), st>>>(
-                    f->d_P, ld, f->d_Vt, m4, ntiles, 0);
-            } else {
-                const int ntiles = SweepBig::num_tiles(n1);
-                const int grid = std::min(ntiles, f->sweep_grid);
-                k_sweep<SweepBig><<<grid, SweepBig::THREADS, SweepBig::smem_bytes(m4), st>>>(
-                    f->d_P, ld, f->d_Vt, m4, ntiles, 0);
-            }
+            const int m4 = round_up(R * kc, 4);
+            const bool first = c0 == 0, last = c0 + kc >= k;
+            FrontArgs a;
+            a.state = f->d_state; a.P = f->d_P; a.ld = ld;
+            a.n0 = first ? n0 : n1; a.n1 = n1; a.nz = f->nz;
+            a.idx = idx + c0; a.poses = pose + 6 * (size_t)c0; a.isnew = isnew ? isnew + c0 : nullptr;
+            a.kc = kc; a.m4 = m4;
+            a.first_chunk = first ? 1 : 0;
+            a.add_q = (first && do_predict) ? 1 : 0;
+            a.use_delta = first ? 0 : 1;
+            a.dx_in = f->d_dx[cur]; a.dx_out = f->d_dx[cur ^ 1];
+            a.Vt = f->d_Vt;
+            a.blocks_out = f->d_blocks + (size_t)c0 * R * W; a.nu_out = f->d_nu + (size_t)R * c0;
+            a.status = f->d_status;
+            a.prof = f->d_prof;
+            const int nblk = 2 * ((n1 + 127) / 128);  // whole 128-row sweep tiles are covered
+            k_front<KIND><<<nblk, FRONT_THREADS, FrontSmem<KIND>::bytes(kc, m4), st>>>(a);
+            cur ^= 1;
+            SweepExtra ex;
+            ex.n = n1; ex.add_q = a.add_q; ex.nz = f->nz;
+            ex.apply_kind = last ? KIND : -1;
+            ex.as_written = (KIND == 0 && f->quat_mode == ASB_QUAT_AS_WRITTEN) ? 1 : 0;
+            ex.nlm = (n1 - CAM) / Dims<KIND>::D; ex.state = f->d_state; ex.dx = f->d_dx[cur];
+            launch_sweep(f, n1, m4, 0, ex);
         }
+        f->dx_last = f->d_dx[cur];
     }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(ASB_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(e));
@@ -196,7 +214,7 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
     f->ncap = CAM + f->D * max_landmarks;
     f->ld = round_up(f->ncap, PAD);
     f->max_obs = std::max(64, std::min(max_landmarks * 2, 4096));
-    f->kc_max = (M_MAX - 2) / f->R;  // rows per chunk: R*kc rounded up to 4 must be <= M_MAX
+    f->kc_max = kind == ASB_KIND_EKF ? FrontLimits<0>::KC_MAX : FrontLimits<1>::KC_MAX;  // front.cuh
     cudaDeviceProp prop;
     ASB_CUDA(cudaGetDeviceProperties(&prop, device));
     f->sweep_grid = prop.multiProcessorCount;
@@ -207,17 +225,17 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
     const size_t ld = f->ld;
     ASB_CUDA(dmalloc(&f->d_state, ld));
     ASB_CUDA(dmalloc(&f->d_P, ld * ld));
-    ASB_CUDA(dmalloc(&f->d_G, (size_t)M_MAX * ld));
     ASB_CUDA(dmalloc(&f->d_Vt, (size_t)M_MAX * V_LDB * (ld / V_BLK)));
     ASB_CUDA(cudaMemsetAsync(f->d_Vt, 0, (size_t)M_MAX * V_LDB * (ld / V_BLK) * sizeof(double), f->stream));
     ASB_CUDA(dmalloc(&f->d_blocks, (size_t)f->max_obs * f->R * f->W));
     ASB_CUDA(dmalloc(&f->d_nu, (size_t)f->max_obs * f->R));
-    ASB_CUDA(dmalloc(&f->d_L, (size_t)M_MAX * M_MAX));
-    ASB_CUDA(dmalloc(&f->d_invd, (size_t)M_MAX));
-    ASB_CUDA(dmalloc(&f->d_y, (size_t)M_MAX));
-    ASB_CUDA(dmalloc(&f->d_dx, ld));
+    ASB_CUDA(dmalloc(&f->d_dx[0], ld));
+    ASB_CUDA(dmalloc(&f->d_dx[1], ld));
+    f->dx_last = f->d_dx[0];
     ASB_CUDA(dmalloc(&f->d_unc, 16));
     ASB_CUDA(dmalloc(&f->d_status, 1));
+    ASB_CUDA(dmalloc(&f->d_prof, 16));
+    ASB_CUDA(cudaMemsetAsync(f->d_prof, 0, 16 * sizeof(unsigned long long), f->stream));
     ASB_CUDA(dmalloc(&f->d_idx, (size_t)N_SLOTS * f->max_obs));
     ASB_CUDA(dmalloc(&f->d_pose, (size_t)N_SLOTS * f->max_obs * 6));
     ASB_CUDA(dmalloc(&f->d_new, (size_t)N_SLOTS * f->max_obs));
@@ -226,9 +244,9 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
     ASB_CUDA(cudaMallocHost(&f->h_new, (size_t)N_SLOTS * f->max_obs));
     for (auto& e : f->slot_ev) ASB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     ASB_CUDA(cudaMemsetAsync(f->d_P, 0, ld * ld * sizeof(double), f->stream));
-    ASB_CUDA(cudaMemsetAsync(f->d_G, 0, (size_t)M_MAX * ld * sizeof(double), f->stream));
     ASB_CUDA(cudaMemsetAsync(f->d_state, 0, ld * sizeof(double), f->stream));
-    ASB_CUDA(cudaMemsetAsync(f->d_dx, 0, ld * sizeof(double), f->stream));
+    ASB_CUDA(cudaMemsetAsync(f->d_dx[0], 0, ld * sizeof(double), f->stream));
+    ASB_CUDA(cudaMemsetAsync(f->d_dx[1], 0, ld * sizeof(double), f->stream));
     ASB_CUDA(cudaMemsetAsync(f->d_status, 0, sizeof(int), f->stream));
     // state = pose0; P = init_cam * I10  (EKF:46-48)
     std::vector<double> p0(CAM * f->ld, 0.0);
@@ -242,9 +260,8 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
     const int big = (int)prop.sharedMemPerBlockOptin - 2048;  // static smem (mbarriers) counts too
     ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepBig>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepDual>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
-    ASB_CUDA(cudaFuncSetAttribute(k_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
-    ASB_CUDA(cudaFuncSetAttribute(k_chol<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
-    ASB_CUDA(cudaFuncSetAttribute(k_chol<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    ASB_CUDA(cudaFuncSetAttribute(k_front<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    ASB_CUDA(cudaFuncSetAttribute(k_front<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     *out = f;
     return ASB_OK;
 }
@@ -252,9 +269,9 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
 int asb_filter_destroy(asb_filter* f) {
     ASB_CHECK_HANDLE(f);
     cudaStreamSynchronize(f->stream);
-    cudaFree(f->d_state); cudaFree(f->d_P); cudaFree(f->d_G); cudaFree(f->d_Vt); cudaFree(f->d_blocks); cudaFree(f->d_nu);
-    cudaFree(f->d_L); cudaFree(f->d_invd); cudaFree(f->d_y); cudaFree(f->d_dx); cudaFree(f->d_unc);
-    cudaFree(f->d_status); cudaFree(f->d_idx); cudaFree(f->d_pose); cudaFree(f->d_new);
+    cudaFree(f->d_state); cudaFree(f->d_P); cudaFree(f->d_Vt); cudaFree(f->d_blocks); cudaFree(f->d_nu);
+    cudaFree(f->d_dx[0]); cudaFree(f->d_dx[1]); cudaFree(f->d_unc);
+    cudaFree(f->d_status); cudaFree(f->d_prof); cudaFree(f->d_idx); cudaFree(f->d_pose); cudaFree(f->d_new);
     cudaFree(f->s_idx); cudaFree(f->s_pose); cudaFree(f->s_new);
     cudaFreeHost(f->h_idx); cudaFreeHost(f->h_pose); cudaFreeHost(f->h_new);
     for (auto& e : f->slot_ev) cudaEventDestroy(e);
@@ -509,21 +526,15 @@ int asb_device_views(asb_filter* f, void** d_state, void** d_cov, int* ld) {
 int asb_bench_sweep(asb_filter* f, int m4, int config, int dbg, int reps, double* us_per_launch) {
     ASB_CHECK_HANDLE(f);
     if (!us_per_launch || m4 < 4 || m4 > M_MAX || (m4 & 3) || reps < 1) return fail(ASB_ERR_BAD_ARG, "bad args");
-    const int n1 = f->n_state(), ld = f->ld;
+    const int n1 = f->n_state();
     cudaEvent_t e0, e1;
     ASB_CUDA(cudaEventCreate(&e0));
     ASB_CUDA(cudaEventCreate(&e1));
+    SweepExtra ex{};
+    ex.n = n1; ex.apply_kind = -1;
     for (int rep = -2; rep < reps; ++rep) {
         if (rep == 0) ASB_CUDA(cudaEventRecord(e0, f->stream));
-        if (config == 1) {
-            const int ntiles = SweepDual::num_tiles(n1);
-            k_sweep<SweepDual><<<std::min(ntiles, 2 * f->sweep_grid), SweepDual::THREADS, SweepDual::smem_bytes(m4),
-                                 f->stream>>>(f->d_P, ld, f->d_Vt, m4, ntiles, dbg);
-        } else {
-            const int ntiles = SweepBig::num_tiles(n1);
-            k_sweep<SweepBig><<<std::min(ntiles, f->sweep_grid), SweepBig::THREADS, SweepBig::smem_bytes(m4),
-                                f->stream>>>(f->d_P, ld, f->d_Vt, m4, ntiles, dbg);
-        }
+        launch_sweep(f, n1, m4, dbg, ex, config);
     }
     ASB_CUDA(cudaEventRecord(e1, f->stream));
     ASB_CUDA(cudaEventSynchronize(e1));
@@ -535,6 +546,17 @@ int asb_bench_sweep(asb_filter* f, int m4, int config, int dbg, int reps, double
     return ASB_OK;
 }
 
+int asb_front_profile(asb_filter* f, double us[12]) {
+    ASB_CHECK_HANDLE(f);
+    if (!us) return fail(ASB_ERR_BAD_ARG, "us is NULL");
+    unsigned long long t[16];
+    ASB_CUDA(cudaStreamSynchronize(f->stream));
+    ASB_CUDA(cudaMemcpy(t, f->d_prof, sizeof t, cudaMemcpyDeviceToHost));
+    for (int i = 0; i < 7; ++i) us[i] = 1e-3 * (double)(long long)(t[i + 1] - t[i]);
+    for (int i = 8; i < 13; ++i) us[i - 1] = (double)(long long)(t[i + 1] - t[i]);  // clocks, one Cholesky step
+    return ASB_OK;
+}
+
 int asb_get_last_update(asb_filter* f, double* nu, double* blocks, double* dx, int* m) {
     ASB_CHECK_HANDLE(f);
     ASB_CUDA(cudaStreamSynchronize(f->stream));
@@ -543,7 +565,7 @@ int asb_get_last_update(asb_filter* f, double* nu, double* blocks, double* dx, i
     if (nu && k) ASB_CUDA(cudaMemcpy(nu, f->d_nu, (size_t)f->R * k * sizeof(double), cudaMemcpyDeviceToHost));
     if (blocks && k)
         ASB_CUDA(cudaMemcpy(blocks, f->d_blocks, (size_t)k * f->R * f->W * sizeof(double), cudaMemcpyDeviceToHost));
-    if (dx) ASB_CUDA(cudaMemcpy(dx, f->d_dx, (size_t)f->n_state() * sizeof(double), cudaMemcpyDeviceToHost));
+    if (dx) ASB_CUDA(cudaMemcpy(dx, f->dx_last, (size_t)f->n_state() * sizeof(double), cudaMemcpyDeviceToHost));
     return ASB_OK;
 }
 

@@ -10,7 +10,25 @@
 #include <cstdint>
 #include <cuda_runtime.h>
 
+#include "model.cuh"
+
 namespace asb {
+
+// Work folded into the sweep launch so that a frame is two launches (k_front, k_sweep):
+//   predict   P += diag(Q) (EKF:95-105) is added on the diagonal tiles as they stream by
+//             (k_front already used P + diag(Q) in registers);
+//   apply     the state update + multiplicative quaternion reset (EKF:134-152, ROT:143-177)
+//             is done by CTA 0 before it starts on its tiles.
+struct SweepExtra {
+    int n;                 // live state dims (diagonal entries i < n receive Q)
+    int add_q;
+    Noise nz;
+    int apply_kind;        // -1: none, 0: EKF, 1: EKF_Rotations
+    int as_written;
+    int nlm;
+    double* state;
+    const double* dx;
+};
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
     return (uint32_t)__cvta_generic_to_shared(p);
@@ -90,7 +108,8 @@ using SweepDual = SweepCfg<2, 4, 4, 2, 2>;   // 64 x 64 tile, 2 CTAs / SM: one c
 // latency hides behind the tile's own math.
 template <class C>
 __global__ void __launch_bounds__(C::THREADS, C::MINB)
-k_sweep(double* __restrict__ P, int ld, const double* __restrict__ Vt, int m4, int ntiles, int dbg) {
+k_sweep(double* __restrict__ P, int ld, const double* __restrict__ Vt, int m4, int ntiles, int dbg,
+        SweepExtra ex) {
     // dbg (asb_bench_sweep only; 0 in the product path): 1 skip MMAs, 2 skip mirror stores,
     // 4 skip direct stores, 8 skip P loads
     constexpr int RM = C::RM, RN = C::RN, TI = C::TI, TJ = C::TJ;
@@ -102,6 +121,28 @@ k_sweep(double* __restrict__ P, int ld, const double* __restrict__ Vt, int m4, i
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, t4 = lane & 3;
     const int wi = warp / C::WN, wj = warp % C::WN;
+    if (blockIdx.x == 0 && ex.apply_kind >= 0) {  // state update (k_apply folded in)
+        if (tid == 0) {
+            double cam[CAM], d[CAM];
+#pragma unroll
+            for (int c = 0; c < CAM; ++c) { cam[c] = ex.state[c]; d[c] = ex.dx[c]; }
+            camera_reset(cam, d, ex.as_written);
+#pragma unroll
+            for (int c = 0; c < CAM; ++c) ex.state[c] = cam[c];
+        }
+        if (ex.apply_kind == 0) {
+            for (int e = tid; e < 3 * ex.nlm; e += C::THREADS) ex.state[CAM + e] += ex.dx[CAM + e];
+        } else {
+            for (int t = tid; t < ex.nlm; t += C::THREADS) {
+                double lm[10], d[10];
+#pragma unroll
+                for (int c = 0; c < 10; ++c) { lm[c] = ex.state[CAM + 10 * t + c]; d[c] = ex.dx[CAM + 10 * t + c]; }
+                landmark_update<1>(lm, d);
+#pragma unroll
+                for (int c = 0; c < 10; ++c) ex.state[CAM + 10 * t + c] = lm[c];
+            }
+        }
+    }
     if (tid == 0) {
         mbar_init(&bar[0], 1);
         mbar_init(&bar[1], 1);
@@ -200,12 +241,13 @@ k_sweep(double* __restrict__ P, int ld, const double* __restrict__ Vt, int m4, i
             for (int rm = 0; rm < RM; ++rm)
 #pragma unroll
                 for (int rn = 0; rn < RN; ++rn) {
-                    const double o[2] = {pf[rm][rn].x - acc[rm][rn][0], pf[rm][rn].y - acc[rm][rn][1]};
+                    double o[2] = {pf[rm][rn].x - acc[rm][rn][0], pf[rm][rn].y - acc[rm][rn][1]};
                     const int i = ri + 8 * rm;
 #pragma unroll
                     for (int e = 0; e < 2; ++e) {
                         const int j = cj + 8 * rn + e;
                         if (i >= j) {
+                            if (i == j && ex.add_q && i < ex.n) o[e] += process_noise(ex.nz, i);
                             P[(long long)i * ld + j] = o[e];
                             if (i > j) P[(long long)j * ld + i] = o[e];
                         }

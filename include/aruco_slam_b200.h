@@ -173,6 +173,13 @@ ASB_API int asb_fp64_peak(int device, int which, double* tflops);
  * 1 = 64x64 tiles 2 CTAs/SM.  dbg != 0 disables parts of the kernel (experiments; the
  * filter's P is garbage afterwards).  V is whatever the last update left in the panel. */
 ASB_API int asb_bench_sweep(asb_filter* f, int m4, int config, int dbg, int reps, double* us_per_launch);
+/* Durations (us, globaltimer) of the phases of the last k_front launch as seen by CTA 0:
+ * index set + copy issue, model + copy wait, S build, Cholesky, G slice, V = W G, panel store +
+ * growth; then us[7..11] = clocks of one Cholesky step: diagonal block, panel, barrier,
+ * trailing update, barrier. */
+ASB_API int asb_front_profile(asb_filter* f, double us[12]);
+/* Dependent-issue latencies in clocks: DFMA, rsqrt(double)+add, LDS.64 (with cvt), BAR.SYNC of 256 threads. */
+ASB_API int asb_latency_probe(int device, double clocks[4]);
 /* Streaming copy bandwidth (GB/s, read+write bytes) over `bytes` of HBM. */
 ASB_API int asb_copy_bandwidth(int device, int64_t bytes, double* gbs);
 

@@ -12,3 +12,12 @@ for cfg in (0, 1):
         us = C.c_double()
         _lib.check(lib.asb_bench_sweep(f._h, 60, cfg, dbg, 50, C.byref(us)))
         print(f"config {cfg} dbg {dbg:2d}: {us.value:8.2f} us", flush=True)
+# phases of k_front on a real frame
+rng = np.random.default_rng(0)
+for rep in range(3):
+    ids = rng.choice(2000, 20, replace=False)
+    poses = np.concatenate([rng.normal(0, 1, (20, 3)) + [0, 0, 5], rng.normal(0, 0.1, (20, 3))], 1)
+    f.observe(ids, poses)
+    us = (C.c_double * 12)()
+    _lib.check(lib.asb_front_profile(f._h, us))
+    print("k_front phases [model, PT, S, chol, gather, solve, store] us:", " ".join(f"{u:6.2f}" for u in us[:7]), "| chol step clks [diag panel bar trail bar]:", " ".join(f"{u:5.0f}" for u in us[7:12]), flush=True)
