@@ -87,6 +87,8 @@ SIGNATURES = {
     "asb_bench_sweep": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, _dp]),
     "asb_front_profile": (C.c_int, [_vp, _dp]),
     "asb_latency_probe": (C.c_int, [C.c_int, _dp]),
+    "asb_stream_bandwidth": (C.c_int, [C.c_int, C.c_int64, C.c_int, _dp]),
+    "asb_tilepattern_bandwidth": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, _dp]),
     "asb_fp64_peak": (C.c_int, [C.c_int, C.c_int, _dp]),
     "asb_copy_bandwidth": (C.c_int, [C.c_int, C.c_int64, _dp]),
 }

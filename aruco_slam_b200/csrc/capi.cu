@@ -130,6 +130,52 @@ __global__ void k_copy(const double2* __restrict__ src, double2* __restrict__ ds
         __stcs(dst + i, __ldcs(src + i));
 }
 
+// write-only / read-only / 1 read : 2 writes streams, 256-bit accesses
+__global__ void k_stream(const double* __restrict__ src, double* __restrict__ d1, double* __restrict__ d2, long long n4,
+                         int mode, double* sink) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    double acc = 0.0;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+        double a = 1.0, b = 2.0, c = 3.0, d = 4.0;
+        if (mode != 0) asm volatile("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(src + 4 * i));
+        if (mode == 1) acc += a + b + c + d;
+        if (mode == 0 || mode == 2)
+            asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(d1 + 4 * i), "d"(a), "d"(b), "d"(c), "d"(d) : "memory");
+        if (mode == 2)
+            asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(d2 + 4 * i), "d"(a), "d"(b), "d"(c), "d"(d) : "memory");
+    }
+    if (acc == 123.456) *sink = acc;
+}
+
+// The sweep's memory pattern without any math: lower-triangle TS x TS tiles of an n x n
+// matrix (leading dimension ld): read tile (I,J), write it back, write it to (J,I) (not
+// transposed inside: same bytes, same addresses pattern as the mirror).  One warp per row
+// slice: lanes cover 32 x 32 B = 1 KB or less of a row.
+template <int TS>
+__global__ void k_tilepattern(double* P, int ld, int ntile_side) {
+    const int ntiles = ntile_side * (ntile_side + 1) / 2;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+    const int t_begin = (int)((long long)ntiles * blockIdx.x / gridDim.x);
+    const int t_end = (int)((long long)ntiles * (blockIdx.x + 1) / gridDim.x);
+    for (int t = t_begin; t < t_end; ++t) {
+        int I = (int)((sqrt(8.0 * t + 1.0) - 1.0) * 0.5);
+        while ((I + 1) * (I + 2) / 2 <= t) ++I;
+        while (I * (I + 1) / 2 > t) --I;
+        const int J = t - I * (I + 1) / 2;
+        for (int e = warp * 32 + lane; e < TS * (TS / 4); e += nw * 32) {  // 32-byte pieces, row-major
+            const int r = e / (TS / 4), c = 4 * (e % (TS / 4));
+            double a, b, cc, d;
+            asm volatile("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(a), "=d"(b), "=d"(cc), "=d"(d)
+                         : "l"(P + (long long)(I * TS + r) * ld + J * TS + c));
+            asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(P + (long long)(I * TS + r) * ld + J * TS + c),
+                         "d"(a), "d"(b), "d"(cc), "d"(d) : "memory");
+            if (I != J)
+                asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(P + (long long)(J * TS + r) * ld + I * TS + c),
+                             "d"(a), "d"(b), "d"(cc), "d"(d) : "memory");
+        }
+    }
+}
+
 }  // namespace asb
 
 using namespace asb;
@@ -206,6 +252,68 @@ int asb_latency_probe(int device, double clocks[4]) {
     ASB_CUDA(cudaMemcpy(h, out, sizeof h, cudaMemcpyDeviceToHost));
     cudaFree(out);
     for (int i = 0; i < 4; ++i) clocks[i] = h[i];
+    return ASB_OK;
+}
+
+int asb_stream_bandwidth(int device, int64_t bytes, int mode, double* gbs) {
+    if (!gbs || bytes < (1 << 20) || mode < 0 || mode > 2) return fail(ASB_ERR_BAD_ARG, "bad args");
+    ASB_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    ASB_CUDA(cudaGetDeviceProperties(&prop, device));
+    double *a = nullptr, *b = nullptr, *c = nullptr;
+    const long long n4 = bytes / 32;
+    ASB_CUDA(cudaMalloc(&a, n4 * 32));
+    ASB_CUDA(cudaMalloc(&b, n4 * 32));
+    ASB_CUDA(cudaMalloc(&c, n4 * 32));
+    ASB_CUDA(cudaMemset(a, 0, n4 * 32));
+    cudaEvent_t e0, e1;
+    ASB_CUDA(cudaEventCreate(&e0));
+    ASB_CUDA(cudaEventCreate(&e1));
+    double best = 0;
+    for (int rep = 0; rep < 6; ++rep) {
+        ASB_CUDA(cudaEventRecord(e0));
+        k_stream<<<prop.multiProcessorCount * 8, 512>>>(a, b, c, n4, mode, b);
+        ASB_CUDA(cudaEventRecord(e1));
+        ASB_CUDA(cudaEventSynchronize(e1));
+        float ms = 0;
+        ASB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        const double moved = (mode == 2 ? 3.0 : 1.0) * n4 * 32.0;
+        best = std::max(best, moved / (ms * 1e-3) / 1e9);
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaFree(a); cudaFree(b); cudaFree(c);
+    *gbs = best;
+    return ASB_OK;
+}
+
+int asb_tilepattern_bandwidth(int device, int n, int tile, int ctas_per_sm, double* us) {
+    if (!us || n < 256 || (tile != 64 && tile != 128 && tile != 256)) return fail(ASB_ERR_BAD_ARG, "bad args");
+    ASB_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    ASB_CUDA(cudaGetDeviceProperties(&prop, device));
+    const int side = (n + tile - 1) / tile, ld = (side * tile + 127) / 128 * 128;
+    double* P = nullptr;
+    ASB_CUDA(cudaMalloc(&P, (size_t)ld * ld * sizeof(double)));
+    ASB_CUDA(cudaMemset(P, 0, (size_t)ld * ld * sizeof(double)));
+    cudaEvent_t e0, e1;
+    ASB_CUDA(cudaEventCreate(&e0));
+    ASB_CUDA(cudaEventCreate(&e1));
+    double best = 1e30;
+    for (int rep = 0; rep < 6; ++rep) {
+        ASB_CUDA(cudaEventRecord(e0));
+        const int grid = prop.multiProcessorCount * ctas_per_sm;
+        if (tile == 64) k_tilepattern<64><<<grid, 512>>>(P, ld, side);
+        else if (tile == 128) k_tilepattern<128><<<grid, 512>>>(P, ld, side);
+        else k_tilepattern<256><<<grid, 512>>>(P, ld, side);
+        ASB_CUDA(cudaEventRecord(e1));
+        ASB_CUDA(cudaEventSynchronize(e1));
+        float ms = 0;
+        ASB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        best = std::min(best, 1e3 * (double)ms);
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaFree(P);
+    *us = best;
     return ASB_OK;
 }
 

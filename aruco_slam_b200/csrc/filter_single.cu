@@ -37,7 +37,7 @@ struct asb_filter {
     std::vector<int32_t> id_order;
 
     cudaStream_t own_stream = nullptr, stream = nullptr;
-    double *d_state = nullptr, *d_P = nullptr, *d_Vt = nullptr, *d_blocks = nullptr, *d_nu = nullptr;
+    double *d_state = nullptr, *d_P = nullptr, *d_Vr = nullptr, *d_Vc = nullptr, *d_blocks = nullptr, *d_nu = nullptr;
     double *d_dx[2] = {nullptr, nullptr}, *dx_last = nullptr, *d_unc = nullptr;
     int* d_status = nullptr;
     unsigned long long* d_prof = nullptr;
@@ -52,7 +52,7 @@ struct asb_filter {
     int* s_idx = nullptr; double* s_pose = nullptr; unsigned char* s_new = nullptr;
     std::vector<FrameRec> frames;
     int next_frame = 0;
-    int sweep_grid = 0, smem_optin = 0, force_big = 0;
+    int sweep_grid = 0, smem_optin = 0, force_big = 0, sweep_config = -1;
 
     int n_state() const { return CAM + D * nlm; }
 };
@@ -80,18 +80,25 @@ static cudaError_t dmalloc(T** p, size_t count) {
 // persistent sweep: 2 CTAs / SM (64 x 64 tiles) while both fit in shared memory, else
 // 1 CTA / SM (128 x 64 tiles)
 static void launch_sweep(asb_filter* f, int n1, int m4, int dbg, const SweepExtra& ex, int config = -1) {
+    if (config < 0) config = f->sweep_config;
+    if (config == 2) {  // warp-specialised variant: kept for experiments (slower than the dual-CTA kernel)
+        const int ntiles = ws::num_tiles(n1);
+        const int grid = std::min(ntiles, f->sweep_grid);
+        k_sweep_ws<<<grid, ws::THREADS, ws::smem_bytes(m4), f->stream>>>(f->d_P, f->ld, f->d_Vr, f->d_Vc, m4, ntiles, dbg, ex);
+        return;
+    }
     const bool dual = config < 0 ? (2 * (SweepDual::smem_bytes(m4) + 1024) <= (size_t)f->smem_optin && !f->force_big)
                                  : config == 1;
     if (dual) {
         const int ntiles = SweepDual::num_tiles(n1);
         const int grid = std::min(ntiles, 2 * f->sweep_grid);
         k_sweep<SweepDual><<<grid, SweepDual::THREADS, SweepDual::smem_bytes(m4), f->stream>>>(
-            f->d_P, f->ld, f->d_Vt, m4, ntiles, dbg, ex);
+            f->d_P, f->ld, f->d_Vr, f->d_Vc, m4, ntiles, dbg, ex);
     } else {
         const int ntiles = SweepBig::num_tiles(n1);
         const int grid = std::min(ntiles, f->sweep_grid);
         k_sweep<SweepBig><<<grid, SweepBig::THREADS, SweepBig::smem_bytes(m4), f->stream>>>(
-            f->d_P, f->ld, f->d_Vt, m4, ntiles, dbg, ex);
+            f->d_P, f->ld, f->d_Vr, f->d_Vc, m4, ntiles, dbg, ex);
     }
 }
 
@@ -123,7 +130,7 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
             a.add_q = (first && do_predict) ? 1 : 0;
             a.use_delta = first ? 0 : 1;
             a.dx_in = f->d_dx[cur]; a.dx_out = f->d_dx[cur ^ 1];
-            a.Vt = f->d_Vt;
+            a.Vr = f->d_Vr; a.Vc = f->d_Vc;
             a.blocks_out = f->d_blocks + (size_t)c0 * R * W; a.nu_out = f->d_nu + (size_t)R * c0;
             a.status = f->d_status;
             a.prof = f->d_prof;
@@ -135,7 +142,7 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
             ex.apply_kind = last ? KIND : -1;
             ex.as_written = (KIND == 0 && f->quat_mode == ASB_QUAT_AS_WRITTEN) ? 1 : 0;
             ex.nlm = (n1 - CAM) / Dims<KIND>::D; ex.state = f->d_state; ex.dx = f->d_dx[cur];
-            launch_sweep(f, n1, m4, 0, ex);
+            launch_sweep(f, n1, m4, 2 << 4, ex);  // dbg bits 4-5 = 2: P loads bypass L1 (.cg)
         }
         f->dx_last = f->d_dx[cur];
     }
@@ -220,13 +227,16 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
     f->sweep_grid = prop.multiProcessorCount;
     f->smem_optin = (int)prop.sharedMemPerBlockOptin;
     if (const char* e = std::getenv("ASB_SWEEP_BIG")) f->force_big = std::atoi(e);
+    if (const char* e = std::getenv("ASB_SWEEP_CONFIG")) f->sweep_config = std::atoi(e);  // experiments: 0 / 1 / 2
     ASB_CUDA(cudaStreamCreateWithFlags(&f->own_stream, cudaStreamNonBlocking));
     f->stream = f->own_stream;
     const size_t ld = f->ld;
     ASB_CUDA(dmalloc(&f->d_state, ld));
     ASB_CUDA(dmalloc(&f->d_P, ld * ld));
-    ASB_CUDA(dmalloc(&f->d_Vt, (size_t)M_MAX * V_LDB * (ld / V_BLK)));
-    ASB_CUDA(cudaMemsetAsync(f->d_Vt, 0, (size_t)M_MAX * V_LDB * (ld / V_BLK) * sizeof(double), f->stream));
+    ASB_CUDA(dmalloc(&f->d_Vr, (size_t)M_MAX * V_LDB * (ld / V_BLK)));
+    ASB_CUDA(dmalloc(&f->d_Vc, (size_t)M_MAX * V_LDB * (ld / V_BLK)));
+    ASB_CUDA(cudaMemsetAsync(f->d_Vr, 0, (size_t)M_MAX * V_LDB * (ld / V_BLK) * sizeof(double), f->stream));
+    ASB_CUDA(cudaMemsetAsync(f->d_Vc, 0, (size_t)M_MAX * V_LDB * (ld / V_BLK) * sizeof(double), f->stream));
     ASB_CUDA(dmalloc(&f->d_blocks, (size_t)f->max_obs * f->R * f->W));
     ASB_CUDA(dmalloc(&f->d_nu, (size_t)f->max_obs * f->R));
     ASB_CUDA(dmalloc(&f->d_dx[0], ld));
@@ -260,6 +270,7 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
     const int big = (int)prop.sharedMemPerBlockOptin - 2048;  // static smem (mbarriers) counts too
     ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepBig>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepDual>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    ASB_CUDA(cudaFuncSetAttribute(k_sweep_ws, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_front<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_front<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     *out = f;
@@ -269,7 +280,7 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
 int asb_filter_destroy(asb_filter* f) {
     ASB_CHECK_HANDLE(f);
     cudaStreamSynchronize(f->stream);
-    cudaFree(f->d_state); cudaFree(f->d_P); cudaFree(f->d_Vt); cudaFree(f->d_blocks); cudaFree(f->d_nu);
+    cudaFree(f->d_state); cudaFree(f->d_P); cudaFree(f->d_Vr); cudaFree(f->d_Vc); cudaFree(f->d_blocks); cudaFree(f->d_nu);
     cudaFree(f->d_dx[0]); cudaFree(f->d_dx[1]); cudaFree(f->d_unc);
     cudaFree(f->d_status); cudaFree(f->d_prof); cudaFree(f->d_idx); cudaFree(f->d_pose); cudaFree(f->d_new);
     cudaFree(f->s_idx); cudaFree(f->s_pose); cudaFree(f->s_new);

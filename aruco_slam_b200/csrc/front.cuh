@@ -45,7 +45,8 @@ struct FrontArgs {
     int use_delta;               // nu' = nu - H dx_in   (chunks after the first)
     const double* dx_in;
     double* dx_out;
-    double* Vt;
+    double* Vr;                  // tiled panel in V_I column order (sweep.cuh)
+    double* Vc;                  // tiled panel in V_J column order
     double* blocks_out;          // (kc, R, W) for asb_get_last_update, may be null
     double* nu_out;              // (R kc)
     int* status;
@@ -492,10 +493,16 @@ k_front(FrontArgs p) {
         if (j < n1) p.dx_out[j] = (p.use_delta ? p.dx_in[j] : 0.0) + dsum;
     }
     {
-        double* vt = p.Vt + (size_t)blockIdx.x * m4 * V_LDB;
-        for (int e = tid; e < m4 * (V_BLK / 2); e += NT) {
-            const int a = e / (V_BLK / 2), jj = (e - a * (V_BLK / 2)) * 2;
-            *reinterpret_cast<double2*>(vt + a * V_LDB + jj) = *reinterpret_cast<const double2*>(s_V + a * V_BLK + jj);
+        // both column orders of the block (sweep.cuh): position of column jj is v_pos_row / v_pos_col
+        double* vr = p.Vr + (size_t)blockIdx.x * m4 * V_LDB;
+        double* vc = p.Vc + (size_t)blockIdx.x * m4 * V_LDB;
+        for (int e = tid; e < m4 * V_BLK; e += NT) {
+            const int a = e / V_BLK, pos = e - a * V_BLK;
+            // inverse maps: which column lands at `pos`
+            const int cr = (pos & ~31) + 4 * (pos & 7) + ((pos & 31) >> 3);
+            const int cc = (pos & ~15) + 4 * ((pos & 7) >> 1) + 2 * ((pos & 15) >> 3) + (pos & 1);
+            vr[a * V_LDB + pos] = s_V[a * V_BLK + cr];
+            vc[a * V_LDB + pos] = s_V[a * V_BLK + cc];
         }
     }
 

@@ -75,10 +75,61 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
 // m4 rows x V_LDB = 68 doubles (64 values + 4 pad), contiguous, so one bulk copy (TMA, SASS
 // UBLKCP) of m4 * 544 bytes brings a whole 64-column panel into shared memory already in
 // its bank-conflict-free layout: V_LDB = 4 mod 16, so the DMMA fragment loads
-// (address = (4 kk + t) * V_LDB + g) hit 32 distinct banks.  k_solve writes this layout.
+// (address = (4 kk + t) * V_LDB + g + 8 r) hit 32 distinct banks.
+//
+// Fragment ownership is chosen for the GLOBAL side: lane (g = lane / 4, t4 = lane % 4) of a
+// warp whose tile starts at (r0, c0) owns
+//     rows     r0 + 4 g + rm                                     (DMMA tile rm = 0..3)
+//     columns  c0 + 16 (rn / 2) + 4 t4 + 2 (rn % 2) + e          (DMMA tile rn, e = 0, 1)
+// i.e. 4 consecutive rows and groups of 4 consecutive columns, so that every access to P is
+// a 256-bit LDG/STG (SASS LDG.E.ENL2.256): a warp instruction covers whole 128-byte lines
+// (8 rows x 128 B direct, 4 rows x 256 B mirrored) instead of 64-byte pieces.  The price is
+// that the V panel is kept in two column orders, one for each role, so that the fragment
+// loads stay g + 8 r:  position of state column c inside its block
+//     as V_I (rows of the tile):     32 (c/32) + (c%32)/4 + 8 (c%4)
+//     as V_J (columns of the tile):  16 (c/16) + 8 ((c%4)/2) + 2 ((c%16)/4) + c%2
+// k_front writes both.
 constexpr int V_BLK = 64, V_LDB = 68;
-__host__ __device__ inline size_t v_index(int m4, int a, int j) {
-    return (size_t)(j / V_BLK) * m4 * V_LDB + (size_t)a * V_LDB + (j % V_BLK);
+__host__ __device__ inline int v_pos_row(int c) { return (c & ~31) + ((c & 31) >> 2) + 8 * (c & 3); }
+__host__ __device__ inline int v_pos_col(int c) { return (c & ~15) + 8 * ((c & 3) >> 1) + 2 * ((c & 15) >> 2) + (c & 1); }
+
+// cache policy experiments (asb_bench_sweep dbg bits 16 / 32): 0 default, 1 evict-first (.cs), 2 L2-only (.cg)
+__device__ __forceinline__ void ld256(const double* p, double& a, double& b, double& c, double& d, int mode = 0) {
+    if (mode == 1) asm volatile("ld.global.cs.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(p));
+    else if (mode == 2) asm volatile("ld.global.cg.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(p));
+    else asm volatile("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(p));
+}
+__device__ __forceinline__ void st256(double* p, double a, double b, double c, double d, int mode = 0) {
+    if (mode == 1) asm volatile("st.global.cs.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(a), "d"(b), "d"(c), "d"(d) : "memory");
+    else if (mode == 2) asm volatile("st.global.cg.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(a), "d"(b), "d"(c), "d"(d) : "memory");
+    else asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(a), "d"(b), "d"(c), "d"(d) : "memory");
+}
+// P sub-tile of one warp <-> registers, fragment ownership as above.  pr = P + (r0 + 4 g) * ld
+// + c0 + 4 t4 (direct), pm = P + (c0 + 4 t4) * ld + r0 + 4 g (mirror).
+template <int RM, int RN>
+__device__ __forceinline__ void tile_load(const double* pr, int ld, double (&v)[RM][RN][2], int mode = 0) {
+#pragma unroll
+    for (int rm = 0; rm < RM; ++rm)
+#pragma unroll
+        for (int q = 0; q < RN / 2; ++q)
+            ld256(pr + (long long)rm * ld + 16 * q, v[rm][2 * q][0], v[rm][2 * q][1], v[rm][2 * q + 1][0], v[rm][2 * q + 1][1], mode);
+}
+template <int RM, int RN>
+__device__ __forceinline__ void tile_store(double* pr, int ld, const double (&v)[RM][RN][2], int mode = 0) {
+#pragma unroll
+    for (int rm = 0; rm < RM; ++rm)
+#pragma unroll
+        for (int q = 0; q < RN / 2; ++q)
+            st256(pr + (long long)rm * ld + 16 * q, v[rm][2 * q][0], v[rm][2 * q][1], v[rm][2 * q + 1][0], v[rm][2 * q + 1][1], mode);
+}
+template <int RM, int RN>
+__device__ __forceinline__ void tile_store_mirror(double* pm, int ld, const double (&v)[RM][RN][2], int mode = 0) {
+    static_assert(RM == 4, "a lane owns 4 consecutive rows");
+#pragma unroll
+    for (int rn = 0; rn < RN; ++rn)
+#pragma unroll
+        for (int e = 0; e < 2; ++e)
+            st256(pm + (long long)(16 * (rn >> 1) + 2 * (rn & 1) + e) * ld, v[0][rn][e], v[1][rn][e], v[2][rn][e], v[3][rn][e], mode);
 }
 
 // Tile shape: WM x WN warps, each owning (8 RM) x (8 RN) elements as RM x RN DMMA tiles.
@@ -108,10 +159,11 @@ using SweepDual = SweepCfg<2, 4, 4, 2, 2>;   // 64 x 64 tile, 2 CTAs / SM: one c
 // latency hides behind the tile's own math.
 template <class C>
 __global__ void __launch_bounds__(C::THREADS, C::MINB)
-k_sweep(double* __restrict__ P, int ld, const double* __restrict__ Vt, int m4, int ntiles, int dbg,
-        SweepExtra ex) {
+k_sweep(double* __restrict__ P, int ld, const double* __restrict__ Vr, const double* __restrict__ Vc, int m4,
+        int ntiles, int dbg, SweepExtra ex) {
     // dbg (asb_bench_sweep only; 0 in the product path): 1 skip MMAs, 2 skip mirror stores,
-    // 4 skip direct stores, 8 skip P loads
+    // 4 skip direct stores, 8 skip P loads; bits 4-5 load cache policy, bits 6-7 store cache
+    // policy (0 default, 1 .cs evict-first, 2 .cg)
     constexpr int RM = C::RM, RN = C::RN, TI = C::TI, TJ = C::TJ;
     extern __shared__ __align__(128) unsigned char smraw[];
     const int blk = m4 * V_LDB;                      // doubles per 64-column block of V
@@ -162,11 +214,11 @@ k_sweep(double* __restrict__ P, int ld, const double* __restrict__ Vt, int m4, i
     const uint32_t blk_bytes = (uint32_t)(blk * sizeof(double));
     auto load_vi = [&](int i0) {  // one thread
         mbar_expect_tx(&bar[0], C::RATIO * blk_bytes);
-        bulk_g2s(VI, Vt + (size_t)(i0 / V_BLK) * blk, C::RATIO * blk_bytes, &bar[0]);
+        bulk_g2s(VI, Vr + (size_t)(i0 / V_BLK) * blk, C::RATIO * blk_bytes, &bar[0]);
     };
     auto load_vj = [&](int buf, int j0) {  // one thread
         mbar_expect_tx(&bar[1 + buf], blk_bytes);
-        bulk_g2s(VJ0 + (size_t)buf * blk, Vt + (size_t)(j0 / V_BLK) * blk, blk_bytes, &bar[1 + buf]);
+        bulk_g2s(VJ0 + (size_t)buf * blk, Vc + (size_t)(j0 / V_BLK) * blk, blk_bytes, &bar[1 + buf]);
     };
 
     uint32_t ph_i = 0, ph_j = 0;  // ph_j: bit b = phase of VJ buffer b
@@ -183,15 +235,17 @@ k_sweep(double* __restrict__ P, int ld, const double* __restrict__ Vt, int m4, i
         const bool has_next = t + 1 < t_end;
         if (tid == 0 && has_next) load_vj(buf ^ 1, Jn * TJ);  // buffer freed by the last __syncthreads
 
-        // P sub-tile -> registers (accumulator-fragment layout)
-        const int ri = i0 + 8 * RM * wi + g, cj = j0 + 8 * RN * wj + 2 * t4;
-        double2 pf[RM][RN];
+        // P sub-tile -> registers (fragment ownership of sweep.cuh's header: 256-bit accesses)
+        const int r0 = i0 + 8 * RM * wi + 4 * g, c0 = j0 + 8 * RN * wj + 4 * t4;
+        double pf[RM][RN][2];
+        if (dbg & 8) {
 #pragma unroll
-        for (int rm = 0; rm < RM; ++rm)
+            for (int rm = 0; rm < RM; ++rm)
 #pragma unroll
-            for (int rn = 0; rn < RN; ++rn)
-                pf[rm][rn] = (dbg & 8) ? make_double2(0.0, 0.0)
-                                       : *reinterpret_cast<const double2*>(P + (long long)(ri + 8 * rm) * ld + cj + 8 * rn);
+                for (int rn = 0; rn < RN; ++rn) pf[rm][rn][0] = pf[rm][rn][1] = 0.0;
+        } else {
+            tile_load<RM, RN>(P + (long long)r0 * ld + c0, ld, pf, (dbg >> 4) & 3);
+        }
 
         double acc[RM][RN][2];
 #pragma unroll
@@ -223,36 +277,31 @@ k_sweep(double* __restrict__ P, int ld, const double* __restrict__ Vt, int m4, i
         }
 
         const bool interior = i0 >= j0 + TJ;  // strictly below the diagonal
+#pragma unroll
+        for (int rm = 0; rm < RM; ++rm)
+#pragma unroll
+            for (int rn = 0; rn < RN; ++rn) {
+                pf[rm][rn][0] -= acc[rm][rn][0];
+                pf[rm][rn][1] -= acc[rm][rn][1];
+            }
         if (interior) {
-#pragma unroll
-            for (int rm = 0; rm < RM; ++rm)
-#pragma unroll
-                for (int rn = 0; rn < RN; ++rn) {
-                    const double o0 = pf[rm][rn].x - acc[rm][rn][0], o1 = pf[rm][rn].y - acc[rm][rn][1];
-                    const int i = ri + 8 * rm, j = cj + 8 * rn;
-                    if (!(dbg & 4)) *reinterpret_cast<double2*>(P + (long long)i * ld + j) = make_double2(o0, o1);
-                    if (!(dbg & 2)) {
-                        P[(long long)j * ld + i] = o0;
-                        P[(long long)(j + 1) * ld + i] = o1;
-                    }
-                }
+            if (!(dbg & 4)) tile_store<RM, RN>(P + (long long)r0 * ld + c0, ld, pf, (dbg >> 6) & 3);
+            if (!(dbg & 2)) tile_store_mirror<RM, RN>(P + (long long)c0 * ld + r0, ld, pf, (dbg >> 6) & 3);
         } else {
 #pragma unroll
             for (int rm = 0; rm < RM; ++rm)
 #pragma unroll
-                for (int rn = 0; rn < RN; ++rn) {
-                    double o[2] = {pf[rm][rn].x - acc[rm][rn][0], pf[rm][rn].y - acc[rm][rn][1]};
-                    const int i = ri + 8 * rm;
+                for (int rn = 0; rn < RN; ++rn)
 #pragma unroll
                     for (int e = 0; e < 2; ++e) {
-                        const int j = cj + 8 * rn + e;
+                        const int i = r0 + rm, j = c0 + 16 * (rn >> 1) + 2 * (rn & 1) + e;
                         if (i >= j) {
-                            if (i == j && ex.add_q && i < ex.n) o[e] += process_noise(ex.nz, i);
-                            P[(long long)i * ld + j] = o[e];
-                            if (i > j) P[(long long)j * ld + i] = o[e];
+                            double o = pf[rm][rn][e];
+                            if (i == j && ex.add_q && i < ex.n) o += process_noise(ex.nz, i);
+                            P[(long long)i * ld + j] = o;
+                            if (i > j) P[(long long)j * ld + i] = o;
                         }
                     }
-                }
         }
         __syncthreads();  // every warp is done with VJ[buf] (and VI) before they are overwritten
         if (has_next && In != I) {
@@ -261,6 +310,253 @@ k_sweep(double* __restrict__ P, int ld, const double* __restrict__ Vt, int m4, i
         }
         I = In;
         J = Jn;
+    }
+}
+
+
+// =========================================================================================
+// k_sweep_ws: warp-specialised version of the sweep (default).  One CTA per SM, 16 warps:
+//   warps 0-7   MMA: 64 x 64 tile as 2 x 4 warps of 32 x 16 (4 x 2 DMMA tiles); they only ever
+//               wait on the V panels and on a free accumulator slot, so the FP64 tensor pipe
+//               is fed continuously; results (V_I^T V_J fragments) go to a per-warp slot in
+//               shared memory (two slots, 512-byte conflict-free rows)
+//   warps 8-15  epilogue: warp 8+w owns the same 32 x 16 sub-tile as MMA warp w: prefetches its
+//               P fragment of the NEXT tile into registers, then out = P (+ Q) - acc, direct
+//               store and mirror store
+//   (lane 0 of warp 8 is also the producer: TMA bulk copies of the V panels, VI and VJ both
+//   double-buffered, issued two tiles ahead)
+// Hand-off through mbarriers only (no CTA-wide barrier inside the tile loop).
+// =========================================================================================
+namespace ws {
+constexpr int TI = 64, TJ = 64, RM = 4, RN = 2, WN = 4;
+constexpr int MMA_WARPS = 8, THREADS = 2 * MMA_WARPS * 32;   // 512 threads: 128 registers each
+constexpr int ACC_SLOT_BYTES = RM * RN * 32 * 16;  // one warp's fragments: 8 x 512 B
+__host__ __device__ inline size_t smem_bytes(int m4) {
+    return (size_t)4 * m4 * V_LDB * sizeof(double) + (size_t)2 * MMA_WARPS * ACC_SLOT_BYTES;
+}
+__host__ __device__ inline int num_tiles(int n) {
+    const int nI = (n + TI - 1) / TI;
+    return nI * (nI + 1) / 2;
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tile_of(int t, int& I, int& J) {  // t = I (I + 1) / 2 + J, J <= I
+    I = (int)((sqrt(8.0 * t + 1.0) - 1.0) * 0.5);
+    while ((I + 1) * (I + 2) / 2 <= t) ++I;
+    while (I * (I + 1) / 2 > t) --I;
+    J = t - I * (I + 1) / 2;
+}
+}  // namespace ws
+
+__global__ void __launch_bounds__(ws::THREADS, 1)
+k_sweep_ws(double* __restrict__ P, int ld, const double* __restrict__ Vr, const double* __restrict__ Vc, int m4,
+           int ntiles, int dbg, SweepExtra ex) {
+    using namespace ws;
+    extern __shared__ __align__(128) unsigned char smraw[];
+    const int blk = m4 * V_LDB;                          // doubles per 64-column block of V
+    double* VIb = reinterpret_cast<double*>(smraw);      // 2 blocks
+    double* VJb = VIb + 2 * (size_t)blk;                 // 2 blocks
+    unsigned char* accb = reinterpret_cast<unsigned char*>(VJb + 2 * (size_t)blk);  // [2][8] slots
+    __shared__ __align__(8) uint64_t vi_full[2], vi_empty[2], vj_full[2], vj_empty[2];
+    __shared__ __align__(8) uint64_t acc_full[2][MMA_WARPS], acc_empty[2][MMA_WARPS];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, t4 = lane & 3;
+
+    if (blockIdx.x == 0 && ex.apply_kind >= 0 && warp >= MMA_WARPS && warp < 2 * MMA_WARPS) {
+        // state update (k_apply folded in), done by the epilogue warps of CTA 0
+        const int et = tid - MMA_WARPS * 32, ent = MMA_WARPS * 32;
+        if (et == 0) {
+            double cam[CAM], d[CAM];
+#pragma unroll
+            for (int c = 0; c < CAM; ++c) { cam[c] = ex.state[c]; d[c] = ex.dx[c]; }
+            camera_reset(cam, d, ex.as_written);
+#pragma unroll
+            for (int c = 0; c < CAM; ++c) ex.state[c] = cam[c];
+        }
+        if (ex.apply_kind == 0) {
+            for (int e = et; e < 3 * ex.nlm; e += ent) ex.state[CAM + e] += ex.dx[CAM + e];
+        } else {
+            for (int t = et; t < ex.nlm; t += ent) {
+                double lm[10], d[10];
+#pragma unroll
+                for (int c = 0; c < 10; ++c) { lm[c] = ex.state[CAM + 10 * t + c]; d[c] = ex.dx[CAM + 10 * t + c]; }
+                landmark_update<1>(lm, d);
+#pragma unroll
+                for (int c = 0; c < 10; ++c) ex.state[CAM + 10 * t + c] = lm[c];
+            }
+        }
+    }
+    if (tid == 0) {
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&vi_full[b], 1); mbar_init(&vj_full[b], 1);
+            mbar_init(&vi_empty[b], MMA_WARPS); mbar_init(&vj_empty[b], MMA_WARPS);
+            for (int w = 0; w < MMA_WARPS; ++w) { mbar_init(&acc_full[b][w], 1); mbar_init(&acc_empty[b][w], 1); }
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    const int t_begin = (int)((long long)ntiles * blockIdx.x / gridDim.x);
+    const int t_end = (int)((long long)ntiles * (blockIdx.x + 1) / gridDim.x);
+    if (t_begin >= t_end) return;
+    int I, J;
+    tile_of(t_begin, I, J);
+    const uint32_t blk_bytes = (uint32_t)(blk * sizeof(double));
+
+    if (warp < MMA_WARPS) {
+        // ---------------- MMA warps ----------------------------------------------------------
+        const int wi = warp / WN, wj = warp % WN;
+        int vi_n = 0, prevI = -1, vis = 0;
+        for (int t = t_begin, n = 0; t < t_end; ++t, ++n) {
+            if (I != prevI) {
+                vis = vi_n & 1;
+                mbar_wait(&vi_full[vis], (vi_n >> 1) & 1);
+                ++vi_n;
+                prevI = I;
+            }
+            const int s = n & 1;
+            mbar_wait(&vj_full[s], (n >> 1) & 1);
+            double acc[RM][RN][2];
+#pragma unroll
+            for (int rm = 0; rm < RM; ++rm)
+#pragma unroll
+                for (int rn = 0; rn < RN; ++rn) acc[rm][rn][0] = acc[rm][rn][1] = 0.0;
+            const double* va = VIb + (size_t)vis * blk + t4 * V_LDB + 32 * wi + g;
+            const double* vb = VJb + (size_t)s * blk + t4 * V_LDB + 16 * wj + g;
+#pragma unroll 3
+            for (int kk = 0; kk < ((dbg & 1) ? 4 : m4); kk += 4) {
+                double a[RM], b[RN];
+#pragma unroll
+                for (int r = 0; r < RM; ++r) a[r] = va[kk * V_LDB + 8 * r];
+#pragma unroll
+                for (int r = 0; r < RN; ++r) b[r] = vb[kk * V_LDB + 8 * r];
+#pragma unroll
+                for (int rm = 0; rm < RM; ++rm)
+#pragma unroll
+                    for (int rn = 0; rn < RN; ++rn) dmma884(acc[rm][rn][0], acc[rm][rn][1], a[rm], b[rn]);
+            }
+            int In = I, Jn = J + 1;
+            if (Jn > I) { In = I + 1; Jn = 0; }
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(&vj_empty[s]);
+                if (In != I) mbar_arrive(&vi_empty[vis]);
+            }
+            if (n >= 2) mbar_wait(&acc_empty[s][warp], ((n >> 1) - 1) & 1);
+            double2* slot = reinterpret_cast<double2*>(accb + ((size_t)s * MMA_WARPS + warp) * ACC_SLOT_BYTES) + lane;
+#pragma unroll
+            for (int rm = 0; rm < RM; ++rm)
+#pragma unroll
+                for (int rn = 0; rn < RN; ++rn) slot[(rm * RN + rn) * 32] = make_double2(acc[rm][rn][0], acc[rm][rn][1]);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_full[s][warp]);
+            I = In;
+            J = Jn;
+        }
+    } else {
+        // ---------------- epilogue warps ---------------------------------------------------
+        const int w = warp - MMA_WARPS, wi = w / WN, wj = w % WN;
+        auto load_p = [&](double (&pf)[RM][RN][2], int Ix, int Jx) {
+            if (dbg & 8) {
+#pragma unroll
+                for (int rm = 0; rm < RM; ++rm)
+#pragma unroll
+                    for (int rn = 0; rn < RN; ++rn) pf[rm][rn][0] = pf[rm][rn][1] = 0.0;
+            } else {
+                tile_load<RM, RN>(P + (long long)(Ix * TI + 32 * wi + 4 * g) * ld + Jx * TJ + 16 * wj + 4 * t4, ld, pf, (dbg >> 4) & 3);
+            }
+        };
+        // producer state (lane 0 of epilogue warp 0): cursor over this CTA's tile sequence
+        int qI = I, qJ = J, q = 0, vi_n = 0, prevI = -1;
+        const int nt = t_end - t_begin;
+        auto produce = [&]() {  // V panels of the q-th tile; its slots were released by tile q - 2
+            if (q >= nt) return;
+            if (qI != prevI) {
+                const int s = vi_n & 1;
+                if (vi_n >= 2) mbar_wait(&vi_empty[s], ((vi_n >> 1) - 1) & 1);
+                mbar_expect_tx(&vi_full[s], blk_bytes);
+                bulk_g2s(VIb + (size_t)s * blk, Vr + (size_t)qI * blk, blk_bytes, &vi_full[s]);
+                ++vi_n;
+                prevI = qI;
+            }
+            const int s = q & 1;
+            if (q >= 2) mbar_wait(&vj_empty[s], ((q >> 1) - 1) & 1);
+            mbar_expect_tx(&vj_full[s], blk_bytes);
+            bulk_g2s(VJb + (size_t)s * blk, Vc + (size_t)qJ * blk, blk_bytes, &vj_full[s]);
+            if (++qJ > qI) { ++qI; qJ = 0; }
+            ++q;
+        };
+        const bool is_producer = (w == 0 && lane == 0);
+        if (is_producer) { produce(); produce(); }
+        // L2 prefetch cursor, PD tiles ahead of the register prefetch: under load the HBM read
+        // latency (reads queue behind twice their volume of writes) exceeds one tile time, so
+        // the lines are pulled into L2 early and the 256-bit loads one tile ahead hit L2.
+        // Each lane prefetches one 128-byte line: row 32 wi + lane of its warp's sub-tile.
+        constexpr int PD = 3;
+        int fI = I, fJ = J, fq = 0;
+        auto l2_prefetch = [&]() {
+            if (fq < nt && !(dbg & 8)) {
+                const double* a = P + (long long)(fI * TI + 32 * wi + lane) * ld + fJ * TJ + 16 * wj;
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(a));
+            }
+            if (++fJ > fI) { ++fI; fJ = 0; }
+            ++fq;
+        };
+        if (!(dbg & 256))
+            for (int i = 0; i < PD + 1; ++i) l2_prefetch();
+        double pf[RM][RN][2], pn[RM][RN][2];
+        load_p(pf, I, J);
+        for (int t = t_begin, n = 0; t < t_end; ++t, ++n) {
+            int In = I, Jn = J + 1;
+            if (Jn > I) { In = I + 1; Jn = 0; }
+            if (t + 1 < t_end) load_p(pn, In, Jn);   // next tile's P flies during this tile's epilogue
+            if (!(dbg & 256)) l2_prefetch();
+            const int s = n & 1;
+            mbar_wait(&acc_full[s][w], (n >> 1) & 1);
+            if (is_producer) produce();              // tile n + 2: the MMA warps are done with tile n's panels
+            __syncwarp();
+            const double2* slot = reinterpret_cast<const double2*>(accb + ((size_t)s * MMA_WARPS + w) * ACC_SLOT_BYTES) + lane;
+            double2 ac[RM][RN];
+#pragma unroll
+            for (int rm = 0; rm < RM; ++rm)
+#pragma unroll
+                for (int rn = 0; rn < RN; ++rn) ac[rm][rn] = slot[(rm * RN + rn) * 32];
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty[s][w]);
+            const int r0 = I * TI + 32 * wi + 4 * g, c0 = J * TJ + 16 * wj + 4 * t4;
+#pragma unroll
+            for (int rm = 0; rm < RM; ++rm)
+#pragma unroll
+                for (int rn = 0; rn < RN; ++rn) {
+                    pf[rm][rn][0] -= ac[rm][rn].x;
+                    pf[rm][rn][1] -= ac[rm][rn].y;
+                }
+            if (I != J) {  // strictly below the diagonal
+                if (!(dbg & 4)) tile_store<RM, RN>(P + (long long)r0 * ld + c0, ld, pf, (dbg >> 6) & 3);
+                if (!(dbg & 2)) tile_store_mirror<RM, RN>(P + (long long)c0 * ld + r0, ld, pf, (dbg >> 6) & 3);
+            } else {
+#pragma unroll
+                for (int rm = 0; rm < RM; ++rm)
+#pragma unroll
+                    for (int rn = 0; rn < RN; ++rn)
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            const int i = r0 + rm, j = c0 + 16 * (rn >> 1) + 2 * (rn & 1) + e;
+                            if (i >= j) {
+                                double o = pf[rm][rn][e];
+                                if (i == j && ex.add_q && i < ex.n) o += process_noise(ex.nz, i);
+                                P[(long long)i * ld + j] = o;
+                                if (i > j) P[(long long)j * ld + i] = o;
+                            }
+                        }
+            }
+#pragma unroll
+            for (int rm = 0; rm < RM; ++rm)
+#pragma unroll
+                for (int rn = 0; rn < RN; ++rn) { pf[rm][rn][0] = pn[rm][rn][0]; pf[rm][rn][1] = pn[rm][rn][1]; }
+            I = In;
+            J = Jn;
+        }
     }
 }
 

@@ -180,6 +180,12 @@ ASB_API int asb_bench_sweep(asb_filter* f, int m4, int config, int dbg, int reps
 ASB_API int asb_front_profile(asb_filter* f, double us[12]);
 /* Dependent-issue latencies in clocks: DFMA, rsqrt(double)+add, LDS.64 (with cvt), BAR.SYNC of 256 threads. */
 ASB_API int asb_latency_probe(int device, double clocks[4]);
+/* HBM stream bandwidth (GB/s of bytes moved): mode 0 write-only, 1 read-only, 2 one read + two writes
+ * (the sweep's mix), 256-bit accesses. */
+ASB_API int asb_stream_bandwidth(int device, int64_t bytes, int mode, double* gbs);
+/* The sweep's memory pattern with no math (read lower-triangle tile, write it, write its mirror
+ * location) on an n x n FP64 matrix with tile = 64 / 128 / 256: best time in us. */
+ASB_API int asb_tilepattern_bandwidth(int device, int n, int tile, int ctas_per_sm, double* us);
 /* Streaming copy bandwidth (GB/s, read+write bytes) over `bytes` of HBM. */
 ASB_API int asb_copy_bandwidth(int device, int64_t bytes, double* gbs);
 
