@@ -52,7 +52,7 @@ struct asb_filter {
     int* s_idx = nullptr; double* s_pose = nullptr; unsigned char* s_new = nullptr;
     std::vector<FrameRec> frames;
     int next_frame = 0;
-    int sweep_grid = 0, smem_optin = 0, force_big = 0, sweep_config = -1;
+    int sweep_grid = 0, smem_optin = 0, force_big = 0, sweep_config = -1, front_dbg = 0;
 
     int n_state() const { return CAM + D * nlm; }
 };
@@ -134,6 +134,7 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
             a.blocks_out = f->d_blocks + (size_t)c0 * R * W; a.nu_out = f->d_nu + (size_t)R * c0;
             a.status = f->d_status;
             a.prof = f->d_prof;
+            a.dbg = f->front_dbg;
             const int nblk = 2 * ((n1 + 127) / 128);  // whole 128-row sweep tiles are covered
             k_front<KIND><<<nblk, FRONT_THREADS, FrontSmem<KIND>::bytes(kc, m4), st>>>(a);
             cur ^= 1;
@@ -227,6 +228,7 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
     f->sweep_grid = prop.multiProcessorCount;
     f->smem_optin = (int)prop.sharedMemPerBlockOptin;
     if (const char* e = std::getenv("ASB_SWEEP_BIG")) f->force_big = std::atoi(e);
+    if (const char* e = std::getenv("ASB_FRONT_DBG")) f->front_dbg = std::atoi(e);  // experiments (front.cuh)
     if (const char* e = std::getenv("ASB_SWEEP_CONFIG")) f->sweep_config = std::atoi(e);  // experiments: 0 / 1 / 2
     ASB_CUDA(cudaStreamCreateWithFlags(&f->own_stream, cudaStreamNonBlocking));
     f->stream = f->own_stream;

@@ -50,6 +50,7 @@ struct FrontArgs {
     double* blocks_out;          // (kc, R, W) for asb_get_last_update, may be null
     double* nu_out;              // (R kc)
     int* status;
+    int dbg;                     // experiments only (ASB_FRONT_DBG): 1 skip trailing, 2 skip panel, 4 skip diag, 8 skip extract
     unsigned long long* prof;    // phase timestamps of CTA 0 (globaltimer ns), 8 slots, may be null
 };
 
@@ -68,27 +69,28 @@ __device__ __forceinline__ void front_stamp(const FrontArgs& p, int slot) {
 // Chunk limits (rows per chunk m = R kc): shared memory holds PT (nT^2), GT (m x nT), the
 // augmented S ((2m+1) x (m|1)), the staged rows (nT x 64) and the model blocks.
 template <int KIND> struct FrontLimits;
-template <> struct FrontLimits<0> { static constexpr int KC_MAX = 22; };   // m = 66, 203 KB
+template <> struct FrontLimits<0> { static constexpr int KC_MAX = 21; };   // m = 63 (<= 8 column tiles, 16 row tiles)
 template <> struct FrontLimits<1> { static constexpr int KC_MAX = 8; };    // m = 56, 212 KB
 
 template <int KIND>
 struct FrontSmem {
     static constexpr int D = Dims<KIND>::D, R = Dims<KIND>::R, W = CAM + D;
     static __host__ __device__ size_t region1(int kc, int m4) {   // PT, later the G slice
-        const size_t nT = CAM + D * kc, pt = nT * nT, gs = (size_t)m4 * FRONT_LDG;
-        return ((pt > gs ? pt : gs) + 1) & ~(size_t)1;   // keep 16-byte alignment behind it
+        const size_t nT = CAM + D * kc, pt = nT * nT;
+        (void)m4;
+        return (pt + 1) & ~(size_t)1;   // keep 16-byte alignment behind it
     }
     static __host__ __device__ size_t s_rows(int kc) {            // S with nu appended, padded to even
         const size_t m = R * kc;
-        return ((2 * m + 1) * (m | 1) + 1) & ~(size_t)1;
+        return (size_t)128 * (m | 1);   // rows 0..m: [S; nu^T], rows 64..127: G^T of the block
     }
     static __host__ __device__ size_t gt_rows(int kc) {           // GT = H PT, row stride nT|1
         const size_t m = R * kc, nT = CAM + D * kc;
         return (m * (nT | 1) + 1) & ~(size_t)1;
     }
     static __host__ __device__ size_t region3(int kc, int m4) {   // staged rows, later the V slice
-        const size_t nT = CAM + D * kc, st = nT * V_BLK, vs = (size_t)m4 * V_BLK;
-        return st > vs ? st : vs;   // multiple of 64
+        (void)m4;
+        return (size_t)(CAM + D * kc) * V_BLK;
     }
     static __host__ __device__ size_t bytes(int kc, int m4) {
         const int m = R * kc, nT = CAM + D * kc, lds = m | 1;
@@ -117,17 +119,14 @@ k_front(FrontArgs p) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int kc = p.kc, m = R * kc, m4 = p.m4, nT = CAM + D * kc;
     const int lds = m | 1;
-    const int Mr = 2 * m + 1;    // rows of the augmented matrix [S; nu^T; I]
     const int ld = p.ld, n0 = p.n0, n1 = p.n1;
     const int j0 = blockIdx.x * V_BLK;
 
     // ---- shared memory carve-up ---------------------------------------------------------
     double* s_PT = reinterpret_cast<double*>(fsm);                       // nT x nT (dense)
-    double* s_G = s_PT;                                                  // m4 x FRONT_LDG (after S is built)
-    double* s_S = s_PT + FrontSmem<KIND>::region1(kc, m4);               // Mr x lds
+    double* s_S = s_PT + FrontSmem<KIND>::region1(kc, m4);               // 128 x lds: [S; nu^T] and G^T at row 64
     double* s_GT = s_S + FrontSmem<KIND>::s_rows(kc);                    // m x ldt
     double* s_stage = s_GT + FrontSmem<KIND>::gt_rows(kc);                           // nT x 64: P_eff[T, this block's columns]
-    double* s_V = s_stage;                                               // m4 x 64 (after G is built)
     double* s_blk = s_stage + FrontSmem<KIND>::region3(kc, m4);          // kc x R x W
     double* s_lm = s_blk + (size_t)kc * R * W;                           // kc x D
     double* s_dinv = s_lm + (size_t)kc * D;                              // m4
@@ -175,10 +174,6 @@ k_front(FrontArgs p) {
     front_stamp(p, 1);
 
     // ---- phase 2 (while the copies fly): measurement model, 
-    for (int e = tid; e < m * lds; e += NT) {   // identity rows of the augmented S
-        const int r = e / lds, c = e - r * lds;
-        s_S[(m + 1) * lds + e] = (r == c) ? 1.0 : 0.0;
-    }
     for (int o = tid; o < kc; o += NT) {
         double lm[D];
         const int li = CAM + D * s_idx[o];
@@ -297,138 +292,10 @@ k_front(FrontArgs p) {
     __syncthreads();
     front_stamp(p, 3);
 
-    // ---- phase 5: blocked right-looking Cholesky of the augmented matrix ---------------------
-    // rows 0..m-1: S -> L;  row m: nu -> y^T = (L^-1 nu)^T;  rows m+1+j: e_j^T -> (L^-1 e_j)^T,
-    // i.e. s_S[(m+1+b) * lds + a] = W[a][b], W = L^-1.  NB = rows per marker; every thread
-    // factors the NB x NB diagonal block redundantly in registers (no serial thread).
-    bool bad = false;
-    for (int jb = 0; jb < m; jb += NB) {
-        double dblk[NB][NB], dinv[NB];
-        front_clk(p, 8, jb == NB);
-#pragma unroll
-        for (int r = 0; r < NB; ++r)
-#pragma unroll
-            for (int c = 0; c <= r; ++c) dblk[r][c] = s_S[(jb + r) * lds + jb + c];
-        if constexpr (NB == 3) {
-            // closed form with the three reciprocal square roots independent of each other
-            // (leading principal minors): the serial pivot chain is the critical path of the step
-            const double a00 = dblk[0][0], a10 = dblk[1][0], a11 = dblk[1][1];
-            const double a20 = dblk[2][0], a21 = dblk[2][1], a22 = dblk[2][2];
-            const double det2 = a00 * a11 - a10 * a10;
-            const double q3 = a00 * a21 * a21 - 2.0 * a10 * a20 * a21 + a11 * a20 * a20;
-            const double det3 = a22 * det2 - q3;
-            if (!(a00 > 0.0) || !(det2 > 0.0) || !(det3 > 0.0) || !(a00 < 1e300) || !(det3 < 1e300)) bad = true;
-            const double r0 = rsqrt(a00), rd2 = rsqrt(det2), rd3 = rsqrt(det3);
-            const double l00 = a00 * r0, sd2 = det2 * rd2;   // sqrt(a00), sqrt(det2)
-            dinv[0] = r0;
-            dinv[1] = rd2 * l00;          // 1 / sqrt(det2 / a00)
-            dinv[2] = rd3 * sd2;          // 1 / sqrt(det3 / det2)
-            dblk[0][0] = l00;
-            dblk[1][0] = a10 * r0;
-            dblk[2][0] = a20 * r0;
-            dblk[1][1] = sd2 * r0;
-            dblk[2][1] = (a21 - dblk[2][0] * dblk[1][0]) * dinv[1];
-            dblk[2][2] = det3 * rd3 * rd2;
-        } else {
-#pragma unroll
-            for (int c = 0; c < NB; ++c) {
-                double pv = dblk[c][c];
-#pragma unroll
-                for (int t = 0; t < c; ++t) pv -= dblk[c][t] * dblk[c][t];
-                if (!(pv > 0.0) || !(pv < 1e300)) bad = true;
-                const double rs = rsqrt(pv);
-                dinv[c] = rs;
-                dblk[c][c] = pv * rs;
-#pragma unroll
-                for (int r = c + 1; r < NB; ++r) {
-                    double v = dblk[r][c];
-#pragma unroll
-                    for (int t = 0; t < c; ++t) v -= dblk[r][t] * dblk[c][t];
-                    dblk[r][c] = v * rs;
-                }
-            }
-        }
-        // identity rows m+1+j with j >= jb+NB are still zero in these columns: skip them
-        const int t0 = jb + NB, rows_end = min(Mr, m + 1 + t0);
-        front_clk(p, 9, jb == NB);
-        for (int i = t0 + tid; i < rows_end; i += NT) {
-            double x[NB];
-#pragma unroll
-            for (int c = 0; c < NB; ++c) x[c] = s_S[i * lds + jb + c];
-#pragma unroll
-            for (int c = 0; c < NB; ++c) {
-                double v = x[c];
-#pragma unroll
-                for (int t = 0; t < c; ++t) v -= x[t] * dblk[c][t];
-                x[c] = v * dinv[c];
-            }
-#pragma unroll
-            for (int c = 0; c < NB; ++c) s_S[i * lds + jb + c] = x[c];
-        }
-#pragma unroll
-        for (int r = 0; r < NB; ++r) {
-            if (tid == r) {
-#pragma unroll
-                for (int c = 0; c <= r; ++c) s_S[(jb + r) * lds + jb + c] = dblk[r][c];
-                s_dinv[jb + r] = dinv[r];
-            }
-        }
-        front_clk(p, 10, jb == NB);
-        __syncthreads();
-        front_clk(p, 11, jb == NB);
-        // trailing update in 4 x 4 register tiles (independent loads, no serial LDS chains):
-        // columns kk in [t0, m), rows i in [kk, rows_end)
-        if (t0 < m) {
-            // thread (tx, ty) of a 16 x 16 grid owns columns kk = t0 + tx + 16 qk and rows
-            // i = t0 + ty + 16 qi: lanes read consecutive rows of the panel (odd row stride)
-            // and consecutive elements of a row, so shared memory is conflict-free
-            const int tx = tid & 15, ty = tid >> 4;
-            double lk[4][NB];
-#pragma unroll
-            for (int qk = 0; qk < 4; ++qk) {
-                const int kk = t0 + tx + 16 * qk;
-#pragma unroll
-                for (int c = 0; c < NB; ++c) lk[qk][c] = kk < m ? s_S[kk * lds + jb + c] : 0.0;
-            }
-            // rows_end - t0 = m + 1 <= 16 * QI: fully unrolled, all loads before the first store
-            constexpr int QI = 5;
-            double li[QI][NB], tv[QI][4];
-#pragma unroll
-            for (int qi = 0; qi < QI; ++qi) {
-                const int i = t0 + ty + 16 * qi;
-#pragma unroll
-                for (int c = 0; c < NB; ++c) li[qi][c] = i < rows_end ? s_S[i * lds + jb + c] : 0.0;
-#pragma unroll
-                for (int qk = 0; qk < 4; ++qk) {
-                    const int kk = t0 + tx + 16 * qk;
-                    tv[qi][qk] = (i < rows_end && kk < m && kk <= i) ? s_S[i * lds + kk] : 0.0;
-                }
-            }
-#pragma unroll
-            for (int qi = 0; qi < QI; ++qi)
-#pragma unroll
-                for (int qk = 0; qk < 4; ++qk)
-#pragma unroll
-                    for (int c = 0; c < NB; ++c) tv[qi][qk] -= li[qi][c] * lk[qk][c];
-#pragma unroll
-            for (int qi = 0; qi < QI; ++qi) {
-                const int i = t0 + ty + 16 * qi;
-#pragma unroll
-                for (int qk = 0; qk < 4; ++qk) {
-                    const int kk = t0 + tx + 16 * qk;
-                    if (i < rows_end && kk < m && kk <= i) s_S[i * lds + kk] = tv[qi][qk];
-                }
-            }
-        }
-        front_clk(p, 12, jb == NB);
-        __syncthreads();
-        front_clk(p, 13, jb == NB);
-    }
-    if (bad && blockIdx.x == 0 && tid == 0) atomicExch(p.status, ASB_ERR_NOT_SPD);
-    for (int a = tid; a < m4; a += NT) s_y[a] = a < m ? s_S[m * lds + a] : 0.0;
-    front_stamp(p, 4);
-
-    // ---- phase 6: G slice = H x staged rows -----------------------------------------------
+    // ---- phase 5: G^T for this block's 64 columns (G = H P_eff[T, block]) appended to S as rows
+    //      GROW..GROW+63: the appended-row trick of the Cholesky below turns row GROW+jj into
+    //      (L^-1 G[:, jj])^T = V[:, jj]^T, so V needs no triangular solve of its own.
+    constexpr int GROW = 64;
     for (int e = tid; e < kc * V_BLK; e += NT) {
         const int o = e / V_BLK, jj = e - o * V_BLK;
         const double* blk = s_blk + (size_t)o * R * W;
@@ -443,52 +310,150 @@ k_front(FrontArgs p) {
             for (int r = 0; r < R; ++r) acc[r] += blk[r * W + c] * pv;
         }
 #pragma unroll
-        for (int r = 0; r < R; ++r) s_G[(R * o + r) * FRONT_LDG + jj] = acc[r];
+        for (int r = 0; r < R; ++r) s_S[(GROW + jj) * lds + R * o + r] = acc[r];
     }
     __syncthreads();
-    front_stamp(p, 5);
+    front_stamp(p, 4);
 
-    // ---- phase 7: V = W G, 4 x 4 register tiles; W[a][b] = s_S[(m+1+b) * lds + a] -----------
-    {
-        const int nta = m4 >> 2;
-        for (int e = tid; e < nta * (V_BLK / 4); e += NT) {
-            const int ta = nta - 1 - (e >> 4), jj0 = (e & 15) << 2, a0 = ta << 2;  // longest tiles first
-            double acc[4][4];
+    // ---- phase 6: blocked right-looking Cholesky of the augmented matrix [S; nu^T; G^T] -------
+    // rows 0..m-1: S -> L;  row m: nu -> y^T = (L^-1 nu)^T;  rows GROW+jj: G[:,jj]^T -> V[:,jj]^T.
+    // NB = rows per marker.  The trailing matrix lives in REGISTERS as 8 x 8 DMMA accumulator
+    // tiles — warp w owns row tile w of the S part and row tile w of the G part, all 8 column
+    // tiles — and is updated with mma.sync m8n8k4 (k = NB padded to 4); shared memory only
+    // carries the current block column, written out before the panel solve.  (With the trailing
+    // matrix in shared memory the update was shared-memory-bandwidth-bound.)
+    static_assert(NT == 256, "tile ownership assumes 8 warps");
+    const int g8 = lane >> 2, t4 = lane & 3;
+    const int r0 = 8 * warp + g8, r1 = GROW + 8 * warp + g8;   // this lane's row in the S / G tile
+    double C[2][8][2];
 #pragma unroll
-            for (int r = 0; r < 4; ++r)
+    for (int ct = 0; ct < 8; ++ct)
 #pragma unroll
-                for (int c = 0; c < 4; ++c) acc[r][c] = 0.0;
-            const int bend = min(a0 + 4, m);
-            const double* wp = s_S + (size_t)(m + 1) * lds + a0;
-            const double* gp = s_G + jj0;
-#pragma unroll 2
-            for (int b = 0; b < bend; ++b) {
-                const double2 g01 = *reinterpret_cast<const double2*>(gp + b * FRONT_LDG);
-                const double2 g23 = *reinterpret_cast<const double2*>(gp + b * FRONT_LDG + 2);
-                const double g[4] = {g01.x, g01.y, g23.x, g23.y};
-                double w[4];
+        for (int e = 0; e < 2; ++e) {
+            const int c = 8 * ct + 2 * t4 + e;
+            C[0][ct][e] = (c < m && r0 <= m && (r0 == m || c <= r0)) ? s_S[r0 * lds + c] : 0.0;
+            C[1][ct][e] = c < m ? s_S[r1 * lds + c] : 0.0;
+        }
+    bool bad = false;
+    for (int jb = 0; jb < m; jb += NB) {
+        const int t0 = jb + NB;
+        if (jb > 0 && !(p.dbg & 8)) {  // block column jb .. jb+NB-1 of the trailing matrix: registers -> shared memory
+            const int ct_lo = jb >> 3, ct_hi = (jb + NB - 1) >> 3;   // the (at most two) column tiles involved
 #pragma unroll
-                for (int r = 0; r < 4; ++r) w[r] = wp[b * lds + r];
+            for (int ct = 0; ct < 8; ++ct) {
+                if (ct < ct_lo || ct > ct_hi) continue;               // warp-uniform: registers stay statically indexed
 #pragma unroll
-                for (int r = 0; r < 4; ++r)
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) acc[r][c] += w[r] * g[c];
+                for (int e = 0; e < 2; ++e) {
+                    const int c = 8 * ct + 2 * t4 + e;
+                    if (c >= jb && c < t0) {
+                        if (r0 >= jb && r0 <= m) s_S[r0 * lds + c] = C[0][ct][e];
+                        s_S[r1 * lds + c] = C[1][ct][e];
+                    }
+                }
             }
+            __syncthreads();
+        }
+        if (tid < 128) {
+            // warps 0-3: factor the NB x NB diagonal block (redundantly per thread, in registers),
+            // then one row of the panel each: S rows t0..m (thread < 64), G rows (thread >= 64)
+            double dblk[NB][NB], dinv[NB];
 #pragma unroll
-            for (int r = 0; r < 4; ++r) {
-                const bool live = a0 + r < m;  // identity padding of L: rows m..m4 of V are zero
-                double2* dst = reinterpret_cast<double2*>(s_V + (a0 + r) * V_BLK + jj0);
-                dst[0] = live ? make_double2(acc[r][0], acc[r][1]) : make_double2(0.0, 0.0);
-                dst[1] = live ? make_double2(acc[r][2], acc[r][3]) : make_double2(0.0, 0.0);
+            for (int r = 0; r < NB; ++r)
+#pragma unroll
+                for (int c = 0; c <= r; ++c) dblk[r][c] = s_S[(jb + r) * lds + jb + c];
+            if (p.dbg & 4) {
+#pragma unroll
+                for (int c = 0; c < NB; ++c) dinv[c] = 1.0;
+            } else if constexpr (NB == 3) {
+                // closed form with the three reciprocal square roots independent of each other
+                // (leading principal minors): the serial pivot chain is the critical path of the step
+                const double a00 = dblk[0][0], a10 = dblk[1][0], a11 = dblk[1][1];
+                const double a20 = dblk[2][0], a21 = dblk[2][1], a22 = dblk[2][2];
+                const double det2 = a00 * a11 - a10 * a10;
+                const double q3 = a00 * a21 * a21 - 2.0 * a10 * a20 * a21 + a11 * a20 * a20;
+                const double det3 = a22 * det2 - q3;
+                if (!(a00 > 0.0) || !(det2 > 0.0) || !(det3 > 0.0) || !(a00 < 1e300) || !(det3 < 1e300)) bad = true;
+                const double rs0 = rsqrt(a00), rd2 = rsqrt(det2), rd3 = rsqrt(det3);
+                const double l00 = a00 * rs0, sd2 = det2 * rd2;   // sqrt(a00), sqrt(det2)
+                dinv[0] = rs0;
+                dinv[1] = rd2 * l00;          // 1 / sqrt(det2 / a00)
+                dinv[2] = rd3 * sd2;          // 1 / sqrt(det3 / det2)
+                dblk[1][0] = a10 * rs0;
+                dblk[2][0] = a20 * rs0;
+                dblk[2][1] = (a21 - dblk[2][0] * dblk[1][0]) * dinv[1];
+            } else {
+#pragma unroll
+                for (int c = 0; c < NB; ++c) {
+                    double pv = dblk[c][c];
+#pragma unroll
+                    for (int t = 0; t < c; ++t) pv -= dblk[c][t] * dblk[c][t];
+                    if (!(pv > 0.0) || !(pv < 1e300)) bad = true;
+                    const double rs = rsqrt(pv);
+                    dinv[c] = rs;
+#pragma unroll
+                    for (int r = c + 1; r < NB; ++r) {
+                        double v = dblk[r][c];
+#pragma unroll
+                        for (int t = 0; t < c; ++t) v -= dblk[r][t] * dblk[c][t];
+                        dblk[r][c] = v * rs;
+                    }
+                }
+            }
+            // (the factored diagonal block itself is never read again: only y and V are used)
+            const int i = tid < 64 ? t0 + tid : GROW + (tid - 64);
+            if ((tid >= 64 || i <= m) && !(p.dbg & 2)) {
+                double x[NB];
+#pragma unroll
+                for (int c = 0; c < NB; ++c) x[c] = s_S[i * lds + jb + c];
+#pragma unroll
+                for (int c = 0; c < NB; ++c) {
+                    double v = x[c];
+#pragma unroll
+                    for (int t = 0; t < c; ++t) v -= x[t] * dblk[c][t];
+                    x[c] = v * dinv[c];
+                }
+#pragma unroll
+                for (int c = 0; c < NB; ++c) s_S[i * lds + jb + c] = x[c];
+            }
+        }
+        __syncthreads();
+        // trailing update C -= L_panel L_panel^T on the register tiles (FP64 tensor pipe)
+        if (t0 < m && !(p.dbg & 1)) {
+            constexpr int KS = (NB + 3) / 4;
+            const bool act0 = (8 * warp + 7 >= t0) && (8 * warp <= m);   // warp-uniform
+            double a0[KS], a1[KS];
+#pragma unroll
+            for (int ks = 0; ks < KS; ++ks) {
+                const int t = 4 * ks + t4;
+                a1[ks] = t < NB ? -s_S[r1 * lds + jb + t] : 0.0;
+                a0[ks] = (act0 && t < NB && r0 >= t0 && r0 <= m) ? -s_S[r0 * lds + jb + t] : 0.0;
+            }
+            const int ct0 = t0 >> 3;
+#pragma unroll
+            for (int ct = 0; ct < 8; ++ct) {
+                if (ct < ct0 || 8 * ct >= m) continue;     // no active column in this tile
+                const int kk = 8 * ct + g8;
+#pragma unroll
+                for (int ks = 0; ks < KS; ++ks) {
+                    const int t = 4 * ks + t4;
+                    const double bv = (t < NB && kk >= t0 && kk < m) ? s_S[kk * lds + jb + t] : 0.0;
+                    dmma884(C[1][ct][0], C[1][ct][1], a1[ks], bv);
+                    if (act0 && ct <= warp) dmma884(C[0][ct][0], C[0][ct][1], a0[ks], bv);
+                }
             }
         }
     }
     __syncthreads();
+    if (bad && blockIdx.x == 0 && tid == 0) atomicExch(p.status, ASB_ERR_NOT_SPD);
+    front_stamp(p, 5);
     front_stamp(p, 6);
-    // dx (+)= V^T y, and this CTA's block of the tiled panel (sweep.cuh): m4 rows x V_LDB
+    // dx (+)= V^T y, and this CTA's block of the tiled panel (sweep.cuh): m4 rows x V_LDB.
+    // V[a][jj] = s_S[(GROW + jj) * lds + a], y[a] = s_S[m * lds + a]
     if (tid < V_BLK) {
         double dsum = 0.0;
-        for (int a = 0; a < m; ++a) dsum += s_V[a * V_BLK + tid] * s_y[a];
+        const double* vrow = s_S + (size_t)(GROW + tid) * lds;
+        const double* yrow = s_S + (size_t)m * lds;
+        for (int a = 0; a < m; ++a) dsum += vrow[a] * yrow[a];
         const int j = j0 + tid;
         if (j < n1) p.dx_out[j] = (p.use_delta ? p.dx_in[j] : 0.0) + dsum;
     }
@@ -501,8 +466,8 @@ k_front(FrontArgs p) {
             // inverse maps: which column lands at `pos`
             const int cr = (pos & ~31) + 4 * (pos & 7) + ((pos & 31) >> 3);
             const int cc = (pos & ~15) + 4 * ((pos & 7) >> 1) + 2 * ((pos & 15) >> 3) + (pos & 1);
-            vr[a * V_LDB + pos] = s_V[a * V_BLK + cr];
-            vc[a * V_LDB + pos] = s_V[a * V_BLK + cc];
+            vr[a * V_LDB + pos] = a < m ? s_S[(GROW + cr) * lds + a] : 0.0;   // rows m..m4: identity padding of L
+            vc[a * V_LDB + pos] = a < m ? s_S[(GROW + cc) * lds + a] : 0.0;
         }
     }
 
