@@ -82,6 +82,7 @@ SIGNATURES = {
     "asb_batch_get_landmark_ids": (C.c_int, [_vp, C.c_int, _ip, C.c_int]),
     "asb_batch_get_cameras": (C.c_int, [_vp, _dp, _ip]),
     "asb_batch_device_views": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp), _intp, _intp]),
+    "asb_batch_profile": (C.c_int, [_vp, _dp]),
     "asb_ippe_square": (C.c_int, [_fp, C.c_int64, _dp, _dp, C.c_double, _dp, C.c_int]),
     "asb_ippe_square_device": (C.c_int, [_vp, C.c_int64, _dp, _dp, C.c_double, _vp, _vp, _vp, _vp]),
     "asb_bench_sweep": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, _dp]),

@@ -30,6 +30,7 @@ struct BatchParams {
     long long state_stride, cov_stride;
     int n_seq, n_frames, t0, t1, max_lm, max_obs, as_written, p_in_smem;
     Noise nz;
+    unsigned long long* prof;   // 10 phase accumulators (clocks) of CTA 0, may be null
 };
 
 __device__ __forceinline__ int tri(int i) { return (i * (i + 1)) >> 1; }
@@ -39,7 +40,7 @@ __device__ __forceinline__ double psym(const double* P, int i, int j) {
 }
 
 template <int KIND, int CK, int NT>
-__global__ void __launch_bounds__(NT)
+__global__ void __launch_bounds__(NT, (NT <= 128 && KIND == 0) ? 4 : 1)
 k_batch(BatchParams p) {
     constexpr int D = Dims<KIND>::D, R = Dims<KIND>::R, W = CAM + D, NB = R;
     constexpr int MC = R * CK;           // max rows per chunk
@@ -66,6 +67,17 @@ k_batch(BatchParams p) {
     double* s_P = reinterpret_cast<double*>(
         (reinterpret_cast<uintptr_t>(s_misc + 4) + 15) & ~uintptr_t(15));  // packed, if it fits
 
+    // phase profile of CTA 0 (clock64 deltas accumulated per phase in registers), measurement aid
+    long long prof_t = clock64(), prof_acc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    const bool prof_on = p.prof && blockIdx.x == 0 && tid == 0;
+#define BPROF(slot)                                  \
+    do {                                             \
+        if (prof_on) {                               \
+            const long long now_ = clock64();        \
+            prof_acc[slot] += now_ - prof_t;         \
+            prof_t = now_;                           \
+        }                                            \
+    } while (0)
     for (int seq = blockIdx.x; seq < p.n_seq; seq += gridDim.x) {
         double* g_state = p.states + (long long)seq * p.state_stride;
         double* g_P = p.covs + (long long)seq * p.cov_stride;
@@ -118,6 +130,7 @@ k_batch(BatchParams p) {
                 s_misc[0] = cur;
             }
             __syncthreads();
+            BPROF(0);
             const int nlm1 = s_misc[0];
             if (s_misc[1] == ASB_ERR_CAPACITY) break;
             const int n1 = CAM + D * nlm1;
@@ -144,6 +157,7 @@ k_batch(BatchParams p) {
             }
             __syncthreads();
 
+            BPROF(1);
             // ---- update, CK markers at a time -----------------------------------------
             for (int c0 = 0; c0 < k; c0 += CK) {
                 const int kc = min(CK, k - c0);
@@ -169,30 +183,34 @@ k_batch(BatchParams p) {
                     for (int r = 0; r < R; ++r) s_nu[R * o + r] = lnu[r];
                 }
                 __syncthreads();
-                // G = H P  (mc x n)
-                for (int e = tid; e < kc * n; e += NT) {
-                    const int o = e / n, j = e - o * n;
-                    const double* blk = s_blk + o * R * W;
-                    const int li = CAM + D * s_idx[c0 + o];
-                    double acc[R];
+                BPROF(2);
+                // G = H P  (mc x n): one thread per state column; the 10 camera rows of P are
+                // read once per column, then D landmark rows per observation
+                for (int j = tid; j < n; j += NT) {
+                    double pc[CAM];
 #pragma unroll
-                    for (int r = 0; r < R; ++r) acc[r] = 0.0;
+                    for (int c = 0; c < CAM; ++c) pc[c] = psym(P, c, j);
+                    for (int o = 0; o < kc; ++o) {
+                        const double* blk = s_blk + o * R * W;
+                        const int li = CAM + D * s_idx[c0 + o];
+                        double pl[D], acc[R];
 #pragma unroll
-                    for (int c = 0; c < CAM; ++c) {
-                        const double pv = psym(P, c, j);
+                        for (int c = 0; c < D; ++c) pl[c] = psym(P, li + c, j);
 #pragma unroll
-                        for (int r = 0; r < R; ++r) acc[r] += blk[r * W + c] * pv;
+                        for (int r = 0; r < R; ++r) {
+                            double sv = 0.0;
+#pragma unroll
+                            for (int c = 0; c < CAM; ++c) sv += blk[r * W + c] * pc[c];
+#pragma unroll
+                            for (int c = 0; c < D; ++c) sv += blk[r * W + CAM + c] * pl[c];
+                            acc[r] = sv;
+                        }
+#pragma unroll
+                        for (int r = 0; r < R; ++r) s_G[(R * o + r) * npad + j] = acc[r];
                     }
-#pragma unroll
-                    for (int c = 0; c < D; ++c) {
-                        const double pv = psym(P, li + c, j);
-#pragma unroll
-                        for (int r = 0; r < R; ++r) acc[r] += blk[r * W + CAM + c] * pv;
-                    }
-#pragma unroll
-                    for (int r = 0; r < R; ++r) s_G[(R * o + r) * npad + j] = acc[r];
                 }
                 __syncthreads();
+                BPROF(3);
                 // S = G H^T + R (lower) with nu appended as row mc
                 for (int e = tid; e < (mc + 1) * mc; e += NT) {
                     const int a = e / mc, b = e - a * mc;
@@ -214,8 +232,43 @@ k_batch(BatchParams p) {
                     s_S[a * LDS_S + b] = s;
                 }
                 __syncthreads();
-                // blocked Cholesky, NB = rows per marker
+                BPROF(4);
                 bool bad = false;
+                if constexpr (MC + 1 <= 32) {
+                    // Cholesky of [S; nu^T] by ONE warp, lane i holding row i in registers; column j
+                    // of L is broadcast with shuffles (no shared-memory round trips, no CTA barrier
+                    // inside the factorisation)
+                    if (tid < 32) {
+                        const int i = tid;
+                        double a[MC], dv[MC];
+#pragma unroll
+                        for (int c = 0; c < MC; ++c)
+                            a[c] = (i <= mc && c < mc && (c <= i)) ? s_S[i * LDS_S + c] : 0.0;
+#pragma unroll
+                        for (int j = 0; j < MC; ++j) {
+                            if (j < mc) {
+                                const double pv = __shfl_sync(0xffffffffu, a[j], j);
+                                if (!(pv > 0.0) || !(pv < 1e300)) bad = true;
+                                const double rs = rsqrt(pv);
+                                dv[j] = rs;
+                                const double lij = a[j] * rs;
+                                a[j] = lij;
+#pragma unroll
+                                for (int c = j + 1; c < MC; ++c) {
+                                    const double lcj = __shfl_sync(0xffffffffu, lij, c);
+                                    a[c] -= lij * lcj;
+                                }
+                            }
+                        }
+#pragma unroll
+                        for (int c = 0; c < MC; ++c) {
+                            if (c < mc && c <= i && i <= mc) s_S[i * LDS_S + c] = a[c];
+                            if (i == 0 && c < mc) s_dinv[c] = dv[c];
+                        }
+                    }
+                    __syncthreads();
+                } else {
+                // blocked Cholesky, NB = rows per marker
                 for (int jb = 0; jb < mc; jb += NB) {
                     double dblk[NB][NB], dinv[NB];
 #pragma unroll
@@ -273,21 +326,33 @@ k_batch(BatchParams p) {
                     }
                     __syncthreads();
                 }
+                }
+                BPROF(5);
                 if (bad && tid == 0) s_misc[1] = ASB_ERR_NOT_SPD;
-                // V = L^-1 G (in place), delta += V^T y   (y = appended row of S)
+                // V = L^-1 G (in place), delta += V^T y   (y = appended row of S): one thread per
+                // column, the column in registers, forward substitution fully unrolled
                 for (int j = tid; j < n; j += NT) {
+                    double v[MC];
+#pragma unroll
+                    for (int a = 0; a < MC; ++a) v[a] = a < mc ? s_G[a * npad + j] : 0.0;
                     double dsum = 0.0;
-                    for (int a = 0; a < mc; ++a) {
-                        double v = s_G[a * npad + j];
-                        const double* la = s_S + a * LDS_S;
-                        for (int b = 0; b < a; ++b) v -= la[b] * s_G[b * npad + j];
-                        v *= s_dinv[a];
-                        s_G[a * npad + j] = v;
-                        dsum += v * s_S[mc * LDS_S + a];
+#pragma unroll
+                    for (int a = 0; a < MC; ++a) {
+                        if (a < mc) {
+                            const double* la = s_S + a * LDS_S;
+                            double t = v[a];
+#pragma unroll
+                            for (int b = 0; b < a; ++b) t -= la[b] * v[b];
+                            t *= s_dinv[a];
+                            v[a] = t;
+                            s_G[a * npad + j] = t;
+                            dsum += t * s_S[mc * LDS_S + a];
+                        }
                     }
                     s_delta[j] += dsum;
                 }
                 __syncthreads();
+                BPROF(6);
                 // P -= V^T V on the packed lower triangle, 4x4 register blocks
                 {
                     const int nb = (n + 3) >> 2;
@@ -330,6 +395,7 @@ k_batch(BatchParams p) {
                     }
                 }
                 __syncthreads();
+                BPROF(8);
             }  // chunks
 
             // ---- state update + quaternion reset --------------------------------------
@@ -337,6 +403,7 @@ k_batch(BatchParams p) {
             for (int l = tid; l < nlm; l += NT)
                 landmark_update<KIND>(s_state + CAM + D * l, s_delta + CAM + D * l);
             __syncthreads();
+            BPROF(9);
         }  // frames
 
         // ---- write back -----------------------------------------------------------------
@@ -350,6 +417,9 @@ k_batch(BatchParams p) {
         }
         __syncthreads();
     }
+    if (prof_on)
+        for (int i = 0; i < 10; ++i) p.prof[i] += (unsigned long long)prof_acc[i];
+#undef BPROF
 }
 
 // Constructor state of every sequence: state = pose0, P = init_cam * I10 (EKF:46-48), empty map.

@@ -24,6 +24,7 @@ struct asb_batch {
     double *d_states = nullptr, *d_covs = nullptr, *d_poses = nullptr, *d_dense = nullptr, *d_pose0 = nullptr;
     int *d_nlm = nullptr, *d_tab = nullptr, *d_status = nullptr, *d_ids = nullptr;
     long long* d_off = nullptr;
+    unsigned long long* d_prof = nullptr;
     int n_frames = 0;
     long long n_obs = 0;
     int sm_count = 0, smem_optin = 0;
@@ -61,6 +62,13 @@ template <int KIND, int CK, int NT>
 static int launch_batch(asb_batch* b, const BatchParams& p, size_t smem, int grid) {
     auto kern = k_batch<KIND, CK, NT>;
     ASB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ASB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    // persistent grid: exactly the CTAs that are co-resident (registers can bind before shared memory)
+    int occ = 0;
+    ASB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, NT, smem));
+    if (occ < 1) return fail(ASB_ERR_CAPACITY, "k_batch does not fit on an SM (%zu B shared memory)", smem);
+    grid = std::min(grid, b->sm_count * occ);
+    if (std::getenv("ASB_BATCH_VERBOSE")) fprintf(stderr, "k_batch<%d,%d,%d>: %d CTAs/SM, grid %d, smem %zu\n", KIND, CK, NT, occ, grid, smem);
     kern<<<grid, NT, smem, b->stream>>>(p);
     ASB_CUDA(cudaGetLastError());
     return ASB_OK;
@@ -118,6 +126,8 @@ int asb_batch_create(int kind, int quat_mode, const double pose0[10], const asb_
     ASB_CUDA(dmalloc(&b->d_states, (size_t)n_seq * b->state_stride));
     ASB_CUDA(dmalloc(&b->d_covs, (size_t)n_seq * b->cov_stride));
     ASB_CUDA(dmalloc(&b->d_nlm, (size_t)n_seq));
+    ASB_CUDA(dmalloc(&b->d_prof, 16));
+    ASB_CUDA(cudaMemset(b->d_prof, 0, 16 * sizeof(unsigned long long)));
     ASB_CUDA(dmalloc(&b->d_tab, (size_t)n_seq * max_landmarks));
     ASB_CUDA(dmalloc(&b->d_status, (size_t)n_seq));
     ASB_CUDA(dmalloc(&b->d_dense, (size_t)b->ncap * b->ncap));
@@ -201,6 +211,7 @@ int asb_batch_run(asb_batch* b, int t0, int t1) {
     p.max_lm = b->max_lm; p.max_obs = b->max_obs;
     p.as_written = (b->kind == ASB_KIND_EKF && b->quat_mode == ASB_QUAT_AS_WRITTEN) ? 1 : 0;
     p.nz = b->nz;
+    p.prof = b->d_prof;
     const size_t base = batch_smem_base(b->D, b->R, b->ck, b->max_lm, b->max_obs);
     const size_t pbytes = (size_t)b->cov_stride * sizeof(double);
     p.p_in_smem = (base + pbytes <= (size_t)b->smem_optin) ? 1 : 0;
@@ -218,6 +229,17 @@ int asb_batch_run(asb_batch* b, int t0, int t1) {
     if (b->kind == ASB_KIND_EKF) { ASB_DISPATCH(0) }
     ASB_DISPATCH(1)
 #undef ASB_DISPATCH
+}
+
+int asb_batch_profile(asb_batch* b, double clocks[10]) {
+    ASB_CHECK_BATCH(b);
+    if (!clocks) return fail(ASB_ERR_BAD_ARG, "clocks is NULL");
+    unsigned long long t[16];
+    ASB_CUDA(cudaStreamSynchronize(b->stream));
+    ASB_CUDA(cudaMemcpy(t, b->d_prof, sizeof t, cudaMemcpyDeviceToHost));
+    ASB_CUDA(cudaMemset(b->d_prof, 0, sizeof t));
+    for (int i = 0; i < 10; ++i) clocks[i] = (double)t[i];
+    return ASB_OK;
 }
 
 int asb_batch_get_dims(asb_batch* b, int seq, int* n_landmarks, int* n_state) {

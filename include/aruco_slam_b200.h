@@ -152,6 +152,10 @@ ASB_API int asb_batch_get_cameras(asb_batch* b, double* out, int32_t* status_or_
 ASB_API int asb_batch_device_views(asb_batch* b, void** d_states, void** d_covs, int* state_stride,
                            int* cov_ld);
 
+/* Clocks CTA 0 spent per phase since the last call (association, augment+predict, model, G, S,
+ * Cholesky, solve, -, P update, apply), measurement aid. */
+ASB_API int asb_batch_profile(asb_batch* b, double clocks[10]);
+
 /* ---- square-marker pose: estimate_pose_of_markers (BASE:92-171), i.e.
  *      cv2.solvePnP(marker_points, c, K, dist, flags=SOLVEPNP_IPPE_SQUARE) per marker ----
  * corners (n,4,2) float32 pixel corners in the order BASE:112-120 expects; camera_matrix
