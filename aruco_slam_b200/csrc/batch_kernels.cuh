@@ -33,14 +33,27 @@ struct BatchParams {
     unsigned long long* prof;   // 10 phase accumulators (clocks) of CTA 0, may be null
 };
 
-__device__ __forceinline__ int tri(int i) { return (i * (i + 1)) >> 1; }
+__host__ __device__ __forceinline__ int tri(int i) { return (i * (i + 1)) >> 1; }
+
+// Shared-memory layout of the covariance ("tile-blocked"): the lower triangle as 8 x 8 tiles,
+// tile (I, J <= I) at tile index tri(I) + J, 64 doubles; diagonal tiles are kept full (both
+// halves).  Inside a tile the 32 16-byte chunks (row r, column pair q -> chunk 4 r + q) are
+// XOR-swizzled with the tile index, so threads that each own a different tile hit different
+// banks with the same logical chunk.  HBM keeps the packed lower triangle.
+__host__ __device__ __forceinline__ int tiled_doubles(int ncap) { return tri((ncap + 7) >> 3) * 64; }
+// row stride of the panels: whole 8-column tiles
+__host__ __device__ __forceinline__ int batch_npad(int ncap) { return ((ncap + 7) & ~7) + 4; }
+__device__ __forceinline__ int tchunk(int tile, int chunk) { return (tile << 6) + (((chunk ^ tile) & 31) << 1); }
+__device__ __forceinline__ int tidx(int i, int j) {   // i >= j
+    return tchunk(tri(i >> 3) + (j >> 3), ((i & 7) << 2) + ((j & 7) >> 1)) + (j & 1);
+}
 // symmetric access into the packed lower triangle
 __device__ __forceinline__ double psym(const double* P, int i, int j) {
     return j <= i ? P[tri(i) + j] : P[tri(j) + i];
 }
 
 template <int KIND, int CK, int NT>
-__global__ void __launch_bounds__(NT, (NT <= 128 && KIND == 0) ? 4 : 1)
+__global__ void __launch_bounds__(NT, (NT <= 128 && KIND == 0) ? 3 : 1)
 k_batch(BatchParams p) {
     constexpr int D = Dims<KIND>::D, R = Dims<KIND>::R, W = CAM + D, NB = R;
     constexpr int MC = R * CK;           // max rows per chunk
@@ -48,7 +61,7 @@ k_batch(BatchParams p) {
     extern __shared__ __align__(16) unsigned char smraw[];
     const int tid = threadIdx.x;
     const int ncap = CAM + D * p.max_lm;
-    const int npad = (ncap + 3) & ~3;
+    const int npad = batch_npad(ncap);
 
     // ---- shared memory carve-up -----------------------------------------------------
     double* s_state = reinterpret_cast<double*>(smraw);       // ncap
@@ -83,12 +96,29 @@ k_batch(BatchParams p) {
         double* g_P = p.covs + (long long)seq * p.cov_stride;
         int* g_tab = p.lm_ids + (long long)seq * p.max_lm;
         double* P = p.p_in_smem ? s_P : g_P;
+        const bool tiled = p.p_in_smem != 0;
+        auto pget = [&](int i, int j) -> double {   // symmetric read
+            const int a = max(i, j), b = min(i, j);
+            return P[tiled ? tidx(a, b) : tri(a) + b];
+        };
+        auto pset = [&](int i, int j, double v) {   // i >= j; diagonal tiles hold both halves
+            if (tiled) {
+                P[tidx(i, j)] = v;
+                if ((i >> 3) == (j >> 3)) P[tchunk(tri(i >> 3) + (j >> 3), ((j & 7) << 2) + ((i & 7) >> 1)) + (i & 1)] = v;
+            } else {
+                P[tri(i) + j] = v;
+            }
+        };
         int nlm = p.nlm[seq];
         int n = CAM + D * nlm;
         for (int i = tid; i < n; i += NT) s_state[i] = g_state[i];
         for (int i = tid; i < nlm; i += NT) s_tab[i] = g_tab[i];
-        if (p.p_in_smem)
-            for (int i = tid; i < tri(n); i += NT) s_P[i] = g_P[i];
+        if (p.p_in_smem) {
+            for (int e = tid; e < tiled_doubles(ncap); e += NT) s_P[e] = 0.0;
+            __syncthreads();
+            for (int i = tid; i < n; i += NT)
+                for (int j = 0; j <= i; ++j) pset(i, j, g_P[tri(i) + j]);
+        }
         if (tid == 0) s_misc[1] = 0;
         __syncthreads();
 
@@ -143,16 +173,20 @@ k_batch(BatchParams p) {
 #pragma unroll
                     for (int c = 0; c < D; ++c) s_state[CAM + D * s_idx[o] + c] = lm[c];
                 }
-                for (int e = tri(n) + tid; e < tri(n1); e += NT) P[e] = 0.0;
-                __syncthreads();
-                for (int i = n + tid; i < n1; i += NT) P[tri(i) + i] = p.nz.init_lm;
+                for (int e = tri(n) + tid; e < tri(n1); e += NT) {   // new rows n..n1-1, all columns <= row
+                    int i = (int)((sqrtf(8.0f * e + 1.0f) - 1.0f) * 0.5f);
+                    while (tri(i + 1) <= e) ++i;
+                    while (tri(i) > e) --i;
+                    const int j = e - tri(i);
+                    pset(i, j, i == j ? p.nz.init_lm : 0.0);
+                }
                 __syncthreads();
             }
             nlm = nlm1;
             n = n1;
             // ---- predict: P += diag(Q); delta = 0 -------------------------------------
             for (int i = tid; i < n; i += NT) {
-                P[tri(i) + i] += process_noise(p.nz, i);
+                pset(i, i, pget(i, i) + process_noise(p.nz, i));
                 s_delta[i] = 0.0;
             }
             __syncthreads();
@@ -189,13 +223,13 @@ k_batch(BatchParams p) {
                 for (int j = tid; j < n; j += NT) {
                     double pc[CAM];
 #pragma unroll
-                    for (int c = 0; c < CAM; ++c) pc[c] = psym(P, c, j);
+                    for (int c = 0; c < CAM; ++c) pc[c] = pget(c, j);
                     for (int o = 0; o < kc; ++o) {
                         const double* blk = s_blk + o * R * W;
                         const int li = CAM + D * s_idx[c0 + o];
                         double pl[D], acc[R];
 #pragma unroll
-                        for (int c = 0; c < D; ++c) pl[c] = psym(P, li + c, j);
+                        for (int c = 0; c < D; ++c) pl[c] = pget(li + c, j);
 #pragma unroll
                         for (int r = 0; r < R; ++r) {
                             double sv = 0.0;
@@ -353,8 +387,51 @@ k_batch(BatchParams p) {
                 }
                 __syncthreads();
                 BPROF(6);
-                // P -= V^T V on the packed lower triangle, 4x4 register blocks
-                {
+                // P -= V^T V.  Shared-memory covariance: one thread per half 8 x 8 tile (4 rows x 8
+                // columns in registers; 4 + 8 panel values per rank-1 term feed 32 FMAs — the 4 x 4
+                // blocks of the HBM path re-read V twice as often and were shared-memory-bound).
+                // [mma.sync m8n8k4 was tried: one warp issues a DMMA only every ~64 clocks, so
+                // with 4 warps per CTA it lost to the FMA pipe.]
+                if (tiled) {
+                    const int nt8 = (n + 7) >> 3;
+                    // columns n..8 nt8 of the panel must be zero
+                    for (int e = tid; e < mc * (8 * nt8 - n); e += NT) s_G[(e / (8 * nt8 - n)) * npad + n + e % (8 * nt8 - n)] = 0.0;
+                    __syncthreads();
+                    for (int task = tid; task < 2 * tri(nt8); task += NT) {
+                        const int tile = task >> 1, h = task & 1;
+                        int I = (int)((sqrtf(8.0f * tile + 1.0f) - 1.0f) * 0.5f);
+                        while (tri(I + 1) <= tile) ++I;
+                        while (tri(I) > tile) --I;
+                        const int J = tile - tri(I);
+                        double acc[4][8];
+#pragma unroll
+                        for (int r = 0; r < 4; ++r)
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                const double2 v = *reinterpret_cast<const double2*>(P + tchunk(tile, 4 * (4 * h + r) + q));
+                                acc[r][2 * q] = v.x; acc[r][2 * q + 1] = v.y;
+                            }
+                        const double* xb = s_G + 8 * I + 4 * h;
+                        const double* yb = s_G + 8 * J;
+#pragma unroll 2
+                        for (int a = 0; a < mc; ++a) {
+                            const double2* xp = reinterpret_cast<const double2*>(xb + a * npad);
+                            const double2* yp = reinterpret_cast<const double2*>(yb + a * npad);
+                            const double2 x0 = xp[0], x1 = xp[1], y0 = yp[0], y1 = yp[1], y2 = yp[2], y3 = yp[3];
+                            const double x[4] = {x0.x, x0.y, x1.x, x1.y};
+                            const double y[8] = {y0.x, y0.y, y1.x, y1.y, y2.x, y2.y, y3.x, y3.y};
+#pragma unroll
+                            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                                for (int c = 0; c < 8; ++c) acc[r][c] -= x[r] * y[c];
+                        }
+#pragma unroll
+                        for (int r = 0; r < 4; ++r)
+#pragma unroll
+                            for (int q = 0; q < 4; ++q)
+                                *reinterpret_cast<double2*>(P + tchunk(tile, 4 * (4 * h + r) + q)) = make_double2(acc[r][2 * q], acc[r][2 * q + 1]);
+                    }
+                } else {
                     const int nb = (n + 3) >> 2;
                     const int nblk = (nb * (nb + 1)) >> 1;
                     for (int blk_id = tid; blk_id < nblk; blk_id += NT) {
@@ -410,7 +487,8 @@ k_batch(BatchParams p) {
         for (int i = tid; i < n; i += NT) g_state[i] = s_state[i];
         for (int i = tid; i < nlm; i += NT) g_tab[i] = s_tab[i];
         if (p.p_in_smem)
-            for (int i = tid; i < tri(n); i += NT) g_P[i] = s_P[i];
+            for (int i = tid; i < n; i += NT)
+                for (int j = 0; j <= i; ++j) g_P[tri(i) + j] = s_P[tidx(i, j)];
         if (tid == 0) {
             p.nlm[seq] = nlm;
             if (s_misc[1] != 0) p.status[seq] = s_misc[1];

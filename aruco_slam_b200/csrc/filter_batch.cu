@@ -51,7 +51,7 @@ static cudaError_t dmalloc(T** p, size_t count) {
 // shared-memory bytes of k_batch excluding the packed covariance (same carve-up as the kernel)
 static size_t batch_smem_base(int D, int R, int CK, int max_lm, int max_obs) {
     const int W = CAM + D, MC = R * CK, LDS_S = (MC + 1) | 1;
-    const int ncap = CAM + D * max_lm, npad = (ncap + 3) & ~3;
+    const int ncap = CAM + D * max_lm, npad = batch_npad(ncap);
     size_t dbl = (size_t)npad * 2 + (size_t)MC * npad + (size_t)CK * R * W + ((MC + 3) & ~3) +
                  (size_t)(MC + 1) * LDS_S + ((MC + 3) & ~3) + (size_t)max_obs * 6;
     size_t ints = (size_t)max_obs * 3 + max_lm + 4;
@@ -213,7 +213,7 @@ int asb_batch_run(asb_batch* b, int t0, int t1) {
     p.nz = b->nz;
     p.prof = b->d_prof;
     const size_t base = batch_smem_base(b->D, b->R, b->ck, b->max_lm, b->max_obs);
-    const size_t pbytes = (size_t)b->cov_stride * sizeof(double);
+    const size_t pbytes = (size_t)tiled_doubles(b->ncap) * sizeof(double);   // tile-blocked copy (batch_kernels.cuh)
     p.p_in_smem = (base + pbytes <= (size_t)b->smem_optin) ? 1 : 0;
     const size_t smem = base + (p.p_in_smem ? pbytes : 0);
     if (smem > (size_t)b->smem_optin)
