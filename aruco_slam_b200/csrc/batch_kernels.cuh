@@ -38,12 +38,21 @@ __host__ __device__ __forceinline__ int tri(int i) { return (i * (i + 1)) >> 1; 
 // Shared-memory layout of the covariance ("tile-blocked"): the lower triangle as 8 x 8 tiles,
 // tile (I, J <= I) at tile index tri(I) + J, 64 doubles; diagonal tiles are kept full (both
 // halves).  Inside a tile the 32 16-byte chunks (row r, column pair q -> chunk 4 r + q) are
-// XOR-swizzled with the tile index, so threads that each own a different tile hit different
-// banks with the same logical chunk.  HBM keeps the packed lower triangle.
+// XOR-swizzled with the tile index, so threads that each own a different (half) tile hit
+// different banks with the same logical chunk.  HBM keeps the packed lower triangle.
+// The panels (G, then V) keep every 8-column group in GW = 10 doubles: four consecutive groups
+// then start in four different 16-byte banks, which is what the 128-bit loads of the rank-m
+// update need (with dense rows groups J and J + 2 collide).
 __host__ __device__ __forceinline__ int tiled_doubles(int ncap) { return tri((ncap + 7) >> 3) * 64; }
 // row stride of the panels: whole 8-column tiles
-__host__ __device__ __forceinline__ int batch_npad(int ncap) { return ((ncap + 7) & ~7) + 4; }
-__device__ __forceinline__ int tchunk(int tile, int chunk) { return (tile << 6) + (((chunk ^ tile) & 31) << 1); }
+constexpr int GW = 10;
+__host__ __device__ __forceinline__ int batch_npad(int ncap) { return GW * ((ncap + 7) >> 3) + 2; }
+__host__ __device__ __forceinline__ int gcol(int j) { return j + ((j >> 3) << 1); }   // column j inside a panel row
+__device__ __forceinline__ int tchunk(int tile, int chunk) {
+    // low bits mixed with 2 tile + (chunk >= 16): the 8 lanes of a quarter-warp — 4 tiles x 2 half tiles —
+    // land in 8 different 16-byte banks (bit 4 of the chunk is preserved, so this is a bijection)
+    return (tile << 6) + ((chunk ^ ((2 * tile + (chunk >> 4)) & 15)) << 1);
+}
 __device__ __forceinline__ int tidx(int i, int j) {   // i >= j
     return tchunk(tri(i >> 3) + (j >> 3), ((i & 7) << 2) + ((j & 7) >> 1)) + (j & 1);
 }
@@ -240,7 +249,7 @@ k_batch(BatchParams p) {
                             acc[r] = sv;
                         }
 #pragma unroll
-                        for (int r = 0; r < R; ++r) s_G[(R * o + r) * npad + j] = acc[r];
+                        for (int r = 0; r < R; ++r) s_G[(R * o + r) * npad + gcol(j)] = acc[r];
                     }
                 }
                 __syncthreads();
@@ -257,9 +266,9 @@ k_batch(BatchParams p) {
                         const int li = CAM + D * s_idx[c0 + o2];
                         s = (a == b) ? p.nz.r : 0.0;
 #pragma unroll
-                        for (int c = 0; c < CAM; ++c) s += g[c] * hb[c];
+                        for (int c = 0; c < CAM; ++c) s += g[gcol(c)] * hb[c];
 #pragma unroll
-                        for (int c = 0; c < D; ++c) s += g[li + c] * hb[CAM + c];
+                        for (int c = 0; c < D; ++c) s += g[gcol(li + c)] * hb[CAM + c];
                     } else {
                         s = s_nu[b];
                     }
@@ -368,7 +377,7 @@ k_batch(BatchParams p) {
                 for (int j = tid; j < n; j += NT) {
                     double v[MC];
 #pragma unroll
-                    for (int a = 0; a < MC; ++a) v[a] = a < mc ? s_G[a * npad + j] : 0.0;
+                    for (int a = 0; a < MC; ++a) v[a] = a < mc ? s_G[a * npad + gcol(j)] : 0.0;
                     double dsum = 0.0;
 #pragma unroll
                     for (int a = 0; a < MC; ++a) {
@@ -379,7 +388,7 @@ k_batch(BatchParams p) {
                             for (int b = 0; b < a; ++b) t -= la[b] * v[b];
                             t *= s_dinv[a];
                             v[a] = t;
-                            s_G[a * npad + j] = t;
+                            s_G[a * npad + gcol(j)] = t;
                             dsum += t * s_S[mc * LDS_S + a];
                         }
                     }
@@ -395,7 +404,7 @@ k_batch(BatchParams p) {
                 if (tiled) {
                     const int nt8 = (n + 7) >> 3;
                     // columns n..8 nt8 of the panel must be zero
-                    for (int e = tid; e < mc * (8 * nt8 - n); e += NT) s_G[(e / (8 * nt8 - n)) * npad + n + e % (8 * nt8 - n)] = 0.0;
+                    for (int e = tid; e < mc * (8 * nt8 - n); e += NT) s_G[(e / (8 * nt8 - n)) * npad + gcol(n + e % (8 * nt8 - n))] = 0.0;
                     __syncthreads();
                     for (int task = tid; task < 2 * tri(nt8); task += NT) {
                         const int tile = task >> 1, h = task & 1;
@@ -411,8 +420,8 @@ k_batch(BatchParams p) {
                                 const double2 v = *reinterpret_cast<const double2*>(P + tchunk(tile, 4 * (4 * h + r) + q));
                                 acc[r][2 * q] = v.x; acc[r][2 * q + 1] = v.y;
                             }
-                        const double* xb = s_G + 8 * I + 4 * h;
-                        const double* yb = s_G + 8 * J;
+                        const double* xb = s_G + GW * I + 4 * h;
+                        const double* yb = s_G + GW * J;
 #pragma unroll 2
                         for (int a = 0; a < mc; ++a) {
                             const double2* xp = reinterpret_cast<const double2*>(xb + a * npad);
@@ -447,10 +456,10 @@ k_batch(BatchParams p) {
                             for (int c = 0; c < 4; ++c) acc[r][c] = 0.0;
                         for (int a = 0; a < mc; ++a) {
                             const double* g = s_G + a * npad;
-                            const double2 xa = *reinterpret_cast<const double2*>(g + i0);
-                            const double2 xb = *reinterpret_cast<const double2*>(g + i0 + 2);
-                            const double2 ya = *reinterpret_cast<const double2*>(g + j0);
-                            const double2 yb = *reinterpret_cast<const double2*>(g + j0 + 2);
+                            const double2 xa = *reinterpret_cast<const double2*>(g + gcol(i0));
+                            const double2 xb = *reinterpret_cast<const double2*>(g + gcol(i0) + 2);
+                            const double2 ya = *reinterpret_cast<const double2*>(g + gcol(j0));
+                            const double2 yb = *reinterpret_cast<const double2*>(g + gcol(j0) + 2);
                             const double xs[4] = {xa.x, xa.y, xb.x, xb.y};
                             const double ys[4] = {ya.x, ya.y, yb.x, yb.y};
 #pragma unroll
