@@ -87,6 +87,8 @@ SIGNATURES = {
     "asb_ippe_square_device": (C.c_int, [_vp, C.c_int64, _dp, _dp, C.c_double, _vp, _vp, _vp, _vp]),
     "asb_bench_sweep": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, _dp]),
     "asb_front_profile": (C.c_int, [_vp, _dp]),
+    "asb_timeline": (C.c_int, [_vp, _dp]),
+    "asb_cta_profile": (C.c_int, [_vp, _dp, C.c_int]),
     "asb_latency_probe": (C.c_int, [C.c_int, _dp]),
     "asb_stream_bandwidth": (C.c_int, [C.c_int, C.c_int64, C.c_int, _dp]),
     "asb_tilepattern_bandwidth": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, _dp]),

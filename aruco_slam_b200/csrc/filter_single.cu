@@ -11,6 +11,7 @@
 
 #include "common.cuh"
 #include "front.cuh"
+#include "pipe.cuh"
 #include "single_kernels.cuh"
 
 using namespace asb;
@@ -53,6 +54,18 @@ struct asb_filter {
     std::vector<FrameRec> frames;
     int next_frame = 0;
     int sweep_grid = 0, smem_optin = 0, force_big = 0, sweep_config = -1, front_dbg = 0;
+    // pipelined engine (pipe.cuh): covariance ping-pong pair, side stream for k_f1
+    int pipeline = 1;
+    double *d_P2 = nullptr, *d_At = nullptr, *d_y = nullptr, *d_Vt = nullptr;
+    int* d_T = nullptr;
+    unsigned int* d_counter = nullptr;
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_ready = nullptr, ev_f1 = nullptr;
+    bool lazy = false;         // d_P2 holds the input of the sweep launched last, d_Vr its panel
+    bool side_waited = false;
+    int prof_slot = 0, spare_ctas = 2;
+    unsigned long long* d_ctaprof = nullptr;   // 3 x 1024: per-CTA start / end / smid of the last sweep         // timeline of the last two updates (asb_timeline)
+    int prev_m4 = 0, prev_add_q = 0;
 
     int n_state() const { return CAM + D * nlm; }
 };
@@ -79,8 +92,11 @@ static cudaError_t dmalloc(T** p, size_t count) {
 // ---------------------------------------------------------------------------------------
 // persistent sweep: 2 CTAs / SM (64 x 64 tiles) while both fit in shared memory, else
 // 1 CTA / SM (128 x 64 tiles)
-static void launch_sweep(asb_filter* f, int n1, int m4, int dbg, const SweepExtra& ex, int config = -1) {
+static void launch_sweep(asb_filter* f, int n1, int m4, int dbg, const SweepExtra& ex, int config = -1,
+                         const double* pin = nullptr, double* pout = nullptr, int spare_ctas = 0) {
     if (config < 0) config = f->sweep_config;
+    if (!pin) pin = f->d_P;
+    if (!pout) pout = f->d_P;
     if (config == 2) {  // warp-specialised variant: kept for experiments (slower than the dual-CTA kernel)
         const int ntiles = ws::num_tiles(n1);
         const int grid = std::min(ntiles, f->sweep_grid);
@@ -91,15 +107,24 @@ static void launch_sweep(asb_filter* f, int n1, int m4, int dbg, const SweepExtr
                                  : config == 1;
     if (dual) {
         const int ntiles = SweepDual::num_tiles(n1);
-        const int grid = std::min(ntiles, 2 * f->sweep_grid);
+        const int grid = std::min(ntiles, 2 * f->sweep_grid - spare_ctas);
         k_sweep<SweepDual><<<grid, SweepDual::THREADS, SweepDual::smem_bytes(m4), f->stream>>>(
-            f->d_P, f->ld, f->d_Vr, f->d_Vc, m4, ntiles, dbg, ex);
+            pin, pout, f->ld, f->d_Vr, f->d_Vc, m4, ntiles, dbg, ex);
     } else {
         const int ntiles = SweepBig::num_tiles(n1);
         const int grid = std::min(ntiles, f->sweep_grid);
         k_sweep<SweepBig><<<grid, SweepBig::THREADS, SweepBig::smem_bytes(m4), f->stream>>>(
-            f->d_P, f->ld, f->d_Vr, f->d_Vc, m4, ntiles, dbg, ex);
+            pin, pout, f->ld, f->d_Vr, f->d_Vc, m4, ntiles, dbg, ex);
     }
+}
+
+// Side stream waits until the state, dx and panel of the previous update are final (k_f2 done);
+// it does NOT wait for the sweep launched after that k_f2.
+static void pipe_wait(asb_filter* f) {
+    if (f->side_waited) return;
+    if (!f->lazy) cudaEventRecord(f->ev_ready, f->stream);   // everything enqueued so far
+    cudaStreamWaitEvent(f->side, f->ev_ready, 0);
+    f->side_waited = true;
 }
 
 template <int KIND>
@@ -108,14 +133,71 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
     constexpr int R = Dims<KIND>::R, W = CAM + Dims<KIND>::D;
     cudaStream_t st = f->stream;
     const int ld = f->ld;
-    if (!do_update || k == 0) {
+    if (do_update && k > 0 && f->pipeline) {
+        // pipelined update (pipe.cuh): per chunk k_f1 on the side stream, k_f2 + k_sweep on the main one
+        int cur = 0;
+        for (int c0 = 0; c0 < k; c0 += f->kc_max) {
+            const int kc = std::min(f->kc_max, k - c0);
+            const int m4 = round_up(R * kc, 4);
+            const bool first = c0 == 0, last = c0 + kc >= k;
+            pipe_wait(f);
+            f->side_waited = false;
+            F1Args a;
+            a.state = f->d_state; a.P = f->lazy ? f->d_P2 : f->d_P; a.ld = ld;
+            a.n0 = first ? n0 : n1; a.n1 = n1; a.nz = f->nz;
+            a.idx = idx + c0; a.poses = pose + 6 * (size_t)c0; a.isnew = isnew ? isnew + c0 : nullptr;
+            a.kc = kc; a.m4 = m4;
+            a.first_chunk = first ? 1 : 0;
+            a.add_q = (first && do_predict) ? 1 : 0;
+            a.use_delta = first ? 0 : 1;
+            a.dx_in = f->d_dx[cur];
+            a.lazy = f->lazy ? 1 : 0; a.Vp = f->d_Vt; a.m4p = f->prev_m4; a.lazy_q = f->prev_add_q;
+            a.At = f->d_At; a.y = f->d_y; a.T = f->d_T;
+            a.blocks_out = f->d_blocks + (size_t)c0 * R * W; a.nu_out = f->d_nu + (size_t)R * c0;
+            a.status = f->d_status;
+            a.dbg = f->front_dbg;
+            unsigned long long* prof = f->d_prof + 16 * f->prof_slot;
+            f->prof_slot ^= 1;
+            a.prof = prof;
+            k_f1<KIND><<<1, FRONT_THREADS, F1Smem<KIND>::bytes(kc, m4), f->side>>>(a);
+            cudaEventRecord(f->ev_f1, f->side);
+            cudaStreamWaitEvent(st, f->ev_f1, 0);
+            F2Args b;
+            b.state = f->d_state; b.P = f->d_P; b.ld = ld; b.n0 = a.n0; b.n1 = n1; b.nz = f->nz;
+            b.kc = kc; b.m4 = m4; b.first_chunk = a.first_chunk; b.add_q = a.add_q; b.use_delta = a.use_delta;
+            b.At = f->d_At; b.y = f->d_y; b.T = f->d_T;
+            b.dx_in = f->d_dx[cur]; b.dx_out = f->d_dx[cur ^ 1];
+            b.Vr = f->d_Vr; b.Vc = f->d_Vc; b.Vt = f->d_Vt;
+            b.apply_kind = last ? KIND : -1;
+            b.as_written = (KIND == 0 && f->quat_mode == ASB_QUAT_AS_WRITTEN) ? 1 : 0;
+            b.nlm = (n1 - CAM) / Dims<KIND>::D;
+            b.counter = f->d_counter;
+            b.prof = prof + 8;
+            const int nblk = 2 * ((n1 + 127) / 128);  // whole 128-row sweep tiles are covered
+            k_f2<KIND><<<nblk, F2_THREADS, F2Smem<KIND>::bytes(kc, m4), st>>>(b);
+            cudaEventRecord(f->ev_ready, st);
+            cur ^= 1;
+            SweepExtra ex{};
+            ex.n = n1; ex.add_q = a.add_q; ex.nz = f->nz;
+            ex.apply_kind = -1;
+            ex.prof = prof + 12;
+            ex.cta_prof = f->d_ctaprof;
+            // the sweep leaves room for k_f1 of the next update: two CTAs fewer than fill the GPU
+            launch_sweep(f, n1, m4, 2 << 4, ex, -1, f->d_P, f->d_P2, f->spare_ctas);
+            std::swap(f->d_P, f->d_P2);
+            f->lazy = true; f->prev_m4 = m4; f->prev_add_q = a.add_q;
+        }
+        f->dx_last = f->d_dx[cur];
+    } else if (!do_update || k == 0) {
+        f->lazy = false;
         // predict() / add_marker() on their own: diagonal add, covariance growth, new states
         long long work = (long long)n0 + (long long)(n1 - n0) * (n1 + n0);
         int grid = (int)std::min<long long>(1 + work / 1024, 592);
         k_prep<KIND><<<grid, 256, 0, st>>>(f->d_state, f->d_P, ld, n0, n1, f->nz, idx, pose, isnew, k,
                                            do_predict ? 1 : 0);
     } else {
-        // update: two launches per chunk of <= kc_max markers (k_front, k_sweep)
+        // unpipelined update (ASB_PIPELINE=0): two launches per chunk of <= kc_max markers (k_front, k_sweep)
+        f->lazy = false;
         int cur = 0;
         for (int c0 = 0; c0 < k; c0 += f->kc_max) {
             const int kc = std::min(f->kc_max, k - c0);
@@ -138,7 +220,7 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
             const int nblk = 2 * ((n1 + 127) / 128);  // whole 128-row sweep tiles are covered
             k_front<KIND><<<nblk, FRONT_THREADS, FrontSmem<KIND>::bytes(kc, m4), st>>>(a);
             cur ^= 1;
-            SweepExtra ex;
+            SweepExtra ex{};
             ex.n = n1; ex.add_q = a.add_q; ex.nz = f->nz;
             ex.apply_kind = last ? KIND : -1;
             ex.as_written = (KIND == 0 && f->quat_mode == ASB_QUAT_AS_WRITTEN) ? 1 : 0;
@@ -161,7 +243,7 @@ static int launch_frame_dyn(asb_filter* f, const int* idx, const double* pose, c
 // Stage k observations into the next ring slot and copy them to the device (async).
 static int stage(asb_filter* f, const std::vector<int>& idx, const double* poses,
                  const std::vector<unsigned char>& isnew, int k, int** d_idx, double** d_pose,
-                 unsigned char** d_new) {
+                 unsigned char** d_new, cudaStream_t st) {
     const int s = f->slot;
     f->slot = (f->slot + 1) % N_SLOTS;
     ASB_CUDA(cudaEventSynchronize(f->slot_ev[s]));
@@ -169,11 +251,11 @@ static int stage(asb_filter* f, const std::vector<int>& idx, const double* poses
     std::memcpy(f->h_idx + o, idx.data(), k * sizeof(int));
     std::memcpy(f->h_pose + 6 * o, poses, (size_t)k * 6 * sizeof(double));
     std::memcpy(f->h_new + o, isnew.data(), k);
-    ASB_CUDA(cudaMemcpyAsync(f->d_idx + o, f->h_idx + o, k * sizeof(int), cudaMemcpyHostToDevice, f->stream));
+    ASB_CUDA(cudaMemcpyAsync(f->d_idx + o, f->h_idx + o, k * sizeof(int), cudaMemcpyHostToDevice, st));
     ASB_CUDA(cudaMemcpyAsync(f->d_pose + 6 * o, f->h_pose + 6 * o, (size_t)k * 6 * sizeof(double),
-                             cudaMemcpyHostToDevice, f->stream));
-    ASB_CUDA(cudaMemcpyAsync(f->d_new + o, f->h_new + o, k, cudaMemcpyHostToDevice, f->stream));
-    ASB_CUDA(cudaEventRecord(f->slot_ev[s], f->stream));
+                             cudaMemcpyHostToDevice, st));
+    ASB_CUDA(cudaMemcpyAsync(f->d_new + o, f->h_new + o, k, cudaMemcpyHostToDevice, st));
+    ASB_CUDA(cudaEventRecord(f->slot_ev[s], st));
     *d_idx = f->d_idx + o;
     *d_pose = f->d_pose + 6 * o;
     *d_new = f->d_new + o;
@@ -230,11 +312,32 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
     if (const char* e = std::getenv("ASB_SWEEP_BIG")) f->force_big = std::atoi(e);
     if (const char* e = std::getenv("ASB_FRONT_DBG")) f->front_dbg = std::atoi(e);  // experiments (front.cuh)
     if (const char* e = std::getenv("ASB_SWEEP_CONFIG")) f->sweep_config = std::atoi(e);  // experiments: 0 / 1 / 2
+    if (const char* e = std::getenv("ASB_PIPELINE")) f->pipeline = std::atoi(e);          // 0: k_front + in-place sweep
     ASB_CUDA(cudaStreamCreateWithFlags(&f->own_stream, cudaStreamNonBlocking));
     f->stream = f->own_stream;
     const size_t ld = f->ld;
     ASB_CUDA(dmalloc(&f->d_state, ld));
     ASB_CUDA(dmalloc(&f->d_P, ld * ld));
+    if (f->pipeline) {
+        ASB_CUDA(dmalloc(&f->d_P2, ld * ld));
+        ASB_CUDA(cudaMemsetAsync(f->d_P2, 0, ld * ld * sizeof(double), f->stream));
+        ASB_CUDA(cudaStreamCreateWithFlags(&f->side, cudaStreamNonBlocking));
+        ASB_CUDA(cudaEventCreateWithFlags(&f->ev_ready, cudaEventDisableTiming));
+        ASB_CUDA(cudaEventCreateWithFlags(&f->ev_f1, cudaEventDisableTiming));
+        const size_t nt_max = CAM + (size_t)f->D * f->kc_max;
+        ASB_CUDA(dmalloc(&f->d_At, nt_max * M_MAX));
+        ASB_CUDA(dmalloc(&f->d_y, (size_t)M_MAX));
+        ASB_CUDA(dmalloc(&f->d_Vt, ld * F1_LDT));
+        ASB_CUDA(cudaMemsetAsync(f->d_Vt, 0, ld * F1_LDT * sizeof(double), f->stream));
+        ASB_CUDA(dmalloc(&f->d_T, nt_max));
+        ASB_CUDA(dmalloc(&f->d_counter, 1));
+        if (const char* e = std::getenv("ASB_SPARE")) f->spare_ctas = std::atoi(e);
+        if (std::getenv("ASB_CTA_PROF")) {
+            ASB_CUDA(dmalloc(&f->d_ctaprof, 3 * 1024));
+            ASB_CUDA(cudaMemsetAsync(f->d_ctaprof, 0, 3 * 1024 * sizeof(unsigned long long), f->stream));
+        }
+        ASB_CUDA(cudaMemsetAsync(f->d_counter, 0, sizeof(unsigned int), f->stream));
+    }
     ASB_CUDA(dmalloc(&f->d_Vr, (size_t)M_MAX * V_LDB * (ld / V_BLK)));
     ASB_CUDA(dmalloc(&f->d_Vc, (size_t)M_MAX * V_LDB * (ld / V_BLK)));
     ASB_CUDA(cudaMemsetAsync(f->d_Vr, 0, (size_t)M_MAX * V_LDB * (ld / V_BLK) * sizeof(double), f->stream));
@@ -246,8 +349,8 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
     f->dx_last = f->d_dx[0];
     ASB_CUDA(dmalloc(&f->d_unc, 16));
     ASB_CUDA(dmalloc(&f->d_status, 1));
-    ASB_CUDA(dmalloc(&f->d_prof, 16));
-    ASB_CUDA(cudaMemsetAsync(f->d_prof, 0, 16 * sizeof(unsigned long long), f->stream));
+    ASB_CUDA(dmalloc(&f->d_prof, 32));
+    ASB_CUDA(cudaMemsetAsync(f->d_prof, 0, 32 * sizeof(unsigned long long), f->stream));
     ASB_CUDA(dmalloc(&f->d_idx, (size_t)N_SLOTS * f->max_obs));
     ASB_CUDA(dmalloc(&f->d_pose, (size_t)N_SLOTS * f->max_obs * 6));
     ASB_CUDA(dmalloc(&f->d_new, (size_t)N_SLOTS * f->max_obs));
@@ -275,6 +378,25 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
     ASB_CUDA(cudaFuncSetAttribute(k_sweep_ws, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_front<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_front<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    ASB_CUDA(cudaFuncSetAttribute(k_f1<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    ASB_CUDA(cudaFuncSetAttribute(k_f1<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    ASB_CUDA(cudaFuncSetAttribute(k_f2<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    ASB_CUDA(cudaFuncSetAttribute(k_f2<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    // One shared-memory carve-out (the maximum) for every kernel of the update: an SM only changes
+    // its L1 / shared split when idle, so kernels that prefer different splits neither overlap
+    // (k_f1 next to the sweep) nor follow each other without a drain.
+    if (!std::getenv("ASB_NO_CARVEOUT")) {
+    ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepBig>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepDual>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    ASB_CUDA(cudaFuncSetAttribute(k_front<0>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    ASB_CUDA(cudaFuncSetAttribute(k_front<1>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    ASB_CUDA(cudaFuncSetAttribute(k_f1<0>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    ASB_CUDA(cudaFuncSetAttribute(k_f1<1>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    ASB_CUDA(cudaFuncSetAttribute(k_f2<0>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    ASB_CUDA(cudaFuncSetAttribute(k_f2<1>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    ASB_CUDA(cudaFuncSetAttribute(k_prep<0>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    ASB_CUDA(cudaFuncSetAttribute(k_prep<1>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    }
     *out = f;
     return ASB_OK;
 }
@@ -282,6 +404,10 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
 int asb_filter_destroy(asb_filter* f) {
     ASB_CHECK_HANDLE(f);
     cudaStreamSynchronize(f->stream);
+    if (f->side) { cudaStreamSynchronize(f->side); cudaStreamDestroy(f->side); }
+    if (f->ev_ready) cudaEventDestroy(f->ev_ready);
+    if (f->ev_f1) cudaEventDestroy(f->ev_f1);
+    cudaFree(f->d_P2); cudaFree(f->d_At); cudaFree(f->d_y); cudaFree(f->d_T); cudaFree(f->d_counter); cudaFree(f->d_ctaprof); cudaFree(f->d_Vt);
     cudaFree(f->d_state); cudaFree(f->d_P); cudaFree(f->d_Vr); cudaFree(f->d_Vc); cudaFree(f->d_blocks); cudaFree(f->d_nu);
     cudaFree(f->d_dx[0]); cudaFree(f->d_dx[1]); cudaFree(f->d_unc);
     cudaFree(f->d_status); cudaFree(f->d_prof); cudaFree(f->d_idx); cudaFree(f->d_pose); cudaFree(f->d_new);
@@ -296,6 +422,7 @@ int asb_filter_destroy(asb_filter* f) {
 
 int asb_filter_set_stream(asb_filter* f, void* cuda_stream) {
     ASB_CHECK_HANDLE(f);
+    f->lazy = false;   // the next k_f1 reads the current covariance buffer, not the previous sweep's input
     ASB_CUDA(cudaStreamSynchronize(f->stream));
     f->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : f->own_stream;
     return ASB_OK;
@@ -343,7 +470,10 @@ static int observe_impl(asb_filter* f, const int32_t* ids, const double* poses, 
     const int n1 = f->n_state();
     int* d_idx = nullptr; double* d_pose = nullptr; unsigned char* d_new = nullptr;
     if (k > 0) {
-        int rc = stage(f, idx, poses, isnew, k, &d_idx, &d_pose, &d_new);
+        // a pipelined update reads its observations in k_f1 on the side stream
+        const bool piped = f->pipeline != 0;
+        if (piped) pipe_wait(f);
+        int rc = stage(f, idx, poses, isnew, k, &d_idx, &d_pose, &d_new, piped ? f->side : f->stream);
         if (rc != ASB_OK) return rc;
     }
     f->last_k = k;
@@ -379,7 +509,7 @@ int asb_add_marker(asb_filter* f, int32_t id, const double pose[6], const double
     f->id_order.push_back(id);
     const int n1 = f->n_state();
     int* d_idx; double* d_pose; unsigned char* d_new;
-    int rc = stage(f, idx, pose, isnew, 1, &d_idx, &d_pose, &d_new);
+    int rc = stage(f, idx, pose, isnew, 1, &d_idx, &d_pose, &d_new, f->stream);
     if (rc != ASB_OK) return rc;
     rc = launch_frame_dyn(f, d_idx, d_pose, d_new, 1, n0, n1, false, false);
     if (rc != ASB_OK) return rc;
@@ -477,6 +607,7 @@ int asb_get_state(asb_filter* f, double* out, int n_state) {
 
 int asb_set_state(asb_filter* f, const double* in, int n_state) {
     ASB_CHECK_HANDLE(f);
+    f->lazy = false;   // the next k_f1 reads the current covariance buffer, not the previous sweep's input
     if (!in || n_state != f->n_state()) return fail(ASB_ERR_BAD_ARG, "n_state %d != %d", n_state, f->n_state());
     ASB_CUDA(cudaStreamSynchronize(f->stream));
     ASB_CUDA(cudaMemcpy(f->d_state, in, n_state * sizeof(double), cudaMemcpyHostToDevice));
@@ -494,6 +625,7 @@ int asb_get_cov(asb_filter* f, double* out, int n_state) {
 
 int asb_set_cov(asb_filter* f, const double* in, int n_state) {
     ASB_CHECK_HANDLE(f);
+    f->lazy = false;   // the next k_f1 reads the current covariance buffer, not the previous sweep's input
     if (!in || n_state != f->n_state()) return fail(ASB_ERR_BAD_ARG, "n_state %d != %d", n_state, f->n_state());
     ASB_CUDA(cudaStreamSynchronize(f->stream));
     ASB_CUDA(cudaMemcpy2D(f->d_P, (size_t)f->ld * sizeof(double), in, (size_t)n_state * sizeof(double),
@@ -519,6 +651,7 @@ int asb_get_landmark_ids(asb_filter* f, int32_t* ids, int capacity) {
 
 int asb_set_landmarks(asb_filter* f, const int32_t* ids, int n) {
     ASB_CHECK_HANDLE(f);
+    f->lazy = false;   // the next k_f1 reads the current covariance buffer, not the previous sweep's input
     if (n < 0 || (n > 0 && !ids)) return fail(ASB_ERR_BAD_ARG, "bad ids");
     if (n > f->cap_lm) return fail(ASB_ERR_CAPACITY, "%d landmarks > max_landmarks %d", n, f->cap_lm);
     f->map.clear();
@@ -530,6 +663,7 @@ int asb_set_landmarks(asb_filter* f, const int32_t* ids, int n) {
 
 int asb_device_views(asb_filter* f, void** d_state, void** d_cov, int* ld) {
     ASB_CHECK_HANDLE(f);
+    f->lazy = false;   // the next k_f1 reads the current covariance buffer, not the previous sweep's input
     if (d_state) *d_state = f->d_state;
     if (d_cov) *d_cov = f->d_P;
     if (ld) *ld = f->ld;
@@ -538,6 +672,7 @@ int asb_device_views(asb_filter* f, void** d_state, void** d_cov, int* ld) {
 
 int asb_bench_sweep(asb_filter* f, int m4, int config, int dbg, int reps, double* us_per_launch) {
     ASB_CHECK_HANDLE(f);
+    f->lazy = false;   // the next k_f1 reads the current covariance buffer, not the previous sweep's input
     if (!us_per_launch || m4 < 4 || m4 > M_MAX || (m4 & 3) || reps < 1) return fail(ASB_ERR_BAD_ARG, "bad args");
     const int n1 = f->n_state();
     cudaEvent_t e0, e1;
@@ -545,9 +680,11 @@ int asb_bench_sweep(asb_filter* f, int m4, int config, int dbg, int reps, double
     ASB_CUDA(cudaEventCreate(&e1));
     SweepExtra ex{};
     ex.n = n1; ex.apply_kind = -1;
+    ex.pol = (dbg >> 12) & 0x1ff;          // experiments: cache policies, serpentine walk
     for (int rep = -2; rep < reps; ++rep) {
         if (rep == 0) ASB_CUDA(cudaEventRecord(e0, f->stream));
-        launch_sweep(f, n1, m4, dbg, ex, config);
+        ex.reverse = (dbg & (1 << 25)) ? 1 : ((dbg & (1 << 24)) ? (rep & 1) : 0);
+        launch_sweep(f, n1, m4, dbg & 0xfff, ex, config);
     }
     ASB_CUDA(cudaEventRecord(e1, f->stream));
     ASB_CUDA(cudaEventSynchronize(e1));
@@ -564,9 +701,52 @@ int asb_front_profile(asb_filter* f, double us[12]) {
     if (!us) return fail(ASB_ERR_BAD_ARG, "us is NULL");
     unsigned long long t[16];
     ASB_CUDA(cudaStreamSynchronize(f->stream));
+    ASB_CUDA(cudaMemcpy(t, f->d_prof + (f->pipeline ? 16 * (f->prof_slot ^ 1) : 0), sizeof t, cudaMemcpyDeviceToHost));
+    for (int i = 0; i < 12; ++i) us[i] = 0.0;
+    if (f->pipeline) {
+        // k_f1: [index set, issue copies, model + wait, lazy operand + Q + S, Cholesky, outputs]; k_f2: [loads, product, stores]
+        for (int i = 0; i < 5; ++i) us[i] = 1e-3 * (double)(long long)(t[i + 1] - t[i]);
+        for (int i = 0; i < 3; ++i) us[8 + i] = 1e-3 * (double)(long long)(t[9 + i] - t[8 + i]);
+        us[5] = 1e-3 * (double)(long long)(t[5] - t[0]);    // k_f1 start -> end
+        us[6] = 1e-3 * (double)(long long)(t[8] - t[0]);    // k_f1 start -> k_f2 start (same update)
+        us[7] = 1e-3 * (double)(long long)(t[11] - t[0]);   // k_f1 start -> k_f2 end
+    } else {
+        for (int i = 0; i < 7; ++i) us[i] = 1e-3 * (double)(long long)(t[i + 1] - t[i]);
+    }
+    return ASB_OK;
+}
+
+int asb_timeline(asb_filter* f, double us[32]) {
+    ASB_CHECK_HANDLE(f);
+    if (!us) return fail(ASB_ERR_BAD_ARG, "us is NULL");
+    unsigned long long t[32];
+    ASB_CUDA(cudaStreamSynchronize(f->stream));
     ASB_CUDA(cudaMemcpy(t, f->d_prof, sizeof t, cudaMemcpyDeviceToHost));
-    for (int i = 0; i < 7; ++i) us[i] = 1e-3 * (double)(long long)(t[i + 1] - t[i]);
-    for (int i = 8; i < 13; ++i) us[i - 1] = (double)(long long)(t[i + 1] - t[i]);  // clocks, one Cholesky step
+    unsigned long long t0 = ~0ull;
+    for (int i = 0; i < 32; ++i) if (t[i] && t[i] < t0) t0 = t[i];
+    // previous update first: the slot written last is prof_slot ^ 1
+    for (int u = 0; u < 2; ++u)
+        for (int i = 0; i < 16; ++i) {
+            const unsigned long long v = t[16 * (u == 0 ? f->prof_slot : f->prof_slot ^ 1) + i];
+            us[16 * u + i] = v ? 1e-3 * (double)(long long)(v - t0) : -1.0;
+        }
+    return ASB_OK;
+}
+
+int asb_cta_profile(asb_filter* f, double* us, int n) {
+    ASB_CHECK_HANDLE(f);
+    if (!us || n < 1 || n > 1024) return fail(ASB_ERR_BAD_ARG, "bad args");
+    if (!f->d_ctaprof) return fail(ASB_ERR_BAD_ARG, "set ASB_CTA_PROF=1 before creating the filter");
+    std::vector<unsigned long long> t(3 * 1024);
+    ASB_CUDA(cudaStreamSynchronize(f->stream));
+    ASB_CUDA(cudaMemcpy(t.data(), f->d_ctaprof, t.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    unsigned long long t0 = ~0ull;
+    for (int b = 0; b < n; ++b) if (t[3 * b] && t[3 * b] < t0) t0 = t[3 * b];
+    for (int b = 0; b < n; ++b) {
+        us[3 * b] = t[3 * b] ? 1e-3 * (double)(long long)(t[3 * b] - t0) : -1.0;
+        us[3 * b + 1] = t[3 * b + 1] ? 1e-3 * (double)(long long)(t[3 * b + 1] - t0) : -1.0;
+        us[3 * b + 2] = (double)t[3 * b + 2];
+    }
     return ASB_OK;
 }
 

@@ -28,7 +28,38 @@ struct SweepExtra {
     int nlm;
     double* state;
     const double* dx;
+    int reverse;           // walk each CTA's tile chunk backwards (odd frames): the tiles a CTA wrote last
+                           // in the previous sweep are the ones it reads first, while they are still in L2
+    unsigned long long* prof;   // CTA 0 stores globaltimer at start / end into prof[0..1] (may be null)
+    unsigned long long* cta_prof;   // every CTA stores its start / end / %smid into cta_prof[3 b .. 3 b + 2] (may be null)
+    int pol;               // cache policies (ld256 / st256 modes): bits 0-2 P loads, 3-5 direct stores,
+                           // 6-8 mirror stores; 0 = take the dbg bits
 };
+
+// State update + multiplicative quaternion reset (EKF:134-152, ROT:143-177) by one CTA.
+__device__ __forceinline__ void apply_state(double* state, const double* dx, int apply_kind, int as_written, int nlm,
+                                            int tid, int nthreads) {
+    if (tid == 0) {
+        double cam[CAM], d[CAM];
+#pragma unroll
+        for (int c = 0; c < CAM; ++c) { cam[c] = state[c]; d[c] = __ldcg(dx + c); }
+        camera_reset(cam, d, as_written);
+#pragma unroll
+        for (int c = 0; c < CAM; ++c) state[c] = cam[c];
+    }
+    if (apply_kind == 0) {
+        for (int e = tid; e < 3 * nlm; e += nthreads) state[CAM + e] += __ldcg(dx + CAM + e);
+    } else {
+        for (int t = tid; t < nlm; t += nthreads) {
+            double lm[10], d[10];
+#pragma unroll
+            for (int c = 0; c < 10; ++c) { lm[c] = state[CAM + 10 * t + c]; d[c] = __ldcg(dx + CAM + 10 * t + c); }
+            landmark_update<1>(lm, d);
+#pragma unroll
+            for (int c = 0; c < 10; ++c) state[CAM + 10 * t + c] = lm[c];
+        }
+    }
+}
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
     return (uint32_t)__cvta_generic_to_shared(p);
@@ -93,15 +124,19 @@ constexpr int V_BLK = 64, V_LDB = 68;
 __host__ __device__ inline int v_pos_row(int c) { return (c & ~31) + ((c & 31) >> 2) + 8 * (c & 3); }
 __host__ __device__ inline int v_pos_col(int c) { return (c & ~15) + 8 * ((c & 3) >> 1) + 2 * ((c & 15) >> 2) + (c & 1); }
 
-// cache policy experiments (asb_bench_sweep dbg bits 16 / 32): 0 default, 1 evict-first (.cs), 2 L2-only (.cg)
+// cache policies: 0 default, 1 evict-first (.cs), 2 L2-only (.cg), 3 L2 evict-last (SASS .ELL2), 4 L2 evict-first (.EFL2)
 __device__ __forceinline__ void ld256(const double* p, double& a, double& b, double& c, double& d, int mode = 0) {
     if (mode == 1) asm volatile("ld.global.cs.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(p));
     else if (mode == 2) asm volatile("ld.global.cg.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(p));
+    else if (mode == 3) asm volatile("ld.global.L2::evict_last.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(p));
+    else if (mode == 4) asm volatile("ld.global.L2::evict_first.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(p));
     else asm volatile("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(p));
 }
 __device__ __forceinline__ void st256(double* p, double a, double b, double c, double d, int mode = 0) {
     if (mode == 1) asm volatile("st.global.cs.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(a), "d"(b), "d"(c), "d"(d) : "memory");
     else if (mode == 2) asm volatile("st.global.cg.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(a), "d"(b), "d"(c), "d"(d) : "memory");
+    else if (mode == 3) asm volatile("st.global.L2::evict_last.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(a), "d"(b), "d"(c), "d"(d) : "memory");
+    else if (mode == 4) asm volatile("st.global.L2::evict_first.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(a), "d"(b), "d"(c), "d"(d) : "memory");
     else asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(a), "d"(b), "d"(c), "d"(d) : "memory");
 }
 // P sub-tile of one warp <-> registers, fragment ownership as above.  pr = P + (r0 + 4 g) * ld
@@ -156,10 +191,12 @@ using SweepDual = SweepCfg<2, 4, 4, 2, 2>;   // 64 x 64 tile, 2 CTAs / SM: one c
 // double-buffered: the bulk copies (TMA, SASS UBLKCP) of tile t+1's VJ fly during tile t's
 // MMAs.  The P sub-tile goes global -> registers in the accumulator-fragment layout at the
 // start of the tile and is only consumed after the k-loop (out = P - V_I^T V_J), so its HBM
-// latency hides behind the tile's own math.
+// latency hides behind the tile's own math.  Pin is read (lower triangle), P is written (both
+// triangles): the same buffer for an in-place update, or the two halves of the pipelined
+// engine's ping-pong pair (filter_single.cu), where the next frame's k_f1 still reads Pin.
 template <class C>
 __global__ void __launch_bounds__(C::THREADS, C::MINB)
-k_sweep(double* __restrict__ P, int ld, const double* __restrict__ Vr, const double* __restrict__ Vc, int m4,
+k_sweep(const double* Pin, double* P, int ld, const double* __restrict__ Vr, const double* __restrict__ Vc, int m4,
         int ntiles, int dbg, SweepExtra ex) {
     // dbg (asb_bench_sweep only; 0 in the product path): 1 skip MMAs, 2 skip mirror stores,
     // 4 skip direct stores, 8 skip P loads; bits 4-5 load cache policy, bits 6-7 store cache
@@ -173,28 +210,21 @@ k_sweep(double* __restrict__ P, int ld, const double* __restrict__ Vr, const dou
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, t4 = lane & 3;
     const int wi = warp / C::WN, wj = warp % C::WN;
-    if (blockIdx.x == 0 && ex.apply_kind >= 0) {  // state update (k_apply folded in)
-        if (tid == 0) {
-            double cam[CAM], d[CAM];
-#pragma unroll
-            for (int c = 0; c < CAM; ++c) { cam[c] = ex.state[c]; d[c] = ex.dx[c]; }
-            camera_reset(cam, d, ex.as_written);
-#pragma unroll
-            for (int c = 0; c < CAM; ++c) ex.state[c] = cam[c];
-        }
-        if (ex.apply_kind == 0) {
-            for (int e = tid; e < 3 * ex.nlm; e += C::THREADS) ex.state[CAM + e] += ex.dx[CAM + e];
-        } else {
-            for (int t = tid; t < ex.nlm; t += C::THREADS) {
-                double lm[10], d[10];
-#pragma unroll
-                for (int c = 0; c < 10; ++c) { lm[c] = ex.state[CAM + 10 * t + c]; d[c] = ex.dx[CAM + 10 * t + c]; }
-                landmark_update<1>(lm, d);
-#pragma unroll
-                for (int c = 0; c < 10; ++c) ex.state[CAM + 10 * t + c] = lm[c];
-            }
-        }
+    if (ex.prof && blockIdx.x == 0 && tid == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        ex.prof[0] = t;
     }
+    if (ex.cta_prof && tid == 0) {
+        unsigned long long t;
+        unsigned int sm;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
+        ex.cta_prof[3 * blockIdx.x] = t;
+        ex.cta_prof[3 * blockIdx.x + 2] = sm;
+    }
+    if (blockIdx.x == 0 && ex.apply_kind >= 0)   // state update (k_apply folded in)
+        apply_state(ex.state, ex.dx, ex.apply_kind, ex.as_written, ex.nlm, tid, C::THREADS);
     if (tid == 0) {
         mbar_init(&bar[0], 1);
         mbar_init(&bar[1], 1);
@@ -205,11 +235,16 @@ k_sweep(double* __restrict__ P, int ld, const double* __restrict__ Vr, const dou
     const int t_begin = (int)((long long)ntiles * blockIdx.x / gridDim.x);
     const int t_end = (int)((long long)ntiles * (blockIdx.x + 1) / gridDim.x);
     if (t_begin >= t_end) return;
+    const bool rev = ex.reverse != 0;
+    const int t_first = rev ? t_end - 1 : t_begin;
     // t = RATIO I (I + 1) / 2 + J
-    int I = (int)((sqrt(8.0 * t_begin / C::RATIO + 1.0) - 1.0) * 0.5);
-    while (C::RATIO * (I + 1) * (I + 2) / 2 <= t_begin) ++I;
-    while (C::RATIO * I * (I + 1) / 2 > t_begin) --I;
-    int J = t_begin - C::RATIO * I * (I + 1) / 2;
+    int I = (int)((sqrt(8.0 * t_first / C::RATIO + 1.0) - 1.0) * 0.5);
+    while (C::RATIO * (I + 1) * (I + 2) / 2 <= t_first) ++I;
+    while (C::RATIO * I * (I + 1) / 2 > t_first) --I;
+    int J = t_first - C::RATIO * I * (I + 1) / 2;
+    const int pol_ld = ex.pol ? (ex.pol & 7) : ((dbg >> 4) & 3);
+    const int pol_st = ex.pol ? ((ex.pol >> 3) & 7) : ((dbg >> 6) & 3);
+    const int pol_mir = ex.pol ? ((ex.pol >> 6) & 7) : ((dbg >> 6) & 3);
 
     const uint32_t blk_bytes = (uint32_t)(blk * sizeof(double));
     auto load_vi = [&](int i0) {  // one thread
@@ -230,8 +265,10 @@ k_sweep(double* __restrict__ P, int ld, const double* __restrict__ Vr, const dou
     int buf = 0;
     for (int t = t_begin; t < t_end; ++t, buf ^= 1) {
         const int i0 = I * TI, j0 = J * TJ;
-        int In = I, Jn = J + 1;
-        if (Jn == C::RATIO * (I + 1)) { In = I + 1; Jn = 0; }
+        int In = I, Jn = rev ? J - 1 : J + 1;
+        if (rev) {
+            if (Jn < 0) { In = I - 1; Jn = C::RATIO * I - 1; }
+        } else if (Jn == C::RATIO * (I + 1)) { In = I + 1; Jn = 0; }
         const bool has_next = t + 1 < t_end;
         if (tid == 0 && has_next) load_vj(buf ^ 1, Jn * TJ);  // buffer freed by the last __syncthreads
 
@@ -244,7 +281,7 @@ k_sweep(double* __restrict__ P, int ld, const double* __restrict__ Vr, const dou
 #pragma unroll
                 for (int rn = 0; rn < RN; ++rn) pf[rm][rn][0] = pf[rm][rn][1] = 0.0;
         } else {
-            tile_load<RM, RN>(P + (long long)r0 * ld + c0, ld, pf, (dbg >> 4) & 3);
+            tile_load<RM, RN>(Pin + (long long)r0 * ld + c0, ld, pf, pol_ld);
         }
 
         double acc[RM][RN][2];
@@ -285,8 +322,8 @@ k_sweep(double* __restrict__ P, int ld, const double* __restrict__ Vr, const dou
                 pf[rm][rn][1] -= acc[rm][rn][1];
             }
         if (interior) {
-            if (!(dbg & 4)) tile_store<RM, RN>(P + (long long)r0 * ld + c0, ld, pf, (dbg >> 6) & 3);
-            if (!(dbg & 2)) tile_store_mirror<RM, RN>(P + (long long)c0 * ld + r0, ld, pf, (dbg >> 6) & 3);
+            if (!(dbg & 4)) tile_store<RM, RN>(P + (long long)r0 * ld + c0, ld, pf, pol_st);
+            if (!(dbg & 2)) tile_store_mirror<RM, RN>(P + (long long)c0 * ld + r0, ld, pf, pol_mir);
         } else {
 #pragma unroll
             for (int rm = 0; rm < RM; ++rm)
@@ -310,6 +347,16 @@ k_sweep(double* __restrict__ P, int ld, const double* __restrict__ Vr, const dou
         }
         I = In;
         J = Jn;
+    }
+    if (ex.prof && blockIdx.x == 0 && tid == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        ex.prof[1] = t;
+    }
+    if (ex.cta_prof && tid == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        ex.cta_prof[3 * blockIdx.x + 1] = t;
     }
 }
 

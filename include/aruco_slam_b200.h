@@ -182,6 +182,12 @@ ASB_API int asb_bench_sweep(asb_filter* f, int m4, int config, int dbg, int reps
  * growth; then us[7..11] = clocks of one Cholesky step: diagonal block, panel, barrier,
  * trailing update, barrier. */
 ASB_API int asb_front_profile(asb_filter* f, double us[12]);
+/* Pipelined engine: globaltimer stamps (us, relative to the earliest) of the last two updates, the
+ * older one first; per update 16 slots: [0..5] k_f1 phases, [8..11] k_f2 phases, [12] / [13] start / end
+ * of CTA 0 of k_sweep; -1 = not written. */
+ASB_API int asb_timeline(asb_filter* f, double us[32]);
+/* Per-CTA (start us, end us, %smid) of the last k_sweep, n CTAs; needs ASB_CTA_PROF=1 at creation. */
+ASB_API int asb_cta_profile(asb_filter* f, double* us, int n);
 /* Dependent-issue latencies in clocks: DFMA, rsqrt(double)+add, LDS.64 (with cvt), BAR.SYNC of 256 threads. */
 ASB_API int asb_latency_probe(int device, double clocks[4]);
 /* HBM stream bandwidth (GB/s of bytes moved): mode 0 write-only, 1 read-only, 2 one read + two writes
