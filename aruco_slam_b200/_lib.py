@@ -14,7 +14,8 @@ from pathlib import Path
 import numpy as np
 
 PKG_DIR = Path(__file__).resolve().parent
-LIB_PATH = PKG_DIR / "libarucoslam_b200.so"
+# ASB_LIB_PATH: A/B experiments against another build of the same library (tools/); never a fallback
+LIB_PATH = Path(os.environ.get("ASB_LIB_PATH") or PKG_DIR / "libarucoslam_b200.so")
 CSRC = PKG_DIR / "csrc"
 
 ASB_OK = 0

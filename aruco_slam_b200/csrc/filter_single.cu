@@ -66,6 +66,20 @@ struct asb_filter {
     int prof_slot = 0, spare_ctas = 2;
     unsigned long long* d_ctaprof = nullptr;   // 3 x 1024: per-CTA start / end / smid of the last sweep         // timeline of the last two updates (asb_timeline)
     int prev_m4 = 0, prev_add_q = 0;
+    // stream mode (asb_stream_run): the sweep of update t is launched AFTER k_f1 of update t+1
+    // (programmatic dependent launches, see launch_frame); until then it is kept here
+    struct PendingSweep {
+        bool valid = false;
+        int n1 = 0, m4 = 0;
+        SweepExtra ex{};
+        const double* pin = nullptr;
+        double* pout = nullptr;
+    } pending;
+    unsigned int* d_tail = nullptr;   // two tile counters used alternately by successive sweeps (sweep.cuh)
+    unsigned int sweep_seq = 0;
+    int tail_tiles = 2;        // tiles per CTA handed out dynamically (ASB_TAIL)
+    bool defer = false;        // set by asb_stream_run around its frame loop
+    int pdl = 1;               // ASB_PDL=0: stream mode uses the side-stream engine as well
 
     int n_state() const { return CAM + D * nlm; }
 };
@@ -92,8 +106,37 @@ static cudaError_t dmalloc(T** p, size_t count) {
 // ---------------------------------------------------------------------------------------
 // persistent sweep: 2 CTAs / SM (64 x 64 tiles) while both fit in shared memory, else
 // 1 CTA / SM (128 x 64 tiles)
-static void launch_sweep(asb_filter* f, int n1, int m4, int dbg, const SweepExtra& ex, int config = -1,
-                         const double* pin = nullptr, double* pout = nullptr, int spare_ctas = 0) {
+// <<<>>> with (optionally) the programmatic-stream-serialization attribute: the kernel may be
+// scheduled as soon as every CTA of the previous kernel of the stream has executed
+// griddepcontrol.launch_dependents (or exited); it orders itself with griddepcontrol.wait.
+template <typename... KA, typename... A>
+static void launch_k(void (*kern)(KA...), int grid, int block, size_t smem, cudaStream_t st, bool pdl, A&&... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3((unsigned)block);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kern, static_cast<KA>(args)...);
+}
+
+static void launch_sweep(asb_filter* f, int n1, int m4, int dbg, const SweepExtra& ex_in, int config = -1,
+                         const double* pin = nullptr, double* pout = nullptr, int spare_ctas = 0, bool pdl = false,
+                         bool dynamic_tail = false) {
+    SweepExtra ex = ex_in;
+    // hybrid tile schedule (sweep.cuh): all but the last tail_tiles tiles of a CTA's share are a
+    // contiguous range, the rest are handed out one at a time
+    auto schedule = [&](int ntiles, int grid) {
+        if (!dynamic_tail || f->tail_tiles <= 0 || !f->d_tail) return;
+        ex.tail = f->d_tail + (f->sweep_seq & 1);
+        ex.tail_reset = f->d_tail + ((f->sweep_seq + 1) & 1);
+        ex.n_static = std::max(0, ntiles / grid - f->tail_tiles);
+        ++f->sweep_seq;
+    };
     if (config < 0) config = f->sweep_config;
     if (!pin) pin = f->d_P;
     if (!pout) pout = f->d_P;
@@ -108,14 +151,25 @@ static void launch_sweep(asb_filter* f, int n1, int m4, int dbg, const SweepExtr
     if (dual) {
         const int ntiles = SweepDual::num_tiles(n1);
         const int grid = std::min(ntiles, 2 * f->sweep_grid - spare_ctas);
-        k_sweep<SweepDual><<<grid, SweepDual::THREADS, SweepDual::smem_bytes(m4), f->stream>>>(
-            pin, pout, f->ld, f->d_Vr, f->d_Vc, m4, ntiles, dbg, ex);
+        schedule(ntiles, grid);
+        launch_k(k_sweep<SweepDual>, grid, SweepDual::THREADS, SweepDual::smem_bytes(m4), f->stream, pdl,
+                 pin, pout, f->ld, f->d_Vr, f->d_Vc, m4, ntiles, dbg, ex);
     } else {
         const int ntiles = SweepBig::num_tiles(n1);
-        const int grid = std::min(ntiles, f->sweep_grid);
-        k_sweep<SweepBig><<<grid, SweepBig::THREADS, SweepBig::smem_bytes(m4), f->stream>>>(
-            pin, pout, f->ld, f->d_Vr, f->d_Vc, m4, ntiles, dbg, ex);
+        const int grid = std::min(ntiles, f->sweep_grid - (spare_ctas ? 1 : 0));
+        schedule(ntiles, grid);
+        launch_k(k_sweep<SweepBig>, grid, SweepBig::THREADS, SweepBig::smem_bytes(m4), f->stream, pdl,
+                 pin, pout, f->ld, f->d_Vr, f->d_Vc, m4, ntiles, dbg, ex);
     }
+}
+
+// Launch the sweep kept back by the stream-mode engine (after_f1: as a programmatic dependent of
+// the k_f1 just launched, so that k_f1 already owns its SM when the sweep's CTAs are placed).
+static void flush_pending(asb_filter* f, bool after_f1) {
+    if (!f->pending.valid) return;
+    f->pending.valid = false;
+    launch_sweep(f, f->pending.n1, f->pending.m4, 2 << 4, f->pending.ex, -1, f->pending.pin, f->pending.pout,
+                 f->spare_ctas, after_f1, true);
 }
 
 // Side stream waits until the state, dx and panel of the previous update are final (k_f2 done);
@@ -140,8 +194,21 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
             const int kc = std::min(f->kc_max, k - c0);
             const int m4 = round_up(R * kc, 4);
             const bool first = c0 == 0, last = c0 + kc >= k;
-            pipe_wait(f);
-            f->side_waited = false;
+            // Stream mode: everything on the main stream in the order
+            //   k_f2(t) -> k_f1(t+1) -> k_sweep(t) -> k_f2(t+1) -> k_f1(t+2) -> k_sweep(t+1) ...
+            // each a programmatic dependent of its predecessor.  k_f1 asks for (nearly) all the shared
+            // memory of an SM and starts BEFORE the sweep it overlaps, so it has that SM to itself and
+            // the sweep's CTAs (two per SM on the others) never share the FP64 pipe with it.
+            // Per-frame calls (observe()): the next frame is not known when the sweep is launched, so
+            // k_f1 goes to the side stream and squeezes in next to one sweep CTA.
+            const bool ordered = f->defer && f->pdl;
+            if (ordered) {
+                if (!f->lazy) flush_pending(f, false);
+            } else {
+                flush_pending(f, false);
+                pipe_wait(f);
+                f->side_waited = false;
+            }
             F1Args a;
             a.state = f->d_state; a.P = f->lazy ? f->d_P2 : f->d_P; a.ld = ld;
             a.n0 = first ? n0 : n1; a.n1 = n1; a.nz = f->nz;
@@ -159,9 +226,14 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
             unsigned long long* prof = f->d_prof + 16 * f->prof_slot;
             f->prof_slot ^= 1;
             a.prof = prof;
-            k_f1<KIND><<<1, FRONT_THREADS, F1Smem<KIND>::bytes(kc, m4), f->side>>>(a);
-            cudaEventRecord(f->ev_f1, f->side);
-            cudaStreamWaitEvent(st, f->ev_f1, 0);
+            if (ordered) {
+                launch_k(k_f1<KIND>, 1, FRONT_THREADS, (size_t)f->smem_optin - 2048, st, true, a);
+                flush_pending(f, true);
+            } else {
+                k_f1<KIND><<<1, FRONT_THREADS, F1Smem<KIND>::bytes(kc, m4), f->side>>>(a);
+                cudaEventRecord(f->ev_f1, f->side);
+                cudaStreamWaitEvent(st, f->ev_f1, 0);
+            }
             F2Args b;
             b.state = f->d_state; b.P = f->d_P; b.ld = ld; b.n0 = a.n0; b.n1 = n1; b.nz = f->nz;
             b.kc = kc; b.m4 = m4; b.first_chunk = a.first_chunk; b.add_q = a.add_q; b.use_delta = a.use_delta;
@@ -174,8 +246,8 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
             b.counter = f->d_counter;
             b.prof = prof + 8;
             const int nblk = 2 * ((n1 + 127) / 128);  // whole 128-row sweep tiles are covered
-            k_f2<KIND><<<nblk, F2_THREADS, F2Smem<KIND>::bytes(kc, m4), st>>>(b);
-            cudaEventRecord(f->ev_ready, st);
+            launch_k(k_f2<KIND>, nblk, F2_THREADS, F2Smem<KIND>::bytes(kc, m4), st, ordered, b);
+            if (!ordered) cudaEventRecord(f->ev_ready, st);
             cur ^= 1;
             SweepExtra ex{};
             ex.n = n1; ex.add_q = a.add_q; ex.nz = f->nz;
@@ -183,12 +255,21 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
             ex.prof = prof + 12;
             ex.cta_prof = f->d_ctaprof;
             // the sweep leaves room for k_f1 of the next update: two CTAs fewer than fill the GPU
-            launch_sweep(f, n1, m4, 2 << 4, ex, -1, f->d_P, f->d_P2, f->spare_ctas);
+            if (ordered) {
+                f->pending.valid = true;
+                f->pending.n1 = n1; f->pending.m4 = m4; f->pending.ex = ex;
+                f->pending.pin = f->d_P; f->pending.pout = f->d_P2;
+            } else {
+                // contiguous tile ranges here: with the dynamic tail the lone sweep CTA next to k_f1 would
+                // take MORE tiles and slow k_f1 (the critical kernel of this mode) further
+                launch_sweep(f, n1, m4, 2 << 4, ex, -1, f->d_P, f->d_P2, f->spare_ctas, false, false);
+            }
             std::swap(f->d_P, f->d_P2);
             f->lazy = true; f->prev_m4 = m4; f->prev_add_q = a.add_q;
         }
         f->dx_last = f->d_dx[cur];
     } else if (!do_update || k == 0) {
+        flush_pending(f, false);
         f->lazy = false;
         // predict() / add_marker() on their own: diagonal add, covariance growth, new states
         long long work = (long long)n0 + (long long)(n1 - n0) * (n1 + n0);
@@ -197,6 +278,7 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
                                            do_predict ? 1 : 0);
     } else {
         // unpipelined update (ASB_PIPELINE=0): two launches per chunk of <= kc_max markers (k_front, k_sweep)
+        flush_pending(f, false);
         f->lazy = false;
         int cur = 0;
         for (int c0 = 0; c0 < k; c0 += f->kc_max) {
@@ -225,7 +307,7 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
             ex.apply_kind = last ? KIND : -1;
             ex.as_written = (KIND == 0 && f->quat_mode == ASB_QUAT_AS_WRITTEN) ? 1 : 0;
             ex.nlm = (n1 - CAM) / Dims<KIND>::D; ex.state = f->d_state; ex.dx = f->d_dx[cur];
-            launch_sweep(f, n1, m4, 2 << 4, ex);  // dbg bits 4-5 = 2: P loads bypass L1 (.cg)
+            launch_sweep(f, n1, m4, 2 << 4, ex, -1, nullptr, nullptr, 0, false, true);  // dbg bits 4-5 = 2: P loads bypass L1 (.cg)
         }
         f->dx_last = f->d_dx[cur];
     }
@@ -332,12 +414,16 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
         ASB_CUDA(dmalloc(&f->d_T, nt_max));
         ASB_CUDA(dmalloc(&f->d_counter, 1));
         if (const char* e = std::getenv("ASB_SPARE")) f->spare_ctas = std::atoi(e);
+        if (const char* e = std::getenv("ASB_PDL")) f->pdl = std::atoi(e);
         if (std::getenv("ASB_CTA_PROF")) {
             ASB_CUDA(dmalloc(&f->d_ctaprof, 3 * 1024));
             ASB_CUDA(cudaMemsetAsync(f->d_ctaprof, 0, 3 * 1024 * sizeof(unsigned long long), f->stream));
         }
         ASB_CUDA(cudaMemsetAsync(f->d_counter, 0, sizeof(unsigned int), f->stream));
     }
+    ASB_CUDA(dmalloc(&f->d_tail, 2));
+    ASB_CUDA(cudaMemsetAsync(f->d_tail, 0, 2 * sizeof(unsigned int), f->stream));
+    if (const char* e = std::getenv("ASB_TAIL")) f->tail_tiles = std::atoi(e);
     ASB_CUDA(dmalloc(&f->d_Vr, (size_t)M_MAX * V_LDB * (ld / V_BLK)));
     ASB_CUDA(dmalloc(&f->d_Vc, (size_t)M_MAX * V_LDB * (ld / V_BLK)));
     ASB_CUDA(cudaMemsetAsync(f->d_Vr, 0, (size_t)M_MAX * V_LDB * (ld / V_BLK) * sizeof(double), f->stream));
@@ -407,7 +493,7 @@ int asb_filter_destroy(asb_filter* f) {
     if (f->side) { cudaStreamSynchronize(f->side); cudaStreamDestroy(f->side); }
     if (f->ev_ready) cudaEventDestroy(f->ev_ready);
     if (f->ev_f1) cudaEventDestroy(f->ev_f1);
-    cudaFree(f->d_P2); cudaFree(f->d_At); cudaFree(f->d_y); cudaFree(f->d_T); cudaFree(f->d_counter); cudaFree(f->d_ctaprof); cudaFree(f->d_Vt);
+    cudaFree(f->d_tail); cudaFree(f->d_P2); cudaFree(f->d_At); cudaFree(f->d_y); cudaFree(f->d_T); cudaFree(f->d_counter); cudaFree(f->d_ctaprof); cudaFree(f->d_Vt);
     cudaFree(f->d_state); cudaFree(f->d_P); cudaFree(f->d_Vr); cudaFree(f->d_Vc); cudaFree(f->d_blocks); cudaFree(f->d_nu);
     cudaFree(f->d_dx[0]); cudaFree(f->d_dx[1]); cudaFree(f->d_unc);
     cudaFree(f->d_status); cudaFree(f->d_prof); cudaFree(f->d_idx); cudaFree(f->d_pose); cudaFree(f->d_new);
@@ -572,6 +658,7 @@ int asb_stream_run(asb_filter* f, int t0, int t1) {
     if (f->frames.empty()) return fail(ASB_ERR_NO_STREAM, "stream_run before stream_upload");
     if (t0 != f->next_frame || t1 < t0 || t1 > (int)f->frames.size())
         return fail(ASB_ERR_BAD_ARG, "frames must run in order: next is %d, got [%d,%d)", f->next_frame, t0, t1);
+    f->defer = true;
     for (int t = t0; t < t1; ++t) {
         const FrameRec& fr = f->frames[t];
         for (int32_t id : fr.new_ids) {
@@ -583,9 +670,12 @@ int asb_stream_run(asb_filter* f, int t0, int t1) {
         if (fr.k == 0) continue;  // BASE:197-204: frames without detections do not predict
         int rc = launch_frame_dyn(f, f->s_idx + fr.off, f->s_pose + 6 * fr.off, f->s_new + fr.off, fr.k, fr.n0,
                                   fr.n1, true, true);
-        if (rc != ASB_OK) return rc;
+        if (rc != ASB_OK) { f->defer = false; flush_pending(f, false); return rc; }
         f->next_frame = t + 1;
     }
+    f->defer = false;
+    if (f->pending.valid) cudaEventRecord(f->ev_ready, f->stream);   // last k_f2: what a per-frame k_f1 on the side stream waits for
+    flush_pending(f, false);   // nothing stays pending across API calls
     f->next_frame = t1;
     return ASB_OK;
 }

@@ -91,11 +91,15 @@ k_f1(F1Args p) {
     double* s_Vg = s_S;                                                  // nT x F1_LDK: Vp[:, T] by column
     __shared__ __align__(8) uint64_t s_bar;
 
-    front_stamp(stampargs, 0);
     if (tid == 0) {
         mbar_init(&s_bar, nT);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    // stream mode (programmatic dependent launches): resident while the previous k_f2 drains; once
+    // that has completed, release the sweep that is queued behind this kernel
+    pdl_wait();
+    pdl_trigger();
+    front_stamp(stampargs, 0);
     // ---- touched index set T ----------------------------------------------------------------
     if (tid < CAM) { s_cam[tid] = p.state[tid]; s_T[tid] = tid; p.T[tid] = tid; }
     for (int e = tid; e < D * kc; e += NT) {
@@ -378,6 +382,8 @@ k_f2(F2Args p) {
     int* s_T = reinterpret_cast<int*>(s_y + m4);                         // nT
     __shared__ int s_last;
 
+    pdl_wait();      // stream mode: made resident while the sweep before it retired
+    pdl_trigger();   // the next k_f1 may take one of the SMs this grid leaves empty; it waits for this grid's end
     front_stamp(stampargs, 0);
     for (int a = tid; a < nT; a += NT) s_T[a] = p.T[a];
     for (int a = tid; a < m4; a += NT) s_y[a] = p.y[a];

@@ -34,6 +34,14 @@ struct SweepExtra {
     unsigned long long* cta_prof;   // every CTA stores its start / end / %smid into cta_prof[3 b .. 3 b + 2] (may be null)
     int pol;               // cache policies (ld256 / st256 modes): bits 0-2 P loads, 3-5 direct stores,
                            // 6-8 mirror stores; 0 = take the dbg bits
+    // Tile schedule.  tail == null: CTA b walks the contiguous range [ntiles b / grid, ntiles (b+1) / grid).
+    // tail != null: CTA b walks n_static contiguous tiles [b n_static, (b+1) n_static) and then takes
+    // single tiles >= grid * n_static from the shared counter *tail until they run out, so that an SM
+    // that is ahead (or a CTA whose range was a tile shorter) absorbs the remainder instead of
+    // idling: with contiguous ranges alone the slowest CTA ends 8 % after the median one.
+    unsigned int* tail;        // counter of this launch (zero on entry)
+    unsigned int* tail_reset;  // counter of the NEXT launch: zeroed by CTA 0
+    int n_static;
 };
 
 // State update + multiplicative quaternion reset (EKF:134-152, ROT:143-177) by one CTA.
@@ -85,6 +93,13 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t phase) {
         "r"(phase)
         : "memory");
 }
+// Programmatic dependent launch (kernels launched with cudaLaunchAttributeProgrammaticStreamSerialization):
+// pdl_trigger lets the next kernel of the stream be scheduled once every CTA of this one has
+// called it; pdl_wait blocks until the previous kernel of the stream has completed and its
+// writes are visible.  Both are no-ops for a kernel launched without the attribute.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // TMA bulk copy global -> shared, completion on an mbarrier (SASS: UBLKCP).
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
     asm volatile(
@@ -223,6 +238,11 @@ k_sweep(const double* Pin, double* P, int ld, const double* __restrict__ Vr, con
         ex.cta_prof[3 * blockIdx.x] = t;
         ex.cta_prof[3 * blockIdx.x + 2] = sm;
     }
+    // Stream-mode ordering (filter_single.cu): k_f1(t+1) -> k_sweep(t) -> k_f2(t+1), each launched
+    // as a programmatic dependent of the one before.  The sweep does not need k_f1's results, so it
+    // only waits for it at the very end (its own completion then implies k_f1's).  The trigger for
+    // k_f2 is at the end as well: released earlier, its CTAs pile up on the first SMs to drain
+    // instead of spreading over the GPU (measured: k_f2 11 -> 15 us).
     if (blockIdx.x == 0 && ex.apply_kind >= 0)   // state update (k_apply folded in)
         apply_state(ex.state, ex.dx, ex.apply_kind, ex.as_written, ex.nlm, tid, C::THREADS);
     if (tid == 0) {
@@ -232,16 +252,14 @@ k_sweep(const double* Pin, double* P, int ld, const double* __restrict__ Vr, con
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
-    const int t_begin = (int)((long long)ntiles * blockIdx.x / gridDim.x);
-    const int t_end = (int)((long long)ntiles * (blockIdx.x + 1) / gridDim.x);
-    if (t_begin >= t_end) return;
+    __shared__ int s_next[2], s_nij[2];
+    const bool dyn = ex.tail != nullptr;
+    const int t_begin = dyn ? (int)blockIdx.x * ex.n_static : (int)((long long)ntiles * blockIdx.x / gridDim.x);
+    const int t_end = dyn ? t_begin + ex.n_static : (int)((long long)ntiles * (blockIdx.x + 1) / gridDim.x);
+    const int dyn_base = (int)gridDim.x * ex.n_static;
     const bool rev = ex.reverse != 0;
-    const int t_first = rev ? t_end - 1 : t_begin;
-    // t = RATIO I (I + 1) / 2 + J
-    int I = (int)((sqrt(8.0 * t_first / C::RATIO + 1.0) - 1.0) * 0.5);
-    while (C::RATIO * (I + 1) * (I + 2) / 2 <= t_first) ++I;
-    while (C::RATIO * I * (I + 1) / 2 > t_first) --I;
-    int J = t_first - C::RATIO * I * (I + 1) / 2;
+    if (dyn && blockIdx.x == 0 && tid == 0) *ex.tail_reset = 0u;
+    if (t_begin >= t_end && !dyn) { pdl_trigger(); pdl_wait(); return; }
     const int pol_ld = ex.pol ? (ex.pol & 7) : ((dbg >> 4) & 3);
     const int pol_st = ex.pol ? ((ex.pol >> 3) & 7) : ((dbg >> 6) & 3);
     const int pol_mir = ex.pol ? ((ex.pol >> 6) & 7) : ((dbg >> 6) & 3);
@@ -255,98 +273,149 @@ k_sweep(const double* Pin, double* P, int ld, const double* __restrict__ Vr, con
         mbar_expect_tx(&bar[1 + buf], blk_bytes);
         bulk_g2s(VJ0 + (size_t)buf * blk, Vc + (size_t)(j0 / V_BLK) * blk, blk_bytes, &bar[1 + buf]);
     };
+    // One thread draws the next tile of the dynamic tail: s_next[slot] = tile or -1, s_nij[slot] = (I << 16) | J,
+    // and starts the bulk copy of its VJ panel into buffer vbuf.  t = RATIO I (I + 1) / 2 + J.
+    auto draw = [&](int slot, int vbuf) {
+        int nx = dyn_base + (int)atomicAdd(ex.tail, 1u);
+        if (nx >= ntiles) nx = -1;
+        s_next[slot] = nx;
+        if (nx >= 0) {
+            int i = (int)((sqrtf(8.0f * (float)nx / (float)C::RATIO + 1.0f) - 1.0f) * 0.5f);   // estimate, fixed up
+            while (C::RATIO * (i + 1) * (i + 2) / 2 <= nx) ++i;
+            while (C::RATIO * i * (i + 1) / 2 > nx) --i;
+            const int j = nx - C::RATIO * i * (i + 1) / 2;
+            s_nij[slot] = (i << 16) | j;
+            load_vj(vbuf, j * TJ);
+        }
+    };
 
     uint32_t ph_i = 0, ph_j = 0;  // ph_j: bit b = phase of VJ buffer b
     bool vi_pending = true;
-    if (tid == 0) {
-        load_vi(I * TI);
-        load_vj(0, J * TJ);
-    }
-    int buf = 0;
-    for (int t = t_begin; t < t_end; ++t, buf ^= 1) {
+
+    // One tile: P sub-tile -> registers, out = P - V_I^T V_J, direct + mirror stores.  draw_slot >= 0: this
+    // is where the next dynamic tile is drawn (after the P loads are in flight: the counter's round
+    // trip hides behind them).  Inlined into both loops below.
+    auto do_tile = [&](const int I, const int J, const int buf, const int draw_slot) {
         const int i0 = I * TI, j0 = J * TJ;
-        int In = I, Jn = rev ? J - 1 : J + 1;
-        if (rev) {
-            if (Jn < 0) { In = I - 1; Jn = C::RATIO * I - 1; }
-        } else if (Jn == C::RATIO * (I + 1)) { In = I + 1; Jn = 0; }
-        const bool has_next = t + 1 < t_end;
-        if (tid == 0 && has_next) load_vj(buf ^ 1, Jn * TJ);  // buffer freed by the last __syncthreads
-
-        // P sub-tile -> registers (fragment ownership of sweep.cuh's header: 256-bit accesses)
-        const int r0 = i0 + 8 * RM * wi + 4 * g, c0 = j0 + 8 * RN * wj + 4 * t4;
-        double pf[RM][RN][2];
-        if (dbg & 8) {
+            // P sub-tile -> registers (fragment ownership of sweep.cuh's header: 256-bit accesses)
+            const int r0 = i0 + 8 * RM * wi + 4 * g, c0 = j0 + 8 * RN * wj + 4 * t4;
+            double pf[RM][RN][2];
+            if (dbg & 8) {
 #pragma unroll
-            for (int rm = 0; rm < RM; ++rm)
+                for (int rm = 0; rm < RM; ++rm)
 #pragma unroll
-                for (int rn = 0; rn < RN; ++rn) pf[rm][rn][0] = pf[rm][rn][1] = 0.0;
-        } else {
-            tile_load<RM, RN>(Pin + (long long)r0 * ld + c0, ld, pf, pol_ld);
-        }
-
-        double acc[RM][RN][2];
-#pragma unroll
-        for (int rm = 0; rm < RM; ++rm)
-#pragma unroll
-            for (int rn = 0; rn < RN; ++rn) acc[rm][rn][0] = acc[rm][rn][1] = 0.0;
-
-        if (vi_pending) {
-            mbar_wait(&bar[0], ph_i);
-            ph_i ^= 1;
-            vi_pending = false;
-        }
-        mbar_wait(&bar[1 + buf], (ph_j >> buf) & 1u);
-        ph_j ^= 1u << buf;
-
-        const double* va = VI + (size_t)((8 * RM * wi) / V_BLK) * blk + t4 * V_LDB + (8 * RM * wi) % V_BLK + g;
-        const double* vb = VJ0 + (size_t)buf * blk + t4 * V_LDB + 8 * RN * wj + g;
-#pragma unroll 3
-        for (int kk = 0; kk < ((dbg & 1) ? 4 : m4); kk += 4) {
-            double a[RM], b[RN];
-#pragma unroll
-            for (int r = 0; r < RM; ++r) a[r] = va[kk * V_LDB + 8 * r];
-#pragma unroll
-            for (int r = 0; r < RN; ++r) b[r] = vb[kk * V_LDB + 8 * r];
-#pragma unroll
-            for (int rm = 0; rm < RM; ++rm)
-#pragma unroll
-                for (int rn = 0; rn < RN; ++rn) dmma884(acc[rm][rn][0], acc[rm][rn][1], a[rm], b[rn]);
-        }
-
-        const bool interior = i0 >= j0 + TJ;  // strictly below the diagonal
-#pragma unroll
-        for (int rm = 0; rm < RM; ++rm)
-#pragma unroll
-            for (int rn = 0; rn < RN; ++rn) {
-                pf[rm][rn][0] -= acc[rm][rn][0];
-                pf[rm][rn][1] -= acc[rm][rn][1];
+                    for (int rn = 0; rn < RN; ++rn) pf[rm][rn][0] = pf[rm][rn][1] = 0.0;
+            } else {
+                tile_load<RM, RN>(Pin + (long long)r0 * ld + c0, ld, pf, pol_ld);
             }
-        if (interior) {
-            if (!(dbg & 4)) tile_store<RM, RN>(P + (long long)r0 * ld + c0, ld, pf, pol_st);
-            if (!(dbg & 2)) tile_store_mirror<RM, RN>(P + (long long)c0 * ld + r0, ld, pf, pol_mir);
-        } else {
+        if (draw_slot >= 0 && tid == 0) draw(draw_slot, buf ^ 1);
+
+            double acc[RM][RN][2];
 #pragma unroll
             for (int rm = 0; rm < RM; ++rm)
 #pragma unroll
-                for (int rn = 0; rn < RN; ++rn)
+                for (int rn = 0; rn < RN; ++rn) acc[rm][rn][0] = acc[rm][rn][1] = 0.0;
+
+            if (vi_pending) {
+                mbar_wait(&bar[0], ph_i);
+                ph_i ^= 1;
+                vi_pending = false;
+            }
+            mbar_wait(&bar[1 + buf], (ph_j >> buf) & 1u);
+            ph_j ^= 1u << buf;
+
+            const double* va = VI + (size_t)((8 * RM * wi) / V_BLK) * blk + t4 * V_LDB + (8 * RM * wi) % V_BLK + g;
+            const double* vb = VJ0 + (size_t)buf * blk + t4 * V_LDB + 8 * RN * wj + g;
+#pragma unroll 3
+            for (int kk = 0; kk < ((dbg & 1) ? 4 : m4); kk += 4) {
+                double a[RM], b[RN];
 #pragma unroll
-                    for (int e = 0; e < 2; ++e) {
-                        const int i = r0 + rm, j = c0 + 16 * (rn >> 1) + 2 * (rn & 1) + e;
-                        if (i >= j) {
-                            double o = pf[rm][rn][e];
-                            if (i == j && ex.add_q && i < ex.n) o += process_noise(ex.nz, i);
-                            P[(long long)i * ld + j] = o;
-                            if (i > j) P[(long long)j * ld + i] = o;
+                for (int r = 0; r < RM; ++r) a[r] = va[kk * V_LDB + 8 * r];
+#pragma unroll
+                for (int r = 0; r < RN; ++r) b[r] = vb[kk * V_LDB + 8 * r];
+#pragma unroll
+                for (int rm = 0; rm < RM; ++rm)
+#pragma unroll
+                    for (int rn = 0; rn < RN; ++rn) dmma884(acc[rm][rn][0], acc[rm][rn][1], a[rm], b[rn]);
+            }
+
+            const bool interior = i0 >= j0 + TJ;  // strictly below the diagonal
+#pragma unroll
+            for (int rm = 0; rm < RM; ++rm)
+#pragma unroll
+                for (int rn = 0; rn < RN; ++rn) {
+                    pf[rm][rn][0] -= acc[rm][rn][0];
+                    pf[rm][rn][1] -= acc[rm][rn][1];
+                }
+            if (interior) {
+                if (!(dbg & 4)) tile_store<RM, RN>(P + (long long)r0 * ld + c0, ld, pf, pol_st);
+                if (!(dbg & 2)) tile_store_mirror<RM, RN>(P + (long long)c0 * ld + r0, ld, pf, pol_mir);
+            } else {
+#pragma unroll
+                for (int rm = 0; rm < RM; ++rm)
+#pragma unroll
+                    for (int rn = 0; rn < RN; ++rn)
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            const int i = r0 + rm, j = c0 + 16 * (rn >> 1) + 2 * (rn & 1) + e;
+                            if (i >= j) {
+                                double o = pf[rm][rn][e];
+                                if (i == j && ex.add_q && i < ex.n) o += process_noise(ex.nz, i);
+                                P[(long long)i * ld + j] = o;
+                                if (i > j) P[(long long)j * ld + i] = o;
+                            }
                         }
-                    }
+            }
+    };
+
+    int buf = 0;
+    int Ivi = -1;   // row block whose VI panel is (being) loaded
+    if (t_begin < t_end) {
+        // ---- contiguous range: tile indices follow arithmetically, everything stays warp-uniform ----
+        const int t_first = rev ? t_end - 1 : t_begin;
+        int I = (int)((sqrt(8.0 * t_first / C::RATIO + 1.0) - 1.0) * 0.5);
+        while (C::RATIO * (I + 1) * (I + 2) / 2 <= t_first) ++I;
+        while (C::RATIO * I * (I + 1) / 2 > t_first) --I;
+        int J = t_first - C::RATIO * I * (I + 1) / 2;
+        if (tid == 0) {
+            load_vi(I * TI);
+            load_vj(0, J * TJ);
         }
-        __syncthreads();  // every warp is done with VJ[buf] (and VI) before they are overwritten
-        if (has_next && In != I) {
-            if (tid == 0) load_vi(In * TI);
-            vi_pending = true;
+        for (int t = t_begin; t < t_end; ++t, buf ^= 1) {
+            int In = I, Jn = rev ? J - 1 : J + 1;
+            if (rev) {
+                if (Jn < 0) { In = I - 1; Jn = C::RATIO * I - 1; }
+            } else if (Jn == C::RATIO * (I + 1)) { In = I + 1; Jn = 0; }
+            const bool has_next = t + 1 < t_end;
+            if (tid == 0 && has_next) load_vj(buf ^ 1, Jn * TJ);  // buffer freed by the last __syncthreads
+            do_tile(I, J, buf, (!has_next && dyn) ? 0 : -1);
+            __syncthreads();  // every warp is done with VJ[buf] (and VI) before they are overwritten
+            Ivi = I;
+            if (has_next && In != I) {
+                if (tid == 0) load_vi(In * TI);
+                vi_pending = true;
+                Ivi = In;
+            }
+            I = In;
+            J = Jn;
         }
-        I = In;
-        J = Jn;
+    } else {
+        if (tid == 0) draw(0, 0);
+        __syncthreads();
+    }
+    if (dyn) {
+        // ---- dynamic tail: single tiles from the shared counter ----
+        for (int slot = 0;; slot ^= 1, buf ^= 1) {
+            if (s_next[slot] < 0) break;
+            const int I = s_nij[slot] >> 16, J = s_nij[slot] & 0xffff;
+            if (I != Ivi) {
+                if (tid == 0) load_vi(I * TI);
+                vi_pending = true;
+                Ivi = I;
+            }
+            do_tile(I, J, buf, slot ^ 1);
+            __syncthreads();
+        }
     }
     if (ex.prof && blockIdx.x == 0 && tid == 0) {
         unsigned long long t;
@@ -358,6 +427,8 @@ k_sweep(const double* Pin, double* P, int ld, const double* __restrict__ Vr, con
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
         ex.cta_prof[3 * blockIdx.x + 1] = t;
     }
+    pdl_trigger();
+    pdl_wait();
 }
 
 
