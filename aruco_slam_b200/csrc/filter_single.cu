@@ -245,7 +245,7 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
             b.nlm = (n1 - CAM) / Dims<KIND>::D;
             b.counter = f->d_counter;
             b.prof = prof + 8;
-            const int nblk = 2 * ((n1 + 127) / 128);  // whole 128-row sweep tiles are covered
+            const int nblk = 4 * ((n1 + 127) / 128);  // whole 128-row sweep tiles are covered, F2_COLS = 32 columns per CTA
             launch_k(k_f2<KIND>, nblk, F2_THREADS, F2Smem<KIND>::bytes(kc, m4), st, ordered, b);
             if (!ordered) cudaEventRecord(f->ev_ready, st);
             cur ^= 1;

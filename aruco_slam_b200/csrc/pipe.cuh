@@ -349,52 +349,71 @@ struct F2Args {
 };
 
 constexpr int F2_THREADS = 256;
-constexpr int F2_LDV = V_BLK + 2;   // row stride of the V slice in shared memory
+constexpr int F2_COLS = 32;           // state columns per CTA: half a 64-column block of the sweep's panels
+constexpr int F2_LDB = F2_COLS + 4;   // row stride of the staged P rows  (= 4 mod 16: conflict-free DMMA B fragments)
+constexpr int F2_LDA = 64 + 4;        // row stride of A^T in shared memory (= 4 mod 16: conflict-free DMMA A fragments)
+constexpr int F2_LDV = F2_COLS + 2;   // row stride of the V slice in shared memory
 
 template <int KIND>
 struct F2Smem {
     static constexpr int D = Dims<KIND>::D;
     static __host__ __device__ size_t bytes(int kc, int m4) {
-        const size_t nT = CAM + D * kc;
-        size_t stage = nT * V_BLK, vs = (size_t)m4 * F2_LDV;
-        size_t dbl = (stage > vs ? stage : vs) + nT * m4 + m4;
+        const size_t nT = CAM + D * kc, kp = (nT + 3) & ~(size_t)3;
+        size_t dbl = kp * F2_LDB + kp * F2_LDA + (size_t)64 * F2_LDV + 64 + 8 * F2_COLS;
         return dbl * sizeof(double) + (nT + 4) * sizeof(int);
     }
 };
 
 template <int KIND>
-__global__ void __launch_bounds__(F2_THREADS, 1)
+__global__ void __launch_bounds__(F2_THREADS, 2)
 k_f2(F2Args p) {
     constexpr int D = Dims<KIND>::D;
     constexpr int NT = F2_THREADS;
     extern __shared__ __align__(16) unsigned char fsm[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int kc = p.kc, m4 = p.m4, nT = CAM + D * kc;
+    const int kc = p.kc, m4 = p.m4, nT = CAM + D * kc, kp = (nT + 3) & ~3;
     const int ld = p.ld, n0 = p.n0, n1 = p.n1;
-    const int j0 = blockIdx.x * V_BLK;
+    const int j0 = blockIdx.x * F2_COLS;
+    const int vblock = blockIdx.x >> 1, half = blockIdx.x & 1;   // 64-column panel block and which half of it
     FrontArgs stampargs{};
     stampargs.prof = p.prof;
 
-    const size_t stage_dbl = (size_t)nT * V_BLK, vs_dbl = (size_t)m4 * F2_LDV;
-    double* s_stage = reinterpret_cast<double*>(fsm);                    // nT x 64: P_eff[T, block]; later V (m4 x F2_LDV)
-    double* s_At = s_stage + (stage_dbl > vs_dbl ? stage_dbl : vs_dbl);  // nT x m4
-    double* s_y = s_At + (size_t)nT * m4;                                // m4
-    int* s_T = reinterpret_cast<int*>(s_y + m4);                         // nT
+    double* s_stage = reinterpret_cast<double*>(fsm);        // kp x F2_LDB: P_eff[T, block] (rows >= nT zero)
+    double* s_At = s_stage + (size_t)kp * F2_LDB;            // kp x F2_LDA: A^T (columns >= m4 and rows >= nT zero)
+    double* s_V = s_At + (size_t)kp * F2_LDA;                // 64 x F2_LDV: V[:, block]
+    double* s_y = s_V + (size_t)64 * F2_LDV;                 // 64
+    double* s_red = s_y + 64;                                // 8 x F2_COLS partial sums of V^T y
+    int* s_T = reinterpret_cast<int*>(s_red + 8 * F2_COLS);  // nT
     __shared__ int s_last;
 
     pdl_wait();      // stream mode: made resident while the sweep before it retired
     pdl_trigger();   // the next k_f1 may take one of the SMs this grid leaves empty; it waits for this grid's end
     front_stamp(stampargs, 0);
     for (int a = tid; a < nT; a += NT) s_T[a] = p.T[a];
-    for (int a = tid; a < m4; a += NT) s_y[a] = p.y[a];
-    for (int e = 2 * tid; e < nT * m4; e += 2 * NT) cp_async16(s_At + e, p.At + e);   // nT m4 is even
+    for (int a = tid; a < 64; a += NT) s_y[a] = a < m4 ? p.y[a] : 0.0;
+    {   // A^T rows (m4 is a multiple of 4: 16-byte pieces never straddle a row)
+        const int pairs = m4 >> 1;
+        for (int e = tid; e < nT * pairs; e += NT) {
+            const int tb = e / pairs, a2 = e - tb * pairs;
+            cp_async16(s_At + (size_t)tb * F2_LDA + 2 * a2, p.At + (size_t)tb * m4 + 2 * a2);
+        }
+        const int padc = 64 - m4;
+        for (int e = tid; e < nT * padc; e += NT) {
+            const int tb = e / padc, a = m4 + (e - tb * padc);
+            s_At[(size_t)tb * F2_LDA + a] = 0.0;
+        }
+        for (int e = tid; e < (kp - nT) * F2_LDA; e += NT) s_At[(size_t)nT * F2_LDA + e] = 0.0;
+        for (int e = tid; e < (kp - nT) * F2_LDB; e += NT) s_stage[(size_t)nT * F2_LDB + e] = 0.0;
+    }
     __syncthreads();
-    // stage[a][0..64) = P_eff[T[a]][j0..j0+64); entries >= n0 are this frame's constants
-    for (int a = warp; a < nT; a += NT / 32) {
+    // stage[a][0..32) = P_eff[T[a]][j0..j0+32); entries >= n0 are this frame's constants.
+    // Half a warp per row: 16 lanes x 16 bytes.
+    for (int a = 2 * warp + (lane >> 4); a < nT; a += 2 * (NT / 32)) {
         const int i = s_T[a];
         const double* prow = p.P + (long long)i * ld;
-        const int j = j0 + 2 * lane;
-        double* dst = s_stage + a * V_BLK + 2 * lane;
+        const int c = 2 * (lane & 15);
+        const int j = j0 + c;
+        double* dst = s_stage + (size_t)a * F2_LDB + c;
         if (i < n0 && j + 1 < n0) {
             cp_async16(dst, prow + j);
         } else {
@@ -410,60 +429,61 @@ k_f2(F2Args p) {
     if (p.add_q) {   // predict folded in: diag(Q) on the staged rows
         for (int a = tid; a < nT; a += NT) {
             const int i = s_T[a];
-            if (i >= j0 && i < j0 + V_BLK) s_stage[a * V_BLK + (i - j0)] += process_noise(p.nz, i);
+            if (i >= j0 && i < j0 + F2_COLS) s_stage[(size_t)a * F2_LDB + (i - j0)] += process_noise(p.nz, i);
         }
         __syncthreads();
     }
     front_stamp(stampargs, 1);
 
-    // V[:, block] = A stage: thread (rg, cg) owns rows 4 rg .. 4 rg + 3 and columns
-    // 2 cg, 2 cg + 1, 32 + 2 cg, 33 + 2 cg (128-bit shared loads, 256 contiguous bytes per half warp)
-    const int rg = tid >> 4, cg = tid & 15;
-    double acc[4][4];
+    // V[:, block] = A stage on the FP64 tensor pipe (DMMA.8x8x4): warp w owns rows 8 w .. 8 w + 7 and all
+    // four 8-column tiles; lane (g, t) holds V[8 w + g][8 ct + 2 t .. + 1].
+    {
+        const int g = lane >> 2, t4 = lane & 3;
+        const int a0 = 8 * warp;
+        if (a0 < m4) {
+            double acc[4][2];
 #pragma unroll
-    for (int r = 0; r < 4; ++r)
+            for (int ct = 0; ct < 4; ++ct) acc[ct][0] = acc[ct][1] = 0.0;
+            const double* ap = s_At + (size_t)t4 * F2_LDA + a0 + g;
+            const double* bp = s_stage + (size_t)t4 * F2_LDB + g;
+#pragma unroll 2
+            for (int kk = 0; kk < kp; kk += 4) {
+                const double av = ap[(size_t)kk * F2_LDA];
+                double bv[4];
 #pragma unroll
-        for (int c = 0; c < 4; ++c) acc[r][c] = 0.0;
-    if (4 * rg < m4) {
-        const double* ap = s_At + 4 * rg;
-        const double* bp = s_stage + 2 * cg;
-#pragma unroll 4
-        for (int tb = 0; tb < nT; ++tb) {
-            const double2 a01 = *reinterpret_cast<const double2*>(ap + (size_t)tb * m4);
-            const double2 a23 = *reinterpret_cast<const double2*>(ap + (size_t)tb * m4 + 2);
-            const double2 b01 = *reinterpret_cast<const double2*>(bp + tb * V_BLK);
-            const double2 b23 = *reinterpret_cast<const double2*>(bp + tb * V_BLK + 32);
-            const double av[4] = {a01.x, a01.y, a23.x, a23.y};
-            const double bv[4] = {b01.x, b01.y, b23.x, b23.y};
+                for (int ct = 0; ct < 4; ++ct) bv[ct] = bp[(size_t)kk * F2_LDB + 8 * ct];
 #pragma unroll
-            for (int r = 0; r < 4; ++r)
+                for (int ct = 0; ct < 4; ++ct) dmma884(acc[ct][0], acc[ct][1], av, bv[ct]);
+            }
 #pragma unroll
-                for (int c = 0; c < 4; ++c) acc[r][c] += av[r] * bv[c];
-        }
-    }
-    __syncthreads();   // the staged rows are dead: their space takes V
-    double* s_V = s_stage;
-    if (4 * rg < m4) {
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            const int col = j0 + 2 * cg + (c & 1) + 32 * (c >> 1);
-            st256(p.Vt + (size_t)col * F1_LDT + 4 * rg, acc[0][c], acc[1][c], acc[2][c], acc[3][c]);
-        }
-#pragma unroll
-        for (int r = 0; r < 4; ++r) {
-            double* row = s_V + (size_t)(4 * rg + r) * F2_LDV + 2 * cg;
-            *reinterpret_cast<double2*>(row) = make_double2(acc[r][0], acc[r][1]);
-            *reinterpret_cast<double2*>(row + 32) = make_double2(acc[r][2], acc[r][3]);
+            for (int ct = 0; ct < 4; ++ct)
+                *reinterpret_cast<double2*>(s_V + (size_t)(a0 + g) * F2_LDV + 8 * ct + 2 * t4) = make_double2(acc[ct][0], acc[ct][1]);
         }
     }
     __syncthreads();
     front_stamp(stampargs, 2);
 
+    // panel by state column for the next k_f1's lazy operand: 4 consecutive rows per 256-bit store
+    {
+        const int q4 = m4 >> 2;
+        for (int e = tid; e < F2_COLS * q4; e += NT) {
+            const int c = e / q4, q = e - c * q4;
+            const double* v = s_V + (size_t)(4 * q) * F2_LDV + c;
+            st256(p.Vt + (size_t)(j0 + c) * F1_LDT + 4 * q, v[0], v[F2_LDV], v[2 * F2_LDV], v[3 * F2_LDV]);
+        }
+    }
     // dx (+)= V^T y; EKF (additive landmark states): each CTA applies its own columns, CTA 0 the camera
     __shared__ double s_dcam[CAM];
-    if (tid < V_BLK) {
+    {
+        double part = 0.0;
+        for (int a = warp; a < m4; a += NT / 32) part += s_V[(size_t)a * F2_LDV + lane] * s_y[a];
+        s_red[warp * F2_COLS + lane] = part;
+    }
+    __syncthreads();
+    if (tid < F2_COLS) {
         double dsum = 0.0;
-        for (int a = 0; a < m4; ++a) dsum += s_V[a * F2_LDV + tid] * s_y[a];
+#pragma unroll
+        for (int w = 0; w < NT / 32; ++w) dsum += s_red[w * F2_COLS + tid];
         const int j = j0 + tid;
         if (j < n1) {
             const double d = (p.use_delta ? p.dx_in[j] : 0.0) + dsum;
@@ -486,21 +506,22 @@ k_f2(F2Args p) {
         }
     }
     {
-        // both column orders of the block (sweep.cuh): position of column jj is v_pos_row / v_pos_col
-        double* vr = p.Vr + (size_t)blockIdx.x * m4 * V_LDB;
-        double* vc = p.Vc + (size_t)blockIdx.x * m4 * V_LDB;
-        for (int e = tid; e < m4 * V_BLK; e += NT) {
-            const int a = e / V_BLK, pos = e - a * V_BLK;
+        // both column orders of this half block (sweep.cuh): position `pos` of the 64-column block holds
+        // column cr (V_I order) / cc (V_J order); both maps stay inside a 32-column half
+        double* vr = p.Vr + (size_t)vblock * m4 * V_LDB;
+        double* vc = p.Vc + (size_t)vblock * m4 * V_LDB;
+        for (int e = tid; e < m4 * F2_COLS; e += NT) {
+            const int a = e / F2_COLS, pos = F2_COLS * half + (e - a * F2_COLS);
             const int cr = (pos & ~31) + 4 * (pos & 7) + ((pos & 31) >> 3);   // inverse maps: which column lands at `pos`
             const int cc = (pos & ~15) + 4 * ((pos & 7) >> 1) + 2 * ((pos & 15) >> 3) + (pos & 1);
-            vr[a * V_LDB + pos] = s_V[a * F2_LDV + cr];
-            vc[a * V_LDB + pos] = s_V[a * F2_LDV + cc];
+            vr[a * V_LDB + pos] = s_V[(size_t)a * F2_LDV + (cr - F2_COLS * half)];
+            vc[a * V_LDB + pos] = s_V[(size_t)a * F2_LDV + (cc - F2_COLS * half)];
         }
     }
 
     // covariance growth for this block's columns (first chunk only; EKF:279-290)
     if (p.first_chunk && n1 > n0) {
-        const int ja = j0, jb = min(j0 + V_BLK, n1);
+        const int ja = j0, jb = min(j0 + F2_COLS, n1);
         if (ja < jb) {
             const int wcols = jb - ja;  // new rows [n0, n1) x [ja, jb)
             for (int e = tid; e < (n1 - n0) * wcols; e += NT) {
