@@ -84,6 +84,20 @@ SIGNATURES = {
     "asb_batch_get_cameras": (C.c_int, [_vp, _dp, _ip]),
     "asb_batch_device_views": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp), _intp, _intp]),
     "asb_batch_profile": (C.c_int, [_vp, _dp]),
+    "asb_shard_partition": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, _intp, _intp, _intp]),
+    "asb_shard_unique_id": (C.c_int, [_vp, C.c_int]),
+    "asb_shard_create": (C.c_int, [C.c_int, C.c_int, _dp, C.POINTER(Noise), C.c_int, C.c_int, C.c_int, C.c_int,
+                                   _vp, C.POINTER(_vp)]),
+    "asb_shard_destroy": (C.c_int, [_vp]),
+    "asb_shard_set_stream": (C.c_int, [_vp, _vp]),
+    "asb_shard_synchronize": (C.c_int, [_vp]),
+    "asb_shard_observe": (C.c_int, [_vp, _ip, _dp, C.c_int]),
+    "asb_shard_stream_upload": (C.c_int, [_vp, _ip, _dp, _lp, C.c_int]),
+    "asb_shard_stream_run": (C.c_int, [_vp, C.c_int, C.c_int]),
+    "asb_shard_get_dims": (C.c_int, [_vp, _intp, _intp]),
+    "asb_shard_get_state": (C.c_int, [_vp, _dp, C.c_int]),
+    "asb_shard_get_cov_rows": (C.c_int, [_vp, _dp, C.c_longlong, _intp]),
+    "asb_shard_get_landmark_ids": (C.c_int, [_vp, _ip, C.c_int]),
     "asb_ippe_square": (C.c_int, [_fp, C.c_int64, _dp, _dp, C.c_double, _dp, C.c_int]),
     "asb_ippe_square_device": (C.c_int, [_vp, C.c_int64, _dp, _dp, C.c_double, _vp, _vp, _vp, _vp]),
     "asb_bench_sweep": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, _dp]),

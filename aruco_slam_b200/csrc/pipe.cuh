@@ -25,6 +25,8 @@ namespace asb {
 struct F1Args {
     double* state;               // read; new-landmark entries are stored
     const double* P;             // covariance to read: the running sweep's INPUT buffer when lazy
+    const double* PT_dense;      // row-sharded engine (filter_shard.cu): P[T,T] (nT x nT, lower triangle valid) summed
+                                 // over the row owners by NCCL; P is not read at all when this is set
     int ld, n0, n1;              // state dims before / after this frame's augmentation
     Noise nz;
     const int* idx;              // landmark index of each observation of the chunk
@@ -126,7 +128,7 @@ k_f1(F1Args p) {
         const double* prow = p.P + (long long)i * ld;
         for (int b = lane; b <= a; b += 32) {
             const int j = s_T[b];
-            if (i < n0 && j < n0) cp_async8(s_PT + a * nT + b, prow + j);
+            if (i < n0 && j < n0) cp_async8(s_PT + a * nT + b, p.PT_dense ? p.PT_dense + a * nT + b : prow + j);
             else s_PT[a * nT + b] = (i == j) ? p.nz.init_lm : 0.0;
         }
     }

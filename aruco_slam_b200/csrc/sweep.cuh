@@ -39,6 +39,11 @@ struct SweepExtra {
     // single tiles >= grid * n_static from the shared counter *tail until they run out, so that an SM
     // that is ahead (or a CTA whose range was a tile shorter) absorbs the remainder instead of
     // idling: with contiguous ranges alone the slowest CTA ends 8 % after the median one.
+    // Row-sharded engine (filter_shard.cu): this GPU owns the full rows [row0, row0 + 64 nI) of P, stored as
+    // a (64 nI) x ld block.  rect != 0: the tile list is the nI x nJ rectangle of 64 x 64 tiles (t = I nJ + J),
+    // every tile is stored directly (no mirror), VI comes from the LOCAL panel block I, the diagonal
+    // (Q, predict) is where row0 + local row == column.  SweepDual only.
+    int rect, row0, nJ;
     unsigned int* tail;        // counter of this launch (zero on entry)
     unsigned int* tail_reset;  // counter of the NEXT launch: zeroed by CTA 0
     int n_static;
@@ -280,10 +285,16 @@ k_sweep(const double* Pin, double* P, int ld, const double* __restrict__ Vr, con
         if (nx >= ntiles) nx = -1;
         s_next[slot] = nx;
         if (nx >= 0) {
-            int i = (int)((sqrtf(8.0f * (float)nx / (float)C::RATIO + 1.0f) - 1.0f) * 0.5f);   // estimate, fixed up
-            while (C::RATIO * (i + 1) * (i + 2) / 2 <= nx) ++i;
-            while (C::RATIO * i * (i + 1) / 2 > nx) --i;
-            const int j = nx - C::RATIO * i * (i + 1) / 2;
+            int i, j;
+            if (ex.rect) {
+                i = nx / ex.nJ;
+                j = nx - i * ex.nJ;
+            } else {
+                i = (int)((sqrtf(8.0f * (float)nx / (float)C::RATIO + 1.0f) - 1.0f) * 0.5f);   // estimate, fixed up
+                while (C::RATIO * (i + 1) * (i + 2) / 2 <= nx) ++i;
+                while (C::RATIO * i * (i + 1) / 2 > nx) --i;
+                j = nx - C::RATIO * i * (i + 1) / 2;
+            }
             s_nij[slot] = (i << 16) | j;
             load_vj(vbuf, j * TJ);
         }
@@ -347,7 +358,20 @@ k_sweep(const double* Pin, double* P, int ld, const double* __restrict__ Vr, con
                     pf[rm][rn][0] -= acc[rm][rn][0];
                     pf[rm][rn][1] -= acc[rm][rn][1];
                 }
-            if (interior) {
+            if (ex.rect) {   // row-sharded engine: local row block, every tile stored directly
+                if (ex.add_q && ex.row0 + i0 < j0 + TJ && ex.row0 + i0 + TI > j0) {   // tile crosses the diagonal
+#pragma unroll
+                    for (int rm = 0; rm < RM; ++rm)
+#pragma unroll
+                        for (int rn = 0; rn < RN; ++rn)
+#pragma unroll
+                            for (int e = 0; e < 2; ++e) {
+                                const int gi = ex.row0 + r0 + rm, j = c0 + 16 * (rn >> 1) + 2 * (rn & 1) + e;
+                                if (gi == j && gi < ex.n) pf[rm][rn][e] += process_noise(ex.nz, gi);
+                            }
+                }
+                tile_store<RM, RN>(P + (long long)r0 * ld + c0, ld, pf, pol_st);
+            } else if (interior) {
                 if (!(dbg & 4)) tile_store<RM, RN>(P + (long long)r0 * ld + c0, ld, pf, pol_st);
                 if (!(dbg & 2)) tile_store_mirror<RM, RN>(P + (long long)c0 * ld + r0, ld, pf, pol_mir);
             } else {
@@ -377,6 +401,10 @@ k_sweep(const double* Pin, double* P, int ld, const double* __restrict__ Vr, con
         while (C::RATIO * (I + 1) * (I + 2) / 2 <= t_first) ++I;
         while (C::RATIO * I * (I + 1) / 2 > t_first) --I;
         int J = t_first - C::RATIO * I * (I + 1) / 2;
+        if (ex.rect) {
+            I = t_first / ex.nJ;
+            J = t_first - I * ex.nJ;
+        }
         if (tid == 0) {
             load_vi(I * TI);
             load_vj(0, J * TJ);
@@ -385,7 +413,7 @@ k_sweep(const double* Pin, double* P, int ld, const double* __restrict__ Vr, con
             int In = I, Jn = rev ? J - 1 : J + 1;
             if (rev) {
                 if (Jn < 0) { In = I - 1; Jn = C::RATIO * I - 1; }
-            } else if (Jn == C::RATIO * (I + 1)) { In = I + 1; Jn = 0; }
+            } else if (Jn == (ex.rect ? ex.nJ : C::RATIO * (I + 1))) { In = I + 1; Jn = 0; }
             const bool has_next = t + 1 < t_end;
             if (tid == 0 && has_next) load_vj(buf ^ 1, Jn * TJ);  // buffer freed by the last __syncthreads
             do_tile(I, J, buf, (!has_next && dyn) ? 0 : -1);
@@ -467,7 +495,7 @@ __device__ __forceinline__ void tile_of(int t, int& I, int& J) {  // t = I (I + 
 }
 }  // namespace ws
 
-__global__ void __launch_bounds__(ws::THREADS, 1)
+static __global__ void __launch_bounds__(ws::THREADS, 1)
 k_sweep_ws(double* __restrict__ P, int ld, const double* __restrict__ Vr, const double* __restrict__ Vc, int m4,
            int ntiles, int dbg, SweepExtra ex) {
     using namespace ws;

@@ -325,6 +325,7 @@ class _CudaFilter(BaseFilter):
 
     def stream_run(self, t0: int, t1: int) -> None:
         _lib.check(self._lib.asb_stream_run(self._h, int(t0), int(t1)))
+        self._refresh_landmarks()
 
     def last_update(self):
         """(nu, blocks (k, r, 10+d), dx) of the last update, for parity tests."""

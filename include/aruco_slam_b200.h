@@ -156,6 +156,35 @@ ASB_API int asb_batch_device_views(asb_batch* b, void** d_states, void** d_covs,
  * Cholesky, solve, -, P update, apply), measurement aid. */
 ASB_API int asb_batch_profile(asb_batch* b, double clocks[10]);
 
+/* ---- row-sharded filter: ONE EKF / EKF_Rotations whose covariance rows are spread over the GPUs
+ *      of a box, one process (rank) per GPU (BASELINE config C3 at N GPUs).
+ * Same algorithm and same results as asb_filter (observe = EKF:58-82 / ROT:66-90); the state and
+ * the id map are replicated, rank g owns rows [row0,row1) of `uncertainty` (EKF:48, EKF:155-156).
+ * Every rank must make the same calls with the same arguments, in the same order: each update
+ * runs two NCCL collectives (all-reduce of P[T,T], all-gather of the K H P panel) on the stream.
+ * NCCL is opened at run time (libnccl.so.2, the copy torch has loaded when called from Python). */
+typedef struct asb_shard asb_shard;
+/* The row partition (callable without a GPU): rows [*row0,*row1) of rank `rank`, and the padded
+ * dimension *ld (= world * rows per rank >= 10 + d*max_landmarks, rows per rank a multiple of 64). */
+ASB_API int asb_shard_partition(int kind, int max_landmarks, int world, int rank, int* row0, int* row1, int* ld);
+/* ncclGetUniqueId: call on rank 0, broadcast the 128 bytes to every rank (torch.distributed, MPI ...). */
+ASB_API int asb_shard_unique_id(void* out128, int bytes);
+ASB_API int asb_shard_create(int kind, int quat_mode, const double pose0[10], const asb_noise* cfg,
+                     int max_landmarks, int device, int rank, int world, const void* unique_id128,
+                     asb_shard** out);
+ASB_API int asb_shard_destroy(asb_shard* s);
+ASB_API int asb_shard_set_stream(asb_shard* s, void* cuda_stream);
+ASB_API int asb_shard_synchronize(asb_shard* s);
+ASB_API int asb_shard_observe(asb_shard* s, const int32_t* ids, const double* poses, int k);
+ASB_API int asb_shard_stream_upload(asb_shard* s, const int32_t* ids, const double* poses,
+                            const int64_t* offsets, int n_frames);
+ASB_API int asb_shard_stream_run(asb_shard* s, int t0, int t1);
+ASB_API int asb_shard_get_dims(asb_shard* s, int* n_landmarks, int* n_state);
+ASB_API int asb_shard_get_state(asb_shard* s, double* out, int n_state);
+/* This rank's live rows of `uncertainty`: (*n_rows, N) row-major, rows row0 .. min(row1, N). */
+ASB_API int asb_shard_get_cov_rows(asb_shard* s, double* out, long long capacity, int* n_rows);
+ASB_API int asb_shard_get_landmark_ids(asb_shard* s, int32_t* ids_in_index_order, int capacity);
+
 /* ---- square-marker pose: estimate_pose_of_markers (BASE:92-171), i.e.
  *      cv2.solvePnP(marker_points, c, K, dist, flags=SOLVEPNP_IPPE_SQUARE) per marker ----
  * corners (n,4,2) float32 pixel corners in the order BASE:112-120 expects; camera_matrix

@@ -83,3 +83,24 @@ def test_gather_results_gloo_world2(n_total):
 def test_gather_results_single_process_identity():
     a = np.arange(30.0).reshape(3, 10)
     assert asb_dist.gather_results(a, 3) is a or np.array_equal(asb_dist.gather_results(a, 3), a)
+
+
+# ---- row-sharded filter (filter_shard.cu): the partition and the row-block gather, on CPU -------
+@pytest.mark.parametrize("kind,max_lm,world", [("ekf", 2000, 1), ("ekf", 2000, 2), ("ekf", 2000, 8),
+                                               ("rot", 64, 4), ("ekf", 1, 8), ("rot", 2000, 3)])
+def test_shard_partition_covers_state(kind, max_lm, world):
+    from aruco_slam_b200 import sharded
+    d = 3 if kind == "ekf" else 10
+    spans = [sharded.partition(kind, max_lm, world, r) for r in range(world)]
+    ld = spans[0][2]
+    assert spans[0][0] == 0 and spans[-1][1] == ld and ld >= 10 + d * max_lm
+    for (a, b, l1), (c, e, l2) in zip(spans, spans[1:]):
+        assert b == c and l1 == l2
+    sizes = {b - a for a, b, _ in spans}
+    assert len(sizes) == 1 and sizes.pop() % 64 == 0   # whole 64-column panel blocks, equal on every rank
+
+
+def test_shard_partition_rejects_bad_rank():
+    from aruco_slam_b200 import _lib, sharded
+    with pytest.raises(_lib.AsbError):
+        sharded.partition("ekf", 10, 2, 2)
