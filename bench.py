@@ -50,7 +50,7 @@ def parse_args():
     ap.add_argument("--kind", default="ekf", choices=["ekf", "rot"])
     ap.add_argument("--quat-mode", default="as_written", choices=["as_written", "scalar_first"])
     ap.add_argument("--no-extras", action="store_true", help="skip the C3 / C4 legs")
-    ap.add_argument("--only", default=None, choices=["c3", "c4"],
+    ap.add_argument("--only", default=None, choices=["c3", "c4", "c3s"],
                     help="profiling aid: run just that leg and print its JSON")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU baseline budget")
     return ap.parse_args()
@@ -273,11 +273,46 @@ def leg_c3(torch, stream_ptr, hbm_peak):
         "value": 20.0 * timed_frames / (ms * 1e-3), "unit": UNIT, "us_per_frame": 1e3 * ms / timed_frames,
         "frames": timed_frames, "gpu_launches_per_frame": 3,
         "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": ach / hbm_peak, "traffic": None,
-                     "note": "achieved = 16*N^2 B per frame / whole-frame time (k_f2 + k_sweep on the critical path, k_f1 of the next frame overlapped)"},
+                     "frac": ach / hbm_peak, "traffic": 391.1e6,
+                     "note": "achieved = 16*N^2 B per frame / whole-frame time (k_f2 + k_sweep on the critical "
+                             "path, k_f1 of the next frame overlapped); traffic = dram read + write bytes of one "
+                             "k_sweep launch, ncu --set full (profiles/r01b_k_sweep.txt): only the lower "
+                             "triangle is read"},
         "e2e": {"value": 20.0 * t_frames / wall, "unit": UNIT, "h2d_bytes_per_step": 20 * 52,
                 "d2h_bytes_per_step": 8 * 6010},
     }
+
+
+def leg_c3_sharded(torch, dist, rank, world, local, stream_ptr, hbm_peak):
+    """C3 with the covariance rows sharded over `world` GPUs (filter_shard.cu): every rank feeds the
+    same stream; two NCCL collectives per frame inside the library; max over ranks."""
+    from aruco_slam_b200 import synth
+    from aruco_slam_b200.sharded import ShardedFilter
+    timed_frames, warm = 200, 20
+    stream, n_build = synth.make_map_build_stream(2000, 20, warm + timed_frames)
+    f = ShardedFilter("ekf", np.array([0, 0, 0, 1, 0, 0, 0, 0, 0, 0.0]), 2000, dist=dist, rank=rank, world=world,
+                      device=local, quat_mode="as_written")
+    f.set_stream(stream_ptr)
+    ids, poses, off = stream.packed()
+    f.stream_upload(ids, poses, off)
+    f.stream_run(0, n_build + warm)
+    ms = timed(torch, dist, lambda: f.stream_run(n_build + warm, n_build + warm + timed_frames), 1)
+    f.synchronize()
+    cam, _ = f.get_poses()
+    n = 6010
+    ach = 16.0 * n * n * timed_frames / (ms * 1e-3) / 1e9
+    out = {"workload": f"C3 row-sharded: single EKF, 2000-marker map (N=6010), 20 markers/frame, covariance rows "
+                       f"over {world} GPU(s), NCCL all-reduce of P[T,T] + all-gather of the V panel per frame",
+           "value": 20.0 * timed_frames / (ms * 1e-3), "unit": UNIT, "us_per_frame": 1e3 * ms / timed_frames,
+           "n_gpus": world, "frames": timed_frames, "rows_per_gpu": f.row1 - f.row0,
+           "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak * world, "unit": "GB/s",
+                        "frac": ach / (hbm_peak * world), "traffic": None,
+                        "note": "16*N^2 B per frame / frame time against world x the measured HBM peak; the "
+                                "rectangular row sweep does 2x the FP64 work of the triangle sweep and each "
+                                "frame pays two NCCL collectives"},
+           "camera_finite": bool(np.isfinite(cam).all())}
+    f.close()
+    return out
 
 
 def leg_c4(torch, stream_ptr, hbm_peak, fp64_peak):
@@ -340,9 +375,15 @@ def run_b200(args):
     assert stream_ptr != 0
 
     if args.only:
-        leg = leg_c3(torch, stream_ptr, hbm_peak) if args.only == "c3" else \
-            leg_c4(torch, stream_ptr, hbm_peak, fp64_peak)
-        print(json.dumps(leg), flush=True)
+        if args.only == "c3s":
+            leg = leg_c3_sharded(torch, dist, rank, world, local, stream_ptr, hbm_peak)
+        else:
+            leg = leg_c3(torch, stream_ptr, hbm_peak) if args.only == "c3" else \
+                leg_c4(torch, stream_ptr, hbm_peak, fp64_peak)
+        if rank == 0:
+            print(json.dumps(leg), flush=True)
+        if dist is not None:
+            dist.destroy_process_group()
         return
 
     # ---- synthetic observations of this rank's shard --------------------------------------
@@ -428,6 +469,13 @@ def run_b200(args):
         "valid": ok, "marker_updates_per_step_per_gpu": n_updates, "gen_seconds": gen_s,
     }
     del batch
+    if world > 1 and not args.no_extras:
+        # the one configuration whose path has a real exchange step: C3 with its rows over all ranks
+        try:
+            leg = leg_c3_sharded(torch, dist, rank, world, local, stream_ptr, hbm_peak)
+        except Exception as exc:
+            leg = {"error": repr(exc)}
+        line["workloads"] = {"c3_sharded": leg}
     if rank == 0 and world == 1:
         if not args.no_extras:
             line["workloads"] = {}
