@@ -29,6 +29,7 @@ struct BatchParams {
     const long long* offsets;  // n_seq * n_frames + 1
     long long state_stride, cov_stride;
     int n_seq, n_frames, t0, t1, max_lm, max_obs, as_written, p_in_smem;
+    int seq0, seq1;        // this launch handles sequences [seq0, seq1)
     Noise nz;
     unsigned long long* prof;   // 10 phase accumulators (clocks) of CTA 0, may be null
 };
@@ -100,7 +101,7 @@ k_batch(BatchParams p) {
             prof_t = now_;                           \
         }                                            \
     } while (0)
-    for (int seq = blockIdx.x; seq < p.n_seq; seq += gridDim.x) {
+    for (int seq = p.seq0 + blockIdx.x; seq < p.seq1; seq += gridDim.x) {
         double* g_state = p.states + (long long)seq * p.state_stride;
         double* g_P = p.covs + (long long)seq * p.cov_stride;
         int* g_tab = p.lm_ids + (long long)seq * p.max_lm;

@@ -30,6 +30,15 @@ struct asb_batch {
     int sm_count = 0, smem_optin = 0;
     int ck = 4;       // markers per chunk (ASB_BATCH_CK)
     int threads = 128;
+    // Pipelined host path: asb_batch_upload copies the observations in N_GROUPS sequence groups on a
+    // copy stream; the asb_batch_run that follows launches one kernel per group as soon as that
+    // group's bytes have landed (two run streams, so the tail of one group's kernel is filled by the
+    // next), i.e. all but the first group's H2D time hides behind compute.
+    static constexpr int N_GROUPS = 8;
+    cudaStream_t copy_stream = nullptr, run_streams[2] = {nullptr, nullptr};
+    cudaEvent_t ev_group[N_GROUPS]{}, ev_main = nullptr, ev_done[2] = {nullptr, nullptr};
+    bool fresh_upload = false;
+    int groups = 1;
 };
 
 static int check(asb_batch* b) {
@@ -59,7 +68,7 @@ static size_t batch_smem_base(int D, int R, int CK, int max_lm, int max_obs) {
 }
 
 template <int KIND, int CK, int NT>
-static int launch_batch(asb_batch* b, const BatchParams& p, size_t smem, int grid) {
+static int launch_batch(asb_batch* b, const BatchParams& p, size_t smem, int grid, cudaStream_t st) {
     auto kern = k_batch<KIND, CK, NT>;
     ASB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     ASB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
@@ -69,15 +78,27 @@ static int launch_batch(asb_batch* b, const BatchParams& p, size_t smem, int gri
     if (occ < 1) return fail(ASB_ERR_CAPACITY, "k_batch does not fit on an SM (%zu B shared memory)", smem);
     grid = std::min(grid, b->sm_count * occ);
     if (std::getenv("ASB_BATCH_VERBOSE")) fprintf(stderr, "k_batch<%d,%d,%d>: %d CTAs/SM, grid %d, smem %zu\n", KIND, CK, NT, occ, grid, smem);
-    kern<<<grid, NT, smem, b->stream>>>(p);
+    kern<<<grid, NT, smem, st>>>(p);
     ASB_CUDA(cudaGetLastError());
     return ASB_OK;
 }
 
 template <int KIND, int CK>
-static int launch_batch_nt(asb_batch* b, const BatchParams& p, size_t smem, int grid) {
-    if (b->threads >= 256) return launch_batch<KIND, CK, 256>(b, p, smem, grid);
-    return launch_batch<KIND, CK, 128>(b, p, smem, grid);
+static int launch_batch_nt(asb_batch* b, const BatchParams& p, size_t smem, int grid, cudaStream_t st) {
+    if (b->threads >= 256) return launch_batch<KIND, CK, 256>(b, p, smem, grid, st);
+    return launch_batch<KIND, CK, 128>(b, p, smem, grid, st);
+}
+
+static int launch_batch_dyn(asb_batch* b, const BatchParams& p, size_t smem, int grid, cudaStream_t st) {
+#define ASB_DISPATCH(KIND)                                                     \
+    switch (b->ck) {                                                           \
+        case 2: return launch_batch_nt<KIND, 2>(b, p, smem, grid, st);         \
+        case 8: return launch_batch_nt<KIND, 8>(b, p, smem, grid, st);         \
+        default: return launch_batch_nt<KIND, 4>(b, p, smem, grid, st);        \
+    }
+    if (b->kind == ASB_KIND_EKF) { ASB_DISPATCH(0) }
+    ASB_DISPATCH(1)
+#undef ASB_DISPATCH
 }
 
 extern "C" {
@@ -123,6 +144,13 @@ int asb_batch_create(int kind, int quat_mode, const double pose0[10], const asb_
     else b->threads = b->ncap > 150 ? 256 : 128;
     ASB_CUDA(cudaStreamCreateWithFlags(&b->own_stream, cudaStreamNonBlocking));
     b->stream = b->own_stream;
+    ASB_CUDA(cudaStreamCreateWithFlags(&b->copy_stream, cudaStreamNonBlocking));
+    for (auto& st : b->run_streams) ASB_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    for (auto& e : b->ev_group) ASB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (auto& e : b->ev_done) ASB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    ASB_CUDA(cudaEventCreateWithFlags(&b->ev_main, cudaEventDisableTiming));
+    b->groups = n_seq >= 8 * asb_batch::N_GROUPS ? asb_batch::N_GROUPS : 1;
+    if (const char* e = std::getenv("ASB_BATCH_GROUPS")) b->groups = std::max(1, std::min(std::atoi(e), (int)asb_batch::N_GROUPS));
     ASB_CUDA(dmalloc(&b->d_states, (size_t)n_seq * b->state_stride));
     ASB_CUDA(dmalloc(&b->d_covs, (size_t)n_seq * b->cov_stride));
     ASB_CUDA(dmalloc(&b->d_nlm, (size_t)n_seq));
@@ -153,6 +181,12 @@ int asb_batch_destroy(asb_batch* b) {
     cudaFree(b->d_status); cudaFree(b->d_ids); cudaFree(b->d_poses); cudaFree(b->d_off);
     cudaFree(b->d_dense); cudaFree(b->d_pose0);
     cudaStreamDestroy(b->own_stream);
+    cudaStreamSynchronize(b->copy_stream);
+    cudaStreamDestroy(b->copy_stream);
+    for (auto& st : b->run_streams) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
+    for (auto& e : b->ev_group) cudaEventDestroy(e);
+    for (auto& e : b->ev_done) cudaEventDestroy(e);
+    cudaEventDestroy(b->ev_main);
     b->magic = 0;
     delete b;
     return ASB_OK;
@@ -193,9 +227,24 @@ int asb_batch_upload(asb_batch* b, const int32_t* ids, const double* poses, cons
         b->n_frames = n_frames;
     }
     static_assert(sizeof(long long) == sizeof(int64_t), "offset width");
-    ASB_CUDA(cudaMemcpyAsync(b->d_ids, ids, (size_t)total * sizeof(int), cudaMemcpyHostToDevice, b->stream));
-    ASB_CUDA(cudaMemcpyAsync(b->d_poses, poses, (size_t)total * 6 * sizeof(double), cudaMemcpyHostToDevice, b->stream));
-    ASB_CUDA(cudaMemcpyAsync(b->d_off, offsets, (size_t)(nrec + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, b->stream));
+    // group g = sequences [n_seq g / G, n_seq (g+1) / G): its ids / poses / offsets are contiguous
+    // (the stream is packed sequence-major).  The copies wait for whatever the main stream has
+    // queued so far (a run that still reads the old observations).
+    ASB_CUDA(cudaEventRecord(b->ev_main, b->stream));
+    ASB_CUDA(cudaStreamWaitEvent(b->copy_stream, b->ev_main, 0));
+    for (int g = 0; g < b->groups; ++g) {
+        const long long s0 = (long long)b->n_seq * g / b->groups, s1 = (long long)b->n_seq * (g + 1) / b->groups;
+        const long long r0 = s0 * n_frames, r1 = s1 * n_frames;
+        const long long o0 = offsets[r0], o1 = offsets[r1];
+        const long long nrecs = r1 - r0 + (g == b->groups - 1 ? 1 : 0);
+        ASB_CUDA(cudaMemcpyAsync(b->d_off + r0, offsets + r0, (size_t)nrecs * sizeof(int64_t), cudaMemcpyHostToDevice, b->copy_stream));
+        if (g < b->groups - 1)   // a kernel reads offsets[r1] as the end of its last record
+            ASB_CUDA(cudaMemcpyAsync(b->d_off + r1, offsets + r1, sizeof(int64_t), cudaMemcpyHostToDevice, b->copy_stream));
+        ASB_CUDA(cudaMemcpyAsync(b->d_ids + o0, ids + o0, (size_t)(o1 - o0) * sizeof(int), cudaMemcpyHostToDevice, b->copy_stream));
+        ASB_CUDA(cudaMemcpyAsync(b->d_poses + 6 * o0, poses + 6 * o0, (size_t)(o1 - o0) * 6 * sizeof(double), cudaMemcpyHostToDevice, b->copy_stream));
+        ASB_CUDA(cudaEventRecord(b->ev_group[g], b->copy_stream));
+    }
+    b->fresh_upload = true;
     return ASB_OK;
 }
 
@@ -219,16 +268,30 @@ int asb_batch_run(asb_batch* b, int t0, int t1) {
     if (smem > (size_t)b->smem_optin)
         return fail(ASB_ERR_CAPACITY, "batched filter needs %zu B shared memory > %d", smem, b->smem_optin);
     const int per_sm = std::max(1, std::min(8, (int)((size_t)(b->smem_optin + 1024) / (smem + 1024))));
-    const int grid = std::min(b->n_seq, b->sm_count * per_sm);
-#define ASB_DISPATCH(KIND)                                                     \
-    switch (b->ck) {                                                           \
-        case 2: return launch_batch_nt<KIND, 2>(b, p, smem, grid);             \
-        case 8: return launch_batch_nt<KIND, 8>(b, p, smem, grid);             \
-        default: return launch_batch_nt<KIND, 4>(b, p, smem, grid);            \
+    if (!b->fresh_upload || b->groups == 1) {
+        // observations already resident: one persistent launch over all sequences
+        if (b->fresh_upload) ASB_CUDA(cudaStreamWaitEvent(b->stream, b->ev_group[0], 0));
+        b->fresh_upload = false;
+        p.seq0 = 0; p.seq1 = b->n_seq;
+        return launch_batch_dyn(b, p, smem, std::min(b->n_seq, b->sm_count * per_sm), b->stream);
     }
-    if (b->kind == ASB_KIND_EKF) { ASB_DISPATCH(0) }
-    ASB_DISPATCH(1)
-#undef ASB_DISPATCH
+    // straight after an upload: one launch per sequence group, each gated on that group's copy
+    b->fresh_upload = false;
+    ASB_CUDA(cudaEventRecord(b->ev_main, b->stream));
+    for (auto& st : b->run_streams) ASB_CUDA(cudaStreamWaitEvent(st, b->ev_main, 0));
+    for (int g = 0; g < b->groups; ++g) {
+        cudaStream_t st = b->run_streams[g & 1];
+        ASB_CUDA(cudaStreamWaitEvent(st, b->ev_group[g], 0));
+        p.seq0 = (int)((long long)b->n_seq * g / b->groups);
+        p.seq1 = (int)((long long)b->n_seq * (g + 1) / b->groups);
+        int rc = launch_batch_dyn(b, p, smem, std::min(p.seq1 - p.seq0, b->sm_count * per_sm), st);
+        if (rc != ASB_OK) return rc;
+    }
+    for (int i = 0; i < 2; ++i) {
+        ASB_CUDA(cudaEventRecord(b->ev_done[i], b->run_streams[i]));
+        ASB_CUDA(cudaStreamWaitEvent(b->stream, b->ev_done[i], 0));
+    }
+    return ASB_OK;
 }
 
 int asb_batch_profile(asb_batch* b, double clocks[10]) {
