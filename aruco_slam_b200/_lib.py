@@ -54,6 +54,7 @@ SIGNATURES = {
     "asb_filter_set_stream": (C.c_int, [_vp, _vp]),
     "asb_filter_synchronize": (C.c_int, [_vp]),
     "asb_observe": (C.c_int, [_vp, _ip, _dp, C.c_int]),
+    "asb_observe_corners": (C.c_int, [_vp, _ip, _fp, C.c_int, _dp, _dp, C.c_double, _dp]),
     "asb_predict": (C.c_int, [_vp]),
     "asb_update": (C.c_int, [_vp, _ip, _dp, C.c_int]),
     "asb_add_marker": (C.c_int, [_vp, C.c_int32, _dp, _dp]),

@@ -46,6 +46,8 @@ struct asb_filter {
     int* h_idx = nullptr; double* h_pose = nullptr; unsigned char* h_new = nullptr;
     int* d_idx = nullptr; double* d_pose = nullptr; unsigned char* d_new = nullptr;
     cudaEvent_t slot_ev[N_SLOTS]{};
+    float* h_corner = nullptr; float* d_corner = nullptr;   // asb_observe_corners: (slot, max_obs, 4, 2) float32
+    cudaEvent_t ev_pose = nullptr;                            // the IPPE poses of that call are back on the host
     int slot = 0;
     int last_k = 0;
     const int* last_idx = nullptr;
@@ -323,19 +325,43 @@ static int launch_frame_dyn(asb_filter* f, const int* idx, const double* pose, c
 }
 
 // Stage k observations into the next ring slot and copy them to the device (async).
+// Corner-fed frames (asb_observe_corners): `poses` is null and the slot's device poses come from the
+// IPPE kernel (ippe.cu) run on the same stream; they are also copied back into the slot's pinned
+// host poses (ev_pose) for the caller.
+struct CornerFeed {
+    const float* corners;
+    const double* camera_matrix;
+    const double* dist_coeffs;
+    double marker_size;
+};
+
 static int stage(asb_filter* f, const std::vector<int>& idx, const double* poses,
                  const std::vector<unsigned char>& isnew, int k, int** d_idx, double** d_pose,
-                 unsigned char** d_new, cudaStream_t st) {
+                 unsigned char** d_new, cudaStream_t st, const CornerFeed* feed = nullptr,
+                 double** h_pose_slot = nullptr) {
     const int s = f->slot;
     f->slot = (f->slot + 1) % N_SLOTS;
     ASB_CUDA(cudaEventSynchronize(f->slot_ev[s]));
     const size_t o = (size_t)s * f->max_obs;
     std::memcpy(f->h_idx + o, idx.data(), k * sizeof(int));
-    std::memcpy(f->h_pose + 6 * o, poses, (size_t)k * 6 * sizeof(double));
     std::memcpy(f->h_new + o, isnew.data(), k);
     ASB_CUDA(cudaMemcpyAsync(f->d_idx + o, f->h_idx + o, k * sizeof(int), cudaMemcpyHostToDevice, st));
-    ASB_CUDA(cudaMemcpyAsync(f->d_pose + 6 * o, f->h_pose + 6 * o, (size_t)k * 6 * sizeof(double),
-                             cudaMemcpyHostToDevice, st));
+    if (feed) {
+        std::memcpy(f->h_corner + 8 * o, feed->corners, (size_t)k * 8 * sizeof(float));
+        ASB_CUDA(cudaMemcpyAsync(f->d_corner + 8 * o, f->h_corner + 8 * o, (size_t)k * 8 * sizeof(float),
+                                 cudaMemcpyHostToDevice, st));
+        int rc = asb_ippe_square_device(f->d_corner + 8 * o, k, feed->camera_matrix, feed->dist_coeffs,
+                                        feed->marker_size, f->d_pose + 6 * o, nullptr, nullptr, st);
+        if (rc != ASB_OK) return rc;
+        ASB_CUDA(cudaMemcpyAsync(f->h_pose + 6 * o, f->d_pose + 6 * o, (size_t)k * 6 * sizeof(double),
+                                 cudaMemcpyDeviceToHost, st));
+        ASB_CUDA(cudaEventRecord(f->ev_pose, st));
+        if (h_pose_slot) *h_pose_slot = f->h_pose + 6 * o;
+    } else {
+        std::memcpy(f->h_pose + 6 * o, poses, (size_t)k * 6 * sizeof(double));
+        ASB_CUDA(cudaMemcpyAsync(f->d_pose + 6 * o, f->h_pose + 6 * o, (size_t)k * 6 * sizeof(double),
+                                 cudaMemcpyHostToDevice, st));
+    }
     ASB_CUDA(cudaMemcpyAsync(f->d_new + o, f->h_new + o, k, cudaMemcpyHostToDevice, st));
     ASB_CUDA(cudaEventRecord(f->slot_ev[s], st));
     *d_idx = f->d_idx + o;
@@ -443,6 +469,9 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
     ASB_CUDA(cudaMallocHost(&f->h_idx, (size_t)N_SLOTS * f->max_obs * sizeof(int)));
     ASB_CUDA(cudaMallocHost(&f->h_pose, (size_t)N_SLOTS * f->max_obs * 6 * sizeof(double)));
     ASB_CUDA(cudaMallocHost(&f->h_new, (size_t)N_SLOTS * f->max_obs));
+    ASB_CUDA(cudaMallocHost(&f->h_corner, (size_t)N_SLOTS * f->max_obs * 8 * sizeof(float)));
+    ASB_CUDA(dmalloc(&f->d_corner, (size_t)N_SLOTS * f->max_obs * 8));
+    ASB_CUDA(cudaEventCreateWithFlags(&f->ev_pose, cudaEventDisableTiming));
     for (auto& e : f->slot_ev) ASB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     ASB_CUDA(cudaMemsetAsync(f->d_P, 0, ld * ld * sizeof(double), f->stream));
     ASB_CUDA(cudaMemsetAsync(f->d_state, 0, ld * sizeof(double), f->stream));
@@ -499,6 +528,8 @@ int asb_filter_destroy(asb_filter* f) {
     cudaFree(f->d_status); cudaFree(f->d_prof); cudaFree(f->d_idx); cudaFree(f->d_pose); cudaFree(f->d_new);
     cudaFree(f->s_idx); cudaFree(f->s_pose); cudaFree(f->s_new);
     cudaFreeHost(f->h_idx); cudaFreeHost(f->h_pose); cudaFreeHost(f->h_new);
+    cudaFreeHost(f->h_corner); cudaFree(f->d_corner);
+    if (f->ev_pose) cudaEventDestroy(f->ev_pose);
     for (auto& e : f->slot_ev) cudaEventDestroy(e);
     cudaStreamDestroy(f->own_stream);
     f->magic = 0;
@@ -520,8 +551,8 @@ int asb_filter_synchronize(asb_filter* f) {
 }
 
 static int observe_impl(asb_filter* f, const int32_t* ids, const double* poses, int k, bool add_new,
-                        bool do_predict) {
-    if (k < 0 || (k > 0 && (!ids || !poses))) return fail(ASB_ERR_BAD_ARG, "bad ids/poses/k");
+                        bool do_predict, const CornerFeed* feed = nullptr, double* poses_out = nullptr) {
+    if (k < 0 || (k > 0 && (!ids || (!poses && !feed)))) return fail(ASB_ERR_BAD_ARG, "bad ids/poses/k");
     if (k > f->max_obs) return fail(ASB_ERR_CAPACITY, "%d observations > per-frame capacity %d", k, f->max_obs);
     std::vector<int> idx(k);
     std::vector<unsigned char> isnew(k, 0);
@@ -559,8 +590,18 @@ static int observe_impl(asb_filter* f, const int32_t* ids, const double* poses, 
         // a pipelined update reads its observations in k_f1 on the side stream
         const bool piped = f->pipeline != 0;
         if (piped) pipe_wait(f);
-        int rc = stage(f, idx, poses, isnew, k, &d_idx, &d_pose, &d_new, piped ? f->side : f->stream);
+        double* h_slot = nullptr;
+        int rc = stage(f, idx, poses, isnew, k, &d_idx, &d_pose, &d_new, piped ? f->side : f->stream, feed, &h_slot);
         if (rc != ASB_OK) return rc;
+        f->last_k = k;
+        f->last_idx = d_idx;
+        rc = launch_frame_dyn(f, d_idx, d_pose, d_new, k, n0, n1, do_predict, true);
+        if (rc == ASB_OK && feed && poses_out) {
+            // only the IPPE kernel and its 48 k bytes are waited for; the update stays queued
+            ASB_CUDA(cudaEventSynchronize(f->ev_pose));
+            std::memcpy(poses_out, h_slot, (size_t)k * 6 * sizeof(double));
+        }
+        return rc;
     }
     f->last_k = k;
     f->last_idx = d_idx;
@@ -570,6 +611,17 @@ static int observe_impl(asb_filter* f, const int32_t* ids, const double* poses, 
 int asb_observe(asb_filter* f, const int32_t* ids, const double* poses, int k) {
     ASB_CHECK_HANDLE(f);
     return observe_impl(f, ids, poses, k, true, true);
+}
+
+// process_frame's hot path in one call (BASE:196-204): estimate_pose_of_markers on the k detected
+// corner sets and observe(ids, those poses), without the poses leaving the device in between.
+int asb_observe_corners(asb_filter* f, const int32_t* ids, const float* corners, int k,
+                        const double camera_matrix[9], const double dist_coeffs[5], double marker_size,
+                        double* poses_out) {
+    ASB_CHECK_HANDLE(f);
+    if (k <= 0 || !ids || !corners || !camera_matrix || !dist_coeffs) return fail(ASB_ERR_BAD_ARG, "bad ids/corners/k/intrinsics");
+    CornerFeed feed{corners, camera_matrix, dist_coeffs, marker_size};
+    return observe_impl(f, ids, nullptr, k, true, true, &feed, poses_out);
 }
 
 int asb_predict(asb_filter* f) {

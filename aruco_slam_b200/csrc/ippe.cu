@@ -10,6 +10,9 @@
 //   (3) IPPE: the two rotations from the homography Jacobian at the origin;
 //   (4) least-squares translation for each rotation (3x3 normal equations);
 //   (5) order by float reprojection error; (6) Rodrigues vector of the better one.
+#include <algorithm>
+#include <mutex>
+
 #include "common.cuh"
 
 namespace asb {
@@ -235,18 +238,28 @@ int asb_ippe_square(const float* corners, int64_t n, const double camera_matrix[
         return fail(ASB_ERR_CUDA, "no CUDA device: this library has no CPU fallback");
     if (n == 0) return ASB_OK;
     ASB_CUDA(cudaSetDevice(device));
-    float* dc = nullptr;
-    double* dout = nullptr;
-    ASB_CUDA(cudaMalloc(&dc, (size_t)n * 8 * sizeof(float)));
-    ASB_CUDA(cudaMalloc(&dout, (size_t)n * 6 * sizeof(double)));
-    ASB_CUDA(cudaMemcpy(dc, corners, (size_t)n * 8 * sizeof(float), cudaMemcpyHostToDevice));
-    int rc = asb_ippe_square_device(dc, n, camera_matrix, dist_coeffs, marker_size, dout, nullptr, nullptr, nullptr);
+    // Device buffers are kept between calls (grow-only, per device): the per-frame caller
+    // (BaseFilter.estimate_pose_of_markers, a few dozen markers) must not pay two cudaMalloc /
+    // cudaFree round trips per frame.
+    struct Cache { float* dc = nullptr; double* dout = nullptr; int64_t cap = 0; };
+    static std::mutex mu;
+    static Cache cache[64];
+    std::lock_guard<std::mutex> lock(mu);
+    Cache& c = cache[device & 63];
+    if (n > c.cap) {
+        cudaFree(c.dc); cudaFree(c.dout);
+        c = Cache{};
+        const int64_t cap = std::max<int64_t>(n, 4096);
+        ASB_CUDA(cudaMalloc(&c.dc, (size_t)cap * 8 * sizeof(float)));
+        ASB_CUDA(cudaMalloc(&c.dout, (size_t)cap * 6 * sizeof(double)));
+        c.cap = cap;
+    }
+    ASB_CUDA(cudaMemcpy(c.dc, corners, (size_t)n * 8 * sizeof(float), cudaMemcpyHostToDevice));
+    int rc = asb_ippe_square_device(c.dc, n, camera_matrix, dist_coeffs, marker_size, c.dout, nullptr, nullptr, nullptr);
     if (rc == ASB_OK) {
-        cudaError_t e = cudaMemcpy(out, dout, (size_t)n * 6 * sizeof(double), cudaMemcpyDeviceToHost);
+        cudaError_t e = cudaMemcpy(out, c.dout, (size_t)n * 6 * sizeof(double), cudaMemcpyDeviceToHost);
         if (e != cudaSuccess) rc = fail(ASB_ERR_CUDA, "ippe D2H: %s", cudaGetErrorString(e));
     }
-    cudaFree(dc);
-    cudaFree(dout);
     return rc;
 }
 

@@ -93,9 +93,13 @@ class BaseFilter:
         detected_poses = np.array([])
         if ids is not None and len(ids) > 0:
             ids = np.asarray(ids).flatten()
-            detected_poses = self.estimate_pose_of_markers(corners, ids, marker_size)
-            if should_filter:
-                self.observe(ids, detected_poses)
+            if should_filter and hasattr(self, "_observe_corners"):
+                # IPPE and the filter update in one call: the poses never leave the device in between
+                detected_poses = self._observe_corners(ids, corners, marker_size)
+            else:
+                detected_poses = self.estimate_pose_of_markers(corners, ids, marker_size)
+                if should_filter:
+                    self.observe(ids, detected_poses)
         if should_filter:
             camera_pose, marker_poses = self.get_poses()
             self._record_pose(camera_pose)
@@ -271,6 +275,19 @@ class _CudaFilter(BaseFilter):
         poses = _lib.as_f64(poses, (-1, 6))
         _lib.check(self._lib.asb_observe(self._h, _lib.iptr(ids), _lib.dptr(poses), ids.size))
         self._refresh_landmarks()
+
+    def _observe_corners(self, ids, corners, marker_size: float) -> np.ndarray:
+        """estimate_pose_of_markers + observe (BASE:196-204) as one library call; returns the
+        detected poses (k,6) like ``estimate_pose_of_markers``."""
+        from .ippe import _corner_array, _intrinsics
+        ids = _lib.as_i32(ids)
+        c = _corner_array(corners)
+        km, dist = _intrinsics(self.calib_matrix, self.dist_coeffs)
+        out = np.empty((c.shape[0], 6), dtype=np.float64)
+        _lib.check(self._lib.asb_observe_corners(self._h, _lib.iptr(ids), _lib.fptr(c), ids.size, _lib.dptr(km),
+                                                 _lib.dptr(dist), float(marker_size), _lib.dptr(out)))
+        self._refresh_landmarks()
+        return out
 
     def predict(self) -> None:
         _lib.check(self._lib.asb_predict(self._h))

@@ -90,6 +90,13 @@ ASB_API int asb_filter_synchronize(asb_filter* f);
 /* observe (EKF:58-82, ROT:66-90): add unseen ids in frame order, predict, update.
  * ids (k) int32, poses (k,6) row-major, HOST pointers. Asynchronous on the stream. */
 ASB_API int asb_observe(asb_filter* f, const int32_t* ids, const double* poses, int k);
+/* process_frame's hot path in one call (BASE:196-204): estimate_pose_of_markers (BASE:92-171) on
+ * the k detected corner sets (k,4,2 float32, HOST) followed by observe(ids, poses); the poses stay
+ * on the device in between.  poses_out (k,6) or NULL: the detected poses for the caller (BASE:212);
+ * the call then waits for the IPPE kernel only, the update stays asynchronous. */
+ASB_API int asb_observe_corners(asb_filter* f, const int32_t* ids, const float* corners, int k,
+                        const double camera_matrix[9], const double dist_coeffs[5], double marker_size,
+                        double* poses_out);
 /* predict (EKF:95-105, ROT:103-113): P += diag(Q); the state is unchanged. */
 ASB_API int asb_predict(asb_filter* f);
 /* update (EKF:107-156, ROT:115-181). Unknown id => ASB_ERR_UNKNOWN_ID, nothing changed. */

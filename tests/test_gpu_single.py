@@ -200,3 +200,27 @@ def test_missing_calibration_raises(tmp_path, monkeypatch):
     monkeypatch.chdir(tmp_path)
     with pytest.raises(FileNotFoundError):
         EKF(np.array([0, 0, 0, 1, 0, 0, 0, 0, 0, 0.0]))
+
+
+@pytest.mark.parametrize("kind", ["ekf", "rot"])
+def test_process_detections_fused_equals_separate_calls(calibration, kind):
+    """BASE:196-212: process_detections (IPPE + observe in one library call, poses kept on the
+    device) gives exactly what estimate_pose_of_markers followed by observe gives."""
+    from aruco_slam_b200 import synth
+    km, dist = calibration
+    a = make_gpu(kind, "as_written", calibration)
+    b = make_gpu(kind, "as_written", calibration)
+    rng = np.random.default_rng(5)
+    corners_all = synth.make_corner_sets(400, km, dist, seed=3)
+    for frame in range(12):
+        k = int(rng.integers(1, 9))
+        ids = rng.choice(20, size=k, replace=False).astype(np.int32)
+        corners = corners_all[rng.choice(400, size=k, replace=False)]
+        cam_a, lm_a, det_a = a.process_detections(corners, ids, True, frame, 0.16)
+        det_b = b.estimate_pose_of_markers(corners, ids, 0.16)
+        b.observe(ids, det_b)
+        cam_b, lm_b = b.get_poses()
+        assert np.array_equal(det_a, det_b)
+        assert np.array_equal(cam_a, cam_b) and np.array_equal(lm_a, lm_b)
+    assert order_of(a.landmarks) == order_of(b.landmarks)
+    assert np.array_equal(a.uncertainty, b.uncertainty)
