@@ -151,6 +151,9 @@ def _cpu_worker(job):
 def cpu_port_throughput(args, workers: int, frames: int, reps: int = 1):
     """marker-updates/s of the numpy oracle: `workers` processes, one sequence each."""
     import multiprocessing as mp
+    # one BLAS thread per worker process: the children read this when they import numpy
+    for var in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ[var] = "1"
     jobs = [(s, args.markers, frames, args.p_visible, args.kind, args.quat_mode)
             for s in range(workers * reps)]
     t0 = time.perf_counter()
@@ -172,8 +175,8 @@ def run_reference(args):
         return
     cores = os.cpu_count() or 1
     workers = max(1, min(cores, 64))
-    frames = 60
-    # size one step to ~10-20 s: oracle runs ~2.5 ms/frame/sequence
+    frames = 500
+    # one step = one 500-frame sequence per worker (~0.5 s at ~1 ms / frame / sequence)
     vals = []
     for _ in range(args.warmup):
         pass  # the pool's own warm pass (imports, page-in) is inside cpu_port_throughput
@@ -485,12 +488,24 @@ def run_b200(args):
                     line["workloads"][name] = leg()
                 except Exception as exc:  # keep the headline line even if an extra leg fails
                     line["workloads"][name] = {"error": repr(exc)}
-        frames = max(20, int(args.cpu_seconds / 2.6e-3 / 1.0))
-        frames = min(frames, args.frames)
-        v, total, wall_cpu = cpu_port_throughput(args, 1, frames)
+        # bounded sample: whole sequences of the same workload on ONE core until the budget is spent
+        frames = min(args.frames, 1000)
+        total, wall_cpu, nseq_cpu = 0, 0.0, 0
+        try:
+            from threadpoolctl import threadpool_limits
+            one_thread = threadpool_limits(limits=1)   # "cores": 1 means one BLAS thread as well
+        except ImportError:
+            one_thread = None
+        while wall_cpu < args.cpu_seconds and nseq_cpu < 64:
+            n_upd, dt = _cpu_worker((nseq_cpu, args.markers, frames, args.p_visible, args.kind, args.quat_mode))
+            total += n_upd
+            wall_cpu += dt
+            nseq_cpu += 1
+        if one_thread is not None:
+            one_thread.restore_original_limits()
         line["cpu_baseline"] = {
-            "value": v, "unit": UNIT, "cores": 1, "kind": "port",
-            "sample": f"1 sequence x {args.markers} markers x {frames} frames of the same workload, "
+            "value": total / wall_cpu, "unit": UNIT, "cores": 1, "kind": "port",
+            "sample": f"{nseq_cpu} sequences x {args.markers} markers x {frames} frames of the same workload, "
                       f"oracle/ekf_oracle.py (numpy restatement of the reference algorithm), "
                       f"{wall_cpu:.1f} s on {os.cpu_count()} host cores (1 used)"}
     if rank == 0:
