@@ -60,6 +60,50 @@ def test_batch_matches_oracle(kind, quat_mode, n_markers, n_frames):
         assert rel_err(cams[s], o.state[:10]) < TOL
 
 
+@pytest.mark.parametrize("kind,quat_mode,n_frames", [("ekf", "scalar_first", 40), ("rot", "scalar_first", 14)])
+def test_batch_c5_shape_64_markers(kind, quat_mode, n_frames):
+    """BASELINE configs[4] shape: 64 markers, p = 0.25.  EKF (N = 202) keeps P in shared memory, one
+    CTA per SM; EKF_Rotations (N = 650, P 3.4 MB) runs with the covariance in HBM."""
+    from aruco_slam_b200 import FilterBatch, synth
+    n_seq = 3
+    streams = [synth.make_stream(70 + s, 64, n_frames, 0.25, kind) for s in range(n_seq)]
+    ids, poses, off = pack(streams, n_frames)
+    b = FilterBatch(kind, n_seq, 64, 64, quat_mode=quat_mode)
+    b.upload(ids, poses, off)
+    b.run()
+    _, status = b.cameras()
+    assert not status.any()
+    for s in range(n_seq):
+        o = run_oracle(kind, quat_mode, streams[s], n_frames)
+        order = [k for k, _ in sorted(o.landmarks.items(), key=lambda kv: kv[1])]
+        assert [int(i) for i in b.landmark_ids(s)] == order
+        assert rel_err(b.state(s), o.state) < TOL
+        assert rel_err(b.uncertainty(s), o.uncertainty) < TOL
+
+
+def test_batch_full_size_c2_properties():
+    """BASELINE configs[1] at full size (4096 sequences x 32 markers x 1000 frames, 64 distinct
+    streams tiled as in bench.py) through the grouped upload -> run path: every sequence finite and
+    status 0; tiled copies of one stream bit-identical (the engine is deterministic and sequences
+    do not interact); first and last sequence within 1e-9 of the free-running oracle over all 1000
+    frames (scalar-first mode: the as-written quaternion reset is chaotic)."""
+    from aruco_slam_b200 import FilterBatch, synth
+    n_seq, n_markers, n_frames, unique = 4096, 32, 1000, 64
+    ids, poses, off = synth.make_batch(n_seq, n_markers, n_frames, 0.5, "ekf", unique=unique)
+    b = FilterBatch("ekf", n_seq, n_markers, n_markers, quat_mode="scalar_first")
+    b.upload(ids, poses, off)
+    b.run()
+    cams, status = b.cameras()
+    assert not status.any() and np.isfinite(cams).all()
+    for s in range(unique):
+        assert np.array_equal(cams[s::unique], np.broadcast_to(cams[s], cams[s::unique].shape)), s
+    for s in (0, n_seq - 1):
+        stream = synth.make_stream(s % unique, n_markers, n_frames, 0.5, "ekf")
+        o = run_oracle("ekf", "scalar_first", stream, n_frames)
+        assert rel_err(b.state(s), o.state) < TOL
+        assert rel_err(b.uncertainty(s), o.uncertainty) < TOL
+
+
 def test_batch_equals_single_filter(calibration):
     """The two engines are independent implementations of the same update."""
     from aruco_slam_b200 import EKF, FilterBatch, synth
