@@ -122,7 +122,9 @@ struct asb_shard {
     int* s_idx = nullptr; double* s_pose = nullptr; unsigned char* s_new = nullptr;
     std::vector<ShFrame> frames;
     int next_frame = 0;
-    int sm_count = 0;
+    int sm_count = 0, smem_optin = 0;
+    int cur = 0;        // which of d_dx[2] holds the latest all-gathered dx
+    int overlap = 1;    // ASB_SHARD_OVERLAP=0: every chunk runs its front serially (no look-ahead)
     int n_state() const { return CAM + D * nlm; }
 };
 
@@ -313,77 +315,160 @@ static cudaError_t dmalloc(T** p, size_t count) {
     return e;
 }
 
+// One update chunk (<= kc_max markers of one frame) as the launch sequence sees it.
+struct ShChunk {
+    const int* idx;
+    const double* pose;
+    const unsigned char* isnew;
+    int kc, n0, n1;      // n0: state dims before this chunk's augmentation (= n1 after the first chunk of a frame)
+    bool first, last;    // first / last chunk of its frame
+};
+
+static void append_chunks(const asb_shard* s, std::vector<ShChunk>& out, const int* idx, const double* pose,
+                          const unsigned char* isnew, int k, int n0, int n1) {
+    for (int c0 = 0; c0 < k; c0 += s->kc_max) {
+        ShChunk c;
+        c.kc = std::min(s->kc_max, k - c0);
+        c.idx = idx + c0; c.pose = pose + 6 * (size_t)c0; c.isnew = isnew ? isnew + c0 : nullptr;
+        c.first = c0 == 0; c.last = c0 + c.kc >= k;
+        c.n0 = c.first ? n0 : n1; c.n1 = n1;
+        out.push_back(c);
+    }
+}
+
+namespace asb {
+// state update + quaternion reset (EKF:134-152 / ROT:143-177) with the all-gathered dx, replicated on every rank
+__global__ void __launch_bounds__(256) k_sh_apply(double* state, const double* dx, int kind, int as_written, int nlm) {
+    apply_state(state, dx, kind, as_written, nlm, threadIdx.x, blockDim.x);
+}
+}  // namespace asb
+
+// The launch sequence for a run of chunks.  With a NEXT chunk known (stream mode, or a frame of
+// more than kc_max markers) the front of chunk i+1 is taken off the critical path exactly as in the
+// single-GPU engine (pipe.cuh):
+//
+//   k_sh_f2(i) -> k_sh_ptt(i+1) -> NCCL group { all-gather V(i), all-gather dx, all-reduce P_in[T(i+1),T(i+1)] }
+//     -> k_sh_apply -> k_f1(i+1) -> k_sweep(i) -> k_sh_f2(i+1) ...
+//
+// k_sh_ptt(i+1) reads the covariance BEFORE sweep i (its all-reduce rides in the same NCCL group
+// as the panel all-gather, so the overlap costs no extra collective launch); k_f1(i+1) brings that
+// block up to date with the panel of chunk i (lazy operand: P[T,T] + Q - V^T V, the panel columns
+// taken from the all-gathered tiled panel) and runs WHILE k_sweep(i) streams the row block: it owns
+// an SM (nearly all of its shared memory) and the sweep is its programmatic dependent launch,
+// waiting for it only at its end.  The first chunk of a run has no look-ahead: k_sh_ptt, a separate
+// all-reduce and k_f1 run serially in front of it.
 template <int KIND>
-static int shard_frame(asb_shard* s, const int* idx, const double* pose, const unsigned char* isnew, int k,
-                       int n0, int n1) {
+static int shard_chunks(asb_shard* s, const std::vector<ShChunk>& chunks) {
     constexpr int R = Dims<KIND>::R, W = CAM + Dims<KIND>::D, D = Dims<KIND>::D;
     NcclApi* nc = nccl_api();
     cudaStream_t st = s->stream;
     const Partition& pt = s->part;
-    int cur = 0;
-    for (int c0 = 0; c0 < k; c0 += s->kc_max) {
-        const int kc = std::min(s->kc_max, k - c0);
-        const int m4 = round_up(R * kc, 4), nT = CAM + D * kc;
-        const bool first = c0 == 0, last = c0 + kc >= k;
-        const int n0c = first ? n0 : n1;
+    const int as_written = (KIND == 0 && s->quat_mode == ASB_QUAT_AS_WRITTEN) ? 1 : 0;
+    const size_t f1_big = (size_t)s->smem_optin - 2048;
+    bool have_front = false;   // k_f1 of the current chunk has already been launched (overlapped with the previous sweep)
+    long long obs_row = 0;     // rows of d_blocks / d_nu used so far in this frame
+
+    auto launch_ptt = [&](const ShChunk& c) {
         ShPttArgs g;
-        g.P = s->d_P; g.ldp = pt.ldp; g.row0 = pt.row0; g.rows = pt.rows; g.n0 = n0c;
-        g.idx = idx + c0; g.kc = kc; g.out = s->d_PTpart;
-        k_sh_ptt<KIND><<<nT, 128, 0, st>>>(g);
-        ASB_NCCL(nc->AllReduce(s->d_PTpart, s->d_PT, (size_t)nT * nT, ncclDouble, ncclSum, s->comm, st));
+        g.P = s->d_P; g.ldp = pt.ldp; g.row0 = pt.row0; g.rows = pt.rows; g.n0 = c.n0;
+        g.idx = c.idx; g.kc = c.kc; g.out = s->d_PTpart;
+        k_sh_ptt<KIND><<<CAM + D * c.kc, 128, 0, st>>>(g);
+    };
+    auto launch_f1 = [&](const ShChunk& c, const ShChunk* prev, long long row) {
+        const int m4 = round_up(R * c.kc, 4);
         F1Args a{};
         a.state = s->d_state; a.P = nullptr; a.PT_dense = s->d_PT; a.ld = pt.ldp;
-        a.n0 = n0c; a.n1 = n1; a.nz = s->nz;
-        a.idx = idx + c0; a.poses = pose + 6 * (size_t)c0; a.isnew = isnew ? isnew + c0 : nullptr;
-        a.kc = kc; a.m4 = m4;
-        a.first_chunk = first ? 1 : 0;
-        a.add_q = first ? 1 : 0;
-        a.use_delta = first ? 0 : 1;
-        a.dx_in = s->d_dx[cur];
-        a.lazy = 0; a.Vp = nullptr; a.m4p = 0; a.lazy_q = 0;
+        a.n0 = c.n0; a.n1 = c.n1; a.nz = s->nz;
+        a.idx = c.idx; a.poses = c.pose; a.isnew = c.isnew;
+        a.kc = c.kc; a.m4 = m4;
+        a.first_chunk = c.first ? 1 : 0;
+        a.add_q = c.first ? 1 : 0;
+        a.use_delta = c.first ? 0 : 1;
+        a.dx_in = s->d_dx[s->cur];
+        a.lazy = prev ? 1 : 0; a.Vp = nullptr;
+        a.Vc_tiled = prev ? s->d_Vc : nullptr;
+        a.m4p = prev ? round_up(R * prev->kc, 4) : 0;
+        a.lazy_q = (prev && prev->first) ? 1 : 0;
         a.At = s->d_At; a.y = s->d_y; a.T = s->d_T;
-        a.blocks_out = s->d_blocks + (size_t)c0 * R * W; a.nu_out = s->d_nu + (size_t)R * c0;
+        a.blocks_out = s->d_blocks + (size_t)row * R * W; a.nu_out = s->d_nu + (size_t)R * row;
         a.status = s->d_status;
         a.dbg = 0; a.prof = nullptr;
-        k_f1<KIND><<<1, FRONT_THREADS, F1Smem<KIND>::bytes(kc, m4), st>>>(a);
+        // overlapped with a sweep: ask for the whole SM so that no sweep CTA shares its FP64 pipe
+        k_f1<KIND><<<1, FRONT_THREADS, prev ? f1_big : F1Smem<KIND>::bytes(c.kc, m4), st>>>(a);
+    };
+
+    for (size_t i = 0; i < chunks.size(); ++i) {
+        const ShChunk& c = chunks[i];
+        const ShChunk* next = (i + 1 < chunks.size() && s->overlap) ? &chunks[i + 1] : nullptr;
+        const int m4 = round_up(R * c.kc, 4);
+        if (c.first) obs_row = 0;
+        if (!have_front) {
+            const int nT = CAM + D * c.kc;
+            launch_ptt(c);
+            ASB_NCCL(nc->AllReduce(s->d_PTpart, s->d_PT, (size_t)nT * nT, ncclDouble, ncclSum, s->comm, st));
+            launch_f1(c, nullptr, obs_row);
+        }
+        obs_row += c.kc;
         ShF2Args b;
         b.P = s->d_P; b.ldp = pt.ldp; b.row0 = pt.row0; b.rows = pt.rows;
-        b.n0 = n0c; b.n1 = n1; b.nz = s->nz; b.kc = kc; b.m4 = m4;
-        b.first_chunk = a.first_chunk; b.add_q = a.add_q; b.use_delta = a.use_delta;
+        b.n0 = c.n0; b.n1 = c.n1; b.nz = s->nz; b.kc = c.kc; b.m4 = m4;
+        b.first_chunk = c.first ? 1 : 0; b.add_q = c.first ? 1 : 0; b.use_delta = c.first ? 0 : 1;
         b.At = s->d_At; b.y = s->d_y; b.T = s->d_T;
-        b.dx_in = s->d_dx[cur]; b.dx_out = s->d_dx[cur ^ 1];
+        b.dx_in = s->d_dx[s->cur]; b.dx_out = s->d_dx[s->cur ^ 1];
         b.Vr = s->d_Vr; b.Vc = s->d_Vc;
-        k_sh_f2<KIND><<<pt.rows / F2_COLS, F2_THREADS, ShF2Smem<KIND>::bytes(kc), st>>>(b);
-        cur ^= 1;
-        // the exchange step: every rank's V_J panel blocks and its slice of dx
+        k_sh_f2<KIND><<<pt.rows / F2_COLS, F2_THREADS, ShF2Smem<KIND>::bytes(c.kc), st>>>(b);
+        s->cur ^= 1;
+        if (next) launch_ptt(*next);   // the covariance as it is BEFORE this chunk's sweep (after its growth stores)
+        // the exchange step: every rank's V_J panel blocks, its slice of dx, and the next chunk's P[T,T]
         const size_t vcount = (size_t)pt.blocks_per_rank * m4 * V_LDB;
         ASB_NCCL(nc->GroupStart());
         ASB_NCCL(nc->AllGather(s->d_Vc + (size_t)s->rank * vcount, s->d_Vc, vcount, ncclDouble, s->comm, st));
-        ASB_NCCL(nc->AllGather(s->d_dx[cur] + pt.row0, s->d_dx[cur], (size_t)pt.rows, ncclDouble, s->comm, st));
+        ASB_NCCL(nc->AllGather(s->d_dx[s->cur] + pt.row0, s->d_dx[s->cur], (size_t)pt.rows, ncclDouble, s->comm, st));
+        if (next) {
+            const int nTn = CAM + D * next->kc;
+            ASB_NCCL(nc->AllReduce(s->d_PTpart, s->d_PT, (size_t)nTn * nTn, ncclDouble, ncclSum, s->comm, st));
+        }
         ASB_NCCL(nc->GroupEnd());
+        if (c.last) k_sh_apply<<<1, 256, 0, st>>>(s->d_state, s->d_dx[s->cur], KIND, as_written, (c.n1 - CAM) / D);
+        if (next) launch_f1(*next, &c, next->first ? 0 : obs_row);
         // rectangular sweep of the own rows that are live (< n1)
-        const int nI = std::max(0, std::min(pt.blocks_per_rank, (n1 - pt.row0 + V_BLK - 1) / V_BLK));
-        const int nJ = (n1 + V_BLK - 1) / V_BLK;
+        const int nI = std::max(0, std::min(pt.blocks_per_rank, (c.n1 - pt.row0 + V_BLK - 1) / V_BLK));
+        const int nJ = (c.n1 + V_BLK - 1) / V_BLK;
         const int ntiles = nI * nJ;
         SweepExtra ex{};
-        ex.n = n1; ex.add_q = a.add_q; ex.nz = s->nz;
-        ex.apply_kind = last ? KIND : -1;
-        ex.as_written = (KIND == 0 && s->quat_mode == ASB_QUAT_AS_WRITTEN) ? 1 : 0;
-        ex.nlm = (n1 - CAM) / D; ex.state = s->d_state; ex.dx = s->d_dx[cur];
+        ex.n = c.n1; ex.add_q = c.first ? 1 : 0; ex.nz = s->nz;
+        ex.apply_kind = -1;
         ex.rect = 1; ex.row0 = pt.row0; ex.nJ = std::max(nJ, 1);
-        const int grid = std::max(1, std::min(ntiles, 2 * s->sm_count));
-        k_sweep<SweepDual><<<grid, SweepDual::THREADS, SweepDual::smem_bytes(m4), st>>>(
-            s->d_P, s->d_P, pt.ldp, s->d_Vr, s->d_Vc, m4, ntiles, 2 << 4, ex);
+        const int grid = std::max(1, std::min(ntiles, 2 * (s->sm_count - (next ? 1 : 0))));
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3((unsigned)grid);
+        cfg.blockDim = dim3(SweepDual::THREADS);
+        cfg.dynamicSmemBytes = SweepDual::smem_bytes(m4);
+        cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = next ? 1 : 0;   // programmatic dependent of the k_f1 just launched
+        cudaLaunchKernelEx(&cfg, k_sweep<SweepDual>, (const double*)s->d_P, s->d_P, pt.ldp, (const double*)s->d_Vr,
+                           (const double*)s->d_Vc, m4, ntiles, 2 << 4, ex);
+        have_front = next != nullptr;
     }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(ASB_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(e));
     return ASB_OK;
 }
 
+static int shard_chunks_dyn(asb_shard* s, const std::vector<ShChunk>& chunks) {
+    if (chunks.empty()) return ASB_OK;
+    return s->kind == ASB_KIND_EKF ? shard_chunks<0>(s, chunks) : shard_chunks<1>(s, chunks);
+}
+
 static int shard_frame_dyn(asb_shard* s, const int* idx, const double* pose, const unsigned char* isnew, int k,
                            int n0, int n1) {
-    return s->kind == ASB_KIND_EKF ? shard_frame<0>(s, idx, pose, isnew, k, n0, n1)
-                                   : shard_frame<1>(s, idx, pose, isnew, k, n0, n1);
+    std::vector<ShChunk> chunks;
+    append_chunks(s, chunks, idx, pose, isnew, k, n0, n1);
+    return shard_chunks_dyn(s, chunks);
 }
 
 extern "C" {
@@ -439,6 +524,8 @@ int asb_shard_create(int kind, int quat_mode, const double pose0[10], const asb_
     cudaDeviceProp prop;
     ASB_CUDA(cudaGetDeviceProperties(&prop, device));
     s->sm_count = prop.multiProcessorCount;
+    s->smem_optin = (int)prop.sharedMemPerBlockOptin;
+    if (const char* e = std::getenv("ASB_SHARD_OVERLAP")) s->overlap = std::atoi(e);
     ncclUniqueId id;
     std::memcpy(&id, unique_id, sizeof id);
     ASB_NCCL(nc->CommInitRank(&s->comm, world, id, rank));
@@ -614,6 +701,7 @@ int asb_shard_stream_run(asb_shard* s, int t0, int t1) {
     if (s->frames.empty()) return fail(ASB_ERR_NO_STREAM, "stream_run before stream_upload");
     if (t0 != s->next_frame || t1 < t0 || t1 > (int)s->frames.size())
         return fail(ASB_ERR_BAD_ARG, "frames must run in order: next is %d, got [%d,%d)", s->next_frame, t0, t1);
+    std::vector<ShChunk> chunks;
     for (int t = t0; t < t1; ++t) {
         const ShFrame& fr = s->frames[t];
         for (int32_t id : fr.new_ids) {
@@ -621,12 +709,10 @@ int asb_shard_stream_run(asb_shard* s, int t0, int t1) {
             s->id_order.push_back(id);
         }
         if (fr.k == 0) continue;
-        int rc = shard_frame_dyn(s, s->s_idx + fr.off, s->s_pose + 6 * fr.off, s->s_new + fr.off, fr.k, fr.n0, fr.n1);
-        if (rc != ASB_OK) return rc;
-        s->next_frame = t + 1;
+        append_chunks(s, chunks, s->s_idx + fr.off, s->s_pose + 6 * fr.off, s->s_new + fr.off, fr.k, fr.n0, fr.n1);
     }
     s->next_frame = t1;
-    return ASB_OK;
+    return shard_chunks_dyn(s, chunks);
 }
 
 int asb_shard_get_dims(asb_shard* s, int* n_landmarks, int* n_state) {

@@ -212,7 +212,7 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
                 f->side_waited = false;
             }
             F1Args a;
-            a.state = f->d_state; a.P = f->lazy ? f->d_P2 : f->d_P; a.PT_dense = nullptr; a.ld = ld;
+            a.state = f->d_state; a.P = f->lazy ? f->d_P2 : f->d_P; a.PT_dense = nullptr; a.Vc_tiled = nullptr; a.ld = ld;
             a.n0 = first ? n0 : n1; a.n1 = n1; a.nz = f->nz;
             a.idx = idx + c0; a.poses = pose + 6 * (size_t)c0; a.isnew = isnew ? isnew + c0 : nullptr;
             a.kc = kc; a.m4 = m4;

@@ -40,6 +40,7 @@ struct F1Args {
     int lazy;                    // P is one sweep behind: subtract Vp^T Vp (and add Q if lazy_q)
     const double* Vp;            // panel of that sweep by state column: column j at Vp + F1_LDT j, m4p values
     int m4p, lazy_q;
+    const double* Vc_tiled;      // row-sharded engine: that panel in the tiled V_J layout (sweep.cuh) instead of Vp
     double* At;                  // out (nT, m4): A^T, A = L^-1 H_T (rows a >= m are zero)
     double* y;                   // out (m4): L^-1 nu (zero padded)
     int* T;                      // out (nT): touched state indices
@@ -116,7 +117,14 @@ k_f1(F1Args p) {
     // ---- all global reads, asynchronously: the lower triangle of P[T,T] (cp.async) and the
     //      previous panel's columns T (one bulk copy, SASS UBLKCP, per column) -------------------
     // Entries in rows / columns >= n0 (this frame's augmentation) are known constants.
-    if (p.lazy && tid < nT) {
+    if (p.lazy && p.Vc_tiled) {
+        for (int e = tid; e < nT * p.m4p; e += NT) {
+            const int col = e / p.m4p, a = e - col * p.m4p;
+            const int i = s_T[col];
+            s_Vg[(size_t)col * F1_LDK + a] =
+                i < n0 ? p.Vc_tiled[((size_t)(i / V_BLK) * p.m4p + a) * V_LDB + v_pos_col(i % V_BLK)] : 0.0;
+        }
+    } else if (p.lazy && tid < nT) {
         const int i = s_T[tid];
         const uint32_t bytes = i < n0 ? (uint32_t)(p.m4p * sizeof(double)) : 0u;
         mbar_expect_tx(&s_bar, bytes);
@@ -193,7 +201,7 @@ k_f1(F1Args p) {
     // Lower triangle only, then mirrored.  Thread tile: rows {ta + G q}, columns {tb + G q'} (q, q' < 4,
     // G = ceil(nT / 4)): lanes read consecutive rows of the gathered panel.
     if (p.lazy) {
-        mbar_wait(&s_bar, 0);
+        if (!p.Vc_tiled) mbar_wait(&s_bar, 0);
         const int G = (nT + 3) >> 2;
         const int kp = (p.m4p + 1) >> 1;   // pairs of k (m4p is a multiple of 4)
         for (int task = tid; task < ftri(G); task += NT) {

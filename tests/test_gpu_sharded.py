@@ -71,8 +71,15 @@ def _worker(rank, world, port, q):
             stream = synth.make_stream(5, n_markers, 30, 0.4, kind)
             frames = stream.n_frames
         f = ShardedFilter(kind, POSE0, n_markers, dist=dist, rank=rank, world=world, device=rank, quat_mode=qm)
-        for t in range(frames):
-            f.observe(stream.ids[t], stream.poses[t])
+        if kind == "ekf":
+            # stream mode: the front of every chunk overlaps the previous chunk's sweep (look-ahead across frames)
+            ids, poses, off = stream.packed()
+            f.stream_upload(ids[:off[frames]], poses[:off[frames]], off[:frames + 1])
+            f.stream_run(0, frames // 2)
+            f.stream_run(frames // 2, frames)
+        else:
+            for t in range(frames):
+                f.observe(stream.ids[t], stream.poses[t])
         out[kind] = (f.state, f.uncertainty, _order(f.landmarks), (f.row0, f.row1))
         f.close()
     q.put((rank, out))
