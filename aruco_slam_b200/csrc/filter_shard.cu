@@ -123,6 +123,9 @@ struct asb_shard {
     std::vector<ShFrame> frames;
     int next_frame = 0;
     int sm_count = 0, smem_optin = 0;
+    unsigned int* d_tail = nullptr;   // two tile counters used alternately by successive sweeps
+    unsigned int sweep_seq = 0;
+    int tail_tiles = 2;
     int cur = 0;        // which of d_dx[2] holds the latest all-gathered dx
     int overlap = 1;    // ASB_SHARD_OVERLAP=0: every chunk runs its front serially (no look-ahead)
     int n_state() const { return CAM + D * nlm; }
@@ -200,6 +203,7 @@ k_sh_f2(ShF2Args p) {
     double* s_red = s_y + 64;                                // 8 x F2_COLS
     int* s_T = reinterpret_cast<int*>(s_red + 8 * F2_COLS);  // nT
 
+    pdl_wait();   // launched as a programmatic dependent of the previous chunk's sweep (which triggers at its end)
     for (int a = tid; a < nT; a += NT) s_T[a] = p.T[a];
     for (int a = tid; a < 64; a += NT) s_y[a] = a < m4 ? p.y[a] : 0.0;
     {
@@ -416,7 +420,19 @@ static int shard_chunks(asb_shard* s, const std::vector<ShChunk>& chunks) {
         b.At = s->d_At; b.y = s->d_y; b.T = s->d_T;
         b.dx_in = s->d_dx[s->cur]; b.dx_out = s->d_dx[s->cur ^ 1];
         b.Vr = s->d_Vr; b.Vc = s->d_Vc;
-        k_sh_f2<KIND><<<pt.rows / F2_COLS, F2_THREADS, ShF2Smem<KIND>::bytes(c.kc), st>>>(b);
+        {
+            cudaLaunchConfig_t cfg{};
+            cfg.gridDim = dim3((unsigned)(pt.rows / F2_COLS));
+            cfg.blockDim = dim3(F2_THREADS);
+            cfg.dynamicSmemBytes = ShF2Smem<KIND>::bytes(c.kc);
+            cfg.stream = st;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            at[0].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = at;
+            cfg.numAttrs = have_front ? 1 : 0;   // the kernel before it in the stream is the previous chunk's sweep
+            cudaLaunchKernelEx(&cfg, k_sh_f2<KIND>, b);
+        }
         s->cur ^= 1;
         if (next) launch_ptt(*next);   // the covariance as it is BEFORE this chunk's sweep (after its growth stores)
         // the exchange step: every rank's V_J panel blocks, its slice of dx, and the next chunk's P[T,T]
@@ -440,6 +456,12 @@ static int shard_chunks(asb_shard* s, const std::vector<ShChunk>& chunks) {
         ex.apply_kind = -1;
         ex.rect = 1; ex.row0 = pt.row0; ex.nJ = std::max(nJ, 1);
         const int grid = std::max(1, std::min(ntiles, 2 * (s->sm_count - (next ? 1 : 0))));
+        if (s->tail_tiles > 0 && ntiles > grid) {   // contiguous range + dynamic tail (sweep.cuh)
+            ex.tail = s->d_tail + (s->sweep_seq & 1);
+            ex.tail_reset = s->d_tail + ((s->sweep_seq + 1) & 1);
+            ex.n_static = std::max(0, ntiles / grid - s->tail_tiles);
+            ++s->sweep_seq;
+        }
         cudaLaunchConfig_t cfg{};
         cfg.gridDim = dim3((unsigned)grid);
         cfg.blockDim = dim3(SweepDual::THREADS);
@@ -547,6 +569,8 @@ int asb_shard_create(int kind, int quat_mode, const double pose0[10], const asb_
     ASB_CUDA(dmalloc(&s->d_blocks, (size_t)s->max_obs * s->R * s->W));
     ASB_CUDA(dmalloc(&s->d_nu, (size_t)s->max_obs * s->R));
     ASB_CUDA(dmalloc(&s->d_status, (size_t)1));
+    ASB_CUDA(dmalloc(&s->d_tail, (size_t)2));
+    if (const char* e = std::getenv("ASB_TAIL")) s->tail_tiles = std::atoi(e);
     ASB_CUDA(dmalloc(&s->d_idx, (size_t)SH_SLOTS * s->max_obs));
     ASB_CUDA(dmalloc(&s->d_pose, (size_t)SH_SLOTS * s->max_obs * 6));
     ASB_CUDA(dmalloc(&s->d_new, (size_t)SH_SLOTS * s->max_obs));
@@ -583,7 +607,7 @@ int asb_shard_destroy(asb_shard* s) {
     cudaStreamSynchronize(s->stream);
     if (s->comm) nccl_api()->CommDestroy(s->comm);
     cudaFree(s->d_state); cudaFree(s->d_P); cudaFree(s->d_PTpart); cudaFree(s->d_PT); cudaFree(s->d_At); cudaFree(s->d_y);
-    cudaFree(s->d_T); cudaFree(s->d_Vr); cudaFree(s->d_Vc); cudaFree(s->d_dx[0]); cudaFree(s->d_dx[1]);
+    cudaFree(s->d_tail); cudaFree(s->d_T); cudaFree(s->d_Vr); cudaFree(s->d_Vc); cudaFree(s->d_dx[0]); cudaFree(s->d_dx[1]);
     cudaFree(s->d_blocks); cudaFree(s->d_nu); cudaFree(s->d_status); cudaFree(s->d_idx); cudaFree(s->d_pose);
     cudaFree(s->d_new); cudaFree(s->s_idx); cudaFree(s->s_pose); cudaFree(s->s_new);
     cudaFreeHost(s->h_idx); cudaFreeHost(s->h_pose); cudaFreeHost(s->h_new);
