@@ -13,12 +13,14 @@
 //   k_f1         S = H P[T,T] H^T + R, Cholesky, y = L^-1 nu, A = L^-1 H_T   (pipe.cuh, redundantly per rank)
 //   k_sh_f2      V[:, own] = A P[own, T]^T, dx[own] = V^T y, own panel blocks
 //                                                                      ---- ncclAllGather (V_J panel 8 m4 N B, dx)
-//   k_sweep      rect mode: P[own, :] -= V[:, own]^T V (+ diag Q), state update on CTA 0  (sweep.cuh)
+//   k_sh_apply   state update + quaternion reset with the gathered dx (replicated)
+//   k_sweep      rect mode: P[own, :] -= V[:, own]^T V (+ diag Q)        (sweep.cuh)
 //
-// Two collectives per chunk, both on the filter's stream between the kernels (no host
-// synchronisation).  The rectangular sweep cannot use the symmetry (each rank computes full rows:
-// 2 N^2 m / G flops per rank), so the row-sharded engine pays 2x the FP64 work of the
-// single-GPU triangle sweep and only wins from G >= 4; see DESIGN.md §6 for the measurements.
+// All collectives are on the filter's stream between the kernels (no host synchronisation).  When
+// the next chunk is known (stream mode, or a frame of more than kc_max markers) its front is taken
+// off the critical path: see shard_chunks() below.  The rectangular sweep cannot use the symmetry
+// (each rank computes full rows: 2 N^2 m / G flops per rank), so at G = 2 a rank does as much FP64
+// work as the single-GPU triangle sweep; DESIGN.md §6 has the measurements.
 #include <dlfcn.h>
 #include <nccl.h>   // types and prototypes only: libnccl.so.2 is opened at run time (the one torch already loaded)
 

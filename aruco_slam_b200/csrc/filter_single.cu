@@ -63,6 +63,8 @@ struct asb_filter {
     unsigned int* d_counter = nullptr;
     cudaStream_t side = nullptr;
     cudaEvent_t ev_ready = nullptr, ev_f1 = nullptr;
+    bool state_at_ready = false;   // the state vector is final at ev_ready (only a sweep is queued behind it):
+                                   // asb_get_state need not wait for that sweep
     bool lazy = false;         // d_P2 holds the input of the sweep launched last, d_Vr its panel
     bool side_waited = false;
     int prof_slot = 0, spare_ctas = 2;
@@ -270,9 +272,11 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
             f->lazy = true; f->prev_m4 = m4; f->prev_add_q = a.add_q;
         }
         f->dx_last = f->d_dx[cur];
+        f->state_at_ready = !(f->defer && f->pdl);   // per-frame mode: ev_ready was recorded right after the last k_f2
     } else if (!do_update || k == 0) {
         flush_pending(f, false);
         f->lazy = false;
+        f->state_at_ready = false;
         // predict() / add_marker() on their own: diagonal add, covariance growth, new states
         long long work = (long long)n0 + (long long)(n1 - n0) * (n1 + n0);
         int grid = (int)std::min<long long>(1 + work / 1024, 592);
@@ -282,6 +286,7 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
         // unpipelined update (ASB_PIPELINE=0): two launches per chunk of <= kc_max markers (k_front, k_sweep)
         flush_pending(f, false);
         f->lazy = false;
+        f->state_at_ready = false;
         int cur = 0;
         for (int c0 = 0; c0 < k; c0 += f->kc_max) {
             const int kc = std::min(f->kc_max, k - c0);
@@ -540,6 +545,7 @@ int asb_filter_destroy(asb_filter* f) {
 int asb_filter_set_stream(asb_filter* f, void* cuda_stream) {
     ASB_CHECK_HANDLE(f);
     f->lazy = false;   // the next k_f1 reads the current covariance buffer, not the previous sweep's input
+    f->state_at_ready = false;
     ASB_CUDA(cudaStreamSynchronize(f->stream));
     f->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : f->own_stream;
     return ASB_OK;
@@ -726,7 +732,10 @@ int asb_stream_run(asb_filter* f, int t0, int t1) {
         f->next_frame = t + 1;
     }
     f->defer = false;
-    if (f->pending.valid) cudaEventRecord(f->ev_ready, f->stream);   // last k_f2: what a per-frame k_f1 on the side stream waits for
+    if (f->pending.valid) {   // last k_f2: what a per-frame k_f1 on the side stream waits for
+        cudaEventRecord(f->ev_ready, f->stream);
+        f->state_at_ready = true;
+    }
     flush_pending(f, false);   // nothing stays pending across API calls
     f->next_frame = t1;
     return ASB_OK;
@@ -742,6 +751,20 @@ int asb_get_dims(asb_filter* f, int* n_landmarks, int* n_state) {
 int asb_get_state(asb_filter* f, double* out, int n_state) {
     ASB_CHECK_HANDLE(f);
     if (!out || n_state != f->n_state()) return fail(ASB_ERR_BAD_ARG, "n_state %d != %d", n_state, f->n_state());
+    if (f->side && f->state_at_ready) {
+        // The state (and the status flag) are final once the last k_f2 is done; the covariance sweep
+        // queued behind it keeps running while the host reads the pose and prepares the next frame.
+        int st = 0;
+        ASB_CUDA(cudaStreamWaitEvent(f->side, f->ev_ready, 0));
+        ASB_CUDA(cudaMemcpyAsync(&st, f->d_status, sizeof(int), cudaMemcpyDeviceToHost, f->side));
+        ASB_CUDA(cudaMemcpyAsync(out, f->d_state, n_state * sizeof(double), cudaMemcpyDeviceToHost, f->side));
+        ASB_CUDA(cudaStreamSynchronize(f->side));
+        if (st != 0) {
+            ASB_CUDA(cudaMemsetAsync(f->d_status, 0, sizeof(int), f->stream));
+            return fail(st, "innovation covariance S was not positive definite / finite");
+        }
+        return ASB_OK;
+    }
     int rc = poll_status(f);
     ASB_CUDA(cudaMemcpy(out, f->d_state, n_state * sizeof(double), cudaMemcpyDeviceToHost));
     return rc;
@@ -750,6 +773,7 @@ int asb_get_state(asb_filter* f, double* out, int n_state) {
 int asb_set_state(asb_filter* f, const double* in, int n_state) {
     ASB_CHECK_HANDLE(f);
     f->lazy = false;   // the next k_f1 reads the current covariance buffer, not the previous sweep's input
+    f->state_at_ready = false;
     if (!in || n_state != f->n_state()) return fail(ASB_ERR_BAD_ARG, "n_state %d != %d", n_state, f->n_state());
     ASB_CUDA(cudaStreamSynchronize(f->stream));
     ASB_CUDA(cudaMemcpy(f->d_state, in, n_state * sizeof(double), cudaMemcpyHostToDevice));
@@ -768,6 +792,7 @@ int asb_get_cov(asb_filter* f, double* out, int n_state) {
 int asb_set_cov(asb_filter* f, const double* in, int n_state) {
     ASB_CHECK_HANDLE(f);
     f->lazy = false;   // the next k_f1 reads the current covariance buffer, not the previous sweep's input
+    f->state_at_ready = false;
     if (!in || n_state != f->n_state()) return fail(ASB_ERR_BAD_ARG, "n_state %d != %d", n_state, f->n_state());
     ASB_CUDA(cudaStreamSynchronize(f->stream));
     ASB_CUDA(cudaMemcpy2D(f->d_P, (size_t)f->ld * sizeof(double), in, (size_t)n_state * sizeof(double),
@@ -794,6 +819,7 @@ int asb_get_landmark_ids(asb_filter* f, int32_t* ids, int capacity) {
 int asb_set_landmarks(asb_filter* f, const int32_t* ids, int n) {
     ASB_CHECK_HANDLE(f);
     f->lazy = false;   // the next k_f1 reads the current covariance buffer, not the previous sweep's input
+    f->state_at_ready = false;
     if (n < 0 || (n > 0 && !ids)) return fail(ASB_ERR_BAD_ARG, "bad ids");
     if (n > f->cap_lm) return fail(ASB_ERR_CAPACITY, "%d landmarks > max_landmarks %d", n, f->cap_lm);
     f->map.clear();
@@ -806,6 +832,7 @@ int asb_set_landmarks(asb_filter* f, const int32_t* ids, int n) {
 int asb_device_views(asb_filter* f, void** d_state, void** d_cov, int* ld) {
     ASB_CHECK_HANDLE(f);
     f->lazy = false;   // the next k_f1 reads the current covariance buffer, not the previous sweep's input
+    f->state_at_ready = false;
     if (d_state) *d_state = f->d_state;
     if (d_cov) *d_cov = f->d_P;
     if (ld) *ld = f->ld;
@@ -815,6 +842,7 @@ int asb_device_views(asb_filter* f, void** d_state, void** d_cov, int* ld) {
 int asb_bench_sweep(asb_filter* f, int m4, int config, int dbg, int reps, double* us_per_launch) {
     ASB_CHECK_HANDLE(f);
     f->lazy = false;   // the next k_f1 reads the current covariance buffer, not the previous sweep's input
+    f->state_at_ready = false;
     if (!us_per_launch || m4 < 4 || m4 > M_MAX || (m4 & 3) || reps < 1) return fail(ASB_ERR_BAD_ARG, "bad args");
     const int n1 = f->n_state();
     cudaEvent_t e0, e1;
