@@ -400,7 +400,7 @@ static int shard_chunks(asb_shard* s, const std::vector<ShChunk>& chunks) {
         a.status = s->d_status;
         a.dbg = 0; a.prof = nullptr;
         // overlapped with a sweep: ask for the whole SM so that no sweep CTA shares its FP64 pipe
-        k_f1<KIND><<<1, FRONT_THREADS, prev ? f1_big : F1Smem<KIND>::bytes(c.kc, m4), st>>>(a);
+        k_f1<KIND, true><<<1, FRONT_THREADS, prev ? f1_big : F1Smem<KIND>::bytes(c.kc, m4), st>>>(a);
     };
 
     for (size_t i = 0; i < chunks.size(); ++i) {
@@ -590,13 +590,13 @@ int asb_shard_create(int kind, int quat_mode, const double pose0[10], const asb_
     }
     const int big = (int)prop.sharedMemPerBlockOptin - 2048;
     ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepDual>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
-    ASB_CUDA(cudaFuncSetAttribute(k_f1<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
-    ASB_CUDA(cudaFuncSetAttribute(k_f1<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    ASB_CUDA(cudaFuncSetAttribute(k_f1<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    ASB_CUDA(cudaFuncSetAttribute(k_f1<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_sh_f2<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_sh_f2<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepDual>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    ASB_CUDA(cudaFuncSetAttribute(k_f1<0>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    ASB_CUDA(cudaFuncSetAttribute(k_f1<1>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    ASB_CUDA(cudaFuncSetAttribute(k_f1<0, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    ASB_CUDA(cudaFuncSetAttribute(k_f1<1, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     ASB_CUDA(cudaFuncSetAttribute(k_sh_f2<0>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     ASB_CUDA(cudaFuncSetAttribute(k_sh_f2<1>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     ASB_CUDA(cudaStreamSynchronize(s->stream));

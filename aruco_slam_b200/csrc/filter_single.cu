@@ -231,10 +231,10 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
             f->prof_slot ^= 1;
             a.prof = prof;
             if (ordered) {
-                launch_k(k_f1<KIND>, 1, FRONT_THREADS, (size_t)f->smem_optin - 2048, st, true, a);
+                launch_k(k_f1<KIND, true>, 1, FRONT_THREADS, (size_t)f->smem_optin - 2048, st, true, a);
                 flush_pending(f, true);
             } else {
-                k_f1<KIND><<<1, FRONT_THREADS, F1Smem<KIND>::bytes(kc, m4), f->side>>>(a);
+                k_f1<KIND, false><<<1, FRONT_THREADS, F1Smem<KIND>::bytes(kc, m4), f->side>>>(a);
                 cudaEventRecord(f->ev_f1, f->side);
                 cudaStreamWaitEvent(st, f->ev_f1, 0);
             }
@@ -498,8 +498,10 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
     ASB_CUDA(cudaFuncSetAttribute(k_sweep_ws, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_front<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_front<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
-    ASB_CUDA(cudaFuncSetAttribute(k_f1<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
-    ASB_CUDA(cudaFuncSetAttribute(k_f1<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    ASB_CUDA(cudaFuncSetAttribute(k_f1<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    ASB_CUDA(cudaFuncSetAttribute(k_f1<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    ASB_CUDA(cudaFuncSetAttribute(k_f1<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    ASB_CUDA(cudaFuncSetAttribute(k_f1<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_f2<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_f2<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     // One shared-memory carve-out (the maximum) for every kernel of the update: an SM only changes
@@ -510,8 +512,10 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
     ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepDual>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     ASB_CUDA(cudaFuncSetAttribute(k_front<0>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     ASB_CUDA(cudaFuncSetAttribute(k_front<1>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    ASB_CUDA(cudaFuncSetAttribute(k_f1<0>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    ASB_CUDA(cudaFuncSetAttribute(k_f1<1>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    ASB_CUDA(cudaFuncSetAttribute(k_f1<0, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    ASB_CUDA(cudaFuncSetAttribute(k_f1<0, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    ASB_CUDA(cudaFuncSetAttribute(k_f1<1, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    ASB_CUDA(cudaFuncSetAttribute(k_f1<1, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     ASB_CUDA(cudaFuncSetAttribute(k_f2<0>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     ASB_CUDA(cudaFuncSetAttribute(k_f2<1>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     ASB_CUDA(cudaFuncSetAttribute(k_prep<0>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));

@@ -68,9 +68,12 @@ struct F1Smem {
     }
 };
 
-template <int KIND>
-// <= 128 registers: the CTA must fit on an SM next to ONE resident sweep CTA (118 registers x 256 threads)
-__global__ void __launch_bounds__(FRONT_THREADS, 2)
+// EXCL = false: <= 128 registers, the CTA must fit on an SM next to ONE resident sweep CTA (122 registers x
+// 256 threads; per-frame calls, side stream).  EXCL = true: the CTA has an SM to itself (stream mode,
+// row-sharded engine): no register cap, and EKF chunks with an even number of markers factor S two
+// markers (6 rows) per block step.
+template <int KIND, bool EXCL>
+__global__ void __launch_bounds__(FRONT_THREADS, EXCL ? 1 : 2)
 k_f1(F1Args p) {
     constexpr int D = Dims<KIND>::D, R = Dims<KIND>::R, W = CAM + D, NB = R;
     constexpr int NT = FRONT_THREADS;
@@ -257,6 +260,7 @@ k_f1(F1Args p) {
         }
     }
     __syncthreads();
+    front_stamp(stampargs, 6);
 
     // ---- predict folded in: diag(Q) -----------------------------------------------------------
     if (p.add_q) {
@@ -272,6 +276,7 @@ k_f1(F1Args p) {
     }
     for (int a = tid; a < m; a += NT) s_S[m * lds + a] = s_nu[a];
     __syncthreads();
+    front_stamp(stampargs, 7);
 
     // ---- S = H PT H^T + R, one task per (observation pair, row): no m x nT intermediate --------
     {
@@ -309,7 +314,15 @@ k_f1(F1Args p) {
     front_stamp(stampargs, 3);
 
     // ---- Cholesky of [S; nu^T; I]: row m -> y^T, row GROW+b -> column b of L^-1 ------------------
-    const bool bad = front_cholesky<NB>(s_S, lds, m, p.dbg);
+    // EKF with an even number of markers: two markers (6 rows) per block step halves the number of serial
+    // steps (each costs two CTA barriers and a shared-memory round trip of the block column)
+    bool bad;
+    if constexpr (KIND == 0 && EXCL) {
+        bad = ((kc & 1) == 0 && !(p.dbg & 16)) ? front_cholesky<2 * NB>(s_S, lds, m, p.dbg)
+                                               : front_cholesky<NB>(s_S, lds, m, p.dbg);
+    } else {
+        bad = front_cholesky<NB>(s_S, lds, m, p.dbg);
+    }
     if (bad && tid == 0) atomicExch(p.status, ASB_ERR_NOT_SPD);
     front_stamp(stampargs, 4);
 
@@ -320,8 +333,17 @@ k_f1(F1Args p) {
         const int tb = e / m4, a = e - tb * m4;
         double s = 0.0;
         if (a < m) {
-            if (tb < CAM) {
-                for (int b = 0; b <= a; ++b) s += s_S[(GROW + b) * lds + a] * s_blk[(size_t)b * W + tb];
+            if (tb < CAM) {   // camera columns: every row of H contributes; four partial sums shorten the chain
+                double s1 = 0.0, s2 = 0.0, s3 = 0.0;
+                int b = 0;
+                for (; b + 3 <= a; b += 4) {
+                    s += s_S[(GROW + b) * lds + a] * s_blk[(size_t)b * W + tb];
+                    s1 += s_S[(GROW + b + 1) * lds + a] * s_blk[(size_t)(b + 1) * W + tb];
+                    s2 += s_S[(GROW + b + 2) * lds + a] * s_blk[(size_t)(b + 2) * W + tb];
+                    s3 += s_S[(GROW + b + 3) * lds + a] * s_blk[(size_t)(b + 3) * W + tb];
+                }
+                for (; b <= a; ++b) s += s_S[(GROW + b) * lds + a] * s_blk[(size_t)b * W + tb];
+                s = (s + s1) + (s2 + s3);
             } else {
                 const int o = (tb - CAM) / D, c = (tb - CAM) - o * D;
 #pragma unroll

@@ -105,8 +105,10 @@ def test_stream_mode_equals_per_frame_calls(calibration):
     b.stream_upload(ids, poses, off)
     b.stream_run(0, 30)
     b.stream_run(30, 60)
-    assert np.array_equal(a.state, b.state)
-    assert np.array_equal(a.uncertainty, b.uncertainty)
+    # not bit-identical: stream mode factors S six rows per block step (k_f1<KIND, true>), per-frame
+    # calls three; same arithmetic otherwise
+    assert rel_err(a.state, b.state) < 1e-12
+    assert rel_err(a.uncertainty, b.uncertainty) < 1e-12
     assert order_of(dict(b.get_lm_estimates())) == order_of(a.landmarks)
 
 

@@ -25,7 +25,7 @@ print("k_f1 [T+issue, model+wait, lazy+Q+S, chol, outputs] us:", " ".join(f"{u:6
 print(f"k_f1 total {us[5]:.2f}; k_f1 start -> k_f2 start {us[6]:.2f}, -> k_f2 end {us[7]:.2f}; k_f2 [loads, product, stores] {us[8]:.2f} {us[9]:.2f} {us[10]:.2f}")
 tl = (C.c_double * 32)()
 _lib.check(lib.asb_timeline(f._h, tl))
-names = {0: "f1 start", 1: "f1 issued", 2: "f1 model", 3: "f1 S", 4: "f1 chol", 5: "f1 end", 8: "f2 start", 9: "f2 loaded", 10: "f2 product", 11: "f2 end", 12: "sweep start", 13: "sweep cta0 end"}
+names = {0: "f1 start", 1: "f1 issued", 2: "f1 model", 3: "f1 S", 4: "f1 chol", 5: "f1 end", 6: "f1 lazy", 7: "f1 Q+I", 8: "f2 start", 9: "f2 loaded", 10: "f2 product", 11: "f2 end", 12: "sweep start", 13: "sweep cta0 end"}
 for u in range(2):
     print(f"update {u}: " + ", ".join(f"{names[i]} {tl[16 * u + i]:.1f}" for i in sorted(names)))
 import os
