@@ -82,6 +82,7 @@ struct asb_filter {
     unsigned int* d_tail = nullptr;   // two tile counters used alternately by successive sweeps (sweep.cuh)
     unsigned int sweep_seq = 0;
     int tail_tiles = 2;        // tiles per CTA handed out dynamically (ASB_TAIL)
+    int lower_only = 0;        // pipelined engine: the sweeps keep only the lower triangle of P up to date (ASB_FULL_P=1: both)
     bool defer = false;        // set by asb_stream_run around its frame loop
     int pdl = 1;               // ASB_PDL=0: stream mode uses the side-stream engine as well
 
@@ -110,6 +111,23 @@ static cudaError_t dmalloc(T** p, size_t count) {
 // ---------------------------------------------------------------------------------------
 // persistent sweep: 2 CTAs / SM (64 x 64 tiles) while both fit in shared memory, else
 // 1 CTA / SM (128 x 64 tiles)
+// P[i][j] = P[j][i] for i < j (32 x 32 tiles through shared memory): the covariance getter of an engine
+// whose sweeps keep only the lower triangle.
+__global__ void __launch_bounds__(256) k_symmetrize(double* P, int ld, int n) {
+    __shared__ double tile[32][33];
+    const int bi = blockIdx.y, bj = blockIdx.x;   // destination tile (rows bi, columns bj), bj >= bi
+    if (bj < bi) return;
+    for (int r = threadIdx.y; r < 32; r += 8) {   // source tile (rows bj, columns bi)
+        const int i = 32 * bj + r, j = 32 * bi + threadIdx.x;
+        tile[r][threadIdx.x] = (i < n && j < n) ? P[(long long)i * ld + j] : 0.0;
+    }
+    __syncthreads();
+    for (int r = threadIdx.y; r < 32; r += 8) {
+        const int i = 32 * bi + r, j = 32 * bj + threadIdx.x;
+        if (i < n && j < n && i < j) P[(long long)i * ld + j] = tile[threadIdx.x][r];
+    }
+}
+
 // <<<>>> with (optionally) the programmatic-stream-serialization attribute: the kernel may be
 // scheduled as soon as every CTA of the previous kernel of the stream has executed
 // griddepcontrol.launch_dependents (or exited); it orders itself with griddepcontrol.wait.
@@ -244,6 +262,7 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
             b.At = f->d_At; b.y = f->d_y; b.T = f->d_T;
             b.dx_in = f->d_dx[cur]; b.dx_out = f->d_dx[cur ^ 1];
             b.Vr = f->d_Vr; b.Vc = f->d_Vc; b.Vt = f->d_Vt;
+            b.lower_only = f->lower_only;
             b.apply_kind = last ? KIND : -1;
             b.as_written = (KIND == 0 && f->quat_mode == ASB_QUAT_AS_WRITTEN) ? 1 : 0;
             b.nlm = (n1 - CAM) / Dims<KIND>::D;
@@ -256,6 +275,7 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
             SweepExtra ex{};
             ex.n = n1; ex.add_q = a.add_q; ex.nz = f->nz;
             ex.apply_kind = -1;
+            ex.lower_only = f->lower_only;
             ex.prof = prof + 12;
             ex.cta_prof = f->d_ctaprof;
             // the sweep leaves room for k_f1 of the next update: two CTAs fewer than fill the GPU
@@ -446,6 +466,7 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
         ASB_CUDA(dmalloc(&f->d_counter, 1));
         if (const char* e = std::getenv("ASB_SPARE")) f->spare_ctas = std::atoi(e);
         if (const char* e = std::getenv("ASB_PDL")) f->pdl = std::atoi(e);
+        f->lower_only = std::getenv("ASB_FULL_P") ? 0 : 1;
         if (std::getenv("ASB_CTA_PROF")) {
             ASB_CUDA(dmalloc(&f->d_ctaprof, 3 * 1024));
             ASB_CUDA(cudaMemsetAsync(f->d_ctaprof, 0, 3 * 1024 * sizeof(unsigned long long), f->stream));
@@ -787,6 +808,11 @@ int asb_set_state(asb_filter* f, const double* in, int n_state) {
 int asb_get_cov(asb_filter* f, double* out, int n_state) {
     ASB_CHECK_HANDLE(f);
     if (!out || n_state != f->n_state()) return fail(ASB_ERR_BAD_ARG, "n_state %d != %d", n_state, f->n_state());
+    if (f->lower_only) {   // the upper triangle is stale: rebuild it from the lower one (in place)
+        const int nt = (n_state + 31) / 32;
+        k_symmetrize<<<dim3(nt, nt), dim3(32, 8), 0, f->stream>>>(f->d_P, f->ld, n_state);
+        ASB_CUDA(cudaGetLastError());
+    }
     int rc = poll_status(f);
     ASB_CUDA(cudaMemcpy2D(out, (size_t)n_state * sizeof(double), f->d_P, (size_t)f->ld * sizeof(double),
                           (size_t)n_state * sizeof(double), n_state, cudaMemcpyDeviceToHost));

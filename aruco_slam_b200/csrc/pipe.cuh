@@ -139,7 +139,10 @@ k_f1(F1Args p) {
         const double* prow = p.P + (long long)i * ld;
         for (int b = lane; b <= a; b += 32) {
             const int j = s_T[b];
-            if (i < n0 && j < n0) cp_async8(s_PT + a * nT + b, p.PT_dense ? p.PT_dense + a * nT + b : prow + j);
+            // the covariance may hold only its lower triangle (SweepExtra::lower_only): read P[max][min]
+            if (i < n0 && j < n0)
+                cp_async8(s_PT + a * nT + b, p.PT_dense ? p.PT_dense + a * nT + b
+                                                        : (j <= i ? prow + j : p.P + (long long)j * ld + i));
             else s_PT[a * nT + b] = (i == j) ? p.nz.init_lm : 0.0;
         }
     }
@@ -374,6 +377,7 @@ struct F2Args {
     double* Vr;                  // tiled panel in V_I column order (sweep.cuh)
     double* Vc;                  // tiled panel in V_J column order
     double* Vt;                  // panel by state column (F1_LDT doubles each) for the next k_f1's lazy operand
+    int lower_only;              // P holds only its lower triangle: row T[a] right of the diagonal is read from column T[a]
     int apply_kind;              // -1: none (more chunks follow), 0: EKF, 1: EKF_Rotations
     int as_written, nlm;
     unsigned int* counter;       // CTAs done (self-resetting)
@@ -446,13 +450,15 @@ k_f2(F2Args p) {
         const int c = 2 * (lane & 15);
         const int j = j0 + c;
         double* dst = s_stage + (size_t)a * F2_LDB + c;
-        if (i < n0 && j + 1 < n0) {
+        if (i < n0 && j + 1 < n0 && (!p.lower_only || j + 1 <= i)) {
             cp_async16(dst, prow + j);
         } else {
 #pragma unroll
             for (int q = 0; q < 2; ++q) {
-                if (i < n0 && j + q < n0) cp_async8(dst + q, prow + j + q);
-                else dst[q] = (i == j + q && i < n1) ? p.nz.init_lm : 0.0;
+                const int jj = j + q;
+                if (i < n0 && jj < n0)
+                    cp_async8(dst + q, (!p.lower_only || jj <= i) ? prow + jj : p.P + (long long)jj * ld + i);
+                else dst[q] = (i == jj && i < n1) ? p.nz.init_lm : 0.0;
             }
         }
     }

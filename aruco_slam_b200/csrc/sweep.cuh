@@ -44,6 +44,10 @@ struct SweepExtra {
     // every tile is stored directly (no mirror), VI comes from the LOCAL panel block I, the diagonal
     // (Q, predict) is where row0 + local row == column.  SweepDual only.
     int rect, row0, nJ;
+    // lower_only: P_out keeps only its lower triangle (i >= j) up to date: no mirror stores, i.e. 8 N^2
+    // instead of 12 N^2 bytes of DRAM traffic per sweep.  The readers of the pipelined engine
+    // (k_f1, k_f2, asb_get_cov) take P[i][j], i < j, from P[j][i].
+    int lower_only;
     unsigned int* tail;        // counter of this launch (zero on entry)
     unsigned int* tail_reset;  // counter of the NEXT launch: zeroed by CTA 0
     int n_static;
@@ -373,7 +377,7 @@ k_sweep(const double* Pin, double* P, int ld, const double* __restrict__ Vr, con
                 tile_store<RM, RN>(P + (long long)r0 * ld + c0, ld, pf, pol_st);
             } else if (interior) {
                 if (!(dbg & 4)) tile_store<RM, RN>(P + (long long)r0 * ld + c0, ld, pf, pol_st);
-                if (!(dbg & 2)) tile_store_mirror<RM, RN>(P + (long long)c0 * ld + r0, ld, pf, pol_mir);
+                if (!(dbg & 2) && !ex.lower_only) tile_store_mirror<RM, RN>(P + (long long)c0 * ld + r0, ld, pf, pol_mir);
             } else {
 #pragma unroll
                 for (int rm = 0; rm < RM; ++rm)
@@ -386,7 +390,7 @@ k_sweep(const double* Pin, double* P, int ld, const double* __restrict__ Vr, con
                                 double o = pf[rm][rn][e];
                                 if (i == j && ex.add_q && i < ex.n) o += process_noise(ex.nz, i);
                                 P[(long long)i * ld + j] = o;
-                                if (i > j) P[(long long)j * ld + i] = o;
+                                if (i > j && !ex.lower_only) P[(long long)j * ld + i] = o;
                             }
                         }
             }
