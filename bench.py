@@ -276,11 +276,11 @@ def leg_c3(torch, stream_ptr, hbm_peak):
         "value": 20.0 * timed_frames / (ms * 1e-3), "unit": UNIT, "us_per_frame": 1e3 * ms / timed_frames,
         "frames": timed_frames, "gpu_launches_per_frame": 3,
         "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": ach / hbm_peak, "traffic": 391.1e6,
+                     "frac": ach / hbm_peak, "traffic": 257.5e6,
                      "note": "achieved = 16*N^2 B per frame / whole-frame time (k_f2 + k_sweep on the critical "
                              "path, k_f1 of the next frame overlapped); traffic = dram read + write bytes of one "
-                             "k_sweep launch, ncu --set full (profiles/r01b_k_sweep.txt): only the lower "
-                             "triangle is read"},
+                             "k_sweep launch, ncu --set full (profiles/r01c_k_sweep.txt): only the lower "
+                             "triangle is read and written (the readers take P[i][j], i < j, from P[j][i])"},
         "e2e": {"value": 20.0 * t_frames / wall, "unit": UNIT, "h2d_bytes_per_step": 20 * 52,
                 "d2h_bytes_per_step": 8 * 6010},
     }

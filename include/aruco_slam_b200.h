@@ -127,7 +127,8 @@ ASB_API int asb_get_landmark_ids(asb_filter* f, int32_t* ids_in_index_order, int
  * setters above.  This is the checkpoint / re-synchronisation path (SURVEY §8c ii). */
 ASB_API int asb_set_landmarks(asb_filter* f, const int32_t* ids_in_index_order, int n);
 /* Raw device pointers for zero-copy consumers (torch.from_blob / cupy): state (N),
- * covariance (row-major with leading dimension *ld doubles). */
+ * covariance (row-major with leading dimension *ld doubles; only the LOWER triangle, i >= j, is
+ * kept up to date by the update kernels - asb_get_cov returns the full symmetric matrix). */
 ASB_API int asb_device_views(asb_filter* f, void** d_state, void** d_cov, int* ld);
 
 /* Intermediates of the last update(), for parity tests (parse_poses EKF:158-200):
