@@ -144,6 +144,33 @@ def test_map_build_reduced_c3(calibration):
     assert rel_err(f.uncertainty, o.uncertainty) < TOL
 
 
+@pytest.mark.parametrize("kind", ["ekf", "rot"])
+def test_stream_mode_matches_oracle(calibration, kind):
+    """asb_stream_run (the bench `value` path: programmatic dependent launches, k_f1 on its own SM,
+    lazy operand, lower-triangle covariance) against the oracle: map build with augmentation every
+    frame and frames of more than one chunk (25 > 21 markers for EKF, 12 > 8 for EKF_Rotations),
+    run split over several calls."""
+    from aruco_slam_b200 import synth
+    if kind == "ekf":
+        stream, n_build = synth.make_map_build_stream(150, 25, 10)
+        frames = n_build + 10
+    else:
+        stream = synth.make_stream(9, 12, 25, 1.0, kind)
+        frames = stream.n_frames
+    o = ekf_oracle.make(kind, "scalar_first")
+    for t in range(frames):
+        o.observe([int(i) for i in stream.ids[t]], stream.poses[t])
+    f = make_gpu(kind, "scalar_first", calibration, 150)
+    ids, poses, off = stream.packed()
+    f.stream_upload(ids[:off[frames]], poses[:off[frames]], off[:frames + 1])
+    f.stream_run(0, 3)
+    f.stream_run(3, 4)
+    f.stream_run(4, frames)
+    assert order_of(f.landmarks) == order_of(o.landmarks)
+    assert rel_err(f.state, o.state) < TOL
+    assert rel_err(f.uncertainty, np.asarray(o.uncertainty)) < TOL
+
+
 def test_full_size_c3_single_steps(calibration):
     """C3 at full size (2000 markers, N = 6010): build on the GPU, copy (state, P,
     landmarks) into the oracle, compare 3 single steps, plus the
