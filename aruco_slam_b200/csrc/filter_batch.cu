@@ -149,7 +149,8 @@ int asb_batch_create(int kind, int quat_mode, const double pose0[10], const asb_
     for (auto& e : b->ev_group) ASB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     for (auto& e : b->ev_done) ASB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     ASB_CUDA(cudaEventCreateWithFlags(&b->ev_main, cudaEventDisableTiming));
-    b->groups = n_seq >= 8 * asb_batch::N_GROUPS ? asb_batch::N_GROUPS : 1;
+    // a group must still fill the GPU a few times over (persistent grid: up to 3 CTAs per SM)
+    b->groups = std::max(1, std::min((int)asb_batch::N_GROUPS, n_seq / (3 * b->sm_count)));
     if (const char* e = std::getenv("ASB_BATCH_GROUPS")) b->groups = std::max(1, std::min(std::atoi(e), (int)asb_batch::N_GROUPS));
     ASB_CUDA(dmalloc(&b->d_states, (size_t)n_seq * b->state_stride));
     ASB_CUDA(dmalloc(&b->d_covs, (size_t)n_seq * b->cov_stride));
