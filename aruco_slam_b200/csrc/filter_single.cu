@@ -82,6 +82,7 @@ struct asb_filter {
     unsigned int* d_tail = nullptr;   // two tile counters used alternately by successive sweeps (sweep.cuh)
     unsigned int sweep_seq = 0;
     int tail_tiles = 2;        // tiles per CTA handed out dynamically (ASB_TAIL)
+    int use_vt = 0;            // ASB_VT=1: k_f2 also writes the panel by state column for k_f1 (bulk copies instead of a gather)
     int lower_only = 0;        // pipelined engine: the sweeps keep only the lower triangle of P up to date (ASB_FULL_P=1: both)
     bool defer = false;        // set by asb_stream_run around its frame loop
     int pdl = 1;               // ASB_PDL=0: stream mode uses the side-stream engine as well
@@ -240,7 +241,10 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
             a.add_q = (first && do_predict) ? 1 : 0;
             a.use_delta = first ? 0 : 1;
             a.dx_in = f->d_dx[cur];
-            a.lazy = f->lazy ? 1 : 0; a.Vp = f->d_Vt; a.m4p = f->prev_m4; a.lazy_q = f->prev_add_q;
+            a.lazy = f->lazy ? 1 : 0; a.m4p = f->prev_m4; a.lazy_q = f->prev_add_q;
+            // the previous panel's columns T: gathered from the tiled V_J panel (k_f2 then writes no third copy)
+            a.Vp = f->use_vt ? f->d_Vt : nullptr;
+            a.Vc_tiled = f->use_vt ? nullptr : f->d_Vc;
             a.At = f->d_At; a.y = f->d_y; a.T = f->d_T;
             a.blocks_out = f->d_blocks + (size_t)c0 * R * W; a.nu_out = f->d_nu + (size_t)R * c0;
             a.status = f->d_status;
@@ -261,7 +265,7 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
             b.kc = kc; b.m4 = m4; b.first_chunk = a.first_chunk; b.add_q = a.add_q; b.use_delta = a.use_delta;
             b.At = f->d_At; b.y = f->d_y; b.T = f->d_T;
             b.dx_in = f->d_dx[cur]; b.dx_out = f->d_dx[cur ^ 1];
-            b.Vr = f->d_Vr; b.Vc = f->d_Vc; b.Vt = f->d_Vt;
+            b.Vr = f->d_Vr; b.Vc = f->d_Vc; b.Vt = f->use_vt ? f->d_Vt : nullptr;
             b.lower_only = f->lower_only;
             b.apply_kind = last ? KIND : -1;
             b.as_written = (KIND == 0 && f->quat_mode == ASB_QUAT_AS_WRITTEN) ? 1 : 0;
@@ -467,6 +471,7 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
         if (const char* e = std::getenv("ASB_SPARE")) f->spare_ctas = std::atoi(e);
         if (const char* e = std::getenv("ASB_PDL")) f->pdl = std::atoi(e);
         f->lower_only = std::getenv("ASB_FULL_P") ? 0 : 1;
+        if (const char* e = std::getenv("ASB_VT")) f->use_vt = std::atoi(e);
         if (std::getenv("ASB_CTA_PROF")) {
             ASB_CUDA(dmalloc(&f->d_ctaprof, 3 * 1024));
             ASB_CUDA(cudaMemsetAsync(f->d_ctaprof, 0, 3 * 1024 * sizeof(unsigned long long), f->stream));

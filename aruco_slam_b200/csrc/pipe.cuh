@@ -425,6 +425,9 @@ k_f2(F2Args p) {
     pdl_wait();      // stream mode: made resident while the sweep before it retired
     pdl_trigger();   // the next k_f1 may take one of the SMs this grid leaves empty; it waits for this grid's end
     front_stamp(stampargs, 0);
+    // EKF: the state entries this CTA will update at the very end (their load latency is off the tail)
+    double state_pre = 0.0;
+    if (KIND == 0 && p.apply_kind == 0 && tid < F2_COLS && j0 + tid < n1) state_pre = p.state[j0 + tid];
     for (int a = tid; a < nT; a += NT) s_T[a] = p.T[a];
     for (int a = tid; a < 64; a += NT) s_y[a] = a < m4 ? p.y[a] : 0.0;
     {   // A^T rows (m4 is a multiple of 4: 16-byte pieces never straddle a row)
@@ -502,7 +505,8 @@ k_f2(F2Args p) {
     front_stamp(stampargs, 2);
 
     // panel by state column for the next k_f1's lazy operand: 4 consecutive rows per 256-bit store
-    {
+    // (null: that k_f1 gathers its columns from the tiled V_J panel instead)
+    if (p.Vt) {
         const int q4 = m4 >> 2;
         for (int e = tid; e < F2_COLS * q4; e += NT) {
             const int c = e / q4, q = e - c * q4;
@@ -527,7 +531,7 @@ k_f2(F2Args p) {
             const double d = (p.use_delta ? p.dx_in[j] : 0.0) + dsum;
             p.dx_out[j] = d;
             if (KIND == 0 && p.apply_kind == 0) {
-                if (j >= CAM) p.state[j] += d;
+                if (j >= CAM) p.state[j] = state_pre + d;
                 else s_dcam[j] = d;
             }
         }
