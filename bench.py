@@ -488,6 +488,9 @@ def run_b200(args):
                     line["workloads"][name] = leg()
                 except Exception as exc:  # keep the headline line even if an extra leg fails
                     line["workloads"][name] = {"error": repr(exc)}
+            # the HBM-bound kernel of the path (north_star's 70 % target) next to the headline roofline
+            if "roofline" in line["workloads"].get("c3", {}):
+                line["roofline_hbm_kernel"] = dict(line["workloads"]["c3"]["roofline"], kernel="k_sweep (C3 leg)")
         # bounded sample: whole sequences of the same workload on ONE core until the budget is spent
         frames = min(args.frames, 1000)
         total, wall_cpu, nseq_cpu = 0, 0.0, 0
