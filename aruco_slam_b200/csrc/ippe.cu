@@ -230,8 +230,9 @@ int asb_ippe_square_device(const float* d_corners, int64_t n, const double camer
     return ASB_OK;
 }
 
-int asb_ippe_square(const float* corners, int64_t n, const double camera_matrix[9],
-                    const double dist_coeffs[5], double marker_size, double* out, int device) {
+// host buffers in, host buffers out; out2 / errs may be null (second solution, float reprojection errors)
+static int ippe_host(const float* corners, int64_t n, const double camera_matrix[9], const double dist_coeffs[5],
+                     double marker_size, double* out, double* out2, float* errs, int device) {
     if (n < 0 || !camera_matrix || (n > 0 && (!corners || !out))) return fail(ASB_ERR_BAD_ARG, "bad ippe arguments");
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
@@ -239,28 +240,44 @@ int asb_ippe_square(const float* corners, int64_t n, const double camera_matrix[
     if (n == 0) return ASB_OK;
     ASB_CUDA(cudaSetDevice(device));
     // Device buffers are kept between calls (grow-only, per device): the per-frame caller
-    // (BaseFilter.estimate_pose_of_markers, a few dozen markers) must not pay two cudaMalloc /
+    // (BaseFilter.estimate_pose_of_markers, a few dozen markers) must not pay cudaMalloc /
     // cudaFree round trips per frame.
-    struct Cache { float* dc = nullptr; double* dout = nullptr; int64_t cap = 0; };
+    struct Cache { float* dc = nullptr; double* dout = nullptr; double* dout2 = nullptr; float* derr = nullptr; int64_t cap = 0; };
     static std::mutex mu;
     static Cache cache[64];
     std::lock_guard<std::mutex> lock(mu);
     Cache& c = cache[device & 63];
     if (n > c.cap) {
-        cudaFree(c.dc); cudaFree(c.dout);
+        cudaFree(c.dc); cudaFree(c.dout); cudaFree(c.dout2); cudaFree(c.derr);
         c = Cache{};
         const int64_t cap = std::max<int64_t>(n, 4096);
         ASB_CUDA(cudaMalloc(&c.dc, (size_t)cap * 8 * sizeof(float)));
         ASB_CUDA(cudaMalloc(&c.dout, (size_t)cap * 6 * sizeof(double)));
+        ASB_CUDA(cudaMalloc(&c.dout2, (size_t)cap * 6 * sizeof(double)));
+        ASB_CUDA(cudaMalloc(&c.derr, (size_t)cap * 2 * sizeof(float)));
         c.cap = cap;
     }
     ASB_CUDA(cudaMemcpy(c.dc, corners, (size_t)n * 8 * sizeof(float), cudaMemcpyHostToDevice));
-    int rc = asb_ippe_square_device(c.dc, n, camera_matrix, dist_coeffs, marker_size, c.dout, nullptr, nullptr, nullptr);
-    if (rc == ASB_OK) {
-        cudaError_t e = cudaMemcpy(out, c.dout, (size_t)n * 6 * sizeof(double), cudaMemcpyDeviceToHost);
-        if (e != cudaSuccess) rc = fail(ASB_ERR_CUDA, "ippe D2H: %s", cudaGetErrorString(e));
-    }
-    return rc;
+    int rc = asb_ippe_square_device(c.dc, n, camera_matrix, dist_coeffs, marker_size, c.dout, out2 ? c.dout2 : nullptr,
+                                    errs ? c.derr : nullptr, nullptr);
+    if (rc != ASB_OK) return rc;
+    ASB_CUDA(cudaMemcpy(out, c.dout, (size_t)n * 6 * sizeof(double), cudaMemcpyDeviceToHost));
+    if (out2) ASB_CUDA(cudaMemcpy(out2, c.dout2, (size_t)n * 6 * sizeof(double), cudaMemcpyDeviceToHost));
+    if (errs) ASB_CUDA(cudaMemcpy(errs, c.derr, (size_t)n * 2 * sizeof(float), cudaMemcpyDeviceToHost));
+    return ASB_OK;
+}
+
+int asb_ippe_square(const float* corners, int64_t n, const double camera_matrix[9],
+                    const double dist_coeffs[5], double marker_size, double* out, int device) {
+    return ippe_host(corners, n, camera_matrix, dist_coeffs, marker_size, out, nullptr, nullptr, device);
+}
+
+// cv2.solvePnPGeneric(..., SOLVEPNP_IPPE_SQUARE): BOTH solutions, the better one first (SURVEY.md 8f row 3:
+// what an orientation-ambiguity gate such as BaseFilter.correct_poses, BASE:274-325, chooses between).
+int asb_ippe_square_both(const float* corners, int64_t n, const double camera_matrix[9], const double dist_coeffs[5],
+                         double marker_size, double* out, double* out2, float* errs, int device) {
+    if (n > 0 && !out2) return fail(ASB_ERR_BAD_ARG, "out2 is NULL");
+    return ippe_host(corners, n, camera_matrix, dist_coeffs, marker_size, out, out2, errs, device);
 }
 
 }  // extern "C"

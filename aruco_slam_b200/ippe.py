@@ -39,6 +39,19 @@ def estimate_pose_of_markers(corners, camera_matrix, dist_coeffs, marker_size: f
     return out
 
 
+def estimate_both_poses(corners, camera_matrix, dist_coeffs, marker_size: float = 0.16, device: int = 0):
+    """``cv2.solvePnPGeneric(..., SOLVEPNP_IPPE_SQUARE)`` for every corner set: (poses (k,2,6) float64
+    ``[tvec, rvec]`` with the better solution first, errors (k,2) float32)."""
+    c = _corner_array(corners)
+    km, dist = _intrinsics(camera_matrix, dist_coeffs)
+    n = c.shape[0]
+    first, second = np.empty((n, 6)), np.empty((n, 6))
+    errs = np.empty((n, 2), dtype=np.float32)
+    _lib.check(_lib.lib().asb_ippe_square_both(_lib.fptr(c), n, _lib.dptr(km), _lib.dptr(dist), float(marker_size),
+                                               _lib.dptr(first), _lib.dptr(second), _lib.fptr(errs), int(device)))
+    return np.stack([first, second], axis=1), errs
+
+
 def estimate_pose_device(d_corners: int, n: int, camera_matrix, dist_coeffs, marker_size: float,
                          d_out: int, d_out2: int | None = None, d_err: int | None = None,
                          stream: int | None = None) -> None:

@@ -199,6 +199,12 @@ ASB_API int asb_shard_get_landmark_ids(asb_shard* s, int32_t* ids_in_index_order
  * 3x3 row-major; dist_coeffs k1 k2 p1 p2 k3; out (n,6) = [tvec, rvec] rows (BASE:171). */
 ASB_API int asb_ippe_square(const float* corners, int64_t n, const double camera_matrix[9],
                     const double dist_coeffs[5], double marker_size, double* out, int device);
+/* cv2.solvePnPGeneric(..., SOLVEPNP_IPPE_SQUARE): both IPPE solutions per corner set, the one with the
+ * smaller reprojection error first (out), the other in out2 (n,6); errs_or_null (n,2) float32 = the two
+ * summed squared reprojection errors in normalised coordinates the ordering was decided on. */
+ASB_API int asb_ippe_square_both(const float* corners, int64_t n, const double camera_matrix[9],
+                         const double dist_coeffs[5], double marker_size, double* out, double* out2,
+                         float* errs_or_null, int device);
 /* Same on DEVICE buffers, asynchronous on `cuda_stream`.  out2_or_null receives the
  * second IPPE solution (n,6) and err_or_null (n,2) the two float reprojection errors. */
 ASB_API int asb_ippe_square_device(const float* d_corners, int64_t n, const double camera_matrix[9],

@@ -148,6 +148,21 @@ def test_ippe_golden_cv2():
     assert et.max() < TOL and er.max() < TOL
 
 
+def test_ippe_both_solutions_golden_cv2():
+    """cv2.solvePnPGeneric(..., SOLVEPNP_IPPE_SQUARE): both solutions, better one first.  The second
+    solution of a near-frontal marker is ill-conditioned (same bound as the oracle's own test)."""
+    from aruco_slam_b200.ippe import estimate_both_poses, estimate_pose_of_markers
+    g = np.load(GOLDEN / "ippe_golden.npz")
+    args = (g["corners"], g["camera_matrix"], g["dist_coeffs"], float(g["marker_size"]))
+    both, errs = estimate_both_poses(*args)
+    assert both.shape == (2000, 2, 6) and errs.shape == (2000, 2)
+    assert np.array_equal(both[:, 0], estimate_pose_of_markers(*args))
+    assert (errs[:, 0] <= errs[:, 1]).all()
+    for j in range(2):
+        et, er = _check_pose(both[:, j], g["both"][:, j])
+        assert np.median(et) < 1e-12 and et.max() < 1e-7 and er.max() < 1e-7, j
+
+
 def test_ippe_large_batch_vs_oracle(calibration):
     from aruco_slam_b200 import estimate_pose_of_markers, synth
     km, dist = calibration
