@@ -169,6 +169,14 @@ static void launch_sweep(asb_filter* f, int n1, int m4, int dbg, const SweepExtr
         k_sweep_ws<<<grid, ws::THREADS, ws::smem_bytes(m4), f->stream>>>(f->d_P, f->ld, f->d_Vr, f->d_Vc, m4, ntiles, dbg, ex);
         return;
     }
+    if (config == 3) {   // three CTAs per SM (sweep.cuh SweepTri)
+        const int ntiles = SweepTri::num_tiles(n1);
+        const int grid = std::min(ntiles, 3 * f->sweep_grid - (spare_ctas ? 3 : 0));
+        schedule(ntiles, grid);
+        launch_k(k_sweep<SweepTri>, grid, SweepTri::THREADS, SweepTri::smem_bytes(m4), f->stream, pdl,
+                 pin, pout, f->ld, f->d_Vr, f->d_Vc, m4, ntiles, dbg, ex);
+        return;
+    }
     const bool dual = config < 0 ? (2 * (SweepDual::smem_bytes(m4) + 1024) <= (size_t)f->smem_optin && !f->force_big)
                                  : config == 1;
     if (dual) {
@@ -440,6 +448,7 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
     f->cap_lm = max_landmarks;
     f->ncap = CAM + f->D * max_landmarks;
     f->ld = round_up(f->ncap, PAD);
+    if (const char* e = std::getenv("ASB_LD_PAD")) f->ld += 16 * std::max(0, std::atoi(e));   // experiment: row stride vs DRAM channel mapping
     f->max_obs = std::max(64, std::min(max_landmarks * 2, 4096));
     f->kc_max = kind == ASB_KIND_EKF ? FrontLimits<0>::KC_MAX : FrontLimits<1>::KC_MAX;  // front.cuh
     cudaDeviceProp prop;
@@ -521,6 +530,8 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
     const int big = (int)prop.sharedMemPerBlockOptin - 2048;  // static smem (mbarriers) counts too
     ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepBig>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepDual>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepTri>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepTri>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     ASB_CUDA(cudaFuncSetAttribute(k_sweep_ws, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_front<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_front<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));

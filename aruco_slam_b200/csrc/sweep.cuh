@@ -192,14 +192,19 @@ __device__ __forceinline__ void tile_store_mirror(double* pm, int ld, const doub
 }
 
 // Tile shape: WM x WN warps, each owning (8 RM) x (8 RN) elements as RM x RN DMMA tiles.
-template <int WM_, int WN_, int RM_, int RN_, int MINB_>
+// LATE: the P sub-tile is loaded AFTER the k-loop instead of being prefetched before it (32 registers
+// fewer during the MMAs); NBUF: VJ buffers (1: the next panel is fetched after this tile's k-loop).
+// Both trade per-CTA latency hiding for occupancy (a third CTA per SM keeps the FP64 tensor pipe fed
+// while the other two are between k-loops).
+template <int WM_, int WN_, int RM_, int RN_, int MINB_, bool LATE_ = false, int NBUF_ = 2>
 struct SweepCfg {
-    static constexpr int WM = WM_, WN = WN_, RM = RM_, RN = RN_, MINB = MINB_;
+    static constexpr int WM = WM_, WN = WN_, RM = RM_, RN = RN_, MINB = MINB_, NBUF = NBUF_;
+    static constexpr bool LATE = LATE_;
     static constexpr int TI = WM * RM * 8, TJ = WN * RN * 8, THREADS = WM * WN * 32;
     static constexpr int RATIO = TI / TJ;             // column tiles per row tile on the diagonal
     static_assert(TJ == V_BLK && TI % V_BLK == 0, "tiles are made of whole V blocks");
     __host__ __device__ static size_t smem_bytes(int m4) {
-        return (size_t)m4 * V_LDB * (RATIO + 2) * sizeof(double);
+        return (size_t)m4 * V_LDB * (RATIO + NBUF) * sizeof(double);
     }
     // lower-triangle tiles of an n x n matrix: row block I has RATIO (I + 1) column tiles
     __host__ __device__ static int num_tiles(int n) {
@@ -209,6 +214,7 @@ struct SweepCfg {
 };
 using SweepBig = SweepCfg<4, 2, 4, 4, 1>;    // 128 x 64 tile, 1 CTA / SM (large m4)
 using SweepDual = SweepCfg<2, 4, 4, 2, 2>;   // 64 x 64 tile, 2 CTAs / SM: one computes while the other drains
+using SweepTri = SweepCfg<2, 4, 4, 2, 3, true, 1>;   // 64 x 64 tile, 3 CTAs / SM (<= 85 registers, 2 panel buffers)
 
 // Persistent kernel.  Each CTA walks a contiguous chunk of the tile list (row-block major),
 // so the TI-column panel VI stays in shared memory while the TJ-column panel VJ is
@@ -300,7 +306,7 @@ k_sweep(const double* Pin, double* P, int ld, const double* __restrict__ Vr, con
                 j = nx - C::RATIO * i * (i + 1) / 2;
             }
             s_nij[slot] = (i << 16) | j;
-            load_vj(vbuf, j * TJ);
+            if (C::NBUF == 2) load_vj(vbuf, j * TJ);   // NBUF == 1: the single buffer is still in use, see do_tile
         }
     };
 
@@ -310,12 +316,14 @@ k_sweep(const double* Pin, double* P, int ld, const double* __restrict__ Vr, con
     // One tile: P sub-tile -> registers, out = P - V_I^T V_J, direct + mirror stores.  draw_slot >= 0: this
     // is where the next dynamic tile is drawn (after the P loads are in flight: the counter's round
     // trip hides behind them).  Inlined into both loops below.
-    auto do_tile = [&](const int I, const int J, const int buf, const int draw_slot) {
+    auto do_tile = [&](const int I, const int J, const int buf_in, const int draw_slot, const int next_j0) {
+        const int buf = C::NBUF == 2 ? buf_in : 0;
         const int i0 = I * TI, j0 = J * TJ;
             // P sub-tile -> registers (fragment ownership of sweep.cuh's header: 256-bit accesses)
             const int r0 = i0 + 8 * RM * wi + 4 * g, c0 = j0 + 8 * RN * wj + 4 * t4;
             double pf[RM][RN][2];
-            if (dbg & 8) {
+            if (C::LATE) {
+            } else if (dbg & 8) {
 #pragma unroll
                 for (int rm = 0; rm < RM; ++rm)
 #pragma unroll
@@ -354,6 +362,24 @@ k_sweep(const double* Pin, double* P, int ld, const double* __restrict__ Vr, con
                     for (int rn = 0; rn < RN; ++rn) dmma884(acc[rm][rn][0], acc[rm][rn][1], a[rm], b[rn]);
             }
 
+            if (C::NBUF == 1) {
+                __syncthreads();   // every warp is done with the VJ buffer: the next tile's panel flies during the epilogue
+                if (tid == 0) {
+                    int nj = next_j0;
+                    if (draw_slot >= 0) nj = s_next[draw_slot] >= 0 ? (s_nij[draw_slot] & 0xffff) * TJ : -1;
+                    if (nj >= 0) load_vj(0, nj);
+                }
+            }
+            if (C::LATE) {
+                if (dbg & 8) {
+#pragma unroll
+                    for (int rm = 0; rm < RM; ++rm)
+#pragma unroll
+                        for (int rn = 0; rn < RN; ++rn) pf[rm][rn][0] = pf[rm][rn][1] = 0.0;
+                } else {
+                    tile_load<RM, RN>(Pin + (long long)r0 * ld + c0, ld, pf, pol_ld);
+                }
+            }
             const bool interior = i0 >= j0 + TJ;  // strictly below the diagonal
 #pragma unroll
             for (int rm = 0; rm < RM; ++rm)
@@ -419,8 +445,8 @@ k_sweep(const double* Pin, double* P, int ld, const double* __restrict__ Vr, con
                 if (Jn < 0) { In = I - 1; Jn = C::RATIO * I - 1; }
             } else if (Jn == (ex.rect ? ex.nJ : C::RATIO * (I + 1))) { In = I + 1; Jn = 0; }
             const bool has_next = t + 1 < t_end;
-            if (tid == 0 && has_next) load_vj(buf ^ 1, Jn * TJ);  // buffer freed by the last __syncthreads
-            do_tile(I, J, buf, (!has_next && dyn) ? 0 : -1);
+            if (C::NBUF == 2 && tid == 0 && has_next) load_vj(buf ^ 1, Jn * TJ);  // buffer freed by the last __syncthreads
+            do_tile(I, J, buf, (!has_next && dyn) ? 0 : -1, has_next ? Jn * TJ : -1);
             __syncthreads();  // every warp is done with VJ[buf] (and VI) before they are overwritten
             Ivi = I;
             if (has_next && In != I) {
@@ -432,7 +458,10 @@ k_sweep(const double* Pin, double* P, int ld, const double* __restrict__ Vr, con
             J = Jn;
         }
     } else {
-        if (tid == 0) draw(0, 0);
+        if (tid == 0) {
+            draw(0, 0);
+            if (C::NBUF == 1 && s_next[0] >= 0) load_vj(0, (s_nij[0] & 0xffff) * TJ);
+        }
         __syncthreads();
     }
     if (dyn) {
@@ -445,7 +474,7 @@ k_sweep(const double* Pin, double* P, int ld, const double* __restrict__ Vr, con
                 vi_pending = true;
                 Ivi = I;
             }
-            do_tile(I, J, buf, slot ^ 1);
+            do_tile(I, J, buf, slot ^ 1, -1);
             __syncthreads();
         }
     }

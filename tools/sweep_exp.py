@@ -7,7 +7,7 @@ km, dist = synth.reference_calibration()
 f = EKF(np.array([0, 0, 0, 1, 0, 0, 0, 0, 0, 0.0]), camera_matrix=km, dist_coeffs=dist, max_landmarks=2000)
 f.set_landmarks(np.arange(2000))
 lib = _lib.lib()
-for cfg in (0, 1, 2):
+for cfg in (0, 1, 2, 3):
     for dbg in [int(a) for a in sys.argv[1:]] or [0]:
         us = C.c_double()
         _lib.check(lib.asb_bench_sweep(f._h, 60, cfg, dbg, 50, C.byref(us)))
