@@ -77,9 +77,12 @@ k_batch(BatchParams p) {
     double* s_state = reinterpret_cast<double*>(smraw);       // ncap
     double* s_delta = s_state + npad;                         // ncap
     double* s_G = s_delta + npad;                             // MC x npad
-    double* s_blk = s_G + (size_t)MC * npad;                  // CK x R x W
-    double* s_nu = s_blk + CK * R * W;                        // MC
-    double* s_S = s_nu + ((MC + 3) & ~3);                     // (MC+1) x LDS_S
+    // measurement-model blocks and raw innovations of TWO chunks: the next chunk's model is evaluated by
+    // the idle warps while warp 0 factors S (the state it is evaluated at does not change inside a frame)
+    double* s_blk0 = s_G + (size_t)MC * npad;                 // 2 x (CK x R x W)
+    double* s_nu0 = s_blk0 + 2 * CK * R * W;                  // 2 x MC (padded)
+    constexpr int NU_LD = (MC + 3) & ~3;
+    double* s_S = s_nu0 + 2 * NU_LD;                          // (MC+1) x LDS_S
     double* s_dinv = s_S + (MC + 1) * LDS_S;                  // MC
     double* s_pose = s_dinv + ((MC + 3) & ~3);                // max_obs x 6
     int* s_ids = reinterpret_cast<int*>(s_pose + (size_t)p.max_obs * 6);   // max_obs
@@ -203,31 +206,27 @@ k_batch(BatchParams p) {
 
             BPROF(1);
             // ---- update, CK markers at a time -----------------------------------------
+            // measurement model of observation c0 + o at the pre-update state -> buffer `which`
+            // (blocks + raw innovation; the correction nu' = nu - H delta is applied where S is built)
+            auto eval_model = [&](int which, int c0m, int o) {
+                double lm[D], lnu[R];
+                const int li = CAM + D * s_idx[c0m + o];
+#pragma unroll
+                for (int c = 0; c < D; ++c) lm[c] = s_state[li + c];
+                observation_model<KIND>(s_state, lm, s_pose + 6 * (c0m + o), lnu, s_blk0 + (which * CK + o) * R * W);
+#pragma unroll
+                for (int r = 0; r < R; ++r) s_nu0[which * NU_LD + R * o + r] = lnu[r];
+            };
+            for (int o = tid; o < min(CK, k); o += NT) eval_model(0, 0, o);
+            __syncthreads();
+            BPROF(2);
             for (int c0 = 0; c0 < k; c0 += CK) {
                 const int kc = min(CK, k - c0);
                 const int mc = R * kc;
-                // measurement model at the pre-update state; nu' = nu - H delta
-                for (int o = tid; o < kc; o += NT) {
-                    double lm[D], lnu[R];
-                    const int li = CAM + D * s_idx[c0 + o];
-#pragma unroll
-                    for (int c = 0; c < D; ++c) lm[c] = s_state[li + c];
-                    double* blk = s_blk + o * R * W;
-                    observation_model<KIND>(s_state, lm, s_pose + 6 * (c0 + o), lnu, blk);
-                    if (c0 > 0) {
-#pragma unroll
-                        for (int r = 0; r < R; ++r) {
-                            double s = lnu[r];
-                            for (int c = 0; c < CAM; ++c) s -= blk[r * W + c] * s_delta[c];
-                            for (int c = 0; c < D; ++c) s -= blk[r * W + CAM + c] * s_delta[li + c];
-                            lnu[r] = s;
-                        }
-                    }
-#pragma unroll
-                    for (int r = 0; r < R; ++r) s_nu[R * o + r] = lnu[r];
-                }
-                __syncthreads();
-                BPROF(2);
+                const int which = (c0 / CK) & 1;
+                const double* s_blk = s_blk0 + which * CK * R * W;
+                const double* s_nu = s_nu0 + which * NU_LD;
+                const int kc_next = min(CK, k - c0 - CK);   // <= 0: this is the last chunk
                 // G = H P  (mc x n): one thread per state column; the 10 camera rows of P are
                 // read once per column, then D landmark rows per observation
                 for (int j = tid; j < n; j += NT) {
@@ -272,6 +271,15 @@ k_batch(BatchParams p) {
                         for (int c = 0; c < D; ++c) s += g[gcol(li + c)] * hb[CAM + c];
                     } else {
                         s = s_nu[b];
+                        if (c0 > 0) {   // nu' = nu - H delta (delta = the correction accumulated by the chunks before)
+                            const int o2 = b / R, ib = b - o2 * R;
+                            const double* hb = s_blk + o2 * R * W + ib * W;
+                            const int li = CAM + D * s_idx[c0 + o2];
+#pragma unroll
+                            for (int c = 0; c < CAM; ++c) s -= hb[c] * s_delta[c];
+#pragma unroll
+                            for (int c = 0; c < D; ++c) s -= hb[CAM + c] * s_delta[li + c];
+                        }
                     }
                     s_S[a * LDS_S + b] = s;
                 }
@@ -309,9 +317,12 @@ k_batch(BatchParams p) {
                             if (c < mc && c <= i && i <= mc) s_S[i * LDS_S + c] = a[c];
                             if (i == 0 && c < mc) s_dinv[c] = dv[c];
                         }
+                    } else if (tid - 32 < kc_next) {
+                        eval_model(which ^ 1, c0 + CK, tid - 32);   // warps 1..: the next chunk's model, meanwhile
                     }
                     __syncthreads();
                 } else {
+                for (int o = tid; o < kc_next; o += NT) eval_model(which ^ 1, c0 + CK, o);
                 // blocked Cholesky, NB = rows per marker
                 for (int jb = 0; jb < mc; jb += NB) {
                     double dblk[NB][NB], dinv[NB];
