@@ -202,6 +202,11 @@ k_batch(BatchParams p) {
                 pset(i, i, pget(i, i) + process_noise(p.nz, i));
                 s_delta[i] = 0.0;
             }
+            {   // the panel's padding columns n .. 8 ceil(n / 8) stay zero for every chunk of this frame:
+                // G and V only ever write columns < n (the rank-m update reads whole 8-column tiles)
+                const int npadc = 8 * ((n + 7) >> 3) - n;
+                for (int e = tid; e < MC * npadc; e += NT) s_G[(e / npadc) * npad + gcol(n + e % npadc)] = 0.0;
+            }
             __syncthreads();
 
             BPROF(1);
@@ -415,9 +420,7 @@ k_batch(BatchParams p) {
                 // with 4 warps per CTA it lost to the FMA pipe.]
                 if (tiled) {
                     const int nt8 = (n + 7) >> 3;
-                    // columns n..8 nt8 of the panel must be zero
-                    for (int e = tid; e < mc * (8 * nt8 - n); e += NT) s_G[(e / (8 * nt8 - n)) * npad + gcol(n + e % (8 * nt8 - n))] = 0.0;
-                    __syncthreads();
+                    // (columns n..8 nt8 of the panel are zero: cleared once per frame, never written)
                     for (int task = tid; task < 2 * tri(nt8); task += NT) {
                         const int tile = task >> 1, h = task & 1;
                         int I = (int)((sqrtf(8.0f * tile + 1.0f) - 1.0f) * 0.5f);
