@@ -260,9 +260,19 @@ k_batch(BatchParams p) {
                 __syncthreads();
                 BPROF(3);
                 // S = G H^T + R (lower) with nu appended as row mc
-                for (int e = tid; e < (mc + 1) * mc; e += NT) {
-                    const int a = e / mc, b = e - a * mc;
-                    if (a < mc && b > a) continue;
+                // tasks: the tri(mc) lower-triangle entries, then the mc entries of the nu row (one round of the CTA
+                // for mc = 12: 90 tasks; indexing the full square left a third of the threads with nothing to do)
+                for (int e = tid; e < tri(mc) + mc; e += NT) {
+                    int a, b;
+                    if (e < tri(mc)) {
+                        a = (int)((sqrtf(8.0f * e + 1.0f) - 1.0f) * 0.5f);
+                        while (tri(a + 1) <= e) ++a;
+                        while (tri(a) > e) --a;
+                        b = e - tri(a);
+                    } else {
+                        a = mc;
+                        b = e - tri(mc);
+                    }
                     double s;
                     if (a < mc) {
                         const int o2 = b / R, ib = b - o2 * R;
