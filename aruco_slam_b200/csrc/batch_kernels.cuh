@@ -236,8 +236,21 @@ k_batch(BatchParams p) {
                 // read once per column, then D landmark rows per observation
                 for (int j = tid; j < n; j += NT) {
                     double pc[CAM];
+                    if (tiled && j >= 8) {
+                        // P[j][0..9] = row j & 7 of tiles (j >> 3, 0) and (j >> 3, 1): five 16-byte chunks with
+                        // one tile index instead of ten swizzled scalar accesses (diagonal tiles hold both halves)
+                        const int t0 = tri(j >> 3), r4 = (j & 7) << 2;
 #pragma unroll
-                    for (int c = 0; c < CAM; ++c) pc[c] = pget(c, j);
+                        for (int q = 0; q < 4; ++q) {
+                            const double2 v = *reinterpret_cast<const double2*>(P + tchunk(t0, r4 + q));
+                            pc[2 * q] = v.x; pc[2 * q + 1] = v.y;
+                        }
+                        const double2 v = *reinterpret_cast<const double2*>(P + tchunk(t0 + 1, r4));
+                        pc[8] = v.x; pc[9] = v.y;
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < CAM; ++c) pc[c] = pget(c, j);
+                    }
                     for (int o = 0; o < kc; ++o) {
                         const double* blk = s_blk + o * R * W;
                         const int li = CAM + D * s_idx[c0 + o];
