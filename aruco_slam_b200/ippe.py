@@ -29,11 +29,16 @@ def _intrinsics(camera_matrix, dist_coeffs):
 
 
 def estimate_pose_of_markers(corners, camera_matrix, dist_coeffs, marker_size: float = 0.16,
-                             device: int = 0) -> np.ndarray:
-    """(k,4,2) float32 corners -> (k,6) float64 ``[tvec, rvec]`` rows (host in, host out)."""
+                             device: int = 0, out: np.ndarray | None = None) -> np.ndarray:
+    """(k,4,2) float32 corners -> (k,6) float64 ``[tvec, rvec]`` rows (host in, host out).
+    ``out``: optional (k,6) float64 C-contiguous result array (e.g. a view of pinned memory: with
+    page-locked ``corners`` / ``out`` the two copies run at full PCIe speed)."""
     c = _corner_array(corners)
     km, dist = _intrinsics(camera_matrix, dist_coeffs)
-    out = np.empty((c.shape[0], 6), dtype=np.float64)
+    if out is None:
+        out = np.empty((c.shape[0], 6), dtype=np.float64)
+    elif out.shape != (c.shape[0], 6) or out.dtype != np.float64 or not out.flags.c_contiguous:
+        raise ValueError("out must be a C-contiguous (k, 6) float64 array")
     _lib.check(_lib.lib().asb_ippe_square(_lib.fptr(c), c.shape[0], _lib.dptr(km), _lib.dptr(dist),
                                           float(marker_size), _lib.dptr(out), int(device)))
     return out
