@@ -101,6 +101,7 @@ SIGNATURES = {
     "asb_shard_get_landmark_ids": (C.c_int, [_vp, _ip, C.c_int]),
     "asb_ippe_square": (C.c_int, [_fp, C.c_int64, _dp, _dp, C.c_double, _dp, C.c_int]),
     "asb_ippe_square_both": (C.c_int, [_fp, C.c_int64, _dp, _dp, C.c_double, _dp, _dp, _fp, C.c_int]),
+    "asb_ippe_square_static": (C.c_int, [_fp, C.c_int64, _dp, _dp, C.c_double, _dp, C.c_int]),
     "asb_ippe_square_device": (C.c_int, [_vp, C.c_int64, _dp, _dp, C.c_double, _vp, _vp, _vp, _vp]),
     "asb_bench_sweep": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, _dp]),
     "asb_front_profile": (C.c_int, [_vp, _dp]),

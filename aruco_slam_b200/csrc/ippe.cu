@@ -280,4 +280,57 @@ int asb_ippe_square_both(const float* corners, int64_t n, const double camera_ma
     return ippe_host(corners, n, camera_matrix, dist_coeffs, marker_size, out, out2, errs, device);
 }
 
+
+// ---- allocation-free variant (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA-graph capture, tight serving loops) ----
+// The device staging that asb_ippe_square keeps in a grow-only cudaMalloc cache lives here in a
+// file-scope array instead: ASB_IPPE_STATIC_MAX corner sets x (32 B of corners + 48 B of poses) =
+// 1.25 MiB, held by every GPU that loads the library until the process exits.  g_ippe_static is a
+// host-side stand-in in host code, NOT a device address: the address the kernel gets comes from
+// cudaGetSymbolAddress, taken once per device with that device current.
+// Every call shares the array and it keeps the last call's contents.  Nothing has to start at zero:
+// the copy overwrites corner rows [0,n) and the kernel writes every pose row [0,n) it returns; rows
+// >= n are stale and never read.  Calls that overlap on the GPU (two host threads on different
+// streams) would race on it: the entry point serialises callers with a mutex and runs on the legacy
+// default stream, so calls through it do not overlap.
+static __device__ __align__(256) unsigned char g_ippe_static[(size_t)ASB_IPPE_STATIC_MAX * 80];
+
+static int ippe_static_scratch(int device, unsigned char** out) {
+    static unsigned char* ptr[64] = {};
+    if (device < 0 || device >= 64) return fail(ASB_ERR_BAD_ARG, "bad device %d", device);
+    ASB_CUDA(cudaSetDevice(device));
+    if (!ptr[device]) {
+        void* p = nullptr;
+        ASB_CUDA(cudaGetSymbolAddress(&p, g_ippe_static));
+        if (!p) return fail(ASB_ERR_CUDA, "cudaGetSymbolAddress returned a null scratch address");
+        ptr[device] = static_cast<unsigned char*>(p);
+    }
+    *out = ptr[device];
+    return ASB_OK;
+}
+
+int asb_ippe_square_static(const float* corners, int64_t n, const double camera_matrix[9],
+                           const double dist_coeffs[5], double marker_size, double* out, int device) {
+    if (n < 0 || !camera_matrix || (n > 0 && (!corners || !out))) return fail(ASB_ERR_BAD_ARG, "bad ippe arguments");
+    if (n > ASB_IPPE_STATIC_MAX)
+        return fail(ASB_ERR_CAPACITY, "asb_ippe_square_static: %lld corner sets exceed the static scratch of %d "
+                    "(ASB_IPPE_STATIC_MAX); use asb_ippe_square", (long long)n, ASB_IPPE_STATIC_MAX);
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(ASB_ERR_CUDA, "no CUDA device: this library has no CPU fallback");
+    if (n == 0) return ASB_OK;
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lock(mu);
+    unsigned char* base = nullptr;
+    int rc = ippe_static_scratch(device, &base);
+    if (rc != ASB_OK) return rc;
+    float* dc = reinterpret_cast<float*>(base);
+    double* dout = reinterpret_cast<double*>(base + (size_t)ASB_IPPE_STATIC_MAX * 32);
+    ASB_CUDA(cudaMemcpy(dc, corners, (size_t)n * 8 * sizeof(float), cudaMemcpyHostToDevice));
+    rc = asb_ippe_square_device(dc, n, camera_matrix, dist_coeffs, marker_size, dout, nullptr, nullptr, nullptr);
+    if (rc != ASB_OK) return rc;
+    ASB_CUDA(cudaMemcpy(out, dout, (size_t)n * 6 * sizeof(double), cudaMemcpyDeviceToHost));
+    return ASB_OK;
+}
+
 }  // extern "C"

@@ -211,6 +211,19 @@ ASB_API int asb_ippe_square_device(const float* d_corners, int64_t n, const doub
                            const double dist_coeffs[5], double marker_size, double* d_out,
                            double* d_out2_or_null, float* d_err_or_null, void* cuda_stream);
 
+/* Allocation-free variant of asb_ippe_square.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture,
+ * tight serving loops, harnesses that forbid it).  Same inputs, outputs and results as
+ * asb_ippe_square (HOST buffers), but the device staging is a file-scope static __device__ array of
+ * ASB_IPPE_STATIC_MAX corner sets x 80 B = 1.25 MiB (held by every GPU that loads the library until
+ * exit) instead of the grow-only cudaMalloc cache; the call makes no cudaMalloc / cudaFree / allocating
+ * library call.  n > ASB_IPPE_STATIC_MAX => ASB_ERR_CAPACITY.  All calls share the one array (it keeps
+ * the previous call's contents; rows [0,n) are overwritten, nothing needs zeroing); callers are
+ * serialised by a mutex on the legacy default stream - work that overlaps on the GPU would race. */
+#define ASB_IPPE_STATIC_MAX 16384
+ASB_API int asb_ippe_square_static(const float* corners, int64_t n, const double camera_matrix[9],
+                           const double dist_coeffs[5], double marker_size, double* out, int device);
+
 /* ---- measurement helpers (bench / profiles) -------------------------------------- */
 /* FP64 pipe micro-benchmarks: achieved TFLOP/s of dependent-free DFMA chains and of
  * mma.sync m8n8k4 f64 (DMMA), timed with CUDA events. which: 0 = DFMA, 1 = DMMA, 2 = both. */
