@@ -74,6 +74,8 @@ SIGNATURES = {
                                    C.c_int, C.c_int, C.POINTER(_vp)]),
     "asb_batch_destroy": (C.c_int, [_vp]),
     "asb_batch_reset": (C.c_int, [_vp]),
+    "asb_batch_set_engine": (C.c_int, [_vp, C.c_int]),
+    "asb_batch_get_engine": (C.c_int, [_vp, _intp]),
     "asb_batch_set_stream": (C.c_int, [_vp, _vp]),
     "asb_batch_synchronize": (C.c_int, [_vp]),
     "asb_batch_upload": (C.c_int, [_vp, _ip, _dp, _lp, C.c_int]),

@@ -1,7 +1,9 @@
-"""Many independent filters advanced together (BASELINE configs C2 / C5): one CTA per
-sequence, filter resident in shared memory.  Each sequence behaves exactly like one
-``EKF`` / ``EKF_Rotations`` instance fed its own frames through ``observe``
-(extended_kalman_filter.py:58-82)."""
+"""Many independent filters advanced together (BASELINE configs C2 / C5).  Each sequence behaves
+exactly like one ``EKF`` / ``EKF_Rotations`` instance fed its own frames through ``observe``
+(extended_kalman_filter.py:58-82, ekf_with_rotations.py:66-90).  Two engines behind one handle:
+``resident`` (one CTA per sequence, the filter in shared memory for all frames) and ``wide``
+(frame-synchronous kernels over all sequences, covariance tiled in HBM: EKF_Rotations at 32 / 64
+markers); ``auto`` picks resident when the covariance fits an SM."""
 from __future__ import annotations
 
 import ctypes as C
@@ -16,7 +18,7 @@ CAM_DIMS = 10
 class FilterBatch:
     def __init__(self, kind: str, n_seq: int, max_landmarks: int, max_obs_per_frame: int, *,
                  quat_mode: str = "as_written", initial_camera_pose=None, noise: dict | None = None,
-                 device: int = 0) -> None:
+                 device: int = 0, engine: str = "auto") -> None:
         kinds = {"ekf": _lib.KIND_EKF, "rot": _lib.KIND_ROT, "ekf_rotations": _lib.KIND_ROT}
         modes = {"as_written": _lib.QUAT_AS_WRITTEN, "scalar_first": _lib.QUAT_SCALAR_FIRST}
         self.kind = kinds[kind]
@@ -40,6 +42,14 @@ class FilterBatch:
         self._h = h
         self.n_frames = 0
         self._keep = None
+        if engine != "auto":
+            _lib.check(self._lib.asb_batch_set_engine(self._h, {"resident": 1, "wide": 2}[engine]))
+
+    @property
+    def engine(self) -> str:
+        e = C.c_int()
+        _lib.check(self._lib.asb_batch_get_engine(self._h, C.byref(e)))
+        return {1: "resident", 2: "wide"}[e.value]
 
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None

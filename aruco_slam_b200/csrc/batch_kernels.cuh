@@ -550,12 +550,18 @@ k_batch(BatchParams p) {
 // Constructor state of every sequence: state = pose0, P = init_cam * I10 (EKF:46-48), empty map.
 __global__ void k_batch_init(double* __restrict__ states, double* __restrict__ covs, int* __restrict__ nlm,
                              int* __restrict__ status, long long state_stride, long long cov_stride,
-                             int n_seq, const double* __restrict__ pose0, double init_cam) {
+                             int n_seq, const double* __restrict__ pose0, double init_cam, int tiled) {
     const int seq = blockIdx.x;
     if (seq >= n_seq) return;
     double* st = states + (long long)seq * state_stride;
     double* cv = covs + (long long)seq * cov_stride;
     for (int i = threadIdx.x; i < CAM; i += blockDim.x) st[i] = pose0[i];
+    if (tiled) {   // wide engine: 8 x 8 tiles (wide_kernels.cuh), the whole buffer was zeroed by the caller
+        for (int i = threadIdx.x; i < CAM; i += blockDim.x)
+            cv[((long long)(tri(i >> 3) + (i >> 3)) << 6) + ((i & 7) << 3) + (i & 7)] = init_cam;
+        if (threadIdx.x == 0) { nlm[seq] = 0; status[seq] = 0; }
+        return;
+    }
     for (int e = threadIdx.x; e < tri(CAM); e += blockDim.x) cv[e] = 0.0;
     __syncthreads();
     for (int i = threadIdx.x; i < CAM; i += blockDim.x) cv[tri(i) + i] = init_cam;

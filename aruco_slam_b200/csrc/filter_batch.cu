@@ -7,6 +7,7 @@
 
 #include "batch_kernels.cuh"
 #include "common.cuh"
+#include "wide_kernels.cuh"
 
 using namespace asb;
 
@@ -39,6 +40,16 @@ struct asb_batch {
     cudaEvent_t ev_group[N_GROUPS]{}, ev_main = nullptr, ev_done[2] = {nullptr, nullptr};
     bool fresh_upload = false;
     int groups = 1;
+    // Wide engine (wide_kernels.cuh): frame-synchronous kernels, covariance tiled in HBM.  Chosen at creation
+    // when the resident engine's shared-memory footprint exceeds an SM (EKF_Rotations at 32 / 64 markers),
+    // or on request (asb_batch_set_engine before the first upload).
+    bool wide = false;
+    int engine_req = 0;            // 0 auto, 1 resident, 2 wide
+    int *w_meta = nullptr, *w_idx = nullptr;
+    double *w_delta = nullptr, *w_H = nullptr, *w_L = nullptr, *w_Dinv = nullptr, *w_y = nullptr, *w_V = nullptr;
+    long long w_vstride = 0;
+    int w_nb64 = 0;
+    std::vector<int> kmax;         // per frame: max observations over the sequences (host, from the offsets)
 };
 
 static int check(asb_batch* b) {
@@ -101,12 +112,102 @@ static int launch_batch_dyn(asb_batch* b, const BatchParams& p, size_t smem, int
 #undef ASB_DISPATCH
 }
 
+// ---- wide engine, host side ------------------------------------------------------------------------
+template <int KIND> static size_t wide_front_smem(int max_lm, int max_obs) {
+    using WD = WideDims<KIND>;
+    const int cap_obs = std::max(max_obs, (int)WCK);
+    return ((size_t)tri(WD::NB) * 64 + (size_t)CAM * WD::TW + WD::M8 + 64 + (size_t)cap_obs * 6) * 8 +
+           ((size_t)cap_obs * 3 + max_lm + 4) * 4;
+}
+template <int KIND> static size_t wide_panel_smem() {
+    using WD = WideDims<KIND>;
+    return ((size_t)WD::M8 * W_VLD + CAM * 64 + WD::M8) * 8 + WCK * 4;
+}
+static size_t wide_sweep_smem() { return (size_t)W_NST * 2 * W_SLAB * W_VLD * 8; }
+
+static int resident_fits(const asb_batch* b) {
+    const size_t base = batch_smem_base(b->D, b->R, b->ck, b->max_lm, b->max_obs);
+    return base + (size_t)tiled_doubles(b->ncap) * sizeof(double) <= (size_t)b->smem_optin;
+}
+
+static void wide_free(asb_batch* b) {
+    cudaFree(b->w_meta); cudaFree(b->w_idx); cudaFree(b->w_delta); cudaFree(b->w_H);
+    cudaFree(b->w_L); cudaFree(b->w_Dinv); cudaFree(b->w_y); cudaFree(b->w_V);
+    b->w_meta = b->w_idx = nullptr;
+    b->w_delta = b->w_H = b->w_L = b->w_Dinv = b->w_y = b->w_V = nullptr;
+}
+
+template <int KIND> static int wide_alloc_kind(asb_batch* b) {
+    using WD = WideDims<KIND>;
+    const size_t ns = (size_t)b->n_seq;
+    b->w_nb64 = (b->ncap + 63) / 64;
+    b->w_vstride = (long long)b->w_nb64 * WD::M8 * W_VLD;
+    ASB_CUDA(dmalloc(&b->w_meta, ns * 8));
+    ASB_CUDA(dmalloc(&b->w_idx, ns * b->max_obs));
+    ASB_CUDA(dmalloc(&b->w_delta, ns * b->state_stride));
+    ASB_CUDA(dmalloc(&b->w_H, ns * WCK * WD::R * WD::W));
+    ASB_CUDA(dmalloc(&b->w_L, ns * tri(WD::NB) * 64));
+    ASB_CUDA(dmalloc(&b->w_Dinv, ns * WD::NB * 64));
+    ASB_CUDA(dmalloc(&b->w_y, ns * WD::M8));
+    ASB_CUDA(dmalloc(&b->w_V, ns * (size_t)b->w_vstride));
+    ASB_CUDA(cudaMemset(b->w_meta, 0, ns * 8 * sizeof(int)));
+    ASB_CUDA(cudaMemset(b->w_V, 0, ns * (size_t)b->w_vstride * sizeof(double)));
+    return ASB_OK;
+}
+
+// (re)allocate the covariance for the chosen engine: packed lower triangle (resident) or 8 x 8 tiles (wide)
+static int alloc_covs(asb_batch* b) {
+    cudaFree(b->d_covs);
+    b->d_covs = nullptr;
+    wide_free(b);
+    b->cov_stride = b->wide ? (long long)tiled_doubles(b->ncap)
+                            : (((long long)b->ncap * (b->ncap + 1) / 2 + 3) & ~3LL);
+    ASB_CUDA(dmalloc(&b->d_covs, (size_t)b->n_seq * b->cov_stride));
+    if (b->wide) return b->kind == ASB_KIND_EKF ? wide_alloc_kind<0>(b) : wide_alloc_kind<1>(b);
+    return ASB_OK;
+}
+
+template <int KIND> static int wide_run(asb_batch* b, int t0, int t1) {
+    WideParams p;
+    p.states = b->d_states; p.covs = b->d_covs; p.nlm = b->d_nlm; p.lm_ids = b->d_tab; p.status = b->d_status;
+    p.ids = b->d_ids; p.poses = b->d_poses; p.offsets = b->d_off;
+    p.state_stride = b->state_stride; p.cov_stride = b->cov_stride;
+    p.n_seq = b->n_seq; p.n_frames = b->n_frames; p.max_lm = b->max_lm; p.max_obs = b->max_obs;
+    p.as_written = (b->kind == ASB_KIND_EKF && b->quat_mode == ASB_QUAT_AS_WRITTEN) ? 1 : 0;
+    p.nz = b->nz;
+    p.meta = b->w_meta; p.idx = b->w_idx; p.delta = b->w_delta; p.H = b->w_H; p.L = b->w_L; p.Dinv = b->w_Dinv;
+    p.y = b->w_y; p.V = b->w_V; p.v_stride = b->w_vstride; p.nb64 = b->w_nb64;
+    const size_t sm_front = wide_front_smem<KIND>(b->max_lm, b->max_obs), sm_panel = wide_panel_smem<KIND>(),
+                 sm_sweep = wide_sweep_smem();
+    if (sm_front > (size_t)b->smem_optin) return fail(ASB_ERR_CAPACITY, "k_wide_front needs %zu B shared memory", sm_front);
+    ASB_CUDA(cudaFuncSetAttribute(k_wide_front<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_front));
+    ASB_CUDA(cudaFuncSetAttribute(k_wide_panel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_panel));
+    ASB_CUDA(cudaFuncSetAttribute(k_wide_sweep<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_sweep));
+    const dim3 g_panel(b->w_nb64, b->n_seq), g_sweep(tri(b->w_nb64), b->n_seq);
+    for (int t = t0; t < t1; ++t) {
+        const int rounds = (b->kmax[t] + WCK - 1) / WCK;
+        for (int r = 0; r < rounds; ++r) {
+            p.t = t; p.round = r;
+            k_wide_front<KIND><<<b->n_seq, 256, sm_front, b->stream>>>(p);
+            k_wide_panel<KIND><<<g_panel, 256, sm_panel, b->stream>>>(p);
+            k_wide_sweep<KIND><<<g_sweep, 256, sm_sweep, b->stream>>>(p);
+        }
+    }
+    k_wide_apply<KIND><<<b->n_seq, 64, 0, b->stream>>>(p);
+    ASB_CUDA(cudaGetLastError());
+    return ASB_OK;
+}
+
 extern "C" {
 
 int asb_batch_reset(asb_batch* b) {
     ASB_CHECK_BATCH(b);
+    if (b->wide) {   // the wide engine relies on every covariance entry outside the live block being zero
+        ASB_CUDA(cudaMemsetAsync(b->d_covs, 0, (size_t)b->n_seq * b->cov_stride * sizeof(double), b->stream));
+        ASB_CUDA(cudaMemsetAsync(b->w_meta, 0, (size_t)b->n_seq * 8 * sizeof(int), b->stream));
+    }
     k_batch_init<<<b->n_seq, 64, 0, b->stream>>>(b->d_states, b->d_covs, b->d_nlm, b->d_status, b->state_stride,
-                                                 b->cov_stride, b->n_seq, b->d_pose0, b->nz.init_cam);
+                                                 b->cov_stride, b->n_seq, b->d_pose0, b->nz.init_cam, b->wide ? 1 : 0);
     ASB_CUDA(cudaGetLastError());
     return ASB_OK;
 }
@@ -133,7 +234,6 @@ int asb_batch_create(int kind, int quat_mode, const double pose0[10], const asb_
     b->n_seq = n_seq; b->max_lm = max_landmarks; b->max_obs = max_obs_per_frame;
     b->ncap = CAM + b->D * max_landmarks;
     b->state_stride = round_up(b->ncap, 4);
-    b->cov_stride = ((long long)b->ncap * (b->ncap + 1) / 2 + 3) & ~3LL;
     cudaDeviceProp prop;
     ASB_CUDA(cudaGetDeviceProperties(&prop, device));
     b->sm_count = prop.multiProcessorCount;
@@ -153,7 +253,11 @@ int asb_batch_create(int kind, int quat_mode, const double pose0[10], const asb_
     b->groups = std::max(1, std::min((int)asb_batch::N_GROUPS, n_seq / (3 * b->sm_count)));
     if (const char* e = std::getenv("ASB_BATCH_GROUPS")) b->groups = std::max(1, std::min(std::atoi(e), (int)asb_batch::N_GROUPS));
     ASB_CUDA(dmalloc(&b->d_states, (size_t)n_seq * b->state_stride));
-    ASB_CUDA(dmalloc(&b->d_covs, (size_t)n_seq * b->cov_stride));
+    b->wide = !resident_fits(b);
+    {
+        int rc = alloc_covs(b);
+        if (rc != ASB_OK) return rc;
+    }
     ASB_CUDA(dmalloc(&b->d_nlm, (size_t)n_seq));
     ASB_CUDA(dmalloc(&b->d_prof, 16));
     ASB_CUDA(cudaMemset(b->d_prof, 0, 16 * sizeof(unsigned long long)));
@@ -181,6 +285,7 @@ int asb_batch_destroy(asb_batch* b) {
     cudaFree(b->d_states); cudaFree(b->d_covs); cudaFree(b->d_nlm); cudaFree(b->d_tab);
     cudaFree(b->d_status); cudaFree(b->d_ids); cudaFree(b->d_poses); cudaFree(b->d_off);
     cudaFree(b->d_dense); cudaFree(b->d_pose0);
+    wide_free(b);
     cudaStreamDestroy(b->own_stream);
     cudaStreamSynchronize(b->copy_stream);
     cudaStreamDestroy(b->copy_stream);
@@ -190,6 +295,29 @@ int asb_batch_destroy(asb_batch* b) {
     cudaEventDestroy(b->ev_main);
     b->magic = 0;
     delete b;
+    return ASB_OK;
+}
+
+int asb_batch_set_engine(asb_batch* b, int engine) {
+    ASB_CHECK_BATCH(b);
+    if (engine < 0 || engine > 2) return fail(ASB_ERR_BAD_ARG, "engine %d", engine);
+    const bool want_wide = engine == 2 || (engine == 0 && !resident_fits(b));
+    if (engine == 1 && !resident_fits(b))
+        return fail(ASB_ERR_CAPACITY, "the resident engine needs the covariance in shared memory (N = %d does not fit)", b->ncap);
+    ASB_CUDA(cudaStreamSynchronize(b->stream));
+    b->engine_req = engine;
+    if (want_wide != b->wide) {
+        b->wide = want_wide;
+        int rc = alloc_covs(b);
+        if (rc != ASB_OK) return rc;
+    }
+    return asb_batch_reset(b);   // switching engines starts the filters over (the covariance layout differs)
+}
+
+int asb_batch_get_engine(asb_batch* b, int* engine) {
+    ASB_CHECK_BATCH(b);
+    if (!engine) return fail(ASB_ERR_BAD_ARG, "engine is NULL");
+    *engine = b->wide ? 2 : 1;
     return ASB_OK;
 }
 
@@ -246,6 +374,14 @@ int asb_batch_upload(asb_batch* b, const int32_t* ids, const double* poses, cons
         ASB_CUDA(cudaEventRecord(b->ev_group[g], b->copy_stream));
     }
     b->fresh_upload = true;
+    if (b->wide) {   // rounds per frame = ceil(max_s k(s, t) / WCK): the frame-synchronous launches need it on the host
+        b->kmax.assign(n_frames, 0);
+        for (long long q = 0; q < b->n_seq; ++q) {
+            const int64_t* o = offsets + q * n_frames;
+            for (int t = 0; t < n_frames; ++t) b->kmax[t] = std::max(b->kmax[t], (int)(o[t + 1] - o[t]));
+        }
+        for (int t = 0; t < n_frames; ++t) b->kmax[t] = std::min(b->kmax[t], b->max_obs);
+    }
     return ASB_OK;
 }
 
@@ -253,6 +389,13 @@ int asb_batch_run(asb_batch* b, int t0, int t1) {
     ASB_CHECK_BATCH(b);
     if (!b->d_off) return fail(ASB_ERR_NO_STREAM, "batch_run before batch_upload");
     if (t0 < 0 || t1 < t0 || t1 > b->n_frames) return fail(ASB_ERR_BAD_ARG, "bad frame range [%d,%d)", t0, t1);
+    if (b->wide) {
+        if (b->fresh_upload) {
+            for (int g = 0; g < b->groups; ++g) ASB_CUDA(cudaStreamWaitEvent(b->stream, b->ev_group[g], 0));
+            b->fresh_upload = false;
+        }
+        return b->kind == ASB_KIND_EKF ? wide_run<0>(b, t0, t1) : wide_run<1>(b, t0, t1);
+    }
     BatchParams p;
     p.states = b->d_states; p.covs = b->d_covs; p.nlm = b->d_nlm; p.lm_ids = b->d_tab; p.status = b->d_status;
     p.ids = b->d_ids; p.poses = b->d_poses; p.offsets = b->d_off;
@@ -341,7 +484,10 @@ int asb_batch_get_cov(asb_batch* b, int seq, double* out, int n_state) {
     if (rc != ASB_OK) return rc;
     if (!out || n_state != n) return fail(ASB_ERR_BAD_ARG, "n_state %d != %d", n_state, n);
     const long long cnt = (long long)n * n;
-    k_unpack<<<(unsigned)((cnt + 255) / 256), 256, 0, b->stream>>>(b->d_covs + (size_t)seq * b->cov_stride, n, b->d_dense);
+    if (b->wide)
+        k_unpack_tiled<<<(unsigned)((cnt + 255) / 256), 256, 0, b->stream>>>(b->d_covs + (size_t)seq * b->cov_stride, n, b->d_dense);
+    else
+        k_unpack<<<(unsigned)((cnt + 255) / 256), 256, 0, b->stream>>>(b->d_covs + (size_t)seq * b->cov_stride, n, b->d_dense);
     ASB_CUDA(cudaGetLastError());
     ASB_CUDA(cudaStreamSynchronize(b->stream));
     ASB_CUDA(cudaMemcpy(out, b->d_dense, cnt * sizeof(double), cudaMemcpyDeviceToHost));

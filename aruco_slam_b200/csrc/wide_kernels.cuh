@@ -1,0 +1,634 @@
+// Wide batched engine: many independent filters whose covariance does NOT fit one CTA's shared
+// memory (EKF_Rotations at 32 / 64 markers: N = 330 / 650, P 0.46 / 1.7 MB per sequence; BASELINE
+// configs C2-ROT / C5-ROT).  Frame-synchronous: for frame t every sequence advances together through
+// three kernels per update chunk (<= WCK = 16 markers, m <= 112 rows), the covariance staying in HBM:
+//
+//   k_wide_front   one CTA per sequence: pending state update + quaternion reset (ROT:143-177),
+//                  id association / augmentation in frame order (ROT:66-90, 275-335), measurement
+//                  model (ROT:337-427 closed form), S = H P[T,T] H^T + R (ROT:128-133) straight from
+//                  the touched 20 x 20 blocks of P, blocked Cholesky on the FP64 tensor pipe,
+//                  y = L^-1 nu', the 8 x 8 inverse diagonal blocks of L
+//   k_wide_panel   one CTA per (sequence, 64 state columns): G = H P[T, cols] (H never materialised),
+//                  V = L^-1 G by blocked forward substitution with DMMA, delta += V^T y
+//   k_wide_sweep   one CTA per (sequence, 64 x 64 lower-triangle tile): P <- P + Q - V^T V
+//                  (= (I - K H) P, ROT:180-181), V slabs by TMA bulk copy on an mbarrier ring, DMMA
+//
+// K is never formed (K nu = V^T y, K H P = V^T V).  Chunks of one frame condition sequentially with
+// the innovation corrected by H delta (DESIGN.md "chunked update"); predict (P += diag Q, ROT:103-113)
+// is folded into the first chunk.  Same model code (model.cuh) as the other engines.
+//
+// Covariance layout in HBM ("tiled"): lower triangle as 8 x 8 tiles, tile (I8, J8 <= I8) at
+// tri(I8) + J8, 64 doubles row-major, diagonal tiles full.  A warp's DMMA accumulator fragment of
+// one tile is then one contiguous 512-byte access (lane l owns doubles 2l, 2l+1).
+#pragma once
+#include <cstdint>
+
+#include "batch_kernels.cuh"
+#include "sweep.cuh"
+
+namespace asb {
+
+constexpr int WCK = 16;         // markers per update chunk
+constexpr int W_VLD = 68;       // doubles per V panel row of a 64-column block (= 4 mod 16: conflict-free fragments)
+constexpr int W_SLAB = 16;      // V rows per pipeline stage of the sweep
+constexpr int W_NST = 4;        // stages
+
+template <int KIND> struct WideDims {
+    static constexpr int R = Dims<KIND>::R, D = Dims<KIND>::D, W = CAM + D;
+    static constexpr int MC = R * WCK;                 // rows per chunk
+    static constexpr int M8 = (MC + 7) & ~7;           // padded to whole 8-row blocks
+    static constexpr int NB = M8 / 8;
+    static constexpr int TW = CAM + D * WCK;           // touched state columns per chunk
+};
+
+struct WideParams {
+    double* states;
+    double* covs;              // tiled layout, cov_stride doubles per sequence
+    int* nlm;
+    int* lm_ids;
+    int* status;
+    const int* ids;
+    const double* poses;
+    const long long* offsets;
+    long long state_stride, cov_stride;
+    int n_seq, n_frames, max_lm, max_obs, as_written;
+    int t, round;
+    Noise nz;
+    // per-sequence scratch
+    int* meta;                 // 8 ints: k, nchunks, chunk size, n, pending, m8 (0 = idle this round), kc, c0
+    int* idx;                  // max_obs landmark indices of the current frame
+    double* delta;             // state_stride
+    double* H;                 // WCK * R * W   measurement blocks of the current chunk
+    double* L;                 // tri(NB) * 64  Cholesky factor, 8 x 8 tiles
+    double* Dinv;              // NB * 64       inverse diagonal blocks
+    double* y;                 // M8
+    double* V;                 // nb64 * M8 * W_VLD panel, 64-column blocks
+    long long v_stride;        // doubles per sequence of V
+    int nb64;                  // 64-column blocks at capacity
+};
+
+__device__ __forceinline__ long long wt_off(int i, int j) {   // (i >> 3) >= (j >> 3)
+    return ((long long)(tri(i >> 3) + (j >> 3)) << 6) + ((i & 7) << 3) + (j & 7);
+}
+__device__ __forceinline__ double wt_sym(const double* __restrict__ P, int i, int j) {
+    return (i >> 3) >= (j >> 3) ? P[wt_off(i, j)] : P[wt_off(j, i)];
+}
+
+// ---- k_wide_front -------------------------------------------------------------------------------
+template <int KIND>
+__global__ void __launch_bounds__(256, 3) k_wide_front(WideParams p) {
+    using WD = WideDims<KIND>;
+    constexpr int D = WD::D, R = WD::R, W = WD::W, M8 = WD::M8, NB = WD::NB, NT = 256;
+    extern __shared__ __align__(16) unsigned char smraw[];
+    double* s_S = reinterpret_cast<double*>(smraw);           // tri(NB) tiles x 64
+    double* s_Pc = s_S + tri(NB) * 64;                        // CAM x TW: P[cam, touched columns]
+    double* s_nu = s_Pc + CAM * WD::TW;                       // M8
+    double* s_dv = s_nu + M8;                                 // 64: inverse of the current diagonal block
+    double* s_pose = s_dv + 64;                               // max(max_obs, WCK) x 6
+    const int cap_obs = max(p.max_obs, WCK);
+    int* s_ids = reinterpret_cast<int*>(s_pose + (size_t)cap_obs * 6);
+    int* s_idx = s_ids + cap_obs;
+    int* s_new = s_idx + cap_obs;
+    int* s_tab = s_new + cap_obs;                             // max_lm
+    int* s_misc = s_tab + p.max_lm;                           // [0] nlm after, [1] status, [2] bad
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int seq = blockIdx.x;
+    int* meta = p.meta + (long long)seq * 8;
+    double* state = p.states + (long long)seq * p.state_stride;
+    double* P = p.covs + (long long)seq * p.cov_stride;
+    double* delta = p.delta + (long long)seq * p.state_stride;
+    int* g_idx = p.idx + (long long)seq * p.max_obs;
+    const long long ob = p.offsets[(long long)seq * p.n_frames + p.t];
+    int k, cs, n;
+
+    if (p.round == 0) {
+        k = (int)(p.offsets[(long long)seq * p.n_frames + p.t + 1] - ob);
+        const int st = p.status[seq];
+        if (k == 0 || k > p.max_obs || st == ASB_ERR_CAPACITY) {   // no detection: no predict either (BASE:197-204)
+            if (tid == 0) {
+                meta[1] = 0; meta[5] = 0;
+                if (k > p.max_obs) p.status[seq] = ASB_ERR_CAPACITY;
+            }
+            return;
+        }
+        int nlm = p.nlm[seq];
+        // pending state update of the previous frame (its delta is complete: all panels ran)
+        if (meta[4]) {
+            if (tid == 0) {
+                double cam[CAM], d[CAM];
+#pragma unroll
+                for (int c = 0; c < CAM; ++c) { cam[c] = state[c]; d[c] = delta[c]; }
+                camera_reset(cam, d, p.as_written);
+#pragma unroll
+                for (int c = 0; c < CAM; ++c) state[c] = cam[c];
+            }
+            for (int l = tid; l < nlm; l += NT) {
+                double lm[D], d[D];
+#pragma unroll
+                for (int c = 0; c < D; ++c) { lm[c] = state[CAM + D * l + c]; d[c] = delta[CAM + D * l + c]; }
+                landmark_update<KIND>(lm, d);
+#pragma unroll
+                for (int c = 0; c < D; ++c) state[CAM + D * l + c] = lm[c];
+            }
+        }
+        for (int o = tid; o < k; o += NT) s_ids[o] = p.ids[ob + o];
+        for (int e = tid; e < 6 * k; e += NT) s_pose[e] = p.poses[6 * ob + e];
+        for (int i = tid; i < nlm; i += NT) s_tab[i] = p.lm_ids[(long long)seq * p.max_lm + i];
+        if (tid == 0) s_misc[1] = 0;
+        __syncthreads();
+        for (int o = tid; o < k; o += NT) {
+            const int id = s_ids[o];
+            int found = -1;
+            for (int i = 0; i < nlm; ++i)
+                if (s_tab[i] == id) { found = i; break; }
+            s_idx[o] = found;
+            s_new[o] = 0;
+        }
+        __syncthreads();
+        if (tid == 0) {   // unseen ids, in frame order; duplicates bind to the first (EKF:75-78)
+            int cur = nlm;
+            for (int o = 0; o < k; ++o) {
+                if (s_idx[o] >= 0) continue;
+                const int id = s_ids[o];
+                int found = -1;
+                for (int i = nlm; i < cur; ++i)
+                    if (s_tab[i] == id) { found = i; break; }
+                if (found < 0) {
+                    if (cur >= p.max_lm) { s_misc[1] = ASB_ERR_CAPACITY; found = 0; }
+                    else { s_tab[cur] = id; found = cur++; s_new[o] = 1; }
+                }
+                s_idx[o] = found;
+            }
+            s_misc[0] = cur;
+        }
+        __syncthreads();
+        const int nlm1 = s_misc[0];
+        if (s_misc[1] == ASB_ERR_CAPACITY) {
+            if (tid == 0) { p.status[seq] = ASB_ERR_CAPACITY; meta[1] = 0; meta[5] = 0; meta[4] = 0; }
+            return;
+        }
+        n = CAM + D * nlm1;
+        if (nlm1 > nlm) {   // augmentation: new landmark states, block-diagonal covariance growth (rows/cols are zero)
+            for (int o = tid; o < k; o += NT) {
+                if (!s_new[o]) continue;
+                double cam[CAM], lm[D];
+#pragma unroll
+                for (int c = 0; c < CAM; ++c) cam[c] = state[c];
+                new_landmark<KIND>(cam, s_pose + 6 * o, lm);
+#pragma unroll
+                for (int c = 0; c < D; ++c) state[CAM + D * s_idx[o] + c] = lm[c];
+            }
+            for (int i = CAM + D * nlm + tid; i < n; i += NT) P[wt_off(i, i)] = p.nz.init_lm;
+            for (int i = nlm + tid; i < nlm1; i += NT) p.lm_ids[(long long)seq * p.max_lm + i] = s_tab[i];
+        }
+        for (int i = tid; i < n; i += NT) delta[i] = 0.0;
+        for (int o = tid; o < k; o += NT) g_idx[o] = s_idx[o];
+        const int nchunks = (k + WCK - 1) / WCK;
+        cs = (k + nchunks - 1) / nchunks;
+        if (tid == 0) {
+            p.nlm[seq] = nlm1;
+            meta[0] = k; meta[1] = nchunks; meta[2] = cs; meta[3] = n; meta[4] = 1;
+        }
+        __syncthreads();   // state / P diagonal / delta writes of this CTA are visible to its own reads below
+    } else {
+        if (p.round >= meta[1]) {
+            if (tid == 0) meta[5] = 0;
+            return;
+        }
+        k = meta[0]; cs = meta[2]; n = meta[3];
+        const int c0r = p.round * cs, kcr = min(cs, k - c0r);
+        for (int o = tid; o < kcr; o += NT) s_idx[c0r + o] = g_idx[c0r + o];
+        for (int e = tid; e < 6 * kcr; e += NT) s_pose[6 * c0r + e] = p.poses[6 * (ob + c0r) + e];
+        __syncthreads();
+    }
+    const int c0 = p.round * cs, kc = min(cs, k - c0), m = R * kc, m8 = (m + 7) & ~7, nb = m8 >> 3;
+    const bool add_q = p.round == 0;
+    double* gH = p.H + (long long)seq * (WCK * R * W);
+    // ---- measurement model at the frame's pre-update state; nu' = nu - H delta -------------------
+    for (int o = tid; o < kc; o += NT) {
+        double cam[CAM], lm[D], lnu[R];
+        double* blk = gH + o * R * W;
+#pragma unroll
+        for (int c = 0; c < CAM; ++c) cam[c] = state[c];
+        const int li = CAM + D * s_idx[c0 + o];
+#pragma unroll
+        for (int c = 0; c < D; ++c) lm[c] = state[li + c];
+        observation_model<KIND>(cam, lm, s_pose + 6 * (c0 + o), lnu, blk);
+        if (p.round > 0) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                double s = lnu[r];
+#pragma unroll
+                for (int c = 0; c < CAM; ++c) s -= blk[r * W + c] * delta[c];
+#pragma unroll
+                for (int c = 0; c < D; ++c) s -= blk[r * W + CAM + c] * delta[li + c];
+                lnu[r] = s;
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < R; ++r) s_nu[R * o + r] = lnu[r];
+    }
+    for (int a = m + tid; a < m8; a += NT) s_nu[a] = 0.0;
+    // P[cam, touched columns] (+ Q on the diagonal in the first round) -> shared
+    const int tw = CAM + D * kc;
+    for (int e = tid; e < CAM * tw; e += NT) {
+        const int c = e / tw, sl = e - c * tw;
+        const int col = sl < CAM ? sl : CAM + D * s_idx[c0 + (sl - CAM) / D] + (sl - CAM) % D;
+        double v = wt_sym(P, c, col);
+        if (add_q && c == col) v += process_noise(p.nz, c);
+        s_Pc[c * WD::TW + sl] = v;
+    }
+    for (int e = tid; e < tri(nb) * 64; e += NT) s_S[e] = 0.0;
+    if (tid == 0) s_misc[2] = 0;
+    __syncthreads();
+    // ---- S = H P[T,T] H^T + R, lower triangle, into 8 x 8 tiles ----------------------------------
+    // item = (observation pair o1 >= o2, row r of o1): g = H1[r] P[T1, T2] (W values), then R dot products
+    for (int it = tid; it < tri(kc) * R; it += NT) {
+        const int pr = it / R, r = it - pr * R;
+        int o1 = (int)((sqrtf(8.0f * pr + 1.0f) - 1.0f) * 0.5f);
+        while (tri(o1 + 1) <= pr) ++o1;
+        while (tri(o1) > pr) --o1;
+        const int o2 = pr - tri(o1);
+        const double* h1 = gH + o1 * R * W + r * W;
+        const double* h2 = gH + o2 * R * W;
+        const int l1 = CAM + D * s_idx[c0 + o1], l2 = CAM + D * s_idx[c0 + o2];
+        const int sl1 = CAM + D * o1, sl2 = CAM + D * o2;
+        double g[W];
+#pragma unroll
+        for (int c2 = 0; c2 < W; ++c2) g[c2] = 0.0;
+#pragma unroll
+        for (int c1 = 0; c1 < CAM; ++c1) {       // camera rows of P: cached
+            const double hv = h1[c1];
+#pragma unroll
+            for (int c2 = 0; c2 < CAM; ++c2) g[c2] += hv * s_Pc[c1 * WD::TW + c2];
+#pragma unroll
+            for (int c2 = 0; c2 < D; ++c2) g[CAM + c2] += hv * s_Pc[c1 * WD::TW + sl2 + c2];
+        }
+#pragma unroll
+        for (int c1 = 0; c1 < D; ++c1) {         // landmark rows: P[l1 + c1, cam] by symmetry, P[l1 + c1, l2 ..] from HBM
+            const double hv = h1[CAM + c1];
+#pragma unroll
+            for (int c2 = 0; c2 < CAM; ++c2) g[c2] += hv * s_Pc[c2 * WD::TW + sl1 + c1];
+#pragma unroll
+            for (int c2 = 0; c2 < D; ++c2) {
+                double v = wt_sym(P, l1 + c1, l2 + c2);
+                if (add_q && l1 + c1 == l2 + c2) v += p.nz.q_lm;
+                g[CAM + c2] += hv * v;
+            }
+        }
+        const int a = R * o1 + r;
+        for (int r2 = 0; r2 < R; ++r2) {
+            const int b = R * o2 + r2;
+            if (b > a) break;
+            double s = (a == b) ? p.nz.r : 0.0;
+#pragma unroll
+            for (int c = 0; c < W; ++c) s += g[c] * h2[r2 * W + c];
+            s_S[wt_off(a, b)] = s;
+        }
+    }
+    for (int a = m + tid; a < m8; a += NT) s_S[wt_off(a, a)] = 1.0;   // padding rows: identity
+    __syncthreads();
+    // ---- blocked right-looking Cholesky (8 x 8 blocks), trailing updates on the FP64 tensor pipe --
+    double* gL = p.L + (long long)seq * (tri(NB) * 64);
+    double* gD = p.Dinv + (long long)seq * (NB * 64);
+    const int g = lane >> 2, t4 = lane & 3;
+    for (int jb = 0; jb < nb; ++jb) {
+        double* dt = s_S + (tri(jb) + jb) * 64;
+        if (warp == 0) {
+            // diagonal block: lane i < 8 holds row i (lower part) in registers, columns broadcast by shuffle
+            double a[8], dvr[8];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) a[c] = (lane < 8 && c <= lane) ? dt[lane * 8 + c] : 0.0;
+            bool bad = false;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const double pv = __shfl_sync(0xffffffffu, a[j], j);
+                if (!(pv > 0.0) || !(pv < 1e300)) bad = true;
+                const double rs = rsqrt(pv);
+                dvr[j] = rs;
+                const double lij = a[j] * rs;
+                a[j] = lij;
+#pragma unroll
+                for (int c = j + 1; c < 8; ++c) {
+                    const double lcj = __shfl_sync(0xffffffffu, lij, c);
+                    a[c] -= lij * lcj;
+                }
+            }
+            if (bad && lane == 0) s_misc[2] = 1;
+            if (lane < 8) {
+#pragma unroll
+                for (int c = 0; c < 8; ++c) dt[lane * 8 + c] = c <= lane ? a[c] : 0.0;
+            }
+            __syncwarp();
+            // inverse of the block: lane c < 8 solves L x = e_c (column c of L^-1)
+            if (lane < 8) {
+                double x[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    double s = (i == lane) ? 1.0 : 0.0;
+#pragma unroll
+                    for (int q = 0; q < i; ++q) s -= dt[i * 8 + q] * x[q];
+                    x[i] = s * dvr[i];
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i) { s_dv[i * 8 + lane] = x[i]; gD[jb * 64 + i * 8 + lane] = x[i]; }
+            }
+        }
+        __syncthreads();
+        // panel: X_ib = S(ib, jb) Dinv^T (two DMMAs per tile), y_jb = Dinv nu_jb
+        for (int ib = jb + 1 + warp; ib < nb; ib += 8) {
+            double* tl = s_S + (tri(ib) + jb) * 64;
+            double c0v = 0.0, c1v = 0.0;
+#pragma unroll
+            for (int kk = 0; kk < 2; ++kk)
+                dmma884(c0v, c1v, tl[g * 8 + 4 * kk + t4], s_dv[g * 8 + 4 * kk + t4]);
+            __syncwarp();
+            *reinterpret_cast<double2*>(tl + g * 8 + 2 * t4) = make_double2(c0v, c1v);
+        }
+        if (warp == 7 && lane < 8) {
+            double s = 0.0;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) s += s_dv[lane * 8 + q] * s_nu[8 * jb + q];
+            __syncwarp(0xff);
+            s_nu[8 * jb + lane] = s;
+        }
+        __syncthreads();
+        // trailing: S(ib, kb) -= X_ib X_kb^T for jb < kb <= ib; nu_ib -= X_ib y_jb
+        const int rem = nb - jb - 1;
+        for (int e = warp; e < tri(rem); e += 8) {
+            int ir = (int)((sqrtf(8.0f * e + 1.0f) - 1.0f) * 0.5f);
+            while (tri(ir + 1) <= e) ++ir;
+            while (tri(ir) > e) --ir;
+            const int ib = jb + 1 + ir, kb = jb + 1 + (e - tri(ir));
+            const double* xi = s_S + (tri(ib) + jb) * 64;
+            const double* xk = s_S + (tri(kb) + jb) * 64;
+            double* ct = s_S + (tri(ib) + kb) * 64;
+            double2 cv = *reinterpret_cast<double2*>(ct + g * 8 + 2 * t4);
+#pragma unroll
+            for (int kk = 0; kk < 2; ++kk)
+                dmma884(cv.x, cv.y, -xi[g * 8 + 4 * kk + t4], xk[g * 8 + 4 * kk + t4]);
+            *reinterpret_cast<double2*>(ct + g * 8 + 2 * t4) = cv;
+        }
+        for (int a = 8 * (jb + 1) + tid; a < m8; a += NT) {
+            const double* xr = s_S + (tri(a >> 3) + jb) * 64 + (a & 7) * 8;
+            double s = s_nu[a];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) s -= xr[q] * s_nu[8 * jb + q];
+            s_nu[a] = s;
+        }
+        __syncthreads();
+    }
+    // ---- outputs ------------------------------------------------------------------------------------
+    for (int e = tid; e < tri(nb) * 64; e += NT) gL[e] = s_S[e];
+    double* gy = p.y + (long long)seq * M8;
+    for (int a = tid; a < m8; a += NT) gy[a] = s_nu[a];
+    if (tid == 0) {
+        meta[5] = m8; meta[6] = kc; meta[7] = c0;
+        if (s_misc[2]) p.status[seq] = ASB_ERR_NOT_SPD;
+    }
+}
+
+// ---- k_wide_panel -------------------------------------------------------------------------------
+template <int KIND>
+__global__ void __launch_bounds__(256, 3) k_wide_panel(WideParams p) {
+    using WD = WideDims<KIND>;
+    constexpr int D = WD::D, R = WD::R, W = WD::W, M8 = WD::M8, NB = WD::NB, NT = 256;
+    extern __shared__ __align__(16) unsigned char smraw[];
+    const int seq = blockIdx.y, jb64 = blockIdx.x;
+    const int* meta = p.meta + (long long)seq * 8;
+    const int m8 = meta[5];
+    if (m8 == 0) return;
+    const int n = meta[3];
+    const int col0 = 64 * jb64;
+    if (col0 >= n) return;
+    const int kc = meta[6], c0 = meta[7], m = R * kc, nb = m8 >> 3;
+    double* Gs = reinterpret_cast<double*>(smraw);            // m8 x W_VLD
+    double* s_Pc = Gs + M8 * W_VLD;                           // CAM x 64
+    double* s_y = s_Pc + CAM * 64;                            // M8
+    int* s_li = reinterpret_cast<int*>(s_y + M8);             // WCK
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const double* P = p.covs + (long long)seq * p.cov_stride;
+    const double* gH = p.H + (long long)seq * (WCK * R * W);
+    const double* gL = p.L + (long long)seq * (tri(NB) * 64);
+    const double* gD = p.Dinv + (long long)seq * (NB * 64);
+    const bool add_q = p.round == 0;
+    for (int o = tid; o < kc; o += NT) s_li[o] = CAM + D * p.idx[(long long)seq * p.max_obs + c0 + o];
+    for (int a = tid; a < m8; a += NT) s_y[a] = p.y[(long long)seq * M8 + a];
+    for (int e = tid; e < CAM * 64; e += NT) {
+        const int c = e >> 6, col = col0 + (e & 63);
+        double v = wt_sym(P, c, col);
+        if (add_q && c == col) v += process_noise(p.nz, c);
+        s_Pc[e] = v;
+    }
+    for (int e = m * W_VLD + tid; e < m8 * W_VLD; e += NT) Gs[e] = 0.0;
+    __syncthreads();
+    // ---- G = H P[T, cols]: item (observation o, 32 columns), o uniform per warp ----------------
+    for (int it = warp; it < 2 * kc; it += 8) {
+        const int o = it >> 1, j = ((it & 1) << 5) + lane, col = col0 + j;
+        const int li = s_li[o];
+        const double* hb = gH + o * R * W;
+        double pl[D];
+#pragma unroll
+        for (int c = 0; c < D; ++c) {
+            double v = wt_sym(P, li + c, col);
+            if (add_q && li + c == col) v += p.nz.q_lm;
+            pl[c] = v;
+        }
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            double s = 0.0;
+#pragma unroll
+            for (int c = 0; c < CAM; ++c) s += __ldg(hb + r * W + c) * s_Pc[c * 64 + j];
+#pragma unroll
+            for (int c = 0; c < D; ++c) s += __ldg(hb + r * W + CAM + c) * pl[c];
+            Gs[(R * o + r) * W_VLD + j] = s;
+        }
+    }
+    __syncthreads();
+    // ---- V = L^-1 G: each warp owns 8 columns for all rows; block row b needs blocks < b ---------
+    const int g = lane >> 2, t4 = lane & 3;
+    double* gs = Gs + 8 * warp;
+    double* gV = p.V + (long long)seq * p.v_stride + (long long)jb64 * (M8 * W_VLD) + 8 * warp;
+    double dx0 = 0.0, dx1 = 0.0;
+    for (int b = 0; b < nb; ++b) {
+        double2 acc = *reinterpret_cast<double2*>(gs + (8 * b + g) * W_VLD + 2 * t4);
+        double e0 = 0.0, e1 = 0.0;
+        const double* lrow = gL + (long long)tri(b) * 64 + g * 8 + t4;
+#pragma unroll 4
+        for (int kk = 0; kk < 2 * b; kk += 2) {
+            const double a0 = -__ldg(lrow + (kk >> 1) * 64), a1 = -__ldg(lrow + (kk >> 1) * 64 + 4);
+            const double b0 = gs[(4 * kk + t4) * W_VLD + g], b1 = gs[(4 * kk + 4 + t4) * W_VLD + g];
+            dmma884(acc.x, acc.y, a0, b0);
+            dmma884(e0, e1, a1, b1);
+        }
+        acc.x += e0; acc.y += e1;
+        __syncwarp();
+        *reinterpret_cast<double2*>(gs + (8 * b + g) * W_VLD + 2 * t4) = acc;
+        __syncwarp();
+        double v0 = 0.0, v1 = 0.0;
+#pragma unroll
+        for (int kk = 0; kk < 2; ++kk)
+            dmma884(v0, v1, __ldg(gD + b * 64 + g * 8 + 4 * kk + t4), gs[(8 * b + 4 * kk + t4) * W_VLD + g]);
+        __syncwarp();
+        *reinterpret_cast<double2*>(gs + (8 * b + g) * W_VLD + 2 * t4) = make_double2(v0, v1);
+        *reinterpret_cast<double2*>(gV + (8 * b + g) * W_VLD + 2 * t4) = make_double2(v0, v1);
+        const double yv = s_y[8 * b + g];
+        dx0 += v0 * yv; dx1 += v1 * yv;
+        __syncwarp();
+    }
+#pragma unroll
+    for (int sh = 4; sh < 32; sh <<= 1) {
+        dx0 += __shfl_xor_sync(0xffffffffu, dx0, sh);
+        dx1 += __shfl_xor_sync(0xffffffffu, dx1, sh);
+    }
+    if (lane < 4) {
+        double* delta = p.delta + (long long)seq * p.state_stride;
+        const int col = col0 + 8 * warp + 2 * lane;
+        if (col < n) delta[col] += dx0;
+        if (col + 1 < n) delta[col + 1] += dx1;
+    }
+}
+
+// ---- k_wide_sweep -------------------------------------------------------------------------------
+// CTA = 64 x 64 tile (I, J <= I) of one sequence, 8 warps of 32 x 16 (4 x 2 DMMA tiles).
+template <int KIND>
+__global__ void __launch_bounds__(256, 3) k_wide_sweep(WideParams p) {
+    using WD = WideDims<KIND>;
+    constexpr int M8 = WD::M8;
+    extern __shared__ __align__(128) unsigned char smraw[];
+    __shared__ __align__(8) uint64_t bar[W_NST];
+    const int seq = blockIdx.y;
+    const int* meta = p.meta + (long long)seq * 8;
+    const int m8 = meta[5];
+    if (m8 == 0) return;
+    const int n = meta[3], nt8 = (n + 7) >> 3, nb64 = (n + 63) >> 6;
+    const int task = blockIdx.x;
+    int I = (int)((sqrtf(8.0f * task + 1.0f) - 1.0f) * 0.5f);
+    while (tri(I + 1) <= task) ++I;
+    while (tri(I) > task) --I;
+    const int J = task - tri(I);
+    if (I >= nb64) return;
+    double* stage = reinterpret_cast<double*>(smraw);          // W_NST x 2 x W_SLAB x W_VLD
+    constexpr int SLAB_D = W_SLAB * W_VLD;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, t4 = lane & 3, wi = warp >> 2, wj = warp & 3;
+    double* P = p.covs + (long long)seq * p.cov_stride;
+    const double* Vb = p.V + (long long)seq * p.v_stride;
+    const double* VIg = Vb + (long long)I * (M8 * W_VLD);
+    const double* VJg = Vb + (long long)J * (M8 * W_VLD);
+    const int nslab = (m8 + W_SLAB - 1) / W_SLAB;
+    if (tid == 0) {
+        for (int s = 0; s < W_NST; ++s) mbar_init(&bar[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    auto issue = [&](int s) {   // thread 0: slab s -> stage s % W_NST
+        const int rows = min(W_SLAB, m8 - s * W_SLAB);
+        const uint32_t bytes = (uint32_t)(rows * W_VLD * sizeof(double));
+        double* dst = stage + (size_t)(s % W_NST) * 2 * SLAB_D;
+        mbar_expect_tx(&bar[s % W_NST], 2 * bytes);
+        bulk_g2s(dst, VIg + (long long)s * SLAB_D, bytes, &bar[s % W_NST]);
+        bulk_g2s(dst + SLAB_D, VJg + (long long)s * SLAB_D, bytes, &bar[s % W_NST]);
+    };
+    if (tid == 0)
+        for (int s = 0; s < min(W_NST, nslab); ++s) issue(s);
+    // P sub-tiles -> registers (consumed after the k-loop, so the latency hides behind the MMAs)
+    bool valid[4][2];
+    double2 pv[4][2];
+    double acc[4][2][2];
+#pragma unroll
+    for (int rm = 0; rm < 4; ++rm)
+#pragma unroll
+        for (int rn = 0; rn < 2; ++rn) {
+            const int i8 = 8 * I + 4 * wi + rm, j8 = 8 * J + 2 * wj + rn;
+            valid[rm][rn] = i8 < nt8 && j8 <= i8;
+            acc[rm][rn][0] = acc[rm][rn][1] = 0.0;
+            pv[rm][rn] = make_double2(0.0, 0.0);
+            if (valid[rm][rn])
+                pv[rm][rn] = *reinterpret_cast<const double2*>(P + ((long long)(tri(i8) + j8) << 6) + 2 * lane);
+        }
+    bool any_i[4], anyv = false;
+#pragma unroll
+    for (int rm = 0; rm < 4; ++rm) { any_i[rm] = valid[rm][0] || valid[rm][1]; anyv = anyv || any_i[rm]; }
+    for (int s = 0; s < nslab; ++s) {
+        const int st = s % W_NST;
+        mbar_wait(&bar[st], (uint32_t)((s / W_NST) & 1));
+        const double* vi = stage + (size_t)st * 2 * SLAB_D + 32 * wi + g;
+        const double* vj = vi - (32 * wi) + SLAB_D + 16 * wj;
+        const int ksteps = min(W_SLAB, m8 - s * W_SLAB) >> 2;
+        if (anyv) {
+#pragma unroll 2
+            for (int kk = 0; kk < ksteps; ++kk) {
+                double a[4], b[2];
+#pragma unroll
+                for (int rm = 0; rm < 4; ++rm) a[rm] = vi[(4 * kk + t4) * W_VLD + 8 * rm];
+#pragma unroll
+                for (int rn = 0; rn < 2; ++rn) b[rn] = vj[(4 * kk + t4) * W_VLD + 8 * rn];
+#pragma unroll
+                for (int rm = 0; rm < 4; ++rm)
+#pragma unroll
+                    for (int rn = 0; rn < 2; ++rn)
+                        if (valid[rm][rn]) dmma884(acc[rm][rn][0], acc[rm][rn][1], a[rm], b[rn]);
+            }
+        }
+        __syncthreads();   // every warp is done with stage st
+        if (tid == 0 && s + W_NST < nslab) issue(s + W_NST);
+    }
+    const bool add_q = p.round == 0;
+#pragma unroll
+    for (int rm = 0; rm < 4; ++rm)
+#pragma unroll
+        for (int rn = 0; rn < 2; ++rn) {
+            if (!valid[rm][rn]) continue;
+            const int i8 = 8 * I + 4 * wi + rm, j8 = 8 * J + 2 * wj + rn;
+            double o0 = pv[rm][rn].x - acc[rm][rn][0], o1 = pv[rm][rn].y - acc[rm][rn][1];
+            if (add_q && i8 == j8) {
+                const int row = 8 * i8 + g;
+                if (row < n) {
+                    if (g == 2 * t4) o0 += process_noise(p.nz, row);
+                    if (g == 2 * t4 + 1) o1 += process_noise(p.nz, row);
+                }
+            }
+            *reinterpret_cast<double2*>(P + ((long long)(tri(i8) + j8) << 6) + 2 * lane) = make_double2(o0, o1);
+        }
+}
+
+// Final state update of a run (the pending delta of the last frame).
+template <int KIND>
+__global__ void k_wide_apply(WideParams p) {
+    constexpr int D = Dims<KIND>::D;
+    const int seq = blockIdx.x, tid = threadIdx.x;
+    int* meta = p.meta + (long long)seq * 8;
+    if (!meta[4]) return;
+    double* state = p.states + (long long)seq * p.state_stride;
+    const double* delta = p.delta + (long long)seq * p.state_stride;
+    const int nlm = p.nlm[seq];
+    if (tid == 0) {
+        double cam[CAM], d[CAM];
+#pragma unroll
+        for (int c = 0; c < CAM; ++c) { cam[c] = state[c]; d[c] = delta[c]; }
+        camera_reset(cam, d, p.as_written);
+#pragma unroll
+        for (int c = 0; c < CAM; ++c) state[c] = cam[c];
+    }
+    for (int l = tid; l < nlm; l += blockDim.x) {
+        double lm[D], d[D];
+#pragma unroll
+        for (int c = 0; c < D; ++c) { lm[c] = state[CAM + D * l + c]; d[c] = delta[CAM + D * l + c]; }
+        landmark_update<KIND>(lm, d);
+#pragma unroll
+        for (int c = 0; c < D; ++c) state[CAM + D * l + c] = lm[c];
+    }
+    __syncthreads();
+    if (tid == 0) meta[4] = 0;
+}
+
+// tiled covariance -> dense row-major n x n
+__global__ void k_unpack_tiled(const double* __restrict__ tiled, int n, double* __restrict__ dense) {
+    const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= (long long)n * n) return;
+    const int i = (int)(e / n), j = (int)(e % n);
+    dense[e] = wt_sym(tiled, i, j);
+}
+
+}  // namespace asb

@@ -143,6 +143,13 @@ ASB_API int asb_batch_create(int kind, int quat_mode, const double pose0[10], co
 ASB_API int asb_batch_destroy(asb_batch* b);
 /* Back to the constructor's state (pose0, P = init_cam I10, empty maps), asynchronous. */
 ASB_API int asb_batch_reset(asb_batch* b);
+/* Engine behind the handle (no reference counterpart; both give the reference's results).
+ * 1 = resident: one CTA per sequence, the whole filter in shared memory for all frames (EKF up to 64 markers);
+ * 2 = wide: frame-synchronous kernels over all sequences, covariance tiled in HBM (EKF_Rotations at 32 / 64
+ *     markers, whose covariance does not fit an SM);  0 = automatic (resident when it fits).
+ * set_engine resets the filters to their constructor state. */
+ASB_API int asb_batch_set_engine(asb_batch* b, int engine);
+ASB_API int asb_batch_get_engine(asb_batch* b, int* engine);
 ASB_API int asb_batch_set_stream(asb_batch* b, void* cuda_stream);
 ASB_API int asb_batch_synchronize(asb_batch* b);
 /* offsets (n_seq*n_frames + 1) int64: frame t of sequence s = rows

@@ -1,0 +1,98 @@
+"""GPU parity of the wide batched engine (frame-synchronous kernels, covariance tiled in HBM:
+wide_kernels.cuh) against the CPU oracle: 1e-9 relative in FP64, id order bit-exact."""
+import numpy as np
+import pytest
+
+from conftest import rel_err
+from test_gpu_batch_ippe import pack, run_oracle
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-9
+
+
+def _check(b, streams, kind, quat_mode, n_frames):
+    cams, status = b.cameras()
+    assert not status.any(), status
+    for s, stream in enumerate(streams):
+        o = run_oracle(kind, quat_mode, stream, n_frames)
+        order = [k for k, _ in sorted(o.landmarks.items(), key=lambda kv: kv[1])]
+        assert [int(i) for i in b.landmark_ids(s)] == order
+        assert rel_err(b.state(s), o.state) < TOL, (s, rel_err(b.state(s), o.state))
+        assert rel_err(b.uncertainty(s), o.uncertainty) < TOL, (s, rel_err(b.uncertainty(s), o.uncertainty))
+        assert rel_err(cams[s], o.state[:10]) < TOL
+
+
+@pytest.mark.parametrize("kind,quat_mode,n_markers,n_frames,p", [
+    ("rot", "scalar_first", 6, 120, 0.6),      # one chunk per frame
+    ("ekf", "scalar_first", 10, 200, 0.6),
+    ("ekf", "as_written", 10, 40, 0.6),
+    ("rot", "scalar_first", 32, 40, 0.8),      # k ~ 26 > 16: two balanced chunks per frame (C2-ROT shape, N = 330)
+    ("ekf", "scalar_first", 40, 30, 0.9),      # up to three chunks
+])
+def test_wide_matches_oracle(kind, quat_mode, n_markers, n_frames, p):
+    from aruco_slam_b200 import FilterBatch, synth
+    n_seq = 5
+    streams = [synth.make_stream(300 + s, n_markers, n_frames, p, kind) for s in range(n_seq)]
+    # ragged input: empty frames (no detection => no predict), a repeated id, a sequence that ends early
+    streams[1].ids[3] = streams[1].ids[3][:0]
+    streams[1].poses[3] = streams[1].poses[3][:0]
+    streams[2].ids[5] = np.concatenate([streams[2].ids[5], streams[2].ids[5][:1]])
+    streams[2].poses[5] = np.vstack([streams[2].poses[5], streams[2].poses[5][:1] + 1e-3])
+    for t in range(n_frames - 4, n_frames):
+        streams[3].ids[t] = streams[3].ids[t][:0]
+        streams[3].poses[t] = streams[3].poses[t][:0]
+    ids, poses, off = pack(streams, n_frames)
+    b = FilterBatch(kind, n_seq, n_markers, n_markers + 1, quat_mode=quat_mode, engine="wide")
+    assert b.engine == "wide"
+    b.upload(ids, poses, off)
+    b.run(0, n_frames // 2)
+    b.run(n_frames // 2, n_frames)   # state (and a pending update) persists across runs
+    b.synchronize()
+    _check(b, streams, kind, quat_mode, n_frames)
+
+
+def test_wide_is_the_default_for_rotations_at_c2_and_c5_shapes():
+    """EKF_Rotations at 32 markers (N = 330) and 64 markers (N = 650, p = 0.25: BASELINE configs[4]) does not fit
+    an SM's shared memory: the handle picks the wide engine by itself.  200+ frames at the C5 shape."""
+    from aruco_slam_b200 import FilterBatch, synth
+    for n_markers, p, n_frames in ((32, 0.5, 60), (64, 0.25, 200)):
+        n_seq = 3
+        streams = [synth.make_stream(70 + s, n_markers, n_frames, p, "rot") for s in range(n_seq)]
+        ids, poses, off = pack(streams, n_frames)
+        b = FilterBatch("rot", n_seq, n_markers, n_markers, quat_mode="scalar_first")
+        assert b.engine == "wide"
+        b.upload(ids, poses, off)
+        b.run()
+        _check(b, streams, "rot", "scalar_first", n_frames)
+
+
+def test_wide_equals_resident_engine():
+    """Two independent implementations of the same update behind one handle."""
+    from aruco_slam_b200 import FilterBatch, synth
+    n_seq, n_markers, n_frames = 8, 12, 80
+    ids, poses, off = synth.make_batch(n_seq, n_markers, n_frames, 0.7, "ekf")
+    out = {}
+    for engine in ("resident", "wide"):
+        b = FilterBatch("ekf", n_seq, n_markers, n_markers, quat_mode="scalar_first", engine=engine)
+        assert b.engine == engine
+        b.upload(ids, poses, off)
+        b.run()
+        out[engine] = [(b.state(s), b.uncertainty(s)) for s in range(n_seq)]
+    for (s1, p1), (s2, p2) in zip(out["resident"], out["wide"]):
+        assert rel_err(s1, s2) < 1e-10
+        assert rel_err(p1, p2) < 1e-10
+
+
+def test_wide_capacity_flag_and_reset():
+    from aruco_slam_b200 import FilterBatch, synth
+    s = synth.make_stream(1, 10, 5, 1.0, "rot")
+    ids, poses, off = pack([s], 5)
+    b = FilterBatch("rot", 1, 4, 16, engine="wide")   # 10 markers > max_landmarks 4
+    b.upload(ids, poses, off)
+    b.run()
+    _, status = b.cameras()
+    assert status[0] == -4
+    # reset brings the constructor state back (and clears the flag)
+    b.reset()
+    cams, status = b.cameras()
+    assert status[0] == 0 and np.array_equal(cams[0], [0, 0, 0, 1, 0, 0, 0, 0, 0, 0])
