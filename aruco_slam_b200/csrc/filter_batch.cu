@@ -113,17 +113,22 @@ static int launch_batch_dyn(asb_batch* b, const BatchParams& p, size_t smem, int
 }
 
 // ---- wide engine, host side ------------------------------------------------------------------------
-template <int KIND> static size_t wide_front_smem(int max_lm, int max_obs) {
+template <int KIND> static size_t wide_model_smem(int max_lm, int max_obs) {
     using WD = WideDims<KIND>;
     const int cap_obs = std::max(max_obs, (int)WCK);
-    return ((size_t)tri(WD::NB) * 64 + (size_t)CAM * WD::TW + WD::M8 + 64 + (size_t)cap_obs * 6) * 8 +
-           ((size_t)cap_obs * 3 + max_lm + 4) * 4;
+    return ((size_t)CAM * WD::TW + (size_t)cap_obs * 6) * 8 + ((size_t)cap_obs * 3 + max_lm + 4) * 4;
+}
+template <int KIND> static size_t wide_chol_smem() {
+    using WD = WideDims<KIND>;
+    return ((size_t)tri(WD::NB) * 64 + WD::M8 + 64) * 8;
 }
 template <int KIND> static size_t wide_panel_smem() {
     using WD = WideDims<KIND>;
-    return ((size_t)WD::M8 * W_VLD + CAM * 64 + WD::M8) * 8 + WCK * 4;
+    return ((size_t)WD::M8 * W_VLD + 12 * W_VLD + WD::M8) * 8 + WCK * 4;
 }
-static size_t wide_sweep_smem() { return (size_t)W_NST * 2 * W_SLAB * W_VLD * 8; }
+template <int KIND> static size_t wide_sweep_smem() {
+    return ((size_t)WideDims<KIND>::M8 * W_VLD + (size_t)W_NST * W_SLAB * W_VLD) * 8;
+}
 
 static int resident_fits(const asb_batch* b) {
     const size_t base = batch_smem_base(b->D, b->R, b->ck, b->max_lm, b->max_obs);
@@ -177,20 +182,22 @@ template <int KIND> static int wide_run(asb_batch* b, int t0, int t1) {
     p.nz = b->nz;
     p.meta = b->w_meta; p.idx = b->w_idx; p.delta = b->w_delta; p.H = b->w_H; p.L = b->w_L; p.Dinv = b->w_Dinv;
     p.y = b->w_y; p.V = b->w_V; p.v_stride = b->w_vstride; p.nb64 = b->w_nb64;
-    const size_t sm_front = wide_front_smem<KIND>(b->max_lm, b->max_obs), sm_panel = wide_panel_smem<KIND>(),
-                 sm_sweep = wide_sweep_smem();
-    if (sm_front > (size_t)b->smem_optin) return fail(ASB_ERR_CAPACITY, "k_wide_front needs %zu B shared memory", sm_front);
-    ASB_CUDA(cudaFuncSetAttribute(k_wide_front<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_front));
+    const size_t sm_model = wide_model_smem<KIND>(b->max_lm, b->max_obs), sm_chol = wide_chol_smem<KIND>(),
+                 sm_panel = wide_panel_smem<KIND>(), sm_sweep = wide_sweep_smem<KIND>();
+    if (sm_model > (size_t)b->smem_optin) return fail(ASB_ERR_CAPACITY, "k_wide_model needs %zu B shared memory", sm_model);
+    ASB_CUDA(cudaFuncSetAttribute(k_wide_model<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_model));
+    ASB_CUDA(cudaFuncSetAttribute(k_wide_chol<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_chol));
     ASB_CUDA(cudaFuncSetAttribute(k_wide_panel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_panel));
     ASB_CUDA(cudaFuncSetAttribute(k_wide_sweep<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_sweep));
-    const dim3 g_panel(b->w_nb64, b->n_seq), g_sweep(tri(b->w_nb64), b->n_seq);
+    const dim3 g_panel(b->w_nb64, b->n_seq), g_sweep(b->w_nb64, b->n_seq);
     for (int t = t0; t < t1; ++t) {
         const int rounds = (b->kmax[t] + WCK - 1) / WCK;
         for (int r = 0; r < rounds; ++r) {
             p.t = t; p.round = r;
-            k_wide_front<KIND><<<b->n_seq, 256, sm_front, b->stream>>>(p);
+            k_wide_model<KIND><<<b->n_seq, 128, sm_model, b->stream>>>(p);
+            k_wide_chol<KIND><<<b->n_seq, 128, sm_chol, b->stream>>>(p);
             k_wide_panel<KIND><<<g_panel, 256, sm_panel, b->stream>>>(p);
-            k_wide_sweep<KIND><<<g_sweep, 256, sm_sweep, b->stream>>>(p);
+            k_wide_sweep<KIND><<<g_sweep, W_SWEEP_THREADS, sm_sweep, b->stream>>>(p);
         }
     }
     k_wide_apply<KIND><<<b->n_seq, 64, 0, b->stream>>>(p);

@@ -1,17 +1,19 @@
 // Wide batched engine: many independent filters whose covariance does NOT fit one CTA's shared
 // memory (EKF_Rotations at 32 / 64 markers: N = 330 / 650, P 0.46 / 1.7 MB per sequence; BASELINE
 // configs C2-ROT / C5-ROT).  Frame-synchronous: for frame t every sequence advances together through
-// three kernels per update chunk (<= WCK = 16 markers, m <= 112 rows), the covariance staying in HBM:
+// four kernels per update chunk (<= WCK = 16 markers, m <= 112 rows), the covariance staying in HBM:
 //
-//   k_wide_front   one CTA per sequence: pending state update + quaternion reset (ROT:143-177),
+//   k_wide_model   one CTA per sequence: pending state update + quaternion reset (ROT:143-177),
 //                  id association / augmentation in frame order (ROT:66-90, 275-335), measurement
 //                  model (ROT:337-427 closed form), S = H P[T,T] H^T + R (ROT:128-133) straight from
-//                  the touched 20 x 20 blocks of P, blocked Cholesky on the FP64 tensor pipe,
+//                  the touched 20 x 20 blocks of P
+//   k_wide_chol    one CTA per sequence: blocked Cholesky of S on the FP64 tensor pipe,
 //                  y = L^-1 nu', the 8 x 8 inverse diagonal blocks of L
 //   k_wide_panel   one CTA per (sequence, 64 state columns): G = H P[T, cols] (H never materialised),
 //                  V = L^-1 G by blocked forward substitution with DMMA, delta += V^T y
-//   k_wide_sweep   one CTA per (sequence, 64 x 64 lower-triangle tile): P <- P + Q - V^T V
-//                  (= (I - K H) P, ROT:180-181), V slabs by TMA bulk copy on an mbarrier ring, DMMA
+//   k_wide_sweep   one CTA per (sequence, 64-row strip of the lower triangle): P <- P + Q - V^T V
+//                  (= (I - K H) P, ROT:180-181), V_I resident, V_J slabs by TMA bulk copy on an mbarrier
+//                  ring fed by a producer warp, DMMA
 //
 // K is never formed (K nu = V^T y, K H P = V^T V).  Chunks of one frame condition sequentially with
 // the innovation corrected by H delta (DESIGN.md "chunked update"); predict (P += diag Q, ROT:103-113)
@@ -74,24 +76,22 @@ __device__ __forceinline__ double wt_sym(const double* __restrict__ P, int i, in
     return (i >> 3) >= (j >> 3) ? P[wt_off(i, j)] : P[wt_off(j, i)];
 }
 
-// ---- k_wide_front -------------------------------------------------------------------------------
+// ---- k_wide_model: association, augmentation, measurement model, S -> HBM (high occupancy: the serial
+//      model evaluation and the ragged S assembly of one sequence hide behind five other CTAs) --------
 template <int KIND>
-__global__ void __launch_bounds__(256, 3) k_wide_front(WideParams p) {
+__global__ void __launch_bounds__(128, 6) k_wide_model(WideParams p) {
     using WD = WideDims<KIND>;
-    constexpr int D = WD::D, R = WD::R, W = WD::W, M8 = WD::M8, NB = WD::NB, NT = 256;
+    constexpr int D = WD::D, R = WD::R, W = WD::W, M8 = WD::M8, NB = WD::NB, NT = 128;
     extern __shared__ __align__(16) unsigned char smraw[];
-    double* s_S = reinterpret_cast<double*>(smraw);           // tri(NB) tiles x 64
-    double* s_Pc = s_S + tri(NB) * 64;                        // CAM x TW: P[cam, touched columns]
-    double* s_nu = s_Pc + CAM * WD::TW;                       // M8
-    double* s_dv = s_nu + M8;                                 // 64: inverse of the current diagonal block
-    double* s_pose = s_dv + 64;                               // max(max_obs, WCK) x 6
+    double* s_Pc = reinterpret_cast<double*>(smraw);          // CAM x TW: P[cam, touched columns]
+    double* s_pose = s_Pc + CAM * WD::TW;                     // max(max_obs, WCK) x 6
     const int cap_obs = max(p.max_obs, WCK);
     int* s_ids = reinterpret_cast<int*>(s_pose + (size_t)cap_obs * 6);
     int* s_idx = s_ids + cap_obs;
     int* s_new = s_idx + cap_obs;
     int* s_tab = s_new + cap_obs;                             // max_lm
     int* s_misc = s_tab + p.max_lm;                           // [0] nlm after, [1] status, [2] bad
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x;
     const int seq = blockIdx.x;
     int* meta = p.meta + (long long)seq * 8;
     double* state = p.states + (long long)seq * p.state_stride;
@@ -201,9 +201,11 @@ __global__ void __launch_bounds__(256, 3) k_wide_front(WideParams p) {
         for (int e = tid; e < 6 * kcr; e += NT) s_pose[6 * c0r + e] = p.poses[6 * (ob + c0r) + e];
         __syncthreads();
     }
-    const int c0 = p.round * cs, kc = min(cs, k - c0), m = R * kc, m8 = (m + 7) & ~7, nb = m8 >> 3;
+    const int c0 = p.round * cs, kc = min(cs, k - c0), m = R * kc, m8 = (m + 7) & ~7;
     const bool add_q = p.round == 0;
     double* gH = p.H + (long long)seq * (WCK * R * W);
+    double* gS = p.L + (long long)seq * (tri(NB) * 64);       // S tiles (k_wide_chol factors them in place)
+    double* gnu = p.y + (long long)seq * M8;
     // ---- measurement model at the frame's pre-update state; nu' = nu - H delta -------------------
     for (int o = tid; o < kc; o += NT) {
         double cam[CAM], lm[D], lnu[R];
@@ -226,9 +228,9 @@ __global__ void __launch_bounds__(256, 3) k_wide_front(WideParams p) {
             }
         }
 #pragma unroll
-        for (int r = 0; r < R; ++r) s_nu[R * o + r] = lnu[r];
+        for (int r = 0; r < R; ++r) gnu[R * o + r] = lnu[r];
     }
-    for (int a = m + tid; a < m8; a += NT) s_nu[a] = 0.0;
+    for (int a = m + tid; a < m8; a += NT) gnu[a] = 0.0;
     // P[cam, touched columns] (+ Q on the diagonal in the first round) -> shared
     const int tw = CAM + D * kc;
     for (int e = tid; e < CAM * tw; e += NT) {
@@ -238,8 +240,6 @@ __global__ void __launch_bounds__(256, 3) k_wide_front(WideParams p) {
         if (add_q && c == col) v += process_noise(p.nz, c);
         s_Pc[c * WD::TW + sl] = v;
     }
-    for (int e = tid; e < tri(nb) * 64; e += NT) s_S[e] = 0.0;
-    if (tid == 0) s_misc[2] = 0;
     __syncthreads();
     // ---- S = H P[T,T] H^T + R, lower triangle, into 8 x 8 tiles ----------------------------------
     // item = (observation pair o1 >= o2, row r of o1): g = H1[r] P[T1, T2] (W values), then R dot products
@@ -283,14 +283,45 @@ __global__ void __launch_bounds__(256, 3) k_wide_front(WideParams p) {
             double s = (a == b) ? p.nz.r : 0.0;
 #pragma unroll
             for (int c = 0; c < W; ++c) s += g[c] * h2[r2 * W + c];
-            s_S[wt_off(a, b)] = s;
+            gS[wt_off(a, b)] = s;
         }
     }
-    for (int a = m + tid; a < m8; a += NT) s_S[wt_off(a, a)] = 1.0;   // padding rows: identity
-    __syncthreads();
-    // ---- blocked right-looking Cholesky (8 x 8 blocks), trailing updates on the FP64 tensor pipe --
+    if (tid == 0) { meta[5] = m8; meta[6] = kc; meta[7] = c0; }
+}
+
+// ---- k_wide_chol: S = L L^T in place (8 x 8 blocks, trailing updates on the FP64 tensor pipe), y = L^-1 nu',
+//      the inverse diagonal blocks.  One CTA of 4 warps per sequence, S in shared memory. -----------------
+template <int KIND>
+__global__ void __launch_bounds__(128, 4) k_wide_chol(WideParams p) {
+    using WD = WideDims<KIND>;
+    constexpr int M8 = WD::M8, NB = WD::NB, NT = 128, NW = NT / 32, R = WD::R;
+    extern __shared__ __align__(16) unsigned char smraw[];
+    double* s_S = reinterpret_cast<double*>(smraw);           // tri(NB) tiles x 64
+    double* s_nu = s_S + tri(NB) * 64;                        // M8
+    double* s_dv = s_nu + M8;                                 // 64
+    __shared__ int s_bad;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int seq = blockIdx.x;
+    const int* meta = p.meta + (long long)seq * 8;
+    const int m8 = meta[5];
+    if (m8 == 0) return;
+    const int m = R * meta[6], nb = m8 >> 3;
     double* gL = p.L + (long long)seq * (tri(NB) * 64);
     double* gD = p.Dinv + (long long)seq * (NB * 64);
+    double* gy = p.y + (long long)seq * M8;
+    for (int e = tid; e < tri(nb) * 64; e += NT) {
+        // row / column of tile entry e: tile t = e >> 6 -> (ib, jb); padding rows (>= m) are identity,
+        // the strictly upper part of diagonal tiles is never read
+        const int t = e >> 6;
+        int ib = (int)((sqrtf(8.0f * t + 1.0f) - 1.0f) * 0.5f);
+        while (tri(ib + 1) <= t) ++ib;
+        while (tri(ib) > t) --ib;
+        const int jb = t - tri(ib), a = 8 * ib + ((e >> 3) & 7), b = 8 * jb + (e & 7);
+        s_S[e] = a < m ? (b <= a ? gL[e] : 0.0) : (a == b ? 1.0 : 0.0);
+    }
+    for (int a = tid; a < m8; a += NT) s_nu[a] = gy[a];
+    if (tid == 0) s_bad = 0;
+    __syncthreads();
     const int g = lane >> 2, t4 = lane & 3;
     for (int jb = 0; jb < nb; ++jb) {
         double* dt = s_S + (tri(jb) + jb) * 64;
@@ -314,7 +345,7 @@ __global__ void __launch_bounds__(256, 3) k_wide_front(WideParams p) {
                     a[c] -= lij * lcj;
                 }
             }
-            if (bad && lane == 0) s_misc[2] = 1;
+            if (bad && lane == 0) s_bad = 1;
             if (lane < 8) {
 #pragma unroll
                 for (int c = 0; c < 8; ++c) dt[lane * 8 + c] = c <= lane ? a[c] : 0.0;
@@ -336,7 +367,7 @@ __global__ void __launch_bounds__(256, 3) k_wide_front(WideParams p) {
         }
         __syncthreads();
         // panel: X_ib = S(ib, jb) Dinv^T (two DMMAs per tile), y_jb = Dinv nu_jb
-        for (int ib = jb + 1 + warp; ib < nb; ib += 8) {
+        for (int ib = jb + 1 + warp; ib < nb; ib += NW) {
             double* tl = s_S + (tri(ib) + jb) * 64;
             double c0v = 0.0, c1v = 0.0;
 #pragma unroll
@@ -345,7 +376,7 @@ __global__ void __launch_bounds__(256, 3) k_wide_front(WideParams p) {
             __syncwarp();
             *reinterpret_cast<double2*>(tl + g * 8 + 2 * t4) = make_double2(c0v, c1v);
         }
-        if (warp == 7 && lane < 8) {
+        if (warp == NW - 1 && lane < 8) {
             double s = 0.0;
 #pragma unroll
             for (int q = 0; q < 8; ++q) s += s_dv[lane * 8 + q] * s_nu[8 * jb + q];
@@ -355,7 +386,7 @@ __global__ void __launch_bounds__(256, 3) k_wide_front(WideParams p) {
         __syncthreads();
         // trailing: S(ib, kb) -= X_ib X_kb^T for jb < kb <= ib; nu_ib -= X_ib y_jb
         const int rem = nb - jb - 1;
-        for (int e = warp; e < tri(rem); e += 8) {
+        for (int e = warp; e < tri(rem); e += NW) {
             int ir = (int)((sqrtf(8.0f * e + 1.0f) - 1.0f) * 0.5f);
             while (tri(ir + 1) <= e) ++ir;
             while (tri(ir) > e) --ir;
@@ -378,14 +409,9 @@ __global__ void __launch_bounds__(256, 3) k_wide_front(WideParams p) {
         }
         __syncthreads();
     }
-    // ---- outputs ------------------------------------------------------------------------------------
     for (int e = tid; e < tri(nb) * 64; e += NT) gL[e] = s_S[e];
-    double* gy = p.y + (long long)seq * M8;
     for (int a = tid; a < m8; a += NT) gy[a] = s_nu[a];
-    if (tid == 0) {
-        meta[5] = m8; meta[6] = kc; meta[7] = c0;
-        if (s_misc[2]) p.status[seq] = ASB_ERR_NOT_SPD;
-    }
+    if (tid == 0 && s_bad) p.status[seq] = ASB_ERR_NOT_SPD;
 }
 
 // ---- k_wide_panel -------------------------------------------------------------------------------
@@ -403,10 +429,11 @@ __global__ void __launch_bounds__(256, 3) k_wide_panel(WideParams p) {
     if (col0 >= n) return;
     const int kc = meta[6], c0 = meta[7], m = R * kc, nb = m8 >> 3;
     double* Gs = reinterpret_cast<double*>(smraw);            // m8 x W_VLD
-    double* s_Pc = Gs + M8 * W_VLD;                           // CAM x 64
-    double* s_y = s_Pc + CAM * 64;                            // M8
+    double* s_Pc = Gs + M8 * W_VLD;                           // 12 x W_VLD: P[cam, cols], rows 10, 11 zero
+    double* s_y = s_Pc + 12 * W_VLD;                          // M8
     int* s_li = reinterpret_cast<int*>(s_y + M8);             // WCK
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, t4 = lane & 3;
     const double* P = p.covs + (long long)seq * p.cov_stride;
     const double* gH = p.H + (long long)seq * (WCK * R * W);
     const double* gL = p.L + (long long)seq * (tri(NB) * 64);
@@ -414,65 +441,88 @@ __global__ void __launch_bounds__(256, 3) k_wide_panel(WideParams p) {
     const bool add_q = p.round == 0;
     for (int o = tid; o < kc; o += NT) s_li[o] = CAM + D * p.idx[(long long)seq * p.max_obs + c0 + o];
     for (int a = tid; a < m8; a += NT) s_y[a] = p.y[(long long)seq * M8 + a];
-    for (int e = tid; e < CAM * 64; e += NT) {
+    for (int e = tid; e < 12 * 64; e += NT) {
         const int c = e >> 6, col = col0 + (e & 63);
-        double v = wt_sym(P, c, col);
-        if (add_q && c == col) v += process_noise(p.nz, c);
-        s_Pc[e] = v;
+        double v = 0.0;
+        if (c < CAM) {
+            v = wt_sym(P, c, col);
+            if (add_q && c == col) v += process_noise(p.nz, c);
+        }
+        s_Pc[c * W_VLD + (e & 63)] = v;
     }
     for (int e = m * W_VLD + tid; e < m8 * W_VLD; e += NT) Gs[e] = 0.0;
     __syncthreads();
-    // ---- G = H P[T, cols]: item (observation o, 32 columns), o uniform per warp ----------------
-    for (int it = warp; it < 2 * kc; it += 8) {
-        const int o = it >> 1, j = ((it & 1) << 5) + lane, col = col0 + j;
+    // ---- G = H P[T, cols] on the FP64 tensor pipe: per observation an (R <= 8) x (10 + D) x 64 product,
+    //      A = the observation's dense block (rows >= R zero), B = the 10 camera rows of P (shared) and
+    //      the D landmark rows (straight from HBM in fragment order: H is never materialised) ----------
+    constexpr int KL = (D + 3) / 4;
+    for (int o = warp; o < kc; o += 8) {
         const int li = s_li[o];
         const double* hb = gH + o * R * W;
-        double pl[D];
+        double ac[3], al[KL];
 #pragma unroll
-        for (int c = 0; c < D; ++c) {
-            double v = wt_sym(P, li + c, col);
-            if (add_q && li + c == col) v += p.nz.q_lm;
-            pl[c] = v;
-        }
+        for (int kk = 0; kk < 3; ++kk) ac[kk] = (g < R && 4 * kk + t4 < CAM) ? __ldg(hb + g * W + 4 * kk + t4) : 0.0;
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-            double s = 0.0;
+        for (int kk = 0; kk < KL; ++kk) al[kk] = (g < R && 4 * kk + t4 < D) ? __ldg(hb + g * W + CAM + 4 * kk + t4) : 0.0;
 #pragma unroll
-            for (int c = 0; c < CAM; ++c) s += __ldg(hb + r * W + c) * s_Pc[c * 64 + j];
+        for (int nb8 = 0; nb8 < 8; ++nb8) {
+            const int col = col0 + 8 * nb8 + g;
+            double bl[KL];
 #pragma unroll
-            for (int c = 0; c < D; ++c) s += __ldg(hb + r * W + CAM + c) * pl[c];
-            Gs[(R * o + r) * W_VLD + j] = s;
+            for (int kk = 0; kk < KL; ++kk) {
+                const int c = 4 * kk + t4;
+                double v = 0.0;
+                if (c < D) {
+                    v = wt_sym(P, li + c, col);
+                    if (add_q && li + c == col) v += p.nz.q_lm;
+                }
+                bl[kk] = v;
+            }
+            double c0v = 0.0, c1v = 0.0;
+#pragma unroll
+            for (int kk = 0; kk < 3; ++kk) dmma884(c0v, c1v, ac[kk], s_Pc[(4 * kk + t4) * W_VLD + 8 * nb8 + g]);
+#pragma unroll
+            for (int kk = 0; kk < KL; ++kk) dmma884(c0v, c1v, al[kk], bl[kk]);
+            if (g < R) *reinterpret_cast<double2*>(Gs + (R * o + g) * W_VLD + 8 * nb8 + 2 * t4) = make_double2(c0v, c1v);
         }
     }
     __syncthreads();
     // ---- V = L^-1 G: each warp owns 8 columns for all rows; block row b needs blocks < b ---------
-    const int g = lane >> 2, t4 = lane & 3;
     double* gs = Gs + 8 * warp;
     double* gV = p.V + (long long)seq * p.v_stride + (long long)jb64 * (M8 * W_VLD) + 8 * warp;
     double dx0 = 0.0, dx1 = 0.0;
     for (int b = 0; b < nb; ++b) {
+        const double d0 = __ldg(gD + b * 64 + g * 8 + t4), d1 = __ldg(gD + b * 64 + g * 8 + 4 + t4);
+        const double yv = s_y[8 * b + g];
         double2 acc = *reinterpret_cast<double2*>(gs + (8 * b + g) * W_VLD + 2 * t4);
-        double e0 = 0.0, e1 = 0.0;
+        double e0 = 0.0, e1 = 0.0, f0 = 0.0, f1 = 0.0, h0 = 0.0, h1 = 0.0;
         const double* lrow = gL + (long long)tri(b) * 64 + g * 8 + t4;
-#pragma unroll 4
-        for (int kk = 0; kk < 2 * b; kk += 2) {
-            const double a0 = -__ldg(lrow + (kk >> 1) * 64), a1 = -__ldg(lrow + (kk >> 1) * 64 + 4);
-            const double b0 = gs[(4 * kk + t4) * W_VLD + g], b1 = gs[(4 * kk + 4 + t4) * W_VLD + g];
-            dmma884(acc.x, acc.y, a0, b0);
-            dmma884(e0, e1, a1, b1);
+        int tb = 0;
+        for (; tb + 2 <= b; tb += 2) {   // two 8 x 8 tiles of L (4 k-steps) per trip, four independent chains
+            const double a0 = -__ldg(lrow + tb * 64), a1 = -__ldg(lrow + tb * 64 + 4);
+            const double a2 = -__ldg(lrow + tb * 64 + 64), a3 = -__ldg(lrow + tb * 64 + 68);
+            const double* gk = gs + (8 * tb + t4) * W_VLD + g;
+            dmma884(acc.x, acc.y, a0, gk[0]);
+            dmma884(e0, e1, a1, gk[4 * W_VLD]);
+            dmma884(f0, f1, a2, gk[8 * W_VLD]);
+            dmma884(h0, h1, a3, gk[12 * W_VLD]);
         }
-        acc.x += e0; acc.y += e1;
+        if (tb < b) {
+            const double a0 = -__ldg(lrow + tb * 64), a1 = -__ldg(lrow + tb * 64 + 4);
+            const double* gk = gs + (8 * tb + t4) * W_VLD + g;
+            dmma884(acc.x, acc.y, a0, gk[0]);
+            dmma884(e0, e1, a1, gk[4 * W_VLD]);
+        }
+        acc.x += (e0 + f0) + h0; acc.y += (e1 + f1) + h1;
         __syncwarp();
         *reinterpret_cast<double2*>(gs + (8 * b + g) * W_VLD + 2 * t4) = acc;
         __syncwarp();
         double v0 = 0.0, v1 = 0.0;
-#pragma unroll
-        for (int kk = 0; kk < 2; ++kk)
-            dmma884(v0, v1, __ldg(gD + b * 64 + g * 8 + 4 * kk + t4), gs[(8 * b + 4 * kk + t4) * W_VLD + g]);
+        dmma884(v0, v1, d0, gs[(8 * b + t4) * W_VLD + g]);
+        dmma884(v0, v1, d1, gs[(8 * b + 4 + t4) * W_VLD + g]);
         __syncwarp();
         *reinterpret_cast<double2*>(gs + (8 * b + g) * W_VLD + 2 * t4) = make_double2(v0, v1);
         *reinterpret_cast<double2*>(gV + (8 * b + g) * W_VLD + 2 * t4) = make_double2(v0, v1);
-        const double yv = s_y[8 * b + g];
         dx0 += v0 * yv; dx1 += v1 * yv;
         __syncwarp();
     }
@@ -490,107 +540,125 @@ __global__ void __launch_bounds__(256, 3) k_wide_panel(WideParams p) {
 }
 
 // ---- k_wide_sweep -------------------------------------------------------------------------------
-// CTA = 64 x 64 tile (I, J <= I) of one sequence, 8 warps of 32 x 16 (4 x 2 DMMA tiles).
+// CTA = one 64-row strip I of one sequence: walks the tiles (I, J = 0..I) with its own 64 columns of the
+// panel (V_I) resident in shared memory and V_J streamed in W_SLAB-row slabs through a W_NST-stage ring
+// (TMA bulk copies, full / empty mbarriers) by a dedicated producer warp, so the ring never drains between
+// tiles.  8 consumer warps of 32 x 16 (4 x 2 DMMA tiles); the P sub-tiles go HBM -> registers in the
+// accumulator-fragment layout at the start of a tile and are consumed after its k-loop.
+constexpr int W_SWEEP_THREADS = 288;
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 template <int KIND>
-__global__ void __launch_bounds__(256, 3) k_wide_sweep(WideParams p) {
+__global__ void __launch_bounds__(W_SWEEP_THREADS, 2) k_wide_sweep(WideParams p) {
     using WD = WideDims<KIND>;
     constexpr int M8 = WD::M8;
     extern __shared__ __align__(128) unsigned char smraw[];
-    __shared__ __align__(8) uint64_t bar[W_NST];
+    __shared__ __align__(8) uint64_t bar_full[W_NST], bar_empty[W_NST], bar_vi;
     const int seq = blockIdx.y;
     const int* meta = p.meta + (long long)seq * 8;
     const int m8 = meta[5];
     if (m8 == 0) return;
     const int n = meta[3], nt8 = (n + 7) >> 3, nb64 = (n + 63) >> 6;
-    const int task = blockIdx.x;
-    int I = (int)((sqrtf(8.0f * task + 1.0f) - 1.0f) * 0.5f);
-    while (tri(I + 1) <= task) ++I;
-    while (tri(I) > task) --I;
-    const int J = task - tri(I);
+    const int I = (int)gridDim.x - 1 - (int)blockIdx.x;        // heavy strips first
     if (I >= nb64) return;
-    double* stage = reinterpret_cast<double*>(smraw);          // W_NST x 2 x W_SLAB x W_VLD
     constexpr int SLAB_D = W_SLAB * W_VLD;
+    double* VI = reinterpret_cast<double*>(smraw);               // M8 x W_VLD
+    double* ring = VI + M8 * W_VLD;                              // W_NST x W_SLAB x W_VLD
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int g = lane >> 2, t4 = lane & 3, wi = warp >> 2, wj = warp & 3;
     double* P = p.covs + (long long)seq * p.cov_stride;
     const double* Vb = p.V + (long long)seq * p.v_stride;
-    const double* VIg = Vb + (long long)I * (M8 * W_VLD);
-    const double* VJg = Vb + (long long)J * (M8 * W_VLD);
     const int nslab = (m8 + W_SLAB - 1) / W_SLAB;
     if (tid == 0) {
-        for (int s = 0; s < W_NST; ++s) mbar_init(&bar[s], 1);
+        for (int s = 0; s < W_NST; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 8); }
+        mbar_init(&bar_vi, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
-    auto issue = [&](int s) {   // thread 0: slab s -> stage s % W_NST
-        const int rows = min(W_SLAB, m8 - s * W_SLAB);
-        const uint32_t bytes = (uint32_t)(rows * W_VLD * sizeof(double));
-        double* dst = stage + (size_t)(s % W_NST) * 2 * SLAB_D;
-        mbar_expect_tx(&bar[s % W_NST], 2 * bytes);
-        bulk_g2s(dst, VIg + (long long)s * SLAB_D, bytes, &bar[s % W_NST]);
-        bulk_g2s(dst + SLAB_D, VJg + (long long)s * SLAB_D, bytes, &bar[s % W_NST]);
-    };
-    if (tid == 0)
-        for (int s = 0; s < min(W_NST, nslab); ++s) issue(s);
-    // P sub-tiles -> registers (consumed after the k-loop, so the latency hides behind the MMAs)
-    bool valid[4][2];
-    double2 pv[4][2];
-    double acc[4][2][2];
-#pragma unroll
-    for (int rm = 0; rm < 4; ++rm)
-#pragma unroll
-        for (int rn = 0; rn < 2; ++rn) {
-            const int i8 = 8 * I + 4 * wi + rm, j8 = 8 * J + 2 * wj + rn;
-            valid[rm][rn] = i8 < nt8 && j8 <= i8;
-            acc[rm][rn][0] = acc[rm][rn][1] = 0.0;
-            pv[rm][rn] = make_double2(0.0, 0.0);
-            if (valid[rm][rn])
-                pv[rm][rn] = *reinterpret_cast<const double2*>(P + ((long long)(tri(i8) + j8) << 6) + 2 * lane);
-        }
-    bool any_i[4], anyv = false;
-#pragma unroll
-    for (int rm = 0; rm < 4; ++rm) { any_i[rm] = valid[rm][0] || valid[rm][1]; anyv = anyv || any_i[rm]; }
-    for (int s = 0; s < nslab; ++s) {
-        const int st = s % W_NST;
-        mbar_wait(&bar[st], (uint32_t)((s / W_NST) & 1));
-        const double* vi = stage + (size_t)st * 2 * SLAB_D + 32 * wi + g;
-        const double* vj = vi - (32 * wi) + SLAB_D + 16 * wj;
-        const int ksteps = min(W_SLAB, m8 - s * W_SLAB) >> 2;
-        if (anyv) {
-#pragma unroll 2
-            for (int kk = 0; kk < ksteps; ++kk) {
-                double a[4], b[2];
-#pragma unroll
-                for (int rm = 0; rm < 4; ++rm) a[rm] = vi[(4 * kk + t4) * W_VLD + 8 * rm];
-#pragma unroll
-                for (int rn = 0; rn < 2; ++rn) b[rn] = vj[(4 * kk + t4) * W_VLD + 8 * rn];
-#pragma unroll
-                for (int rm = 0; rm < 4; ++rm)
-#pragma unroll
-                    for (int rn = 0; rn < 2; ++rn)
-                        if (valid[rm][rn]) dmma884(acc[rm][rn][0], acc[rm][rn][1], a[rm], b[rn]);
-            }
-        }
-        __syncthreads();   // every warp is done with stage st
-        if (tid == 0 && s + W_NST < nslab) issue(s + W_NST);
-    }
-    const bool add_q = p.round == 0;
-#pragma unroll
-    for (int rm = 0; rm < 4; ++rm)
-#pragma unroll
-        for (int rn = 0; rn < 2; ++rn) {
-            if (!valid[rm][rn]) continue;
-            const int i8 = 8 * I + 4 * wi + rm, j8 = 8 * J + 2 * wj + rn;
-            double o0 = pv[rm][rn].x - acc[rm][rn][0], o1 = pv[rm][rn].y - acc[rm][rn][1];
-            if (add_q && i8 == j8) {
-                const int row = 8 * i8 + g;
-                if (row < n) {
-                    if (g == 2 * t4) o0 += process_noise(p.nz, row);
-                    if (g == 2 * t4 + 1) o1 += process_noise(p.nz, row);
+    if (warp == 8) {   // ---- producer ----
+        if (lane == 0) {
+            const uint32_t vib = (uint32_t)(m8 * W_VLD * sizeof(double));
+            mbar_expect_tx(&bar_vi, vib);
+            bulk_g2s(VI, Vb + (long long)I * (M8 * W_VLD), vib, &bar_vi);
+            int cnt = 0;
+            for (int J = 0; J <= I; ++J) {
+                const double* VJg = Vb + (long long)J * (M8 * W_VLD);
+                for (int s = 0; s < nslab; ++s, ++cnt) {
+                    const int st = cnt % W_NST;
+                    if (cnt >= W_NST) mbar_wait(&bar_empty[st], (uint32_t)(((cnt / W_NST) - 1) & 1));
+                    const uint32_t bytes = (uint32_t)(min(W_SLAB, m8 - s * W_SLAB) * W_VLD * sizeof(double));
+                    mbar_expect_tx(&bar_full[st], bytes);
+                    bulk_g2s(ring + (size_t)st * SLAB_D, VJg + (long long)s * SLAB_D, bytes, &bar_full[st]);
                 }
             }
-            *reinterpret_cast<double2*>(P + ((long long)(tri(i8) + j8) << 6) + 2 * lane) = make_double2(o0, o1);
         }
+        return;
+    }
+    // ---- consumers ----
+    const int g = lane >> 2, t4 = lane & 3, wi = warp >> 2, wj = warp & 3;
+    const bool add_q = p.round == 0;
+    const double* vi = VI + 32 * wi + g;
+    int cnt = 0;
+    bool vi_ready = false;
+    for (int J = 0; J <= I; ++J) {
+        bool valid[4][2];
+        double2 pv[4][2];
+        double acc[4][2][2];
+        bool anyv = false;
+#pragma unroll
+        for (int rm = 0; rm < 4; ++rm)
+#pragma unroll
+            for (int rn = 0; rn < 2; ++rn) {
+                const int i8 = 8 * I + 4 * wi + rm, j8 = 8 * J + 2 * wj + rn;
+                valid[rm][rn] = i8 < nt8 && j8 <= i8;
+                anyv = anyv || valid[rm][rn];
+                acc[rm][rn][0] = acc[rm][rn][1] = 0.0;
+                pv[rm][rn] = make_double2(0.0, 0.0);
+                if (valid[rm][rn])
+                    pv[rm][rn] = *reinterpret_cast<const double2*>(P + ((long long)(tri(i8) + j8) << 6) + 2 * lane);
+            }
+        if (!vi_ready) { mbar_wait(&bar_vi, 0); vi_ready = true; }
+        for (int s = 0; s < nslab; ++s, ++cnt) {
+            const int st = cnt % W_NST;
+            mbar_wait(&bar_full[st], (uint32_t)((cnt / W_NST) & 1));
+            if (anyv) {
+                const double* vj = ring + (size_t)st * SLAB_D + 16 * wj + g;
+                const double* via = vi + (size_t)s * SLAB_D;
+                const int ksteps = min(W_SLAB, m8 - s * W_SLAB) >> 2;
+#pragma unroll 2
+                for (int kk = 0; kk < ksteps; ++kk) {
+                    double a[4], b[2];
+#pragma unroll
+                    for (int rm = 0; rm < 4; ++rm) a[rm] = via[(4 * kk + t4) * W_VLD + 8 * rm];
+#pragma unroll
+                    for (int rn = 0; rn < 2; ++rn) b[rn] = vj[(4 * kk + t4) * W_VLD + 8 * rn];
+#pragma unroll
+                    for (int rm = 0; rm < 4; ++rm)
+#pragma unroll
+                        for (int rn = 0; rn < 2; ++rn)
+                            if (valid[rm][rn]) dmma884(acc[rm][rn][0], acc[rm][rn][1], a[rm], b[rn]);
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bar_empty[st]);
+        }
+#pragma unroll
+        for (int rm = 0; rm < 4; ++rm)
+#pragma unroll
+            for (int rn = 0; rn < 2; ++rn) {
+                if (!valid[rm][rn]) continue;
+                const int i8 = 8 * I + 4 * wi + rm, j8 = 8 * J + 2 * wj + rn;
+                double o0 = pv[rm][rn].x - acc[rm][rn][0], o1 = pv[rm][rn].y - acc[rm][rn][1];
+                if (add_q && i8 == j8) {
+                    const int row = 8 * i8 + g;
+                    if (row < n) {
+                        if (g == 2 * t4) o0 += process_noise(p.nz, row);
+                        if (g == 2 * t4 + 1) o1 += process_noise(p.nz, row);
+                    }
+                }
+                *reinterpret_cast<double2*>(P + ((long long)(tri(i8) + j8) << 6) + 2 * lane) = make_double2(o0, o1);
+            }
+    }
 }
 
 // Final state update of a run (the pending delta of the last frame).

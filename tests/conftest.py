@@ -8,6 +8,8 @@ import pytest
 ROOT = Path(__file__).resolve().parent.parent
 if str(ROOT) not in sys.path:
     sys.path.insert(0, str(ROOT))
+if str(ROOT / "oracle") not in sys.path:   # tests/test_oracle_vs_reference.py imports make_golden helpers
+    sys.path.append(str(ROOT / "oracle"))
 
 GOLDEN = ROOT / "tests" / "golden"
 

@@ -8,7 +8,7 @@ import socket
 import numpy as np
 import pytest
 
-from conftest import rel_err
+from conftest import assert_parity, rel_err
 from oracle import ekf_oracle
 
 pytestmark = pytest.mark.gpu
@@ -32,8 +32,7 @@ def test_world1_matches_oracle(kind, quat_mode, n_markers, n_frames):
         f.observe(s.ids[t], s.poses[t])
         o.observe([int(i) for i in s.ids[t]], s.poses[t])
     assert _order(f.landmarks) == _order(o.landmarks)
-    assert rel_err(f.state, o.state) < TOL
-    assert rel_err(f.uncertainty, np.asarray(o.uncertainty)) < TOL
+    assert_parity("row-sharded world 1 vs oracle", f.state, f.uncertainty, o.state, o.uncertainty, TOL)
 
 
 def test_world1_map_build_equals_single_gpu_engine(calibration):

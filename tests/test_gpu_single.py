@@ -4,7 +4,7 @@ FP64 (BASELINE.json north_star); id association bit-exact."""
 import numpy as np
 import pytest
 
-from conftest import GOLDEN, rel_err
+from conftest import GOLDEN, assert_parity, rel_err, sensitivity_floor
 from oracle import ekf_oracle
 
 pytestmark = pytest.mark.gpu
@@ -52,8 +52,8 @@ def test_one_step_goldens(golden_steps, calibration, mode):
             hd[r * o:r * o + r, 0:10] = blocks[o][:, 0:10]
             hd[r * o:r * o + r, s:s + d] = blocks[o][:, 10:]
         assert rel_err(hd, g[f"{key}/H"]) < TOL, key
-        assert rel_err(f.state, g[f"{key}/post_state"]) < TOL, key
-        assert rel_err(f.uncertainty, g[f"{key}/post_P"]) < TOL, key
+        assert_parity(f"single one-step vs reference golden {key}", f.state, f.uncertainty,
+                      g[f"{key}/post_state"], g[f"{key}/post_P"], TOL)
 
 
 @pytest.mark.parametrize("mode", list(MODES))
@@ -71,8 +71,10 @@ def test_free_running_stream(calibration, mode):
             worst = max(worst, rel_err(f.state[:10], cam[t]))
     assert worst < TOL, worst
     if mode != "ekf_as_written":
-        assert rel_err(f.state, g["final_state"]) < TOL
-        assert rel_err(f.uncertainty, g["final_P"]) < TOL
+        frames = [(g["ids"][off[t]:off[t + 1]], g["poses"][off[t]:off[t + 1]]) for t in range(n_frames)]
+        floor = sensitivity_floor(kind, qm, [f_[0] for f_ in frames], [f_[1] for f_ in frames])
+        assert_parity(f"single free-running {n_frames} frames vs reference stream golden [{mode}]", f.state,
+                      f.uncertainty, g["final_state"], g["final_P"], TOL, floor=floor)
         assert order_of(f.landmarks) == [int(i) for i in g["lm"]]
 
 
@@ -90,6 +92,9 @@ def test_as_written_resynchronised_every_frame(calibration):
         o.observe([int(i) for i in s.ids[t]], s.poses[t])
         f.observe(s.ids[t], s.poses[t])
         worst = max(worst, rel_err(f.state, o.state), rel_err(f.uncertainty, o.uncertainty))
+        if t in (1, 150, s.n_frames - 1):
+            assert_parity(f"single as-written EKF re-synchronised, frame {t}", f.state, f.uncertainty, o.state,
+                          o.uncertainty, TOL)
     assert worst < TOL, worst
 
 
@@ -124,8 +129,7 @@ def test_chunked_update_many_observations(calibration, kind):
     for t in range(s.n_frames):
         o.observe([int(i) for i in s.ids[t]], s.poses[t])
         f.observe(s.ids[t], s.poses[t])
-        assert rel_err(f.state, o.state) < TOL
-        assert rel_err(f.uncertainty, o.uncertainty) < TOL
+        assert_parity(f"single chunked update {kind} frame {t}", f.state, f.uncertainty, o.state, o.uncertainty, TOL)
 
 
 def test_map_build_reduced_c3(calibration):
@@ -140,8 +144,7 @@ def test_map_build_reduced_c3(calibration):
         f.observe(stream.ids[t], stream.poses[t])
     assert f.num_landmarks == 200
     assert order_of(f.landmarks) == order_of(o.landmarks)
-    assert rel_err(f.state, o.state) < TOL
-    assert rel_err(f.uncertainty, o.uncertainty) < TOL
+    assert_parity("single C3 reduced (200 markers) build + run", f.state, f.uncertainty, o.state, o.uncertainty, TOL)
 
 
 @pytest.mark.parametrize("kind", ["ekf", "rot"])
@@ -167,8 +170,7 @@ def test_stream_mode_matches_oracle(calibration, kind):
     f.stream_run(3, 4)
     f.stream_run(4, frames)
     assert order_of(f.landmarks) == order_of(o.landmarks)
-    assert rel_err(f.state, o.state) < TOL
-    assert rel_err(f.uncertainty, np.asarray(o.uncertainty)) < TOL
+    assert_parity(f"single stream mode {kind}", f.state, f.uncertainty, o.state, o.uncertainty, TOL)
 
 
 def test_full_size_c3_single_steps(calibration):
@@ -192,8 +194,8 @@ def test_full_size_c3_single_steps(calibration):
         o.observe([int(i) for i in stream.ids[t]], stream.poses[t])
         f.stream_run(t, t + 1)
         p_after = f.uncertainty
-        assert rel_err(f.state, o.state) < TOL
-        assert rel_err(p_after, o.uncertainty) < TOL
+        assert_parity(f"single C3 full size (N = 6010) one step, frame {t}", f.state, p_after, o.state,
+                      o.uncertainty, TOL)
         assert np.array_equal(p_after, p_after.T)
         q = np.full(6010, 0.01)
         q[0:3], q[3:7], q[7:10] = 0.3, 0.0, 0.5
