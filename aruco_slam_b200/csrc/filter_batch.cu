@@ -116,7 +116,7 @@ static int launch_batch_dyn(asb_batch* b, const BatchParams& p, size_t smem, int
 template <int KIND> static size_t wide_model_smem(int max_lm, int max_obs) {
     using WD = WideDims<KIND>;
     const int cap_obs = std::max(max_obs, (int)WCK);
-    return ((size_t)CAM * WD::TW + (size_t)cap_obs * 6) * 8 + ((size_t)cap_obs * 3 + max_lm + 4) * 4;
+    return ((size_t)CAM * WD::TW + (size_t)WCK * 8 * WD::HLS + (size_t)cap_obs * 6) * 8 + ((size_t)cap_obs * 3 + max_lm + 4) * 4;
 }
 template <int KIND> static size_t wide_chol_smem() {
     using WD = WideDims<KIND>;

@@ -41,6 +41,7 @@ template <int KIND> struct WideDims {
     static constexpr int M8 = (MC + 7) & ~7;           // padded to whole 8-row blocks
     static constexpr int NB = M8 / 8;
     static constexpr int TW = CAM + D * WCK;           // touched state columns per chunk
+    static constexpr int HLS = 16 + 8 * ((D + 7) / 8) + 4;   // padded block row: [cam 16 | lm 8 ceil(D/8)] + 4 (= 4 mod 16)
 };
 
 struct WideParams {
@@ -79,12 +80,14 @@ __device__ __forceinline__ double wt_sym(const double* __restrict__ P, int i, in
 // ---- k_wide_model: association, augmentation, measurement model, S -> HBM (high occupancy: the serial
 //      model evaluation and the ragged S assembly of one sequence hide behind five other CTAs) --------
 template <int KIND>
-__global__ void __launch_bounds__(128, 6) k_wide_model(WideParams p) {
+__global__ void __launch_bounds__(128, 5) k_wide_model(WideParams p) {
     using WD = WideDims<KIND>;
     constexpr int D = WD::D, R = WD::R, W = WD::W, M8 = WD::M8, NB = WD::NB, NT = 128;
     extern __shared__ __align__(16) unsigned char smraw[];
+    constexpr int HLS = WD::HLS;
     double* s_Pc = reinterpret_cast<double*>(smraw);          // CAM x TW: P[cam, touched columns]
-    double* s_pose = s_Pc + CAM * WD::TW;                     // max(max_obs, WCK) x 6
+    double* s_H = s_Pc + CAM * WD::TW;                        // WCK x 8 x HLS padded measurement blocks
+    double* s_pose = s_H + WCK * 8 * HLS;                     // max(max_obs, WCK) x 6
     const int cap_obs = max(p.max_obs, WCK);
     int* s_ids = reinterpret_cast<int*>(s_pose + (size_t)cap_obs * 6);
     int* s_idx = s_ids + cap_obs;
@@ -240,50 +243,93 @@ __global__ void __launch_bounds__(128, 6) k_wide_model(WideParams p) {
         if (add_q && c == col) v += process_noise(p.nz, c);
         s_Pc[c * WD::TW + sl] = v;
     }
+    __syncthreads();   // the blocks in gH (written by this CTA's model threads) are complete
+    // measurement blocks in fragment-friendly padded form: s_H[o][g < 8][HLS], columns 0..9 camera, 16..16+D-1
+    // landmark, everything else (rows >= R included) zero
+    for (int e = tid; e < kc * 8 * HLS; e += NT) {
+        const int o = e / (8 * HLS), rem = e - o * (8 * HLS), gg = rem / HLS, c = rem - gg * HLS;
+        double v = 0.0;
+        if (gg < R) {
+            if (c < CAM) v = gH[o * R * W + gg * W + c];
+            else if (c >= 16 && c < 16 + D) v = gH[o * R * W + gg * W + CAM + (c - 16)];
+        }
+        s_H[e] = v;
+    }
     __syncthreads();
-    // ---- S = H P[T,T] H^T + R, lower triangle, into 8 x 8 tiles ----------------------------------
-    // item = (observation pair o1 >= o2, row r of o1): g = H1[r] P[T1, T2] (W values), then R dot products
-    for (int it = tid; it < tri(kc) * R; it += NT) {
-        const int pr = it / R, r = it - pr * R;
-        int o1 = (int)((sqrtf(8.0f * pr + 1.0f) - 1.0f) * 0.5f);
-        while (tri(o1 + 1) <= pr) ++o1;
-        while (tri(o1) > pr) --o1;
-        const int o2 = pr - tri(o1);
-        const double* h1 = gH + o1 * R * W + r * W;
-        const double* h2 = gH + o2 * R * W;
-        const int l1 = CAM + D * s_idx[c0 + o1], l2 = CAM + D * s_idx[c0 + o2];
-        const int sl1 = CAM + D * o1, sl2 = CAM + D * o2;
-        double g[W];
+    // ---- S = H P[T,T] H^T + R (lower triangle) on the FP64 tensor pipe, one warp per observation pair
+    //      (o1 >= o2):  M (8 x [16 | 8 LN]) = H1 ([12 | 4 LK] padded) x P[T1, T2];  S_blk = M x H2^T.
+    //      P[T1, T2]: camera rows / columns from the shared copy, the D x D landmark block from HBM. ----
+    {
+        const int lane = tid & 31, warp = tid >> 5, g = lane >> 2, t4 = lane & 3;
+        constexpr int LK = (D + 3) / 4, LN = (D + 7) / 8, NTL = 2 + LN;
+        for (int pr = warp; pr < tri(kc); pr += NT / 32) {
+            int o1 = (int)((sqrtf(8.0f * pr + 1.0f) - 1.0f) * 0.5f);
+            while (tri(o1 + 1) <= pr) ++o1;
+            while (tri(o1) > pr) --o1;
+            const int o2 = pr - tri(o1);
+            const int l1 = CAM + D * s_idx[c0 + o1], l2 = CAM + D * s_idx[c0 + o2];
+            const int sl1 = CAM + D * o1, sl2 = CAM + D * o2;
+            const double* h1 = s_H + o1 * 8 * HLS + g * HLS;
+            const double* h2 = s_H + o2 * 8 * HLS + g * HLS;
+            double mc[NTL][2];
 #pragma unroll
-        for (int c2 = 0; c2 < W; ++c2) g[c2] = 0.0;
+            for (int nt = 0; nt < NTL; ++nt) mc[nt][0] = mc[nt][1] = 0.0;
+            // camera rows of P[T1, T2] (k = 0..11, rows 10, 11 zero)
 #pragma unroll
-        for (int c1 = 0; c1 < CAM; ++c1) {       // camera rows of P: cached
-            const double hv = h1[c1];
+            for (int kk = 0; kk < 3; ++kk) {
+                const int k = 4 * kk + t4;
+                const double a = h1[k];
+                const double* pc = s_Pc + (k < CAM ? k : 0) * WD::TW;
 #pragma unroll
-            for (int c2 = 0; c2 < CAM; ++c2) g[c2] += hv * s_Pc[c1 * WD::TW + c2];
+                for (int nt = 0; nt < 2; ++nt) {
+                    const int nn = 8 * nt + g;
+                    dmma884(mc[nt][0], mc[nt][1], a, (k < CAM && nn < CAM) ? pc[nn] : 0.0);
+                }
 #pragma unroll
-            for (int c2 = 0; c2 < D; ++c2) g[CAM + c2] += hv * s_Pc[c1 * WD::TW + sl2 + c2];
-        }
-#pragma unroll
-        for (int c1 = 0; c1 < D; ++c1) {         // landmark rows: P[l1 + c1, cam] by symmetry, P[l1 + c1, l2 ..] from HBM
-            const double hv = h1[CAM + c1];
-#pragma unroll
-            for (int c2 = 0; c2 < CAM; ++c2) g[c2] += hv * s_Pc[c2 * WD::TW + sl1 + c1];
-#pragma unroll
-            for (int c2 = 0; c2 < D; ++c2) {
-                double v = wt_sym(P, l1 + c1, l2 + c2);
-                if (add_q && l1 + c1 == l2 + c2) v += p.nz.q_lm;
-                g[CAM + c2] += hv * v;
+                for (int nt = 0; nt < LN; ++nt) {
+                    const int nn = 8 * nt + g;
+                    dmma884(mc[2 + nt][0], mc[2 + nt][1], a, (k < CAM && nn < D) ? pc[sl2 + nn] : 0.0);
+                }
             }
-        }
-        const int a = R * o1 + r;
-        for (int r2 = 0; r2 < R; ++r2) {
-            const int b = R * o2 + r2;
-            if (b > a) break;
-            double s = (a == b) ? p.nz.r : 0.0;
+            // landmark rows (k' = 0..4 LK - 1): P[l1 + k', cam] by symmetry from the shared copy, P[l1 + k', l2 + n'] from HBM
 #pragma unroll
-            for (int c = 0; c < W; ++c) s += g[c] * h2[r2 * W + c];
-            gS[wt_off(a, b)] = s;
+            for (int kk = 0; kk < LK; ++kk) {
+                const int k = 4 * kk + t4;
+                const double a = h1[16 + k];
+#pragma unroll
+                for (int nt = 0; nt < 2; ++nt) {
+                    const int nn = 8 * nt + g;
+                    dmma884(mc[nt][0], mc[nt][1], a, (k < D && nn < CAM) ? s_Pc[nn * WD::TW + sl1 + k] : 0.0);
+                }
+#pragma unroll
+                for (int nt = 0; nt < LN; ++nt) {
+                    const int nn = 8 * nt + g;
+                    double v = 0.0;
+                    if (k < D && nn < D) {
+                        v = wt_sym(P, l1 + k, l2 + nn);
+                        if (add_q && l1 + k == l2 + nn) v += p.nz.q_lm;
+                    }
+                    dmma884(mc[2 + nt][0], mc[2 + nt][1], a, v);
+                }
+            }
+            // S_blk = M H2^T: M from accumulator to A-fragment layout with shuffles; k over the columns of M
+            double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+            for (int kq = 0; kq < 3 + LK; ++kq) {
+                // column of M: camera part columns 4 kq + t4 (tiles 0, 1), landmark part 16 + 4 (kq - 3) + t4
+                const int col = kq < 3 ? 4 * kq + t4 : 16 + 4 * (kq - 3) + t4;
+                const int nt = kq < 3 ? (kq >> 1) : 2 + ((kq - 3) >> 1);
+                const int cc = col & 7;
+                const int src = (lane & ~3) | (cc >> 1);
+                const double v0 = __shfl_sync(0xffffffffu, mc[nt][0], src), v1 = __shfl_sync(0xffffffffu, mc[nt][1], src);
+                dmma884(s0, s1, (cc & 1) ? v1 : v0, h2[col]);
+            }
+            const int ra = R * o1 + g;
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int cb = 2 * t4 + e, rb = R * o2 + cb;
+                if (g < R && cb < R && rb <= ra) gS[wt_off(ra, rb)] = (e ? s1 : s0) + (ra == rb ? p.nz.r : 0.0);
+            }
         }
     }
     if (tid == 0) { meta[5] = m8; meta[6] = kc; meta[7] = c0; }
@@ -309,15 +355,19 @@ __global__ void __launch_bounds__(128, 4) k_wide_chol(WideParams p) {
     double* gL = p.L + (long long)seq * (tri(NB) * 64);
     double* gD = p.Dinv + (long long)seq * (NB * 64);
     double* gy = p.y + (long long)seq * M8;
-    for (int e = tid; e < tri(nb) * 64; e += NT) {
-        // row / column of tile entry e: tile t = e >> 6 -> (ib, jb); padding rows (>= m) are identity,
-        // the strictly upper part of diagonal tiles is never read
-        const int t = e >> 6;
+    for (int t = warp; t < tri(nb); t += NW) {
+        // tile t = (ib, jb): padding rows (>= m) are identity, the strictly upper part of diagonal tiles is
+        // never read.  One coalesced 512-byte read per tile.
         int ib = (int)((sqrtf(8.0f * t + 1.0f) - 1.0f) * 0.5f);
         while (tri(ib + 1) <= t) ++ib;
         while (tri(ib) > t) --ib;
-        const int jb = t - tri(ib), a = 8 * ib + ((e >> 3) & 7), b = 8 * jb + (e & 7);
-        s_S[e] = a < m ? (b <= a ? gL[e] : 0.0) : (a == b ? 1.0 : 0.0);
+        const int jb = t - tri(ib);
+        const double2 v = *reinterpret_cast<const double2*>(gL + t * 64 + 2 * lane);
+        const int a = 8 * ib + (lane >> 2), b = 8 * jb + 2 * (lane & 3);
+        double2 o;
+        o.x = a < m ? (b <= a ? v.x : 0.0) : (a == b ? 1.0 : 0.0);
+        o.y = a < m ? (b + 1 <= a ? v.y : 0.0) : (a == b + 1 ? 1.0 : 0.0);
+        *reinterpret_cast<double2*>(s_S + t * 64 + 2 * lane) = o;
     }
     for (int a = tid; a < m8; a += NT) s_nu[a] = gy[a];
     if (tid == 0) s_bad = 0;
@@ -554,7 +604,16 @@ __global__ void __launch_bounds__(W_SWEEP_THREADS, 2) k_wide_sweep(WideParams p)
     using WD = WideDims<KIND>;
     constexpr int M8 = WD::M8;
     extern __shared__ __align__(128) unsigned char smraw[];
-    __shared__ __align__(8) uint64_t bar_full[W_NST], bar_empty[W_NST], bar_vi;
+    constexpr int NSL = (M8 + W_SLAB - 1) / W_SLAB;             // slabs of a full panel
+    __shared__ __align__(8) uint64_t bar_full[W_NST], bar_empty[W_NST], bar_vi[NSL];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // barrier set-up first: the init fence waits for the thread's outstanding memory operations, so it goes
+    // before the first global load of the kernel
+    if (tid == 0) {
+        for (int s = 0; s < W_NST; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 8); }
+        for (int s = 0; s < NSL; ++s) mbar_init(&bar_vi[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     const int seq = blockIdx.y;
     const int* meta = p.meta + (long long)seq * 8;
     const int m8 = meta[5];
@@ -565,28 +624,24 @@ __global__ void __launch_bounds__(W_SWEEP_THREADS, 2) k_wide_sweep(WideParams p)
     constexpr int SLAB_D = W_SLAB * W_VLD;
     double* VI = reinterpret_cast<double*>(smraw);               // M8 x W_VLD
     double* ring = VI + M8 * W_VLD;                              // W_NST x W_SLAB x W_VLD
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     double* P = p.covs + (long long)seq * p.cov_stride;
     const double* Vb = p.V + (long long)seq * p.v_stride;
     const int nslab = (m8 + W_SLAB - 1) / W_SLAB;
-    if (tid == 0) {
-        for (int s = 0; s < W_NST; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 8); }
-        mbar_init(&bar_vi, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
     __syncthreads();
-    if (warp == 8) {   // ---- producer ----
+    if (warp == 8) {   // ---- producer: V_I and V_J slabs interleaved, so the first MMAs need two slabs only ----
         if (lane == 0) {
-            const uint32_t vib = (uint32_t)(m8 * W_VLD * sizeof(double));
-            mbar_expect_tx(&bar_vi, vib);
-            bulk_g2s(VI, Vb + (long long)I * (M8 * W_VLD), vib, &bar_vi);
+            const double* VIg = Vb + (long long)I * (M8 * W_VLD);
             int cnt = 0;
             for (int J = 0; J <= I; ++J) {
                 const double* VJg = Vb + (long long)J * (M8 * W_VLD);
                 for (int s = 0; s < nslab; ++s, ++cnt) {
+                    const uint32_t bytes = (uint32_t)(min(W_SLAB, m8 - s * W_SLAB) * W_VLD * sizeof(double));
+                    if (J == 0) {
+                        mbar_expect_tx(&bar_vi[s], bytes);
+                        bulk_g2s(VI + (size_t)s * SLAB_D, VIg + (long long)s * SLAB_D, bytes, &bar_vi[s]);
+                    }
                     const int st = cnt % W_NST;
                     if (cnt >= W_NST) mbar_wait(&bar_empty[st], (uint32_t)(((cnt / W_NST) - 1) & 1));
-                    const uint32_t bytes = (uint32_t)(min(W_SLAB, m8 - s * W_SLAB) * W_VLD * sizeof(double));
                     mbar_expect_tx(&bar_full[st], bytes);
                     bulk_g2s(ring + (size_t)st * SLAB_D, VJg + (long long)s * SLAB_D, bytes, &bar_full[st]);
                 }
@@ -599,7 +654,6 @@ __global__ void __launch_bounds__(W_SWEEP_THREADS, 2) k_wide_sweep(WideParams p)
     const bool add_q = p.round == 0;
     const double* vi = VI + 32 * wi + g;
     int cnt = 0;
-    bool vi_ready = false;
     for (int J = 0; J <= I; ++J) {
         bool valid[4][2];
         double2 pv[4][2];
@@ -617,9 +671,9 @@ __global__ void __launch_bounds__(W_SWEEP_THREADS, 2) k_wide_sweep(WideParams p)
                 if (valid[rm][rn])
                     pv[rm][rn] = *reinterpret_cast<const double2*>(P + ((long long)(tri(i8) + j8) << 6) + 2 * lane);
             }
-        if (!vi_ready) { mbar_wait(&bar_vi, 0); vi_ready = true; }
         for (int s = 0; s < nslab; ++s, ++cnt) {
             const int st = cnt % W_NST;
+            if (J == 0) mbar_wait(&bar_vi[s], 0);
             mbar_wait(&bar_full[st], (uint32_t)((cnt / W_NST) & 1));
             if (anyv) {
                 const double* vj = ring + (size_t)st * SLAB_D + 16 * wj + g;
