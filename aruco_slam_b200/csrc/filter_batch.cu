@@ -49,6 +49,10 @@ struct asb_batch {
     double *w_delta = nullptr, *w_H = nullptr, *w_L = nullptr, *w_Dinv = nullptr, *w_y = nullptr, *w_V = nullptr;
     long long w_vstride = 0;
     int w_nb64 = 0;
+    static constexpr int W_MAX_GROUPS = 4;
+    int w_groups = 1;
+    cudaStream_t w_streams[W_MAX_GROUPS]{};
+    cudaEvent_t w_done[W_MAX_GROUPS]{};
     std::vector<int> kmax;         // per frame: max observations over the sequences (host, from the offsets)
 };
 
@@ -155,6 +159,10 @@ template <int KIND> static int wide_alloc_kind(asb_batch* b) {
     ASB_CUDA(dmalloc(&b->w_Dinv, ns * WD::NB * 64));
     ASB_CUDA(dmalloc(&b->w_y, ns * WD::M8));
     ASB_CUDA(dmalloc(&b->w_V, ns * (size_t)b->w_vstride));
+    for (auto& st : b->w_streams) if (!st) ASB_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    for (auto& e : b->w_done) if (!e) ASB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    b->w_groups = b->n_seq >= 1024 ? 2 : 1;
+    if (const char* e = std::getenv("ASB_WIDE_GROUPS")) b->w_groups = std::max(1, std::min(std::atoi(e), (int)asb_batch::W_MAX_GROUPS));
     ASB_CUDA(cudaMemset(b->w_meta, 0, ns * 8 * sizeof(int)));
     ASB_CUDA(cudaMemset(b->w_V, 0, ns * (size_t)b->w_vstride * sizeof(double)));
     return ASB_OK;
@@ -189,18 +197,33 @@ template <int KIND> static int wide_run(asb_batch* b, int t0, int t1) {
     ASB_CUDA(cudaFuncSetAttribute(k_wide_chol<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_chol));
     ASB_CUDA(cudaFuncSetAttribute(k_wide_panel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_panel));
     ASB_CUDA(cudaFuncSetAttribute(k_wide_sweep<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_sweep));
-    const dim3 g_panel(b->w_nb64, b->n_seq), g_sweep(b->w_nb64, b->n_seq);
-    for (int t = t0; t < t1; ++t) {
-        const int rounds = (b->kmax[t] + WCK - 1) / WCK;
-        for (int r = 0; r < rounds; ++r) {
-            p.t = t; p.round = r;
-            k_wide_model<KIND><<<b->n_seq, 128, sm_model, b->stream>>>(p);
-            k_wide_chol<KIND><<<b->n_seq, 128, sm_chol, b->stream>>>(p);
-            k_wide_panel<KIND><<<g_panel, 256, sm_panel, b->stream>>>(p);
-            k_wide_sweep<KIND><<<g_sweep, W_SWEEP_THREADS, sm_sweep, b->stream>>>(p);
+    // Sequence groups on separate streams: the latency-bound kernels of one group (model, chol) overlap the
+    // tensor-pipe-bound ones (panel, sweep) of the others.  Frames stay ordered inside a group (stream order).
+    const int ngroups = b->w_groups;
+    ASB_CUDA(cudaEventRecord(b->ev_main, b->stream));
+    for (int gidx = 0; gidx < ngroups; ++gidx) {
+        cudaStream_t st = ngroups == 1 ? b->stream : b->w_streams[gidx];
+        if (ngroups > 1) ASB_CUDA(cudaStreamWaitEvent(st, b->ev_main, 0));
+        const int s0 = (int)((long long)b->n_seq * gidx / ngroups), s1 = (int)((long long)b->n_seq * (gidx + 1) / ngroups);
+        if (s1 == s0) continue;
+        p.seq0 = s0;
+        const dim3 g_panel(b->w_nb64, s1 - s0), g_sweep(b->w_nb64, s1 - s0);
+        for (int t = t0; t < t1; ++t) {
+            const int rounds = (b->kmax[t] + WCK - 1) / WCK;
+            for (int r = 0; r < rounds; ++r) {
+                p.t = t; p.round = r;
+                k_wide_model<KIND><<<s1 - s0, 128, sm_model, st>>>(p);
+                k_wide_chol<KIND><<<s1 - s0, 128, sm_chol, st>>>(p);
+                k_wide_panel<KIND><<<g_panel, 256, sm_panel, st>>>(p);
+                k_wide_sweep<KIND><<<g_sweep, W_SWEEP_THREADS, sm_sweep, st>>>(p);
+            }
+        }
+        k_wide_apply<KIND><<<s1 - s0, 64, 0, st>>>(p);
+        if (ngroups > 1) {
+            ASB_CUDA(cudaEventRecord(b->w_done[gidx], st));
+            ASB_CUDA(cudaStreamWaitEvent(b->stream, b->w_done[gidx], 0));
         }
     }
-    k_wide_apply<KIND><<<b->n_seq, 64, 0, b->stream>>>(p);
     ASB_CUDA(cudaGetLastError());
     return ASB_OK;
 }
@@ -293,6 +316,8 @@ int asb_batch_destroy(asb_batch* b) {
     cudaFree(b->d_status); cudaFree(b->d_ids); cudaFree(b->d_poses); cudaFree(b->d_off);
     cudaFree(b->d_dense); cudaFree(b->d_pose0);
     wide_free(b);
+    for (auto& st : b->w_streams) if (st) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
+    for (auto& e : b->w_done) if (e) cudaEventDestroy(e);
     cudaStreamDestroy(b->own_stream);
     cudaStreamSynchronize(b->copy_stream);
     cudaStreamDestroy(b->copy_stream);

@@ -56,6 +56,7 @@ struct WideParams {
     long long state_stride, cov_stride;
     int n_seq, n_frames, max_lm, max_obs, as_written;
     int t, round;
+    int seq0;                  // this launch covers sequences seq0 + blockIdx (sequence groups run on separate streams)
     Noise nz;
     // per-sequence scratch
     int* meta;                 // 8 ints: k, nchunks, chunk size, n, pending, m8 (0 = idle this round), kc, c0
@@ -95,7 +96,7 @@ __global__ void __launch_bounds__(128, 5) k_wide_model(WideParams p) {
     int* s_tab = s_new + cap_obs;                             // max_lm
     int* s_misc = s_tab + p.max_lm;                           // [0] nlm after, [1] status, [2] bad
     const int tid = threadIdx.x;
-    const int seq = blockIdx.x;
+    const int seq = p.seq0 + blockIdx.x;
     int* meta = p.meta + (long long)seq * 8;
     double* state = p.states + (long long)seq * p.state_stride;
     double* P = p.covs + (long long)seq * p.cov_stride;
@@ -347,7 +348,7 @@ __global__ void __launch_bounds__(128, 4) k_wide_chol(WideParams p) {
     double* s_dv = s_nu + M8;                                 // 64
     __shared__ int s_bad;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int seq = blockIdx.x;
+    const int seq = p.seq0 + blockIdx.x;
     const int* meta = p.meta + (long long)seq * 8;
     const int m8 = meta[5];
     if (m8 == 0) return;
@@ -470,7 +471,7 @@ __global__ void __launch_bounds__(256, 3) k_wide_panel(WideParams p) {
     using WD = WideDims<KIND>;
     constexpr int D = WD::D, R = WD::R, W = WD::W, M8 = WD::M8, NB = WD::NB, NT = 256;
     extern __shared__ __align__(16) unsigned char smraw[];
-    const int seq = blockIdx.y, jb64 = blockIdx.x;
+    const int seq = p.seq0 + blockIdx.y, jb64 = blockIdx.x;
     const int* meta = p.meta + (long long)seq * 8;
     const int m8 = meta[5];
     if (m8 == 0) return;
@@ -506,18 +507,14 @@ __global__ void __launch_bounds__(256, 3) k_wide_panel(WideParams p) {
     //      A = the observation's dense block (rows >= R zero), B = the 10 camera rows of P (shared) and
     //      the D landmark rows (straight from HBM in fragment order: H is never materialised) ----------
     constexpr int KL = (D + 3) / 4;
-    for (int o = warp; o < kc; o += 8) {
+    for (int it = warp; it < 4 * kc; it += 8) {      // item = (observation, 16 of the 64 columns)
+        const int o = it >> 2, q = it & 3;
         const int li = s_li[o];
         const double* hb = gH + o * R * W;
-        double ac[3], al[KL];
+        double ac[3], al[KL], bl[2][KL];
 #pragma unroll
-        for (int kk = 0; kk < 3; ++kk) ac[kk] = (g < R && 4 * kk + t4 < CAM) ? __ldg(hb + g * W + 4 * kk + t4) : 0.0;
-#pragma unroll
-        for (int kk = 0; kk < KL; ++kk) al[kk] = (g < R && 4 * kk + t4 < D) ? __ldg(hb + g * W + CAM + 4 * kk + t4) : 0.0;
-#pragma unroll
-        for (int nb8 = 0; nb8 < 8; ++nb8) {
-            const int col = col0 + 8 * nb8 + g;
-            double bl[KL];
+        for (int nb8 = 0; nb8 < 2; ++nb8) {           // all landmark-row loads of the item first
+            const int col = col0 + 16 * q + 8 * nb8 + g;
 #pragma unroll
             for (int kk = 0; kk < KL; ++kk) {
                 const int c = 4 * kk + t4;
@@ -526,14 +523,22 @@ __global__ void __launch_bounds__(256, 3) k_wide_panel(WideParams p) {
                     v = wt_sym(P, li + c, col);
                     if (add_q && li + c == col) v += p.nz.q_lm;
                 }
-                bl[kk] = v;
+                bl[nb8][kk] = v;
             }
+        }
+#pragma unroll
+        for (int kk = 0; kk < 3; ++kk) ac[kk] = (g < R && 4 * kk + t4 < CAM) ? __ldg(hb + g * W + 4 * kk + t4) : 0.0;
+#pragma unroll
+        for (int kk = 0; kk < KL; ++kk) al[kk] = (g < R && 4 * kk + t4 < D) ? __ldg(hb + g * W + CAM + 4 * kk + t4) : 0.0;
+#pragma unroll
+        for (int nb8 = 0; nb8 < 2; ++nb8) {
+            const int jc = 16 * q + 8 * nb8;
             double c0v = 0.0, c1v = 0.0;
 #pragma unroll
-            for (int kk = 0; kk < 3; ++kk) dmma884(c0v, c1v, ac[kk], s_Pc[(4 * kk + t4) * W_VLD + 8 * nb8 + g]);
+            for (int kk = 0; kk < 3; ++kk) dmma884(c0v, c1v, ac[kk], s_Pc[(4 * kk + t4) * W_VLD + jc + g]);
 #pragma unroll
-            for (int kk = 0; kk < KL; ++kk) dmma884(c0v, c1v, al[kk], bl[kk]);
-            if (g < R) *reinterpret_cast<double2*>(Gs + (R * o + g) * W_VLD + 8 * nb8 + 2 * t4) = make_double2(c0v, c1v);
+            for (int kk = 0; kk < KL; ++kk) dmma884(c0v, c1v, al[kk], bl[nb8][kk]);
+            if (g < R) *reinterpret_cast<double2*>(Gs + (R * o + g) * W_VLD + jc + 2 * t4) = make_double2(c0v, c1v);
         }
     }
     __syncthreads();
@@ -547,21 +552,28 @@ __global__ void __launch_bounds__(256, 3) k_wide_panel(WideParams p) {
         double2 acc = *reinterpret_cast<double2*>(gs + (8 * b + g) * W_VLD + 2 * t4);
         double e0 = 0.0, e1 = 0.0, f0 = 0.0, f1 = 0.0, h0 = 0.0, h1 = 0.0;
         const double* lrow = gL + (long long)tri(b) * 64 + g * 8 + t4;
+        // L fragments are fetched one trip (two 8 x 8 tiles, four k-steps) ahead of the MMAs that use them
         int tb = 0;
-        for (; tb + 2 <= b; tb += 2) {   // two 8 x 8 tiles of L (4 k-steps) per trip, four independent chains
-            const double a0 = -__ldg(lrow + tb * 64), a1 = -__ldg(lrow + tb * 64 + 4);
-            const double a2 = -__ldg(lrow + tb * 64 + 64), a3 = -__ldg(lrow + tb * 64 + 68);
+        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+        if (b >= 2) { a0 = -__ldg(lrow); a1 = -__ldg(lrow + 4); a2 = -__ldg(lrow + 64); a3 = -__ldg(lrow + 68); }
+        for (; tb + 2 <= b; tb += 2) {   // four independent accumulator chains
+            double n0 = 0.0, n1 = 0.0, n2 = 0.0, n3 = 0.0;
+            if (tb + 4 <= b) {
+                n0 = -__ldg(lrow + (tb + 2) * 64); n1 = -__ldg(lrow + (tb + 2) * 64 + 4);
+                n2 = -__ldg(lrow + (tb + 3) * 64); n3 = -__ldg(lrow + (tb + 3) * 64 + 4);
+            }
             const double* gk = gs + (8 * tb + t4) * W_VLD + g;
             dmma884(acc.x, acc.y, a0, gk[0]);
             dmma884(e0, e1, a1, gk[4 * W_VLD]);
             dmma884(f0, f1, a2, gk[8 * W_VLD]);
             dmma884(h0, h1, a3, gk[12 * W_VLD]);
+            a0 = n0; a1 = n1; a2 = n2; a3 = n3;
         }
         if (tb < b) {
-            const double a0 = -__ldg(lrow + tb * 64), a1 = -__ldg(lrow + tb * 64 + 4);
+            const double l0 = -__ldg(lrow + tb * 64), l1 = -__ldg(lrow + tb * 64 + 4);
             const double* gk = gs + (8 * tb + t4) * W_VLD + g;
-            dmma884(acc.x, acc.y, a0, gk[0]);
-            dmma884(e0, e1, a1, gk[4 * W_VLD]);
+            dmma884(acc.x, acc.y, l0, gk[0]);
+            dmma884(e0, e1, l1, gk[4 * W_VLD]);
         }
         acc.x += (e0 + f0) + h0; acc.y += (e1 + f1) + h1;
         __syncwarp();
@@ -596,8 +608,11 @@ __global__ void __launch_bounds__(256, 3) k_wide_panel(WideParams p) {
 // tiles.  8 consumer warps of 32 x 16 (4 x 2 DMMA tiles); the P sub-tiles go HBM -> registers in the
 // accumulator-fragment layout at the start of a tile and are consumed after its k-loop.
 constexpr int W_SWEEP_THREADS = 288;
+// "empty" arrival of a consumer warp.  .relaxed: the default .release semantics make the arrive wait for the
+// warp's outstanding global loads (the P sub-tiles prefetched for the end of the tile), which serialises what
+// the prefetch is there to overlap; the stage's shared-memory reads have already been consumed by issued MMAs.
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+    asm volatile("mbarrier.arrive.relaxed.cta.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 template <int KIND>
 __global__ void __launch_bounds__(W_SWEEP_THREADS, 2) k_wide_sweep(WideParams p) {
@@ -614,7 +629,7 @@ __global__ void __launch_bounds__(W_SWEEP_THREADS, 2) k_wide_sweep(WideParams p)
         for (int s = 0; s < NSL; ++s) mbar_init(&bar_vi[s], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    const int seq = blockIdx.y;
+    const int seq = p.seq0 + blockIdx.y;
     const int* meta = p.meta + (long long)seq * 8;
     const int m8 = meta[5];
     if (m8 == 0) return;
@@ -719,7 +734,7 @@ __global__ void __launch_bounds__(W_SWEEP_THREADS, 2) k_wide_sweep(WideParams p)
 template <int KIND>
 __global__ void k_wide_apply(WideParams p) {
     constexpr int D = Dims<KIND>::D;
-    const int seq = blockIdx.x, tid = threadIdx.x;
+    const int seq = p.seq0 + blockIdx.x, tid = threadIdx.x;
     int* meta = p.meta + (long long)seq * 8;
     if (!meta[4]) return;
     double* state = p.states + (long long)seq * p.state_stride;
