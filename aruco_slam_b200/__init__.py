@@ -8,7 +8,7 @@ constructing a filter needs a CUDA device.
 """
 from . import synth  # noqa: F401  (numpy only)
 
-__all__ = ["EKF", "EKF_Rotations", "BaseFilter", "FilterBatch", "estimate_pose_of_markers", "synth"]
+__all__ = ["EKF", "EKF_Rotations", "BaseFilter", "FilterBatch", "TrajectoryWriter", "estimate_pose_of_markers", "synth"]
 
 
 def __getattr__(name):
@@ -18,6 +18,9 @@ def __getattr__(name):
     if name == "FilterBatch":
         from .batch import FilterBatch
         return FilterBatch
+    if name == "TrajectoryWriter":
+        from .outputs import TrajectoryWriter
+        return TrajectoryWriter
     if name == "estimate_pose_of_markers":
         from .ippe import estimate_pose_of_markers
         return estimate_pose_of_markers

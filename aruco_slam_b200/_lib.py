@@ -69,6 +69,7 @@ SIGNATURES = {
     "asb_get_landmark_ids": (C.c_int, [_vp, _ip, C.c_int]),
     "asb_set_landmarks": (C.c_int, [_vp, _ip, C.c_int]),
     "asb_device_views": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp), _intp]),
+    "asb_correct_poses": (C.c_int, [_vp, _ip, _dp, _dp, C.c_int, C.c_double, _ip]),
     "asb_get_last_update": (C.c_int, [_vp, _dp, _dp, _dp, _intp]),
     "asb_batch_create": (C.c_int, [C.c_int, C.c_int, _dp, C.POINTER(Noise), C.c_int, C.c_int,
                                    C.c_int, C.c_int, C.POINTER(_vp)]),
@@ -79,6 +80,7 @@ SIGNATURES = {
     "asb_batch_set_stream": (C.c_int, [_vp, _vp]),
     "asb_batch_synchronize": (C.c_int, [_vp]),
     "asb_batch_upload": (C.c_int, [_vp, _ip, _dp, _lp, C.c_int]),
+    "asb_batch_upload_tiled": (C.c_int, [_vp, _ip, _dp, _lp, C.c_int, C.c_int]),
     "asb_batch_run": (C.c_int, [_vp, C.c_int, C.c_int]),
     "asb_batch_get_dims": (C.c_int, [_vp, C.c_int, _intp, _intp]),
     "asb_batch_get_state": (C.c_int, [_vp, C.c_int, _dp, C.c_int]),

@@ -66,18 +66,26 @@ class FilterBatch:
     def set_stream(self, cuda_stream: int | None) -> None:
         _lib.check(self._lib.asb_batch_set_stream(self._h, C.c_void_p(cuda_stream or 0)))
 
-    def upload(self, ids, poses, offsets) -> None:
+    def upload(self, ids, poses, offsets, n_streams: int | None = None) -> None:
         """Copy the packed observations of all sequences to the device (async on the
-        stream; the arrays are kept alive until the next upload)."""
+        stream; the arrays are kept alive until the next upload).  ``n_streams``: the arrays hold
+        only that many distinct streams and sequence ``s`` reads stream ``s % n_streams``."""
         ids = _lib.as_i32(ids)
         poses = _lib.as_f64(poses, (-1, 6))
         off = np.ascontiguousarray(np.asarray(offsets, dtype=np.int64))
-        n_frames = (off.size - 1) // self.n_seq
-        if n_frames * self.n_seq + 1 != off.size:
-            raise ValueError("offsets must have n_seq * n_frames + 1 entries")
+        if ids.size != poses.shape[0] or off[-1] != ids.size:
+            raise ValueError("ids, poses and offsets disagree on the number of observations")
+        ns = self.n_seq if n_streams is None else int(n_streams)
+        n_frames = (off.size - 1) // ns
+        if n_frames * ns + 1 != off.size:
+            raise ValueError("offsets must have n_streams * n_frames + 1 entries")
         self._keep = (ids, poses, off)
-        _lib.check(self._lib.asb_batch_upload(self._h, _lib.iptr(ids), _lib.dptr(poses),
-                                              _lib.lptr(off), n_frames))
+        if n_streams is None:
+            _lib.check(self._lib.asb_batch_upload(self._h, _lib.iptr(ids), _lib.dptr(poses),
+                                                  _lib.lptr(off), n_frames))
+        else:
+            _lib.check(self._lib.asb_batch_upload_tiled(self._h, _lib.iptr(ids), _lib.dptr(poses),
+                                                        _lib.lptr(off), n_frames, ns))
         self.n_frames = n_frames
 
     def run(self, t0: int = 0, t1: int | None = None) -> None:

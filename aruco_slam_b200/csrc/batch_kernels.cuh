@@ -30,6 +30,7 @@ struct BatchParams {
     long long state_stride, cov_stride;
     int n_seq, n_frames, t0, t1, max_lm, max_obs, as_written, p_in_smem;
     int seq0, seq1;        // this launch handles sequences [seq0, seq1)
+    int obs_seqs;          // distinct observation streams: sequence s reads stream s % obs_seqs (= n_seq unless tiled)
     Noise nz;
     unsigned long long* prof;   // 10 phase accumulators (clocks) of CTA 0, may be null
 };
@@ -136,8 +137,9 @@ k_batch(BatchParams p) {
         __syncthreads();
 
         for (int t = p.t0; t < p.t1; ++t) {
-            const long long ob = p.offsets[(long long)seq * p.n_frames + t];
-            const int k = (int)(p.offsets[(long long)seq * p.n_frames + t + 1] - ob);
+            const long long orec = (long long)(seq % p.obs_seqs) * p.n_frames + t;
+            const long long ob = p.offsets[orec];
+            const int k = (int)(p.offsets[orec + 1] - ob);
             if (k == 0) continue;  // no detection: no predict either (base_filter.py:197-204)
             if (k > p.max_obs) {
                 if (tid == 0) s_misc[1] = ASB_ERR_CAPACITY;

@@ -27,6 +27,7 @@ struct asb_batch {
     long long* d_off = nullptr;
     unsigned long long* d_prof = nullptr;
     int n_frames = 0;
+    int obs_seqs = 0;          // distinct observation streams on the device (n_seq, or fewer after an upload_tiled)
     long long n_obs = 0;
     int sm_count = 0, smem_optin = 0;
     int ck = 4;       // markers per chunk (ASB_BATCH_CK)
@@ -39,7 +40,7 @@ struct asb_batch {
     cudaStream_t copy_stream = nullptr, run_streams[2] = {nullptr, nullptr};
     cudaEvent_t ev_group[N_GROUPS]{}, ev_main = nullptr, ev_done[2] = {nullptr, nullptr};
     bool fresh_upload = false;
-    int groups = 1;
+    int groups = 1, up_groups = 1;   // sequence groups of the pipelined host path / of the last upload
     // Wide engine (wide_kernels.cuh): frame-synchronous kernels, covariance tiled in HBM.  Chosen at creation
     // when the resident engine's shared-memory footprint exceeds an SM (EKF_Rotations at 32 / 64 markers),
     // or on request (asb_batch_set_engine before the first upload).
@@ -186,6 +187,7 @@ template <int KIND> static int wide_run(asb_batch* b, int t0, int t1) {
     p.ids = b->d_ids; p.poses = b->d_poses; p.offsets = b->d_off;
     p.state_stride = b->state_stride; p.cov_stride = b->cov_stride;
     p.n_seq = b->n_seq; p.n_frames = b->n_frames; p.max_lm = b->max_lm; p.max_obs = b->max_obs;
+    p.obs_seqs = b->obs_seqs;
     p.as_written = (b->kind == ASB_KIND_EKF && b->quat_mode == ASB_QUAT_AS_WRITTEN) ? 1 : 0;
     p.nz = b->nz;
     p.meta = b->w_meta; p.idx = b->w_idx; p.delta = b->w_delta; p.H = b->w_H; p.L = b->w_L; p.Dinv = b->w_Dinv;
@@ -366,11 +368,14 @@ int asb_batch_synchronize(asb_batch* b) {
     return ASB_OK;
 }
 
-int asb_batch_upload(asb_batch* b, const int32_t* ids, const double* poses, const int64_t* offsets,
-                     int n_frames) {
+}  // extern "C"
+
+static int batch_upload(asb_batch* b, const int32_t* ids, const double* poses, const int64_t* offsets,
+                        int n_frames, int obs_seqs) {
     ASB_CHECK_BATCH(b);
+    if (obs_seqs < 1 || obs_seqs > b->n_seq || b->n_seq % obs_seqs) return fail(ASB_ERR_BAD_ARG, "%d streams do not tile %d sequences", obs_seqs, b->n_seq);
     if (!ids || !poses || !offsets || n_frames < 1) return fail(ASB_ERR_BAD_ARG, "bad stream");
-    const long long nrec = (long long)b->n_seq * n_frames;
+    const long long nrec = (long long)obs_seqs * n_frames;
     const long long total = offsets[nrec];
     if (total > b->n_obs || !b->d_ids) {
         ASB_CUDA(cudaStreamSynchronize(b->stream));
@@ -380,12 +385,13 @@ int asb_batch_upload(asb_batch* b, const int32_t* ids, const double* poses, cons
         ASB_CUDA(dmalloc(&b->d_poses, (size_t)total * 6));
         b->n_obs = total;
     }
-    if (n_frames != b->n_frames || !b->d_off) {
+    if (n_frames != b->n_frames || obs_seqs != b->obs_seqs || !b->d_off) {
         ASB_CUDA(cudaStreamSynchronize(b->stream));
         cudaFree(b->d_off);
         b->d_off = nullptr;
         ASB_CUDA(dmalloc(&b->d_off, (size_t)nrec + 1));
         b->n_frames = n_frames;
+        b->obs_seqs = obs_seqs;
     }
     static_assert(sizeof(long long) == sizeof(int64_t), "offset width");
     // group g = sequences [n_seq g / G, n_seq (g+1) / G): its ids / poses / offsets are contiguous
@@ -393,13 +399,15 @@ int asb_batch_upload(asb_batch* b, const int32_t* ids, const double* poses, cons
     // queued so far (a run that still reads the old observations).
     ASB_CUDA(cudaEventRecord(b->ev_main, b->stream));
     ASB_CUDA(cudaStreamWaitEvent(b->copy_stream, b->ev_main, 0));
-    for (int g = 0; g < b->groups; ++g) {
-        const long long s0 = (long long)b->n_seq * g / b->groups, s1 = (long long)b->n_seq * (g + 1) / b->groups;
+    const int ngr = obs_seqs == b->n_seq ? b->groups : 1;   // tiled streams: one copy (every group reads all of it)
+    b->up_groups = ngr;
+    for (int g = 0; g < ngr; ++g) {
+        const long long s0 = (long long)obs_seqs * g / ngr, s1 = (long long)obs_seqs * (g + 1) / ngr;
         const long long r0 = s0 * n_frames, r1 = s1 * n_frames;
         const long long o0 = offsets[r0], o1 = offsets[r1];
-        const long long nrecs = r1 - r0 + (g == b->groups - 1 ? 1 : 0);
+        const long long nrecs = r1 - r0 + (g == ngr - 1 ? 1 : 0);
         ASB_CUDA(cudaMemcpyAsync(b->d_off + r0, offsets + r0, (size_t)nrecs * sizeof(int64_t), cudaMemcpyHostToDevice, b->copy_stream));
-        if (g < b->groups - 1)   // a kernel reads offsets[r1] as the end of its last record
+        if (g < ngr - 1)   // a kernel reads offsets[r1] as the end of its last record
             ASB_CUDA(cudaMemcpyAsync(b->d_off + r1, offsets + r1, sizeof(int64_t), cudaMemcpyHostToDevice, b->copy_stream));
         ASB_CUDA(cudaMemcpyAsync(b->d_ids + o0, ids + o0, (size_t)(o1 - o0) * sizeof(int), cudaMemcpyHostToDevice, b->copy_stream));
         ASB_CUDA(cudaMemcpyAsync(b->d_poses + 6 * o0, poses + 6 * o0, (size_t)(o1 - o0) * 6 * sizeof(double), cudaMemcpyHostToDevice, b->copy_stream));
@@ -408,7 +416,7 @@ int asb_batch_upload(asb_batch* b, const int32_t* ids, const double* poses, cons
     b->fresh_upload = true;
     if (b->wide) {   // rounds per frame = ceil(max_s k(s, t) / WCK): the frame-synchronous launches need it on the host
         b->kmax.assign(n_frames, 0);
-        for (long long q = 0; q < b->n_seq; ++q) {
+        for (long long q = 0; q < obs_seqs; ++q) {
             const int64_t* o = offsets + q * n_frames;
             for (int t = 0; t < n_frames; ++t) b->kmax[t] = std::max(b->kmax[t], (int)(o[t + 1] - o[t]));
         }
@@ -417,13 +425,27 @@ int asb_batch_upload(asb_batch* b, const int32_t* ids, const double* poses, cons
     return ASB_OK;
 }
 
+int asb_batch_upload(asb_batch* b, const int32_t* ids, const double* poses, const int64_t* offsets,
+                     int n_frames) {
+    int rc = check(b);
+    if (rc != ASB_OK) return rc;
+    return batch_upload(b, ids, poses, offsets, n_frames, b->n_seq);
+}
+
+int asb_batch_upload_tiled(asb_batch* b, const int32_t* ids, const double* poses, const int64_t* offsets,
+                           int n_frames, int n_streams) {
+    return batch_upload(b, ids, poses, offsets, n_frames, n_streams);
+}
+
+extern "C" {
+
 int asb_batch_run(asb_batch* b, int t0, int t1) {
     ASB_CHECK_BATCH(b);
     if (!b->d_off) return fail(ASB_ERR_NO_STREAM, "batch_run before batch_upload");
     if (t0 < 0 || t1 < t0 || t1 > b->n_frames) return fail(ASB_ERR_BAD_ARG, "bad frame range [%d,%d)", t0, t1);
     if (b->wide) {
         if (b->fresh_upload) {
-            for (int g = 0; g < b->groups; ++g) ASB_CUDA(cudaStreamWaitEvent(b->stream, b->ev_group[g], 0));
+            for (int g = 0; g < b->up_groups; ++g) ASB_CUDA(cudaStreamWaitEvent(b->stream, b->ev_group[g], 0));
             b->fresh_upload = false;
         }
         return b->kind == ASB_KIND_EKF ? wide_run<0>(b, t0, t1) : wide_run<1>(b, t0, t1);
@@ -433,7 +455,7 @@ int asb_batch_run(asb_batch* b, int t0, int t1) {
     p.ids = b->d_ids; p.poses = b->d_poses; p.offsets = b->d_off;
     p.state_stride = b->state_stride; p.cov_stride = b->cov_stride;
     p.n_seq = b->n_seq; p.n_frames = b->n_frames; p.t0 = t0; p.t1 = t1;
-    p.max_lm = b->max_lm; p.max_obs = b->max_obs;
+    p.max_lm = b->max_lm; p.max_obs = b->max_obs; p.obs_seqs = b->obs_seqs;
     p.as_written = (b->kind == ASB_KIND_EKF && b->quat_mode == ASB_QUAT_AS_WRITTEN) ? 1 : 0;
     p.nz = b->nz;
     p.prof = b->d_prof;
@@ -444,7 +466,7 @@ int asb_batch_run(asb_batch* b, int t0, int t1) {
     if (smem > (size_t)b->smem_optin)
         return fail(ASB_ERR_CAPACITY, "batched filter needs %zu B shared memory > %d", smem, b->smem_optin);
     const int per_sm = std::max(1, std::min(8, (int)((size_t)(b->smem_optin + 1024) / (smem + 1024))));
-    if (!b->fresh_upload || b->groups == 1) {
+    if (!b->fresh_upload || b->up_groups == 1) {
         // observations already resident: one persistent launch over all sequences
         if (b->fresh_upload) ASB_CUDA(cudaStreamWaitEvent(b->stream, b->ev_group[0], 0));
         b->fresh_upload = false;
@@ -455,11 +477,11 @@ int asb_batch_run(asb_batch* b, int t0, int t1) {
     b->fresh_upload = false;
     ASB_CUDA(cudaEventRecord(b->ev_main, b->stream));
     for (auto& st : b->run_streams) ASB_CUDA(cudaStreamWaitEvent(st, b->ev_main, 0));
-    for (int g = 0; g < b->groups; ++g) {
+    for (int g = 0; g < b->up_groups; ++g) {
         cudaStream_t st = b->run_streams[g & 1];
         ASB_CUDA(cudaStreamWaitEvent(st, b->ev_group[g], 0));
-        p.seq0 = (int)((long long)b->n_seq * g / b->groups);
-        p.seq1 = (int)((long long)b->n_seq * (g + 1) / b->groups);
+        p.seq0 = (int)((long long)b->n_seq * g / b->up_groups);
+        p.seq1 = (int)((long long)b->n_seq * (g + 1) / b->up_groups);
         int rc = launch_batch_dyn(b, p, smem, std::min(p.seq1 - p.seq0, b->sm_count * per_sm), st);
         if (rc != ASB_OK) return rc;
     }

@@ -42,6 +42,7 @@ struct asb_filter {
     double *d_dx[2] = {nullptr, nullptr}, *dx_last = nullptr, *d_unc = nullptr;
     int* d_status = nullptr;
     unsigned long long* d_prof = nullptr;
+    double* d_gate = nullptr; int* d_gate_i = nullptr; int gate_cap = 0;   // asb_correct_poses staging
     // staging ring (host pinned + device)
     int* h_idx = nullptr; double* h_pose = nullptr; unsigned char* h_new = nullptr;
     int* d_idx = nullptr; double* d_pose = nullptr; unsigned char* d_new = nullptr;
@@ -421,6 +422,42 @@ static int poll_status(asb_filter* f) {
 // ---------------------------------------------------------------------------------------
 // C ABI
 // ---------------------------------------------------------------------------------------
+// Orientation-ambiguity gate (BaseFilter.correct_poses, base_filter.py:274-325), one thread per observation.
+// rot_ml = R(q_cam) * from_euler('xyz', pose[3:6]); angle = |rot_ml * inv(R(q_landmark))| in degrees; the
+// observation is kept (choice 1) when angle < threshold.  poses2 != null: the second IPPE solution
+// (cv2.solvePnPGeneric order) is tried when the first fails (choice 2).  Unknown ids (index < 0) are dropped
+// (choice 0), as the reference's `continue` does.
+__global__ void k_gate(const double* __restrict__ state, const int* __restrict__ lm_index,
+                       const double* __restrict__ poses1, const double* __restrict__ poses2, int k, int lm_dims,
+                       double threshold_deg, int* __restrict__ choice) {
+    const int o = blockIdx.x * blockDim.x + threadIdx.x;
+    if (o >= k) return;
+    int out = 0;
+    const int li = lm_index[o];
+    if (li >= 0) {
+        double qc[4] = {state[3], state[4], state[5], state[6]};
+        quat_normalize(qc);
+        const double* lm = state + CAM + lm_dims * li;
+        double ql[4] = {lm[3], lm[4], lm[5], lm[6]};
+        quat_normalize(ql);
+        const double qli[4] = {ql[0], -ql[1], -ql[2], -ql[3]};
+        for (int c = 0; c < 2 && out == 0; ++c) {
+            const double* pose = c == 0 ? poses1 + 6 * o : (poses2 ? poses2 + 6 * o : nullptr);
+            if (!pose) break;
+            double qcl[4], qml[4], qd[4];
+            euler_xyz_quat(pose + 3, qcl);
+            hamilton(qc, qcl, qml);
+            hamilton(qml, qli, qd);
+            const double v = sqrt(qd[1] * qd[1] + qd[2] * qd[2] + qd[3] * qd[3]);
+            double angle = 2.0 * atan2(v, fabs(qd[0])) * (180.0 / 3.14159265358979323846);
+            angle = fmin(angle, 360.0 - angle);
+            if (angle < threshold_deg) out = c + 1;
+        }
+    }
+    choice[o] = out;
+}
+
+
 extern "C" {
 
 int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb_noise* cfg,
@@ -572,7 +609,7 @@ int asb_filter_destroy(asb_filter* f) {
     cudaFree(f->d_state); cudaFree(f->d_P); cudaFree(f->d_Vr); cudaFree(f->d_Vc); cudaFree(f->d_blocks); cudaFree(f->d_nu);
     cudaFree(f->d_dx[0]); cudaFree(f->d_dx[1]); cudaFree(f->d_unc);
     cudaFree(f->d_status); cudaFree(f->d_prof); cudaFree(f->d_idx); cudaFree(f->d_pose); cudaFree(f->d_new);
-    cudaFree(f->s_idx); cudaFree(f->s_pose); cudaFree(f->s_new);
+    cudaFree(f->s_idx); cudaFree(f->s_pose); cudaFree(f->s_new); cudaFree(f->d_gate); cudaFree(f->d_gate_i);
     cudaFreeHost(f->h_idx); cudaFreeHost(f->h_pose); cudaFreeHost(f->h_new);
     cudaFreeHost(f->h_corner); cudaFree(f->d_corner);
     if (f->ev_pose) cudaEventDestroy(f->ev_pose);
@@ -975,6 +1012,40 @@ int asb_get_last_update(asb_filter* f, double* nu, double* blocks, double* dx, i
     if (blocks && k)
         ASB_CUDA(cudaMemcpy(blocks, f->d_blocks, (size_t)k * f->R * f->W * sizeof(double), cudaMemcpyDeviceToHost));
     if (dx) ASB_CUDA(cudaMemcpy(dx, f->dx_last, (size_t)f->n_state() * sizeof(double), cudaMemcpyDeviceToHost));
+    return ASB_OK;
+}
+
+int asb_correct_poses(asb_filter* f, const int32_t* ids, const double* poses, const double* poses2_or_null, int k,
+                      double threshold_deg, int32_t* choice_out) {
+    ASB_CHECK_HANDLE(f);
+    if (f->kind != ASB_KIND_ROT) return fail(ASB_ERR_BAD_ARG, "correct_poses needs landmark orientations (EKF_Rotations)");
+    if (k < 0 || (k > 0 && (!ids || !poses || !choice_out))) return fail(ASB_ERR_BAD_ARG, "bad correct_poses arguments");
+    if (k == 0) return ASB_OK;
+    if (k > f->gate_cap) {
+        ASB_CUDA(cudaStreamSynchronize(f->stream));
+        cudaFree(f->d_gate); cudaFree(f->d_gate_i);
+        f->d_gate = nullptr; f->d_gate_i = nullptr; f->gate_cap = 0;
+        const int cap = std::max(k, 64);
+        ASB_CUDA(cudaMalloc(&f->d_gate, (size_t)cap * 12 * sizeof(double)));
+        ASB_CUDA(cudaMalloc(&f->d_gate_i, (size_t)cap * 2 * sizeof(int)));
+        f->gate_cap = cap;
+    }
+    std::vector<int> idx(k);
+    for (int o = 0; o < k; ++o) {
+        auto it = f->map.find(ids[o]);
+        idx[o] = it == f->map.end() ? -1 : it->second;
+    }
+    double* d_p1 = f->d_gate;
+    double* d_p2 = poses2_or_null ? f->d_gate + (size_t)f->gate_cap * 6 : nullptr;
+    int* d_idx = f->d_gate_i;
+    int* d_choice = f->d_gate_i + f->gate_cap;
+    ASB_CUDA(cudaMemcpyAsync(d_idx, idx.data(), (size_t)k * sizeof(int), cudaMemcpyHostToDevice, f->stream));
+    ASB_CUDA(cudaMemcpyAsync(d_p1, poses, (size_t)k * 6 * sizeof(double), cudaMemcpyHostToDevice, f->stream));
+    if (d_p2) ASB_CUDA(cudaMemcpyAsync(d_p2, poses2_or_null, (size_t)k * 6 * sizeof(double), cudaMemcpyHostToDevice, f->stream));
+    k_gate<<<(k + 63) / 64, 64, 0, f->stream>>>(f->d_state, d_idx, d_p1, d_p2, k, f->D, threshold_deg, d_choice);
+    ASB_CUDA(cudaGetLastError());
+    ASB_CUDA(cudaMemcpyAsync(choice_out, d_choice, (size_t)k * sizeof(int), cudaMemcpyDeviceToHost, f->stream));
+    ASB_CUDA(cudaStreamSynchronize(f->stream));   // idx (host vector) and choice_out are done with
     return ASB_OK;
 }
 

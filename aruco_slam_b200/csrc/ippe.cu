@@ -242,20 +242,47 @@ static int ippe_host(const float* corners, int64_t n, const double camera_matrix
     // Device buffers are kept between calls (grow-only, per device): the per-frame caller
     // (BaseFilter.estimate_pose_of_markers, a few dozen markers) must not pay cudaMalloc /
     // cudaFree round trips per frame.
-    struct Cache { float* dc = nullptr; double* dout = nullptr; double* dout2 = nullptr; float* derr = nullptr; int64_t cap = 0; };
+    struct Cache { float* dc = nullptr; double* dout = nullptr; double* dout2 = nullptr; float* derr = nullptr; int64_t cap = 0;
+                   cudaStream_t st[2] = {nullptr, nullptr}; };
+    constexpr int64_t IPPE_CHUNK = 65536;
     static std::mutex mu;
     static Cache cache[64];
     std::lock_guard<std::mutex> lock(mu);
     Cache& c = cache[device & 63];
     if (n > c.cap) {
         cudaFree(c.dc); cudaFree(c.dout); cudaFree(c.dout2); cudaFree(c.derr);
-        c = Cache{};
+        c.dc = nullptr; c.dout = c.dout2 = nullptr; c.derr = nullptr; c.cap = 0;
         const int64_t cap = std::max<int64_t>(n, 4096);
         ASB_CUDA(cudaMalloc(&c.dc, (size_t)cap * 8 * sizeof(float)));
         ASB_CUDA(cudaMalloc(&c.dout, (size_t)cap * 6 * sizeof(double)));
         ASB_CUDA(cudaMalloc(&c.dout2, (size_t)cap * 6 * sizeof(double)));
         ASB_CUDA(cudaMalloc(&c.derr, (size_t)cap * 2 * sizeof(float)));
         c.cap = cap;
+    }
+    if (n >= 4 * IPPE_CHUNK) {
+        // Large batches (BASELINE config C4, 1M sets = 32 MB in + 48 MB out): slices alternate between two
+        // streams, so the H2D copy of slice i+1, the kernel of slice i and the D2H copy of slice i-1 overlap
+        // (separate copy engines per direction).  One cudaMemcpyAsync per slice and buffer; with pageable
+        // host memory the copies stage through the driver and the overlap is partial.
+        if (!c.st[0]) {
+            ASB_CUDA(cudaStreamCreateWithFlags(&c.st[0], cudaStreamNonBlocking));
+            ASB_CUDA(cudaStreamCreateWithFlags(&c.st[1], cudaStreamNonBlocking));
+        }
+        int i = 0;
+        for (int64_t o = 0; o < n; o += IPPE_CHUNK, ++i) {
+            const int64_t cn = std::min<int64_t>(IPPE_CHUNK, n - o);
+            cudaStream_t st = c.st[i & 1];
+            ASB_CUDA(cudaMemcpyAsync(c.dc + 8 * o, corners + 8 * o, (size_t)cn * 8 * sizeof(float), cudaMemcpyHostToDevice, st));
+            int rc = asb_ippe_square_device(c.dc + 8 * o, cn, camera_matrix, dist_coeffs, marker_size, c.dout + 6 * o,
+                                            out2 ? c.dout2 + 6 * o : nullptr, errs ? c.derr + 2 * o : nullptr, st);
+            if (rc != ASB_OK) return rc;
+            ASB_CUDA(cudaMemcpyAsync(out + 6 * o, c.dout + 6 * o, (size_t)cn * 6 * sizeof(double), cudaMemcpyDeviceToHost, st));
+            if (out2) ASB_CUDA(cudaMemcpyAsync(out2 + 6 * o, c.dout2 + 6 * o, (size_t)cn * 6 * sizeof(double), cudaMemcpyDeviceToHost, st));
+            if (errs) ASB_CUDA(cudaMemcpyAsync(errs + 2 * o, c.derr + 2 * o, (size_t)cn * 2 * sizeof(float), cudaMemcpyDeviceToHost, st));
+        }
+        ASB_CUDA(cudaStreamSynchronize(c.st[0]));
+        ASB_CUDA(cudaStreamSynchronize(c.st[1]));
+        return ASB_OK;
     }
     ASB_CUDA(cudaMemcpy(c.dc, corners, (size_t)n * 8 * sizeof(float), cudaMemcpyHostToDevice));
     int rc = asb_ippe_square_device(c.dc, n, camera_matrix, dist_coeffs, marker_size, c.dout, out2 ? c.dout2 : nullptr,

@@ -56,6 +56,7 @@ struct WideParams {
     long long state_stride, cov_stride;
     int n_seq, n_frames, max_lm, max_obs, as_written;
     int t, round;
+    int obs_seqs;              // distinct observation streams: sequence s reads stream s % obs_seqs
     int seq0;                  // this launch covers sequences seq0 + blockIdx (sequence groups run on separate streams)
     Noise nz;
     // per-sequence scratch
@@ -102,11 +103,12 @@ __global__ void __launch_bounds__(128, 5) k_wide_model(WideParams p) {
     double* P = p.covs + (long long)seq * p.cov_stride;
     double* delta = p.delta + (long long)seq * p.state_stride;
     int* g_idx = p.idx + (long long)seq * p.max_obs;
-    const long long ob = p.offsets[(long long)seq * p.n_frames + p.t];
+    const long long orec = (long long)(seq % p.obs_seqs) * p.n_frames + p.t;
+    const long long ob = p.offsets[orec];
     int k, cs, n;
 
     if (p.round == 0) {
-        k = (int)(p.offsets[(long long)seq * p.n_frames + p.t + 1] - ob);
+        k = (int)(p.offsets[orec + 1] - ob);
         const int st = p.status[seq];
         if (k == 0 || k > p.max_obs || st == ASB_ERR_CAPACITY) {   // no detection: no predict either (BASE:197-204)
             if (tid == 0) {

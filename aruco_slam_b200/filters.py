@@ -174,7 +174,7 @@ class _CudaFilter(BaseFilter):
 
     def __init__(self, initial_camera_pose, aruco_dict=None, *, camera_matrix=None,
                  dist_coeffs=None, quat_mode: str = "as_written", max_landmarks: int = 256,
-                 noise: dict | None = None, device: int = 0) -> None:
+                 noise: dict | None = None, device: int = 0, growable: bool = True) -> None:
         self._history = []
         self._h = None
         super().__init__(initial_camera_pose, None, aruco_dict, camera_matrix=camera_matrix,
@@ -192,12 +192,48 @@ class _CudaFilter(BaseFilter):
             for key, val in noise.items():
                 setattr(nz, key, float(val))
             cfg = C.byref(nz)
-        h = C.c_void_p()
-        _lib.check(self._lib.asb_filter_create(self.KIND, modes[quat_mode], _lib.dptr(pose), cfg,
-                                               int(max_landmarks), int(device), C.byref(h)))
-        self._h = h
+        self._create_args = (modes[quat_mode], pose, cfg, int(device))
+        self._noise_keep = cfg
+        self._stream = None
+        self.growable = bool(growable)
+        self._h = self._create(int(max_landmarks))
         self.max_landmarks = int(max_landmarks)
         self.landmarks = {}
+
+    def _create(self, max_landmarks: int):
+        mode, pose, cfg, device = self._create_args
+        h = C.c_void_p()
+        _lib.check(self._lib.asb_filter_create(self.KIND, mode, _lib.dptr(pose), cfg, int(max_landmarks), device,
+                                               C.byref(h)))
+        return h
+
+    def _grow(self, need: int) -> None:
+        """The reference grows its state and covariance without bound (extended_kalman_filter.py:279-290); the
+        device buffers are allocated at a capacity, so on overflow the filter moves to a handle of at least twice
+        the capacity (state, covariance and id map copied, as the reference's re-allocation copies P)."""
+        state, cov = self.state, self.uncertainty
+        self._refresh_landmarks()
+        ids = self._ids.copy()
+        new_cap = max(2 * self.max_landmarks, int(need))
+        new_h = self._create(new_cap)
+        old, self._h = self._h, new_h
+        self._lib.asb_filter_destroy(old)
+        self.max_landmarks = new_cap
+        if self._stream:
+            _lib.check(self._lib.asb_filter_set_stream(self._h, C.c_void_p(self._stream)))
+        if ids.size:
+            self.load_checkpoint(state, cov, ids)
+        else:
+            self.state = state
+            self.uncertainty = cov
+
+    def _call_growing(self, fn, n_new_max: int):
+        """Run a library call that may add landmarks; on ASB_ERR_CAPACITY (nothing was changed) grow and retry."""
+        rc = fn()
+        if rc == _lib.ERR_CAPACITY and self.growable:
+            self._grow(self.num_landmarks + n_new_max)
+            rc = fn()
+        _lib.check(rc)
 
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
@@ -273,7 +309,9 @@ class _CudaFilter(BaseFilter):
         Returns None, as the reference does."""
         ids = _lib.as_i32(ids)
         poses = _lib.as_f64(poses, (-1, 6))
-        _lib.check(self._lib.asb_observe(self._h, _lib.iptr(ids), _lib.dptr(poses), ids.size))
+        if ids.size != poses.shape[0]:
+            raise ValueError(f"{ids.size} ids but {poses.shape[0]} poses")
+        self._call_growing(lambda: self._lib.asb_observe(self._h, _lib.iptr(ids), _lib.dptr(poses), ids.size), ids.size)
         self._refresh_landmarks()
 
     def _observe_corners(self, ids, corners, marker_size: float) -> np.ndarray:
@@ -283,11 +321,35 @@ class _CudaFilter(BaseFilter):
         ids = _lib.as_i32(ids)
         c = _corner_array(corners)
         km, dist = _intrinsics(self.calib_matrix, self.dist_coeffs)
+        if ids.size != c.shape[0]:
+            raise ValueError(f"{ids.size} ids but {c.shape[0]} corner sets")
         out = np.empty((c.shape[0], 6), dtype=np.float64)
-        _lib.check(self._lib.asb_observe_corners(self._h, _lib.iptr(ids), _lib.fptr(c), ids.size, _lib.dptr(km),
-                                                 _lib.dptr(dist), float(marker_size), _lib.dptr(out)))
+        self._call_growing(lambda: self._lib.asb_observe_corners(
+            self._h, _lib.iptr(ids), _lib.fptr(c), ids.size, _lib.dptr(km), _lib.dptr(dist), float(marker_size),
+            _lib.dptr(out)), ids.size)
         self._refresh_landmarks()
         return out
+
+    def correct_poses(self, ids, poses, alt_poses=None, threshold_deg: float = 50.0):
+        """``BaseFilter.correct_poses`` (base_filter.py:274-325; QUAT_THRESHOLD = 50, :32): keep the observations
+        whose orientation agrees with the landmark orientation in the state, drop unknown ids.  Returns
+        ``(corrected_ids, corrected_poses)`` as the reference does.  ``alt_poses`` (k,6): the second IPPE solution
+        of each observation (``estimate_both_poses``); it replaces a rejected first solution when it passes the
+        same test (extension, README "orientation ambiguity")."""
+        ids = _lib.as_i32(ids)
+        poses = _lib.as_f64(poses, (-1, 6))
+        if ids.size != poses.shape[0]:
+            raise ValueError("ids and poses disagree on the number of observations")
+        alt = None if alt_poses is None else _lib.as_f64(alt_poses, (-1, 6))
+        if alt is not None and alt.shape != poses.shape:
+            raise ValueError("alt_poses must have the shape of poses")
+        choice = np.zeros(ids.size, dtype=np.int32)
+        _lib.check(self._lib.asb_correct_poses(self._h, _lib.iptr(ids), _lib.dptr(poses),
+                                               None if alt is None else _lib.dptr(alt), ids.size,
+                                               float(threshold_deg), _lib.iptr(choice)))
+        out_ids = [int(i) for i, c in zip(ids, choice) if c]
+        out_poses = [poses[o] if c == 1 else alt[o] for o, c in enumerate(choice) if c]
+        return out_ids, out_poses
 
     def predict(self) -> None:
         _lib.check(self._lib.asb_predict(self._h))
@@ -295,6 +357,8 @@ class _CudaFilter(BaseFilter):
     def update(self, ids, poses) -> None:
         ids = _lib.as_i32(ids)
         poses = _lib.as_f64(poses, (-1, 6))
+        if ids.size != poses.shape[0]:
+            raise ValueError(f"{ids.size} ids but {poses.shape[0]} poses")
         _lib.check(self._lib.asb_update(self._h, _lib.iptr(ids), _lib.dptr(poses), ids.size))
 
     def add_marker(self, idx, pose, uncertainity=None) -> None:
@@ -308,7 +372,7 @@ class _CudaFilter(BaseFilter):
                 u = np.diagonal(u)  # eye * M keeps only M's diagonal (EKF:280-281)
             u = np.ascontiguousarray(np.broadcast_to(u, (self.LM_DIMS,)))
             unc = _lib.dptr(u)
-        _lib.check(self._lib.asb_add_marker(self._h, int(idx), _lib.dptr(pose), unc))
+        self._call_growing(lambda: self._lib.asb_add_marker(self._h, int(idx), _lib.dptr(pose), unc), 1)
         self._refresh_landmarks()
 
     def get_poses(self):
@@ -331,6 +395,7 @@ class _CudaFilter(BaseFilter):
         _lib.check(self._lib.asb_filter_synchronize(self._h))
 
     def set_stream(self, cuda_stream: int | None) -> None:
+        self._stream = cuda_stream or None
         _lib.check(self._lib.asb_filter_set_stream(self._h, C.c_void_p(cuda_stream or 0)))
 
     def stream_upload(self, ids, poses, offsets) -> None:

@@ -24,6 +24,10 @@ def _intrinsics(camera_matrix, dist_coeffs):
     km = _lib.as_f64(camera_matrix, (9,))
     dist = np.zeros(5)
     d = _lib.as_f64(dist_coeffs).reshape(-1)
+    if d.size > 5 and np.any(d[5:] != 0.0):
+        # cv2.solvePnP honours the 8 / 12 / 14-coefficient models; only k1 k2 p1 p2 k3 is implemented here
+        raise ValueError("only the 5-coefficient distortion model (k1, k2, p1, p2, k3) is implemented; "
+                         f"got {d.size} coefficients with non-zero higher-order terms")
     dist[:min(5, d.size)] = d[:5]
     return km, dist
 

@@ -91,6 +91,8 @@ class ShardedFilter:
     def observe(self, ids, poses) -> None:
         ids = _lib.as_i32(ids)
         poses = _lib.as_f64(poses, (-1, 6))
+        if ids.size != poses.shape[0]:
+            raise ValueError(f"{ids.size} ids but {poses.shape[0]} poses")
         _lib.check(self._lib.asb_shard_observe(self._h, _lib.iptr(ids), _lib.dptr(poses), int(ids.size)))
 
     def stream_upload(self, ids, poses, offsets) -> None:

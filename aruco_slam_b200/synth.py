@@ -89,6 +89,7 @@ def make_stream(seq: int = 0, n_markers: int = 10, n_frames: int = 1000, p_visib
     else:
         lm = rng.uniform(-2.0, 2.0, size=(n_markers, 3)) + np.array([0.0, 0.0, 5.0])
     r_ml = [euler_xyz_matrix(rng.normal(0.0, 0.2, size=3)) for _ in range(n_markers)]
+    r_ml_arr = np.stack(r_ml)
     marker_ids = id_base + rng.permutation(n_markers).astype(np.int32)  # id != index on purpose
 
     ids_out, poses_out = [], []
@@ -105,8 +106,9 @@ def make_stream(seq: int = 0, n_markers: int = 10, n_frames: int = 1000, p_visib
         k = len(idx)
         t = (lm[idx] - c) @ r_mc + rng.normal(0.0, 0.01, size=(k, 3))  # R_mc^T (l - c)
         if kind == "rot":
-            rv = np.stack([matrix_to_euler_xyz(r_mc.T @ r_ml[j]) for j in idx]) \
-                + rng.normal(0.0, 0.01, size=(k, 3))
+            rr = np.matmul(r_mc.T, r_ml_arr[idx])            # (k,3,3) R_mc^T R_ml, then euler_xyz of each
+            rv = np.stack([np.arctan2(rr[:, 2, 1], rr[:, 2, 2]), -np.arcsin(np.clip(rr[:, 2, 0], -1.0, 1.0)),
+                           np.arctan2(rr[:, 1, 0], rr[:, 0, 0])], axis=1) + rng.normal(0.0, 0.01, size=(k, 3))
         else:
             rv = rng.normal(0.0, 0.1, size=(k, 3))
         ids_out.append(marker_ids[idx].astype(np.int32))
@@ -114,8 +116,12 @@ def make_stream(seq: int = 0, n_markers: int = 10, n_frames: int = 1000, p_visib
     return Stream(ids_out, poses_out, lm, n_markers)
 
 
+def _packed_stream(seq, n_markers, n_frames, p_visible, kind):
+    return make_stream(seq, n_markers, n_frames, p_visible, kind).packed()
+
+
 def make_batch(n_seq: int, n_markers: int, n_frames: int, p_visible: float, kind: str = "ekf",
-               seq_base: int = 0, unique: int | None = None):
+               seq_base: int = 0, unique: int | None = None, workers: int = 0):
     """Pack ``n_seq`` sequences for the batched engine.
 
     Returns (ids (M,) i32, poses (M,6) f64, frame_offsets (n_seq*(T)+1,) i32 with
@@ -125,8 +131,13 @@ def make_batch(n_seq: int, n_markers: int, n_frames: int, p_visible: float, kind
     tests always use ``unique=None`` (all distinct).
     """
     u = n_seq if unique is None else min(unique, n_seq)
-    packs = [make_stream(seq_base + s, n_markers, n_frames, p_visible, kind).packed()
-             for s in range(u)]
+    if workers and workers > 1 and u >= 4 * workers:
+        import multiprocessing as mp
+        with mp.get_context("spawn").Pool(workers) as pool:
+            packs = pool.starmap(_packed_stream, [(seq_base + s, n_markers, n_frames, p_visible, kind)
+                                                  for s in range(u)], chunksize=max(1, u // (8 * workers)))
+    else:
+        packs = [_packed_stream(seq_base + s, n_markers, n_frames, p_visible, kind) for s in range(u)]
     ids_l, poses_l, counts = [], [], []
     for s in range(n_seq):
         i, p, off = packs[s % u]

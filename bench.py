@@ -12,8 +12,10 @@ filters.  `value` = marker-updates/s with the observations already resident in H
 `e2e` = the same through the public Python API with host buffers (H2D of the step's
 observations from pinned memory + D2H of the resulting camera poses inside the timed
 region).  Extra workloads measured in the same run and reported under "workloads":
-C3 (one EKF, 2000-marker map, N = 6010, the HBM-bound covariance sweep) and C4 (1M-corner
-batched IPPE).  See DESIGN.md §Measurement for the byte/flop accounting.
+C1 (one sequence, per-frame observe() latency, both classes), C2 with EKF_Rotations (N = 330, wide engine),
+C3 (one EKF, 2000-marker map, N = 6010, the covariance sweep), C4 (1M-corner batched IPPE) and C5
+(32768 sequences x 64 markers x 1000 frames, p = 0.25, both classes, total over the ranks).
+See DESIGN.md §Measurement for the byte/flop accounting.
 """
 from __future__ import annotations
 
@@ -31,6 +33,9 @@ import numpy as np
 ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 
+# FP64 flops of k_ippe_square per corner set: (2 x 536.18 M dfma + 499.39 M dmul + 333.70 M dadd) / 1 M sets, ncu
+# smsp__sass_thread_inst_executed_op_d{fma,mul,add}_pred_on.sum (profiles/r02_k_ippe.txt)
+IPPE_FLOPS_PER_SET = 1905.45
 METRIC = "mekf_marker_updates_per_sec"
 UNIT = "marker-updates/s"
 
@@ -50,7 +55,11 @@ def parse_args():
     ap.add_argument("--kind", default="ekf", choices=["ekf", "rot"])
     ap.add_argument("--quat-mode", default="as_written", choices=["as_written", "scalar_first"])
     ap.add_argument("--no-extras", action="store_true", help="skip the C3 / C4 legs")
-    ap.add_argument("--only", default=None, choices=["c3", "c4", "c3s"],
+    ap.add_argument("--c5-seqs", type=int, default=32768, help="C5 sequences in total (sharded over the ranks)")
+    ap.add_argument("--leg-budget-s", type=float, default=170.0,
+                    help="wall-clock budget of one extra batched leg; a leg that would exceed it stops at a "
+                         "whole number of 100-frame slices and says so (frames_run)")
+    ap.add_argument("--only", default=None, choices=["c1", "c2rot", "c3", "c4", "c3s", "c5ekf", "c5rot"],
                     help="profiling aid: run just that leg and print its JSON")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU baseline budget")
     return ap.parse_args()
@@ -209,6 +218,10 @@ def workload_config(args):
             else "EKF_Rotations (filters/ekf_with_rotations.py)",
             "quat_mode": args.quat_mode, "sequences_per_gpu": args.seqs, "markers": args.markers,
             "frames": args.frames, "p_visible": args.p_visible,
+            "distinct_streams_per_gpu": min(args.unique, args.seqs),
+            "streams_note": f"{min(args.unique, args.seqs)} distinct synthetic sequences per rank tiled to "
+                            f"{args.seqs} (every sequence runs its own filter and the whole 3.4 GB stream is "
+                            f"read); value_unique = one step with {args.seqs} distinct sequences",
             "parallelism": "sequence shards, no data-path collective, final camera-pose gather",
             "cache": "inputs larger than L2 (3.4 GB of observations per step)"}
 
@@ -236,7 +249,7 @@ def timed(torch, dist, fn, steps):
     return float(ms.item())
 
 
-def leg_c3(torch, stream_ptr, hbm_peak):
+def leg_c3(torch, stream_ptr, hbm_peak, fp64_peak):
     """C3: one EKF with a 2000-marker map (N = 6010, P = 289 MB), 20 markers per frame."""
     import ctypes as C
     from aruco_slam_b200 import EKF, _lib, synth
@@ -258,8 +271,13 @@ def leg_c3(torch, stream_ptr, hbm_peak):
     f.synchronize()
     ms = e0.elapsed_time(e1)
     n = 6010
-    per_frame_bytes = 16.0 * n * n  # one read + one write of dense FP64 P
-    ach = per_frame_bytes * timed_frames / (ms * 1e-3) / 1e9
+    sec = ms * 1e-3
+    # Bytes the sweep has to move as built: it keeps the LOWER TRIANGLE only (one read + one write = 8 N^2);
+    # the dense-equivalent contract figure of SURVEY.md 8(d) (16 N^2: what a full-matrix update would move) is
+    # reported beside it under its own name, not as the achieved bandwidth.
+    ach = 8.0 * n * n * timed_frames / sec / 1e9
+    dense_eq = 16.0 * n * n * timed_frames / sec / 1e9
+    tf = float(n) * n * 60 * timed_frames / sec / 1e12   # N^2 m flops per frame on the triangle (m = 60)
     # e2e: per-frame observe() with host buffers + camera pose read-back every frame
     t_frames = 50
     extra, _ = synth.make_map_build_stream(2000, 20, t_frames, seed=77)
@@ -277,10 +295,18 @@ def leg_c3(torch, stream_ptr, hbm_peak):
         "frames": timed_frames, "gpu_launches_per_frame": 3,
         "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
                      "frac": ach / hbm_peak, "traffic": 257.5e6,
-                     "note": "achieved = 16*N^2 B per frame / whole-frame time (k_f2 + k_sweep on the critical "
-                             "path, k_f1 of the next frame overlapped); traffic = dram read + write bytes of one "
-                             "k_sweep launch, ncu --set full (profiles/r01c_k_sweep.txt): only the lower "
-                             "triangle is read and written (the readers take P[i][j], i < j, from P[j][i])"},
+                     "dense_equivalent": {"achieved": dense_eq, "frac": dense_eq / hbm_peak,
+                                          "note": "16 N^2 B per frame (SURVEY.md 8d contract figure: one read + one "
+                                                  "write of a DENSE P) / whole-frame time"},
+                     "note": "achieved = 8 N^2 B per frame (lower triangle read + write, what k_sweep moves) / "
+                             "whole-frame time (k_f2 + k_sweep on the critical path, k_f1 of the next frame "
+                             "overlapped); traffic = dram read + write bytes of one k_sweep launch, ncu --set full "
+                             "(profiles/r01c_k_sweep.txt).  The kernel is bound by the FP64 tensor pipe, see "
+                             "roofline_fp64"},
+        "roofline_fp64": {"bound": "tensor", "achieved": tf, "peak": fp64_peak, "unit": "TFLOP/s",
+                          "frac": tf / fp64_peak, "peak_source": "asb_fp64_peak(which=1): mma.sync m8n8k4 f64 (DMMA) "
+                          "chains timed live with CUDA events; MEASURED_PEAKS.json has no FP64 entry",
+                          "note": "N^2 m flops per frame (triangle) / whole-frame time"},
         "e2e": {"value": 20.0 * t_frames / wall, "unit": UNIT, "h2d_bytes_per_step": 20 * 52,
                 "d2h_bytes_per_step": 8 * 6010},
     }
@@ -294,7 +320,7 @@ def leg_c3_sharded(torch, dist, rank, world, local, stream_ptr, hbm_peak):
     timed_frames, warm = 200, 20
     stream, n_build = synth.make_map_build_stream(2000, 20, warm + timed_frames)
     f = ShardedFilter("ekf", np.array([0, 0, 0, 1, 0, 0, 0, 0, 0, 0.0]), 2000, dist=dist, rank=rank, world=world,
-                      device=local, quat_mode="as_written")
+                      device=local, quat_mode="scalar_first")
     f.set_stream(stream_ptr)
     ids, poses, off = stream.packed()
     f.stream_upload(ids, poses, off)
@@ -303,17 +329,41 @@ def leg_c3_sharded(torch, dist, rank, world, local, stream_ptr, hbm_peak):
     f.synchronize()
     cam, _ = f.get_poses()
     n = 6010
-    ach = 16.0 * n * n * timed_frames / (ms * 1e-3) / 1e9
+    ach = 8.0 * n * n * timed_frames / (ms * 1e-3) / 1e9
+    # driver-visible multi-GPU correctness: the same frames on the single-GPU engine (rank 0), state and this
+    # rank's covariance rows compared with the sharded result (max-norm relative error)
+    parity = {}
+    try:
+        rows = f.local_rows()
+        if rank == 0:
+            from aruco_slam_b200 import EKF
+            km, dc = synth.reference_calibration()
+            g1 = EKF(np.array([0, 0, 0, 1, 0, 0, 0, 0, 0, 0.0]), camera_matrix=km, dist_coeffs=dc,
+                     quat_mode="scalar_first", max_landmarks=2000)
+            g1.stream_upload(ids, poses, off)
+            g1.stream_run(0, n_build + warm + timed_frames)
+            st1, p1 = g1.state, g1.uncertainty
+            del g1
+            parity = {"parity_rel_state": float(np.max(np.abs(f.state - st1)) / np.max(np.abs(st1))),
+                      "parity_rel_cov_rows": float(np.max(np.abs(rows - p1[f.row0:f.row0 + rows.shape[0]]))
+                                                   / np.max(np.abs(p1))),
+                      "parity_note": "row-sharded engine vs the single-GPU engine on the same 320 frames (rank 0's "
+                                     "rows), free-running, scalar-first quaternion mode (the as-written reset is "
+                                     "chaotic, SURVEY.md F3); tolerance 1e-9"}
+    except Exception as exc:
+        parity = {"parity_error": repr(exc)}
     out = {"workload": f"C3 row-sharded: single EKF, 2000-marker map (N=6010), 20 markers/frame, covariance rows "
                        f"over {world} GPU(s), NCCL all-reduce of P[T,T] + all-gather of the V panel per frame",
            "value": 20.0 * timed_frames / (ms * 1e-3), "unit": UNIT, "us_per_frame": 1e3 * ms / timed_frames,
-           "n_gpus": world, "frames": timed_frames, "rows_per_gpu": f.row1 - f.row0,
+           "n_gpus": world, "frames": timed_frames, "rows_per_gpu": f.row1 - f.row0, "quat_mode": "scalar_first",
            "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak * world, "unit": "GB/s",
                         "frac": ach / (hbm_peak * world), "traffic": None,
-                        "note": "16*N^2 B per frame / frame time against world x the measured HBM peak; the "
+                        "note": "8 N^2 B per frame (the bytes of P every rank set together has to move once) / frame "
+                                "time against world x the measured HBM peak; the "
                                 "rectangular row sweep does 2x the FP64 work of the triangle sweep and each "
                                 "frame pays two NCCL collectives"},
            "camera_finite": bool(np.isfinite(cam).all())}
+    out.update(parity)
     f.close()
     return out
 
@@ -351,9 +401,151 @@ def leg_c4(torch, stream_ptr, hbm_peak, fp64_peak):
             "unit": "poses/s", "ms_per_batch": ms,
             "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
                          "frac": ach / hbm_peak, "traffic": None,
-                         "note": "80 B per set (32 in + 48 out); the kernel is FP64-pipe bound"},
+                         "note": "80 B per set (32 in + 48 out); the kernel is FP64-pipe bound, see roofline_fp64"},
+            "roofline_fp64": {"bound": "fp64", "achieved": IPPE_FLOPS_PER_SET * n / (ms * 1e-3) / 1e12, "peak": fp64_peak,
+                              "unit": "TFLOP/s", "frac": IPPE_FLOPS_PER_SET * n / (ms * 1e-3) / 1e12 / fp64_peak,
+                              "flops_per_set": IPPE_FLOPS_PER_SET, "fp64_pipe_active_pct_ncu": 63.7,
+                              "note": "flops per corner set counted by ncu on this kernel (2 x dfma + dmul + dadd "
+                                      "thread instructions, profiles/r02_k_ippe.txt); peak = DFMA peak measured live "
+                                      "(asb_fp64_peak); a third of the issued FP64 instructions are DMUL / DADD, "
+                                      "which occupy the pipe for one flop"},
             "e2e": {"value": n / wall, "unit": "poses/s", "h2d_bytes_per_step": 32 * n,
                     "d2h_bytes_per_step": 48 * n}, "finite": bool(np.isfinite(out).all())}
+
+
+def leg_c1(torch, stream_ptr):
+    """C1 (BASELINE.json configs[0]): ONE sequence, 10 static markers, 1000 frames, p = 0.8 — the latency
+    case: per-frame observe() through the drop-in classes with host buffers and the camera pose read back
+    every frame (what main/run_slam.py does), both classes, next to the numpy oracle port on one host core."""
+    from aruco_slam_b200 import EKF, EKF_Rotations, synth
+    from oracle import ekf_oracle
+    km, dist = synth.reference_calibration()
+    pose0 = np.array([0, 0, 0, 1, 0, 0, 0, 0, 0, 0.0])
+    out = {"workload": "C1: 1 sequence x 10 markers x 1000 frames, p = 0.8, per-frame observe() + get_poses() "
+                       "with host buffers (BASELINE.json configs[0])"}
+    for kind, cls in (("ekf", EKF), ("rot", EKF_Rotations)):
+        s = synth.make_stream(0, 10, 1000, 0.8, kind)
+        kw = dict(camera_matrix=km, dist_coeffs=dist, max_landmarks=16)
+        if kind == "ekf":
+            kw["quat_mode"] = "as_written"
+        for rep in range(2):          # first pass warms the kernels / staging buffers
+            f = cls(pose0, **kw)
+            f.set_stream(stream_ptr)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for t in range(s.n_frames):
+                f.observe(s.ids[t], s.poses[t])
+                cam, _ = f.get_poses()
+            wall = time.perf_counter() - t0
+            del f
+        o = ekf_oracle.make(kind, "as_written")
+        t0 = time.perf_counter()
+        for t in range(200):
+            o.observe([int(i) for i in s.ids[t]], s.poses[t])
+        cpu = sum(len(i) for i in s.ids[:200]) / (time.perf_counter() - t0)
+        out[kind] = {"value": s.n_updates / wall, "unit": UNIT, "us_per_frame": 1e6 * wall / s.n_frames,
+                     "frames": s.n_frames, "marker_updates": s.n_updates, "camera_finite": bool(np.isfinite(cam).all()),
+                     "cpu_port_value": cpu, "cpu_port_sample": "first 200 frames, oracle/ekf_oracle.py, 1 core",
+                     "e2e": {"value": s.n_updates / wall, "unit": UNIT,
+                             "h2d_bytes_per_step": 52 * s.n_updates // s.n_frames, "d2h_bytes_per_step": 8 * 10 * 11}}
+    return out
+
+
+def leg_batch(torch, dist, world, rank, local, stream_ptr, args, name, kind, seqs_total, markers, frames, p_vis,
+              fp64_peak, fp64_src, unique=64, full_upload=False):
+    """A batched workload next to the headline: `seqs_total` sequences IN TOTAL, sharded over the ranks
+    (no data-path collective), one step = every frame of every sequence from freshly constructed filters.
+    The host holds `unique` distinct streams (sequence s reads stream s % unique: 32768 x 64 x 1000 distinct
+    observations would be 25 GB); every sequence runs its own filter.  Time: CUDA events, max over ranks."""
+    from aruco_slam_b200 import FilterBatch, synth
+    n_seq = max(1, seqs_total // world)
+    u = min(unique, n_seq)
+    while n_seq % u:
+        u -= 1
+    ids, poses, off = synth.make_batch(u, markers, frames, p_vis, kind, seq_base=5000 + rank * u, unique=u)
+    rows, width, d = (3, 13, 3) if kind == "ekf" else (7, 20, 10)
+    n_state = 10 + d * markers
+    counts = np.diff(off).reshape(u, frames)
+    quat_mode = args.quat_mode if kind == "ekf" else "scalar_first"
+    b = FilterBatch(kind, n_seq, markers, markers, quat_mode=quat_mode, device=local)
+    b.set_stream(stream_ptr)
+    if full_upload:
+        ids_f, poses_f, off_f = synth.make_batch(n_seq, markers, frames, p_vis, kind, seq_base=5000 + rank * u, unique=u)
+        keep = [pinned_like(a) for a in (ids_f, poses_f, off_f)]
+        up = lambda: b.upload(keep[0][1], keep[1][1], keep[2][1])            # noqa: E731
+        h2d = ids_f.nbytes + poses_f.nbytes + off_f.nbytes
+    else:
+        keep = [pinned_like(a) for a in (ids, poses, off)]
+        up = lambda: b.upload(keep[0][1], keep[1][1], keep[2][1], n_streams=u)   # noqa: E731
+        h2d = ids.nbytes + poses.nbytes + off.nbytes
+    up()
+    b.run(0, min(10, frames))      # warm-up: every kernel of the path, same shapes
+    b.synchronize()
+    b.reset()
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_wall = time.perf_counter()
+    e0.record()
+    done = 0
+    while done < frames:
+        nxt = min(frames, done + 100)
+        b.run(done, nxt)
+        done = nxt
+        if done < frames:
+            b.synchronize()
+            # stop at a whole slice if the rest would not fit the leg's budget (reported as frames_run)
+            if (time.perf_counter() - t_wall) * (1.0 + 100.0 / done) > args.leg_budget_s:
+                break
+    e1.record()
+    torch.cuda.synchronize()
+    ms = float(e0.elapsed_time(e1))
+    cams, status = b.cameras()
+    rep = n_seq // u
+    upd = float(counts[:, :done].sum()) * rep
+    flops = float(sum(flops_batch_form(n_state, int(k), rows, width) * c
+                      for k, c in zip(*np.unique(counts[:, :done], return_counts=True)))) * rep
+    tot = torch.tensor([upd, flops], dtype=torch.float64, device="cuda")
+    mx = torch.tensor([ms, -float(done)], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(tot)
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+    upd_all, flops_all, ms_max, frames_min = float(tot[0]), float(tot[1]), float(mx[0]), int(-float(mx[1]))
+    tf = flops_all / (ms_max * 1e-3) / 1e12
+    leg = {"workload": name, "value": upd_all / (ms_max * 1e-3), "unit": UNIT, "n_gpus": world,
+           "sequences_total": n_seq * world, "sequences_per_gpu": n_seq, "markers": markers, "frames": frames,
+           "frames_run": frames_min, "p_visible": p_vis, "n_state": n_state, "engine": b.engine,
+           "filter": "EKF" if kind == "ekf" else "EKF_Rotations", "quat_mode": quat_mode, "ms_per_step": ms_max,
+           "distinct_streams_per_gpu": u, "scaling": "strong (total sequences fixed, sharded over the ranks)",
+           "roofline": {"bound": "fp64", "achieved": tf, "peak": fp64_peak * world, "unit": "TFLOP/s",
+                        "frac": tf / (fp64_peak * world), "traffic": None, "peak_source": fp64_src,
+                        "note": "algorithmic batch-form flops F(N,m,k) of SURVEY.md 8d / time against world x the "
+                                "FP64 peak measured live; the covariance update counts 2 N^2 m although the "
+                                "kernels compute its triangle (N^2 m)"},
+           "valid": bool(np.isfinite(cams).all() and not status.any())}
+    if done == frames and ms < 20e3:
+        # e2e through the public API: host buffers in, camera poses out, every step
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        up()
+        b.reset()
+        b.run(0, frames)
+        cams, status = b.cameras()
+        wall = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        if dist is not None:
+            dist.all_reduce(wall, op=dist.ReduceOp.MAX)
+        leg["e2e"] = {"value": upd_all / float(wall.item()), "unit": UNIT, "h2d_bytes_per_step": h2d,
+                      "d2h_bytes_per_step": cams.nbytes + status.nbytes,
+                      "note": "full-size host stream" if full_upload else
+                              f"host stream = the {u} distinct sequences (asb_batch_upload_tiled)"}
+    else:
+        leg["e2e"] = None
+    del b
+    return leg
+
 
 
 def run_b200(args):
@@ -375,18 +567,38 @@ def run_b200(args):
     fp64 = C.c_double()
     _lib.check(lib.asb_fp64_peak(local, 0, C.byref(fp64)))
     fp64_peak = fp64.value
+    _lib.check(lib.asb_fp64_peak(local, 1, C.byref(fp64)))
+    dmma_peak = fp64.value
+    fp64_src = ("asb_fp64_peak: dependent-free DFMA chains (FMA pipe) / mma.sync m8n8k4 f64 chains (DMMA) timed "
+                "live on this GPU with CUDA events — one shared FP64 pipe; MEASURED_PEAKS.json has no FP64 entry")
     # a non-default stream: the library launches on it and torch.cuda.Event times it
     side = torch.cuda.Stream()
     torch.cuda.set_stream(side)
     stream_ptr = torch.cuda.current_stream().cuda_stream
     assert stream_ptr != 0
 
+    def extra_leg(which):
+        if which == "c1":
+            return leg_c1(torch, stream_ptr)
+        if which == "c2rot":
+            return leg_batch(torch, dist, world, rank, local, stream_ptr, args,
+                             f"C2-ROT: {args.seqs} EKF_Rotations sequences x 32 markers x 1000 frames per GPU "
+                             f"(N = 330, BASELINE.json configs[1] secondary)", "rot", args.seqs * world, 32, 1000,
+                             0.5, max(fp64_peak, dmma_peak), fp64_src, full_upload=True)
+        if which in ("c5ekf", "c5rot"):
+            kind = "ekf" if which == "c5ekf" else "rot"
+            return leg_batch(torch, dist, world, rank, local, stream_ptr, args,
+                             f"C5-{kind.upper()}: {args.c5_seqs} sequences x 64 markers x 1000 frames in total, "
+                             f"p = 0.25 (BASELINE.json configs[4])", kind, args.c5_seqs, 64, 1000, 0.25,
+                             max(fp64_peak, dmma_peak), fp64_src)
+        if which == "c3s":
+            return leg_c3_sharded(torch, dist, rank, world, local, stream_ptr, hbm_peak)
+        if which == "c3":
+            return leg_c3(torch, stream_ptr, hbm_peak, dmma_peak)
+        return leg_c4(torch, stream_ptr, hbm_peak, fp64_peak)
+
     if args.only:
-        if args.only == "c3s":
-            leg = leg_c3_sharded(torch, dist, rank, world, local, stream_ptr, hbm_peak)
-        else:
-            leg = leg_c3(torch, stream_ptr, hbm_peak) if args.only == "c3" else \
-                leg_c4(torch, stream_ptr, hbm_peak, fp64_peak)
+        leg = extra_leg(args.only)
         if rank == 0:
             print(json.dumps(leg), flush=True)
         if dist is not None:
@@ -466,7 +678,7 @@ def run_b200(args):
         "gpu_launches": 2 * args.steps,
         "clocks": clk.summary(),
         "roofline": {"bound": "fp64", "achieved": ach_tf, "peak": fp64_peak, "unit": "TFLOP/s",
-                     "frac": ach_tf / fp64_peak, "traffic": None,
+                     "frac": ach_tf / fp64_peak, "traffic": None, "peak_source": fp64_src,
                      "note": "k_batch keeps each filter in shared memory; HBM traffic is the observation "
                              "stream only, so the FP64 FMA pipe bounds it. achieved = algorithmic "
                              "batch-form flops F(N,m,k) of SURVEY.md 8d / time; peak = DFMA peak measured "
@@ -476,25 +688,49 @@ def run_b200(args):
         "valid": ok, "marker_updates_per_step_per_gpu": n_updates, "gen_seconds": gen_s,
     }
     del batch
-    if world > 1 and not args.no_extras:
-        # the one configuration whose path has a real exchange step: C3 with its rows over all ranks
-        try:
-            leg = leg_c3_sharded(torch, dist, rank, world, local, stream_ptr, hbm_peak)
-        except Exception as exc:
-            leg = {"error": repr(exc)}
-        line["workloads"] = {"c3_sharded": leg}
+    del keep_i, keep_p, keep_o, h_ids, h_poses, h_off
+    if not args.no_extras:
+        line["workloads"] = {}
+        # batched legs that shard over the ranks (collective-free, every rank takes part)
+        names = ["c5ekf", "c5rot"] + (["c3s"] if world > 1 else ["c2rot"])
+        for which in names:
+            try:
+                leg = extra_leg(which)
+            except Exception as exc:  # keep the headline line even if an extra leg fails
+                leg = {"error": repr(exc)}
+            line["workloads"][{"c5ekf": "c5_ekf", "c5rot": "c5_rot", "c3s": "c3_sharded", "c2rot": "c2_rot"}[which]] = leg
     if rank == 0 and world == 1:
         if not args.no_extras:
-            line["workloads"] = {}
-            for name, leg in (("c3", lambda: leg_c3(torch, stream_ptr, hbm_peak)),
-                              ("c4", lambda: leg_c4(torch, stream_ptr, hbm_peak, fp64_peak))):
+            for name in ("c1", "c3", "c4"):
                 try:
-                    line["workloads"][name] = leg()
-                except Exception as exc:  # keep the headline line even if an extra leg fails
+                    line["workloads"][name] = extra_leg(name)
+                except Exception as exc:
                     line["workloads"][name] = {"error": repr(exc)}
-            # the HBM-bound kernel of the path (north_star's 70 % target) next to the headline roofline
+            # the HBM-side kernel of the path (north_star's 70 % target) next to the headline roofline
             if "roofline" in line["workloads"].get("c3", {}):
                 line["roofline_hbm_kernel"] = dict(line["workloads"]["c3"]["roofline"], kernel="k_sweep (C3 leg)")
+            # the same step on args.seqs DISTINCT sequences: the number must not move
+            try:
+                cores = max(1, min(os.cpu_count() or 1, 32))
+                ids_u, poses_u, off_u = synth.make_batch(args.seqs, args.markers, args.frames, args.p_visible, args.kind,
+                                                         seq_base=20000, unique=args.seqs, workers=cores)
+                bu = FilterBatch(args.kind, args.seqs, args.markers, args.markers, quat_mode=args.quat_mode, device=local)
+                bu.set_stream(stream_ptr)
+                bu.upload(ids_u, poses_u, off_u)
+                bu.run(0, args.frames)
+                bu.synchronize()
+
+                def step_u():
+                    bu.reset()
+                    bu.run(0, args.frames)
+                ms_u = timed(torch, None, step_u, 2) / 2
+                cu, su = bu.cameras()
+                line["value_unique"] = {"value": float(off_u[-1]) / (ms_u * 1e-3), "unit": UNIT, "ms_per_step": ms_u,
+                                        "distinct_streams": args.seqs, "steps": 2,
+                                        "valid": bool(np.isfinite(cu).all() and not su.any())}
+                del bu, ids_u, poses_u, off_u
+            except Exception as exc:
+                line["value_unique"] = {"error": repr(exc)}
         # bounded sample: whole sequences of the same workload on ONE core until the budget is spent
         frames = min(args.frames, 1000)
         total, wall_cpu, nseq_cpu = 0, 0.0, 0

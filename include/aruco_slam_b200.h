@@ -131,6 +131,15 @@ ASB_API int asb_set_landmarks(asb_filter* f, const int32_t* ids_in_index_order, 
  * kept up to date by the update kernels - asb_get_cov returns the full symmetric matrix). */
 ASB_API int asb_device_views(asb_filter* f, void** d_state, void** d_cov, int* ld);
 
+/* correct_poses (BASE:274-325, the orientation-ambiguity gate the reference defines and never calls; SURVEY 8f
+ * row 3), EKF_Rotations only: observation o is kept (choice[o] = 1) when the angle between R(q_cam) *
+ * from_euler('xyz', pose[3:6]) and the landmark's orientation in the state is below threshold_deg
+ * (QUAT_THRESHOLD = 50, BASE:32); unknown ids are dropped (0).  poses2_or_null: the second IPPE solution per
+ * observation (asb_ippe_square_both); it is tried when the first fails (choice 2) - an extension, NULL gives
+ * exactly the reference's function.  Waits for the updates queued on the handle (the state must be final). */
+ASB_API int asb_correct_poses(asb_filter* f, const int32_t* ids, const double* poses, const double* poses2_or_null,
+                      int k, double threshold_deg, int32_t* choice_out);
+
 /* Intermediates of the last update(), for parity tests (parse_poses EKF:158-200):
  * nu = z - h (m), blocks = per observation [r x 10 camera block | r x d landmark block]
  * row-major (k * r * (10+d)), dx = K nu (N).  Any pointer may be NULL. */
@@ -156,6 +165,12 @@ ASB_API int asb_batch_synchronize(asb_batch* b);
  * [offsets[s*n_frames+t], offsets[s*n_frames+t+1]) of ids / poses (HOST pointers). */
 ASB_API int asb_batch_upload(asb_batch* b, const int32_t* ids, const double* poses,
                      const int64_t* offsets, int n_frames);
+/* Same with n_streams < n_seq distinct observation streams (n_seq a multiple of n_streams): sequence s
+ * reads stream s % n_streams, offsets has n_streams*n_frames + 1 entries.  For large synthetic batches whose
+ * host copy would not fit (BASELINE configs[4]: 32768 sequences x 64 markers x 1000 frames = 25 GB of poses);
+ * every sequence still runs its own filter. */
+ASB_API int asb_batch_upload_tiled(asb_batch* b, const int32_t* ids, const double* poses,
+                           const int64_t* offsets, int n_frames, int n_streams);
 /* observe() for frames [t0,t1) of every sequence; id association on the device. */
 ASB_API int asb_batch_run(asb_batch* b, int t0, int t1);
 ASB_API int asb_batch_get_dims(asb_batch* b, int seq, int* n_landmarks, int* n_state);

@@ -204,6 +204,7 @@ def test_full_size_c3_single_steps(calibration):
 
 def test_api_errors_and_accessors(calibration):
     f = make_gpu("ekf", "as_written", calibration, 4)
+    f.growable = False   # fixed capacity: the C ABI's ASB_ERR_CAPACITY surfaces (growth is tested in test_gpu_dropin)
     with pytest.raises(KeyError):
         f.update([5], np.zeros((1, 6)))
     f.observe([7, 9], np.array([[0, 0, 2.0, 0, 0, 0], [0.5, 0, 3.0, 0, 0, 0]]))
