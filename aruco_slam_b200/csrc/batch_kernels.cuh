@@ -28,7 +28,7 @@ struct BatchParams {
     const double* poses;   // packed (.,6)
     const long long* offsets;  // n_seq * n_frames + 1
     long long state_stride, cov_stride;
-    int n_seq, n_frames, t0, t1, max_lm, max_obs, as_written, p_in_smem;
+    int n_seq, n_frames, t0, t1, max_lm, max_obs, as_written;
     int seq0, seq1;        // this launch handles sequences [seq0, seq1)
     int obs_seqs;          // distinct observation streams: sequence s reads stream s % obs_seqs (= n_seq unless tiled)
     Noise nz;
@@ -66,7 +66,7 @@ __device__ __forceinline__ double psym(const double* P, int i, int j) {
 template <int KIND, int CK, int NT>
 __global__ void __launch_bounds__(NT, (NT <= 128 && KIND == 0) ? 3 : 1)
 k_batch(BatchParams p) {
-    constexpr int D = Dims<KIND>::D, R = Dims<KIND>::R, W = CAM + D, NB = R;
+    constexpr int D = Dims<KIND>::D, R = Dims<KIND>::R, W = CAM + D;
     constexpr int MC = R * CK;           // max rows per chunk
     constexpr int LDS_S = (MC + 1) | 1;  // leading dim of S (+ appended nu row)
     extern __shared__ __align__(16) unsigned char smraw[];
@@ -109,25 +109,20 @@ k_batch(BatchParams p) {
         double* g_state = p.states + (long long)seq * p.state_stride;
         double* g_P = p.covs + (long long)seq * p.cov_stride;
         int* g_tab = p.lm_ids + (long long)seq * p.max_lm;
-        double* P = p.p_in_smem ? s_P : g_P;
-        const bool tiled = p.p_in_smem != 0;
+        double* P = s_P;   // the covariance lives in shared memory (filters that do not fit run on the wide engine)
         auto pget = [&](int i, int j) -> double {   // symmetric read
             const int a = max(i, j), b = min(i, j);
-            return P[tiled ? tidx(a, b) : tri(a) + b];
+            return P[tidx(a, b)];
         };
         auto pset = [&](int i, int j, double v) {   // i >= j; diagonal tiles hold both halves
-            if (tiled) {
-                P[tidx(i, j)] = v;
-                if ((i >> 3) == (j >> 3)) P[tchunk(tri(i >> 3) + (j >> 3), ((j & 7) << 2) + ((i & 7) >> 1)) + (i & 1)] = v;
-            } else {
-                P[tri(i) + j] = v;
-            }
+            P[tidx(i, j)] = v;
+            if ((i >> 3) == (j >> 3)) P[tchunk(tri(i >> 3) + (j >> 3), ((j & 7) << 2) + ((i & 7) >> 1)) + (i & 1)] = v;
         };
         int nlm = p.nlm[seq];
         int n = CAM + D * nlm;
         for (int i = tid; i < n; i += NT) s_state[i] = g_state[i];
         for (int i = tid; i < nlm; i += NT) s_tab[i] = g_tab[i];
-        if (p.p_in_smem) {
+        {
             for (int e = tid; e < tiled_doubles(ncap); e += NT) s_P[e] = 0.0;
             __syncthreads();
             for (int i = tid; i < n; i += NT)
@@ -238,7 +233,7 @@ k_batch(BatchParams p) {
                 // read once per column, then D landmark rows per observation
                 for (int j = tid; j < n; j += NT) {
                     double pc[CAM];
-                    if (tiled && j >= 8) {
+                    if (j >= 8) {
                         // P[j][0..9] = row j & 7 of tiles (j >> 3, 0) and (j >> 3, 1): five 16-byte chunks with
                         // one tile index instead of ten swizzled scalar accesses (diagonal tiles hold both halves)
                         const int t0 = tri(j >> 3), r4 = (j & 7) << 2;
@@ -316,7 +311,8 @@ k_batch(BatchParams p) {
                 __syncthreads();
                 BPROF(4);
                 bool bad = false;
-                if constexpr (MC + 1 <= 32) {
+                static_assert(MC + 1 <= 32, "the single-warp Cholesky holds one row of [S; nu^T] per lane");
+                {
                     // Cholesky of [S; nu^T] by ONE warp, lane i holding row i in registers; column j
                     // of L is broadcast with shuffles (no shared-memory round trips, no CTA barrier
                     // inside the factorisation)
@@ -351,66 +347,6 @@ k_batch(BatchParams p) {
                         eval_model(which ^ 1, c0 + CK, tid - 32);   // warps 1..: the next chunk's model, meanwhile
                     }
                     __syncthreads();
-                } else {
-                for (int o = tid; o < kc_next; o += NT) eval_model(which ^ 1, c0 + CK, o);
-                // blocked Cholesky, NB = rows per marker
-                for (int jb = 0; jb < mc; jb += NB) {
-                    double dblk[NB][NB], dinv[NB];
-#pragma unroll
-                    for (int r = 0; r < NB; ++r)
-#pragma unroll
-                        for (int c = 0; c <= r; ++c) dblk[r][c] = s_S[(jb + r) * LDS_S + jb + c];
-#pragma unroll
-                    for (int c = 0; c < NB; ++c) {
-                        double pv = dblk[c][c];
-#pragma unroll
-                        for (int q = 0; q < c; ++q) pv -= dblk[c][q] * dblk[c][q];
-                        if (!(pv > 0.0) || !(pv < 1e300)) bad = true;
-                        const double rs = rsqrt(pv);
-                        dinv[c] = rs;
-                        dblk[c][c] = pv * rs;
-#pragma unroll
-                        for (int r = c + 1; r < NB; ++r) {
-                            double v = dblk[r][c];
-#pragma unroll
-                            for (int q = 0; q < c; ++q) v -= dblk[r][q] * dblk[c][q];
-                            dblk[r][c] = v * rs;
-                        }
-                    }
-                    for (int i = jb + NB + tid; i <= mc; i += NT) {
-                        double x[NB];
-#pragma unroll
-                        for (int c = 0; c < NB; ++c) {
-                            double v = s_S[i * LDS_S + jb + c];
-#pragma unroll
-                            for (int q = 0; q < c; ++q) v -= x[q] * dblk[c][q];
-                            x[c] = v * dinv[c];
-                        }
-#pragma unroll
-                        for (int c = 0; c < NB; ++c) s_S[i * LDS_S + jb + c] = x[c];
-                    }
-#pragma unroll
-                    for (int r = 0; r < NB; ++r) {
-                        if (tid == r) {
-#pragma unroll
-                            for (int c = 0; c <= r; ++c) s_S[(jb + r) * LDS_S + jb + c] = dblk[r][c];
-                            s_dinv[jb + r] = dinv[r];
-                        }
-                    }
-                    __syncthreads();
-                    const int t0 = jb + NB, rem = mc - t0;
-                    if (rem > 0) {
-                        for (int e = tid; e < (rem + 1) * rem; e += NT) {
-                            const int i = t0 + e / rem, kk = t0 + e % rem;
-                            if (i < mc && kk > i) continue;
-                            double s = s_S[i * LDS_S + kk];
-#pragma unroll
-                            for (int c = 0; c < NB; ++c) s -= s_S[i * LDS_S + jb + c] * s_S[kk * LDS_S + jb + c];
-                            s_S[i * LDS_S + kk] = s;
-                        }
-                    }
-                    __syncthreads();
-                }
                 }
                 BPROF(5);
                 if (bad && tid == 0) s_misc[1] = ASB_ERR_NOT_SPD;
@@ -443,7 +379,7 @@ k_batch(BatchParams p) {
                 // blocks of the HBM path re-read V twice as often and were shared-memory-bound).
                 // [mma.sync m8n8k4 was tried: one warp issues a DMMA only every ~64 clocks, so
                 // with 4 warps per CTA it lost to the FMA pipe.]
-                if (tiled) {
+                {
                     const int nt8 = (n + 7) >> 3;
                     // (columns n..8 nt8 of the panel are zero: cleared once per frame, never written)
                     for (int task = tid; task < 2 * tri(nt8); task += NT) {
@@ -480,45 +416,6 @@ k_batch(BatchParams p) {
                             for (int q = 0; q < 4; ++q)
                                 *reinterpret_cast<double2*>(P + tchunk(tile, 4 * (4 * h + r) + q)) = make_double2(acc[r][2 * q], acc[r][2 * q + 1]);
                     }
-                } else {
-                    const int nb = (n + 3) >> 2;
-                    const int nblk = (nb * (nb + 1)) >> 1;
-                    for (int blk_id = tid; blk_id < nblk; blk_id += NT) {
-                        int bi = (int)((sqrtf(8.0f * blk_id + 1.0f) - 1.0f) * 0.5f);
-                        while (tri(bi + 1) <= blk_id) ++bi;
-                        while (tri(bi) > blk_id) --bi;
-                        const int bj = blk_id - tri(bi);
-                        const int i0 = 4 * bi, j0 = 4 * bj;
-                        double acc[4][4];
-#pragma unroll
-                        for (int r = 0; r < 4; ++r)
-#pragma unroll
-                            for (int c = 0; c < 4; ++c) acc[r][c] = 0.0;
-                        for (int a = 0; a < mc; ++a) {
-                            const double* g = s_G + a * npad;
-                            const double2 xa = *reinterpret_cast<const double2*>(g + gcol(i0));
-                            const double2 xb = *reinterpret_cast<const double2*>(g + gcol(i0) + 2);
-                            const double2 ya = *reinterpret_cast<const double2*>(g + gcol(j0));
-                            const double2 yb = *reinterpret_cast<const double2*>(g + gcol(j0) + 2);
-                            const double xs[4] = {xa.x, xa.y, xb.x, xb.y};
-                            const double ys[4] = {ya.x, ya.y, yb.x, yb.y};
-#pragma unroll
-                            for (int r = 0; r < 4; ++r)
-#pragma unroll
-                                for (int c = 0; c < 4; ++c) acc[r][c] += xs[r] * ys[c];
-                        }
-#pragma unroll
-                        for (int r = 0; r < 4; ++r) {
-                            const int i = i0 + r;
-                            if (i >= n) break;
-                            double* row = P + tri(i);
-#pragma unroll
-                            for (int c = 0; c < 4; ++c) {
-                                const int j = j0 + c;
-                                if (j <= i) row[j] -= acc[r][c];
-                            }
-                        }
-                    }
                 }
                 __syncthreads();
                 BPROF(8);
@@ -535,8 +432,7 @@ k_batch(BatchParams p) {
         // ---- write back -----------------------------------------------------------------
         for (int i = tid; i < n; i += NT) g_state[i] = s_state[i];
         for (int i = tid; i < nlm; i += NT) g_tab[i] = s_tab[i];
-        if (p.p_in_smem)
-            for (int i = tid; i < n; i += NT)
+        for (int i = tid; i < n; i += NT)
                 for (int j = 0; j <= i; ++j) g_P[tri(i) + j] = s_P[tidx(i, j)];
         if (tid == 0) {
             p.nlm[seq] = nlm;

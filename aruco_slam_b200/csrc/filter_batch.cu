@@ -30,7 +30,7 @@ struct asb_batch {
     int obs_seqs = 0;          // distinct observation streams on the device (n_seq, or fewer after an upload_tiled)
     long long n_obs = 0;
     int sm_count = 0, smem_optin = 0;
-    int ck = 4;       // markers per chunk (ASB_BATCH_CK)
+    int ck = 4;       // markers per chunk
     int threads = 128;
     // Pipelined host path: asb_batch_upload copies the observations in N_GROUPS sequence groups on a
     // copy stream; the asb_batch_run that follows launches one kernel per group as soon as that
@@ -93,7 +93,6 @@ static int launch_batch(asb_batch* b, const BatchParams& p, size_t smem, int gri
     ASB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, NT, smem));
     if (occ < 1) return fail(ASB_ERR_CAPACITY, "k_batch does not fit on an SM (%zu B shared memory)", smem);
     grid = std::min(grid, b->sm_count * occ);
-    if (std::getenv("ASB_BATCH_VERBOSE")) fprintf(stderr, "k_batch<%d,%d,%d>: %d CTAs/SM, grid %d, smem %zu\n", KIND, CK, NT, occ, grid, smem);
     kern<<<grid, NT, smem, st>>>(p);
     ASB_CUDA(cudaGetLastError());
     return ASB_OK;
@@ -106,15 +105,8 @@ static int launch_batch_nt(asb_batch* b, const BatchParams& p, size_t smem, int 
 }
 
 static int launch_batch_dyn(asb_batch* b, const BatchParams& p, size_t smem, int grid, cudaStream_t st) {
-#define ASB_DISPATCH(KIND)                                                     \
-    switch (b->ck) {                                                           \
-        case 2: return launch_batch_nt<KIND, 2>(b, p, smem, grid, st);         \
-        case 8: return launch_batch_nt<KIND, 8>(b, p, smem, grid, st);         \
-        default: return launch_batch_nt<KIND, 4>(b, p, smem, grid, st);        \
-    }
-    if (b->kind == ASB_KIND_EKF) { ASB_DISPATCH(0) }
-    ASB_DISPATCH(1)
-#undef ASB_DISPATCH
+    if (b->kind == ASB_KIND_EKF) return launch_batch_nt<0, 4>(b, p, smem, grid, st);
+    return launch_batch_nt<1, 4>(b, p, smem, grid, st);
 }
 
 // ---- wide engine, host side ------------------------------------------------------------------------
@@ -163,7 +155,6 @@ template <int KIND> static int wide_alloc_kind(asb_batch* b) {
     for (auto& st : b->w_streams) if (!st) ASB_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
     for (auto& e : b->w_done) if (!e) ASB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     b->w_groups = b->n_seq >= 1024 ? 2 : 1;
-    if (const char* e = std::getenv("ASB_WIDE_GROUPS")) b->w_groups = std::max(1, std::min(std::atoi(e), (int)asb_batch::W_MAX_GROUPS));
     ASB_CUDA(cudaMemset(b->w_meta, 0, ns * 8 * sizeof(int)));
     ASB_CUDA(cudaMemset(b->w_V, 0, ns * (size_t)b->w_vstride * sizeof(double)));
     return ASB_OK;
@@ -244,21 +235,9 @@ int asb_batch_reset(asb_batch* b) {
     return ASB_OK;
 }
 
-int asb_batch_create(int kind, int quat_mode, const double pose0[10], const asb_noise* cfg, int n_seq,
-                     int max_landmarks, int max_obs_per_frame, int device, asb_batch** out) {
-    if (!out) return fail(ASB_ERR_BAD_ARG, "out is NULL");
-    *out = nullptr;
-    if (kind != ASB_KIND_EKF && kind != ASB_KIND_ROT) return fail(ASB_ERR_BAD_ARG, "kind %d", kind);
-    if (quat_mode != ASB_QUAT_AS_WRITTEN && quat_mode != ASB_QUAT_SCALAR_FIRST)
-        return fail(ASB_ERR_BAD_ARG, "quat_mode %d", quat_mode);
-    if (n_seq < 1 || max_landmarks < 1 || max_obs_per_frame < 1) return fail(ASB_ERR_BAD_ARG, "bad sizes");
-    int ndev = 0;
-    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
-        return fail(ASB_ERR_CUDA, "no CUDA device: this library has no CPU fallback");
-    if (device < 0 || device >= ndev) return fail(ASB_ERR_BAD_ARG, "device %d of %d", device, ndev);
-    ASB_CUDA(cudaSetDevice(device));
-    asb_batch* b = new (std::nothrow) asb_batch();
-    if (!b) return fail(ASB_ERR_BAD_ARG, "out of host memory");
+// The part of asb_batch_create that can fail once the handle exists (the caller destroys the handle on error).
+static int batch_build(asb_batch* b, int kind, int quat_mode, const double pose0[10], const asb_noise* cfg, int n_seq,
+                       int max_landmarks, int max_obs_per_frame, int device) {
     b->kind = kind; b->quat_mode = quat_mode; b->device = device;
     b->D = kind == ASB_KIND_EKF ? 3 : 10;
     b->R = kind == ASB_KIND_EKF ? 3 : 7;
@@ -270,10 +249,7 @@ int asb_batch_create(int kind, int quat_mode, const double pose0[10], const asb_
     ASB_CUDA(cudaGetDeviceProperties(&prop, device));
     b->sm_count = prop.multiProcessorCount;
     b->smem_optin = (int)prop.sharedMemPerBlockOptin;
-    if (const char* e = std::getenv("ASB_BATCH_CK")) b->ck = std::atoi(e);
-    if (b->ck != 2 && b->ck != 4 && b->ck != 8) b->ck = 4;
-    if (const char* e = std::getenv("ASB_BATCH_THREADS")) b->threads = std::atoi(e);
-    else b->threads = b->ncap > 150 ? 256 : 128;
+    b->threads = b->ncap > 150 ? 256 : 128;
     ASB_CUDA(cudaStreamCreateWithFlags(&b->own_stream, cudaStreamNonBlocking));
     b->stream = b->own_stream;
     ASB_CUDA(cudaStreamCreateWithFlags(&b->copy_stream, cudaStreamNonBlocking));
@@ -283,7 +259,6 @@ int asb_batch_create(int kind, int quat_mode, const double pose0[10], const asb_
     ASB_CUDA(cudaEventCreateWithFlags(&b->ev_main, cudaEventDisableTiming));
     // a group must still fill the GPU a few times over (persistent grid: up to 3 CTAs per SM)
     b->groups = std::max(1, std::min((int)asb_batch::N_GROUPS, n_seq / (3 * b->sm_count)));
-    if (const char* e = std::getenv("ASB_BATCH_GROUPS")) b->groups = std::max(1, std::min(std::atoi(e), (int)asb_batch::N_GROUPS));
     ASB_CUDA(dmalloc(&b->d_states, (size_t)n_seq * b->state_stride));
     b->wide = !resident_fits(b);
     {
@@ -307,6 +282,30 @@ int asb_batch_create(int kind, int quat_mode, const double pose0[10], const asb_
         if (rc != ASB_OK) return rc;
     }
     ASB_CUDA(cudaStreamSynchronize(b->stream));
+    return ASB_OK;
+}
+
+int asb_batch_create(int kind, int quat_mode, const double pose0[10], const asb_noise* cfg, int n_seq,
+                     int max_landmarks, int max_obs_per_frame, int device, asb_batch** out) {
+    if (!out) return fail(ASB_ERR_BAD_ARG, "out is NULL");
+    *out = nullptr;
+    if (kind != ASB_KIND_EKF && kind != ASB_KIND_ROT) return fail(ASB_ERR_BAD_ARG, "kind %d", kind);
+    if (quat_mode != ASB_QUAT_AS_WRITTEN && quat_mode != ASB_QUAT_SCALAR_FIRST)
+        return fail(ASB_ERR_BAD_ARG, "quat_mode %d", quat_mode);
+    if (n_seq < 1 || max_landmarks < 1 || max_obs_per_frame < 1) return fail(ASB_ERR_BAD_ARG, "bad sizes");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(ASB_ERR_CUDA, "no CUDA device: this library has no CPU fallback");
+    if (device < 0 || device >= ndev) return fail(ASB_ERR_BAD_ARG, "device %d of %d", device, ndev);
+    ASB_CUDA(cudaSetDevice(device));
+    asb_batch* b = new (std::nothrow) asb_batch();
+    if (!b) return fail(ASB_ERR_BAD_ARG, "out of host memory");
+    const int rc = batch_build(b, kind, quat_mode, pose0, cfg, n_seq, max_landmarks, max_obs_per_frame, device);
+    if (rc != ASB_OK) {
+        asb_batch_destroy(b);
+        cudaGetLastError();
+        return rc;
+    }
     *out = b;
     return ASB_OK;
 }
@@ -461,8 +460,7 @@ int asb_batch_run(asb_batch* b, int t0, int t1) {
     p.prof = b->d_prof;
     const size_t base = batch_smem_base(b->D, b->R, b->ck, b->max_lm, b->max_obs);
     const size_t pbytes = (size_t)tiled_doubles(b->ncap) * sizeof(double);   // tile-blocked copy (batch_kernels.cuh)
-    p.p_in_smem = (base + pbytes <= (size_t)b->smem_optin) ? 1 : 0;
-    const size_t smem = base + (p.p_in_smem ? pbytes : 0);
+    const size_t smem = base + pbytes;
     if (smem > (size_t)b->smem_optin)
         return fail(ASB_ERR_CAPACITY, "batched filter needs %zu B shared memory > %d", smem, b->smem_optin);
     const int per_sm = std::max(1, std::min(8, (int)((size_t)(b->smem_optin + 1024) / (smem + 1024))));

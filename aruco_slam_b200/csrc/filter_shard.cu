@@ -129,7 +129,7 @@ struct asb_shard {
     unsigned int sweep_seq = 0;
     int tail_tiles = 2;
     int cur = 0;        // which of d_dx[2] holds the latest all-gathered dx
-    int overlap = 1;    // ASB_SHARD_OVERLAP=0: every chunk runs its front serially (no look-ahead)
+    int overlap = 1;    // look-ahead pipeline: the front of chunk i + 1 overlaps the sweep of chunk i
     int n_state() const { return CAM + D * nlm; }
 };
 
@@ -549,7 +549,6 @@ int asb_shard_create(int kind, int quat_mode, const double pose0[10], const asb_
     ASB_CUDA(cudaGetDeviceProperties(&prop, device));
     s->sm_count = prop.multiProcessorCount;
     s->smem_optin = (int)prop.sharedMemPerBlockOptin;
-    if (const char* e = std::getenv("ASB_SHARD_OVERLAP")) s->overlap = std::atoi(e);
     ncclUniqueId id;
     std::memcpy(&id, unique_id, sizeof id);
     ASB_NCCL(nc->CommInitRank(&s->comm, world, id, rank));
@@ -572,7 +571,6 @@ int asb_shard_create(int kind, int quat_mode, const double pose0[10], const asb_
     ASB_CUDA(dmalloc(&s->d_nu, (size_t)s->max_obs * s->R));
     ASB_CUDA(dmalloc(&s->d_status, (size_t)1));
     ASB_CUDA(dmalloc(&s->d_tail, (size_t)2));
-    if (const char* e = std::getenv("ASB_TAIL")) s->tail_tiles = std::atoi(e);
     ASB_CUDA(dmalloc(&s->d_idx, (size_t)SH_SLOTS * s->max_obs));
     ASB_CUDA(dmalloc(&s->d_pose, (size_t)SH_SLOTS * s->max_obs * 6));
     ASB_CUDA(dmalloc(&s->d_new, (size_t)SH_SLOTS * s->max_obs));

@@ -56,9 +56,11 @@ struct asb_filter {
     int* s_idx = nullptr; double* s_pose = nullptr; unsigned char* s_new = nullptr;
     std::vector<FrameRec> frames;
     int next_frame = 0;
-    int sweep_grid = 0, smem_optin = 0, force_big = 0, sweep_config = -1, front_dbg = 0;
+    // The resident stream bakes landmark indices against the map as it was at upload: every map mutation outside
+    // asb_stream_run bumps map_gen, and a run on a stale upload is refused (ASB_ERR_NO_STREAM).
+    unsigned long long map_gen = 0, stream_gen = 0;
+    int sweep_grid = 0, smem_optin = 0;
     // pipelined engine (pipe.cuh): covariance ping-pong pair, side stream for k_f1
-    int pipeline = 1;
     double *d_P2 = nullptr, *d_At = nullptr, *d_y = nullptr, *d_Vt = nullptr;
     int* d_T = nullptr;
     unsigned int* d_counter = nullptr;
@@ -161,24 +163,9 @@ static void launch_sweep(asb_filter* f, int n1, int m4, int dbg, const SweepExtr
         ex.n_static = std::max(0, ntiles / grid - f->tail_tiles);
         ++f->sweep_seq;
     };
-    if (config < 0) config = f->sweep_config;
     if (!pin) pin = f->d_P;
     if (!pout) pout = f->d_P;
-    if (config == 2) {  // warp-specialised variant: kept for experiments (slower than the dual-CTA kernel)
-        const int ntiles = ws::num_tiles(n1);
-        const int grid = std::min(ntiles, f->sweep_grid);
-        k_sweep_ws<<<grid, ws::THREADS, ws::smem_bytes(m4), f->stream>>>(f->d_P, f->ld, f->d_Vr, f->d_Vc, m4, ntiles, dbg, ex);
-        return;
-    }
-    if (config == 3) {   // three CTAs per SM (sweep.cuh SweepTri)
-        const int ntiles = SweepTri::num_tiles(n1);
-        const int grid = std::min(ntiles, 3 * f->sweep_grid - (spare_ctas ? 3 : 0));
-        schedule(ntiles, grid);
-        launch_k(k_sweep<SweepTri>, grid, SweepTri::THREADS, SweepTri::smem_bytes(m4), f->stream, pdl,
-                 pin, pout, f->ld, f->d_Vr, f->d_Vc, m4, ntiles, dbg, ex);
-        return;
-    }
-    const bool dual = config < 0 ? (2 * (SweepDual::smem_bytes(m4) + 1024) <= (size_t)f->smem_optin && !f->force_big)
+    const bool dual = config < 0 ? (2 * (SweepDual::smem_bytes(m4) + 1024) <= (size_t)f->smem_optin)
                                  : config == 1;
     if (dual) {
         const int ntiles = SweepDual::num_tiles(n1);
@@ -219,7 +206,7 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
     constexpr int R = Dims<KIND>::R, W = CAM + Dims<KIND>::D;
     cudaStream_t st = f->stream;
     const int ld = f->ld;
-    if (do_update && k > 0 && f->pipeline) {
+    if (do_update && k > 0) {
         // pipelined update (pipe.cuh): per chunk k_f1 on the side stream, k_f2 + k_sweep on the main one
         int cur = 0;
         for (int c0 = 0; c0 < k; c0 += f->kc_max) {
@@ -257,7 +244,7 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
             a.At = f->d_At; a.y = f->d_y; a.T = f->d_T;
             a.blocks_out = f->d_blocks + (size_t)c0 * R * W; a.nu_out = f->d_nu + (size_t)R * c0;
             a.status = f->d_status;
-            a.dbg = f->front_dbg;
+            a.dbg = 0;
             unsigned long long* prof = f->d_prof + 16 * f->prof_slot;
             f->prof_slot ^= 1;
             a.prof = prof;
@@ -315,41 +302,6 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
         int grid = (int)std::min<long long>(1 + work / 1024, 592);
         k_prep<KIND><<<grid, 256, 0, st>>>(f->d_state, f->d_P, ld, n0, n1, f->nz, idx, pose, isnew, k,
                                            do_predict ? 1 : 0);
-    } else {
-        // unpipelined update (ASB_PIPELINE=0): two launches per chunk of <= kc_max markers (k_front, k_sweep)
-        flush_pending(f, false);
-        f->lazy = false;
-        f->state_at_ready = false;
-        int cur = 0;
-        for (int c0 = 0; c0 < k; c0 += f->kc_max) {
-            const int kc = std::min(f->kc_max, k - c0);
-            const int m4 = round_up(R * kc, 4);
-            const bool first = c0 == 0, last = c0 + kc >= k;
-            FrontArgs a;
-            a.state = f->d_state; a.P = f->d_P; a.ld = ld;
-            a.n0 = first ? n0 : n1; a.n1 = n1; a.nz = f->nz;
-            a.idx = idx + c0; a.poses = pose + 6 * (size_t)c0; a.isnew = isnew ? isnew + c0 : nullptr;
-            a.kc = kc; a.m4 = m4;
-            a.first_chunk = first ? 1 : 0;
-            a.add_q = (first && do_predict) ? 1 : 0;
-            a.use_delta = first ? 0 : 1;
-            a.dx_in = f->d_dx[cur]; a.dx_out = f->d_dx[cur ^ 1];
-            a.Vr = f->d_Vr; a.Vc = f->d_Vc;
-            a.blocks_out = f->d_blocks + (size_t)c0 * R * W; a.nu_out = f->d_nu + (size_t)R * c0;
-            a.status = f->d_status;
-            a.prof = f->d_prof;
-            a.dbg = f->front_dbg;
-            const int nblk = 2 * ((n1 + 127) / 128);  // whole 128-row sweep tiles are covered
-            k_front<KIND><<<nblk, FRONT_THREADS, FrontSmem<KIND>::bytes(kc, m4), st>>>(a);
-            cur ^= 1;
-            SweepExtra ex{};
-            ex.n = n1; ex.add_q = a.add_q; ex.nz = f->nz;
-            ex.apply_kind = last ? KIND : -1;
-            ex.as_written = (KIND == 0 && f->quat_mode == ASB_QUAT_AS_WRITTEN) ? 1 : 0;
-            ex.nlm = (n1 - CAM) / Dims<KIND>::D; ex.state = f->d_state; ex.dx = f->d_dx[cur];
-            launch_sweep(f, n1, m4, 2 << 4, ex, -1, nullptr, nullptr, 0, false, true);  // dbg bits 4-5 = 2: P loads bypass L1 (.cg)
-        }
-        f->dx_last = f->d_dx[cur];
     }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(ASB_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(e));
@@ -460,21 +412,10 @@ __global__ void k_gate(const double* __restrict__ state, const int* __restrict__
 
 extern "C" {
 
-int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb_noise* cfg,
-                      int max_landmarks, int device, asb_filter** out) {
-    if (!out) return fail(ASB_ERR_BAD_ARG, "out is NULL");
-    *out = nullptr;
-    if (kind != ASB_KIND_EKF && kind != ASB_KIND_ROT) return fail(ASB_ERR_BAD_ARG, "kind %d", kind);
-    if (quat_mode != ASB_QUAT_AS_WRITTEN && quat_mode != ASB_QUAT_SCALAR_FIRST)
-        return fail(ASB_ERR_BAD_ARG, "quat_mode %d", quat_mode);
-    if (max_landmarks < 1) return fail(ASB_ERR_BAD_ARG, "max_landmarks %d", max_landmarks);
-    int ndev = 0;
-    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
-        return fail(ASB_ERR_CUDA, "no CUDA device: this library has no CPU fallback");
-    if (device < 0 || device >= ndev) return fail(ASB_ERR_BAD_ARG, "device %d of %d", device, ndev);
-    ASB_CUDA(cudaSetDevice(device));
-    asb_filter* f = new (std::nothrow) asb_filter();
-    if (!f) return fail(ASB_ERR_BAD_ARG, "out of host memory");
+// Everything of asb_filter_create that can fail after the handle exists; the caller destroys the handle on error,
+// so a failed cudaMalloc (e.g. the second 289 MB covariance buffer at C3 size) strands nothing.
+static int filter_build(asb_filter* f, int kind, int quat_mode, const double pose0[10], const asb_noise* cfg,
+                        int max_landmarks, int device) {
     f->kind = kind;
     f->quat_mode = quat_mode;
     f->device = device;
@@ -485,23 +426,18 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
     f->cap_lm = max_landmarks;
     f->ncap = CAM + f->D * max_landmarks;
     f->ld = round_up(f->ncap, PAD);
-    if (const char* e = std::getenv("ASB_LD_PAD")) f->ld += 16 * std::max(0, std::atoi(e));   // experiment: row stride vs DRAM channel mapping
     f->max_obs = std::max(64, std::min(max_landmarks * 2, 4096));
     f->kc_max = kind == ASB_KIND_EKF ? FrontLimits<0>::KC_MAX : FrontLimits<1>::KC_MAX;  // front.cuh
     cudaDeviceProp prop;
     ASB_CUDA(cudaGetDeviceProperties(&prop, device));
     f->sweep_grid = prop.multiProcessorCount;
     f->smem_optin = (int)prop.sharedMemPerBlockOptin;
-    if (const char* e = std::getenv("ASB_SWEEP_BIG")) f->force_big = std::atoi(e);
-    if (const char* e = std::getenv("ASB_FRONT_DBG")) f->front_dbg = std::atoi(e);  // experiments (front.cuh)
-    if (const char* e = std::getenv("ASB_SWEEP_CONFIG")) f->sweep_config = std::atoi(e);  // experiments: 0 / 1 / 2
-    if (const char* e = std::getenv("ASB_PIPELINE")) f->pipeline = std::atoi(e);          // 0: k_front + in-place sweep
     ASB_CUDA(cudaStreamCreateWithFlags(&f->own_stream, cudaStreamNonBlocking));
     f->stream = f->own_stream;
     const size_t ld = f->ld;
     ASB_CUDA(dmalloc(&f->d_state, ld));
     ASB_CUDA(dmalloc(&f->d_P, ld * ld));
-    if (f->pipeline) {
+    {
         ASB_CUDA(dmalloc(&f->d_P2, ld * ld));
         ASB_CUDA(cudaMemsetAsync(f->d_P2, 0, ld * ld * sizeof(double), f->stream));
         ASB_CUDA(cudaStreamCreateWithFlags(&f->side, cudaStreamNonBlocking));
@@ -514,10 +450,7 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
         ASB_CUDA(cudaMemsetAsync(f->d_Vt, 0, ld * F1_LDT * sizeof(double), f->stream));
         ASB_CUDA(dmalloc(&f->d_T, nt_max));
         ASB_CUDA(dmalloc(&f->d_counter, 1));
-        if (const char* e = std::getenv("ASB_SPARE")) f->spare_ctas = std::atoi(e);
-        if (const char* e = std::getenv("ASB_PDL")) f->pdl = std::atoi(e);
-        f->lower_only = std::getenv("ASB_FULL_P") ? 0 : 1;
-        if (const char* e = std::getenv("ASB_VT")) f->use_vt = std::atoi(e);
+        f->lower_only = 1;
         if (std::getenv("ASB_CTA_PROF")) {
             ASB_CUDA(dmalloc(&f->d_ctaprof, 3 * 1024));
             ASB_CUDA(cudaMemsetAsync(f->d_ctaprof, 0, 3 * 1024 * sizeof(unsigned long long), f->stream));
@@ -526,7 +459,6 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
     }
     ASB_CUDA(dmalloc(&f->d_tail, 2));
     ASB_CUDA(cudaMemsetAsync(f->d_tail, 0, 2 * sizeof(unsigned int), f->stream));
-    if (const char* e = std::getenv("ASB_TAIL")) f->tail_tiles = std::atoi(e);
     ASB_CUDA(dmalloc(&f->d_Vr, (size_t)M_MAX * V_LDB * (ld / V_BLK)));
     ASB_CUDA(dmalloc(&f->d_Vc, (size_t)M_MAX * V_LDB * (ld / V_BLK)));
     ASB_CUDA(cudaMemsetAsync(f->d_Vr, 0, (size_t)M_MAX * V_LDB * (ld / V_BLK) * sizeof(double), f->stream));
@@ -567,11 +499,6 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
     const int big = (int)prop.sharedMemPerBlockOptin - 2048;  // static smem (mbarriers) counts too
     ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepBig>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepDual>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
-    ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepTri>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
-    ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepTri>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    ASB_CUDA(cudaFuncSetAttribute(k_sweep_ws, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
-    ASB_CUDA(cudaFuncSetAttribute(k_front<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
-    ASB_CUDA(cudaFuncSetAttribute(k_front<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_f1<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_f1<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_f1<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
@@ -581,11 +508,9 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
     // One shared-memory carve-out (the maximum) for every kernel of the update: an SM only changes
     // its L1 / shared split when idle, so kernels that prefer different splits neither overlap
     // (k_f1 next to the sweep) nor follow each other without a drain.
-    if (!std::getenv("ASB_NO_CARVEOUT")) {
+    {
     ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepBig>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepDual>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    ASB_CUDA(cudaFuncSetAttribute(k_front<0>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    ASB_CUDA(cudaFuncSetAttribute(k_front<1>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     ASB_CUDA(cudaFuncSetAttribute(k_f1<0, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     ASB_CUDA(cudaFuncSetAttribute(k_f1<0, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     ASB_CUDA(cudaFuncSetAttribute(k_f1<1, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
@@ -594,6 +519,30 @@ int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb
     ASB_CUDA(cudaFuncSetAttribute(k_f2<1>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     ASB_CUDA(cudaFuncSetAttribute(k_prep<0>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     ASB_CUDA(cudaFuncSetAttribute(k_prep<1>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    }
+    return ASB_OK;
+}
+
+int asb_filter_create(int kind, int quat_mode, const double pose0[10], const asb_noise* cfg,
+                      int max_landmarks, int device, asb_filter** out) {
+    if (!out) return fail(ASB_ERR_BAD_ARG, "out is NULL");
+    *out = nullptr;
+    if (kind != ASB_KIND_EKF && kind != ASB_KIND_ROT) return fail(ASB_ERR_BAD_ARG, "kind %d", kind);
+    if (quat_mode != ASB_QUAT_AS_WRITTEN && quat_mode != ASB_QUAT_SCALAR_FIRST)
+        return fail(ASB_ERR_BAD_ARG, "quat_mode %d", quat_mode);
+    if (max_landmarks < 1) return fail(ASB_ERR_BAD_ARG, "max_landmarks %d", max_landmarks);
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(ASB_ERR_CUDA, "no CUDA device: this library has no CPU fallback");
+    if (device < 0 || device >= ndev) return fail(ASB_ERR_BAD_ARG, "device %d of %d", device, ndev);
+    ASB_CUDA(cudaSetDevice(device));
+    asb_filter* f = new (std::nothrow) asb_filter();
+    if (!f) return fail(ASB_ERR_BAD_ARG, "out of host memory");
+    const int rc = filter_build(f, kind, quat_mode, pose0, cfg, max_landmarks, device);
+    if (rc != ASB_OK) {
+        asb_filter_destroy(f);      // frees whatever was allocated (null members are skipped by the runtime)
+        cudaGetLastError();         // drop the error state the clean-up of null handles may have left
+        return rc;
     }
     *out = f;
     return ASB_OK;
@@ -657,6 +606,7 @@ static int observe_impl(asb_filter* f, const int32_t* ids, const double* poses, 
                 isnew[o] = 1;
                 f->map[ids[o]] = f->nlm++;
                 f->id_order.push_back(ids[o]);
+                ++f->map_gen;
             } else {
                 idx[o] = it->second;
             }
@@ -672,7 +622,7 @@ static int observe_impl(asb_filter* f, const int32_t* ids, const double* poses, 
     int* d_idx = nullptr; double* d_pose = nullptr; unsigned char* d_new = nullptr;
     if (k > 0) {
         // a pipelined update reads its observations in k_f1 on the side stream
-        const bool piped = f->pipeline != 0;
+        const bool piped = true;
         if (piped) pipe_wait(f);
         double* h_slot = nullptr;
         int rc = stage(f, idx, poses, isnew, k, &d_idx, &d_pose, &d_new, piped ? f->side : f->stream, feed, &h_slot);
@@ -728,6 +678,7 @@ int asb_add_marker(asb_filter* f, int32_t id, const double pose[6], const double
     std::vector<int> idx(1, f->nlm);
     std::vector<unsigned char> isnew(1, 1);
     f->map[id] = f->nlm++;  // dict assignment: a known id is re-bound (EKF:253)
+    ++f->map_gen;
     f->id_order.push_back(id);
     const int n1 = f->n_state();
     int* d_idx; double* d_pose; unsigned char* d_new;
@@ -759,12 +710,12 @@ int asb_stream_upload(asb_filter* f, const int32_t* ids, const double* poses, co
         FrameRec fr;
         fr.off = offsets[t];
         fr.k = (int)(offsets[t + 1] - offsets[t]);
-        if (fr.k > f->max_obs) return fail(ASB_ERR_CAPACITY, "frame %d: %d observations > %d", t, fr.k, f->max_obs);
+        if (fr.k > f->max_obs) { f->frames.clear(); return fail(ASB_ERR_CAPACITY, "frame %d: %d observations > %d", t, fr.k, f->max_obs); }
         fr.n0 = CAM + f->D * nlm;
         for (int64_t o = fr.off; o < fr.off + fr.k; ++o) {
             auto it = sim.find(ids[o]);
             if (it == sim.end()) {
-                if (nlm + 1 > f->cap_lm) return fail(ASB_ERR_CAPACITY, "stream needs > %d landmarks", f->cap_lm);
+                if (nlm + 1 > f->cap_lm) { f->frames.clear(); return fail(ASB_ERR_CAPACITY, "stream needs > %d landmarks", f->cap_lm); }
                 idx[o] = nlm;
                 isnew[o] = 1;
                 sim[ids[o]] = nlm++;
@@ -786,12 +737,15 @@ int asb_stream_upload(asb_filter* f, const int32_t* ids, const double* poses, co
     ASB_CUDA(cudaMemcpy(f->s_pose, poses, (size_t)total * 6 * sizeof(double), cudaMemcpyHostToDevice));
     ASB_CUDA(cudaMemcpy(f->s_new, isnew.data(), total, cudaMemcpyHostToDevice));
     f->next_frame = 0;
+    f->stream_gen = f->map_gen;
     return ASB_OK;
 }
 
 int asb_stream_run(asb_filter* f, int t0, int t1) {
     ASB_CHECK_HANDLE(f);
     if (f->frames.empty()) return fail(ASB_ERR_NO_STREAM, "stream_run before stream_upload");
+    if (f->stream_gen != f->map_gen)
+        return fail(ASB_ERR_NO_STREAM, "the landmark map changed since stream_upload (observe / add_marker / set_landmarks): upload again");
     if (t0 != f->next_frame || t1 < t0 || t1 > (int)f->frames.size())
         return fail(ASB_ERR_BAD_ARG, "frames must run in order: next is %d, got [%d,%d)", f->next_frame, t0, t1);
     f->defer = true;
@@ -908,6 +862,7 @@ int asb_set_landmarks(asb_filter* f, const int32_t* ids, int n) {
     f->map.clear();
     f->id_order.assign(ids, ids + n);
     for (int i = 0; i < n; ++i) f->map[ids[i]] = i;
+    ++f->map_gen;
     f->nlm = n;
     return ASB_OK;
 }
@@ -954,17 +909,15 @@ int asb_front_profile(asb_filter* f, double us[12]) {
     if (!us) return fail(ASB_ERR_BAD_ARG, "us is NULL");
     unsigned long long t[16];
     ASB_CUDA(cudaStreamSynchronize(f->stream));
-    ASB_CUDA(cudaMemcpy(t, f->d_prof + (f->pipeline ? 16 * (f->prof_slot ^ 1) : 0), sizeof t, cudaMemcpyDeviceToHost));
+    ASB_CUDA(cudaMemcpy(t, f->d_prof + 16 * (f->prof_slot ^ 1), sizeof t, cudaMemcpyDeviceToHost));
     for (int i = 0; i < 12; ++i) us[i] = 0.0;
-    if (f->pipeline) {
+    {
         // k_f1: [index set, issue copies, model + wait, lazy operand + Q + S, Cholesky, outputs]; k_f2: [loads, product, stores]
         for (int i = 0; i < 5; ++i) us[i] = 1e-3 * (double)(long long)(t[i + 1] - t[i]);
         for (int i = 0; i < 3; ++i) us[8 + i] = 1e-3 * (double)(long long)(t[9 + i] - t[8 + i]);
         us[5] = 1e-3 * (double)(long long)(t[5] - t[0]);    // k_f1 start -> end
         us[6] = 1e-3 * (double)(long long)(t[8] - t[0]);    // k_f1 start -> k_f2 start (same update)
         us[7] = 1e-3 * (double)(long long)(t[11] - t[0]);   // k_f1 start -> k_f2 end
-    } else {
-        for (int i = 0; i < 7; ++i) us[i] = 1e-3 * (double)(long long)(t[i + 1] - t[i]);
     }
     return ASB_OK;
 }

@@ -1,27 +1,7 @@
-// k_front: everything of one update chunk that precedes the covariance sweep, in ONE launch.
-//
-//   measurement model      nu = z - h, Jacobian blocks     (parse_poses / landmark_dh, EKF:158-237)
-//   new-landmark states    add_marker                      (EKF:264-274, ROT:300-319)
-//   covariance growth      P <- blockdiag(P, init_lm I)    (EKF:279-290)
-//   predict                P + diag(Q), applied ON THE FLY (EKF:95-105; the sweep writes it back)
-//   S = H P H^T + R = L L^T, y = L^-1 nu                   (EKF:124-129)
-//   V = L^-1 H P, dx (+)= V^T y  (= K nu)                  (EKF:130-131)
-//
-// Grid: one CTA per 64-column block of the V panel.  Every CTA redundantly evaluates the
-// model, gathers the |T| x |T| sub-matrix of P over the touched state indices T (camera
-// + observed landmarks), builds S from it and factors it — S does not depend on the full
-// G = H P, so nothing serialises on a single CTA and there is no inter-kernel hand-off of
-// L / y through HBM.  All HBM reads of the kernel (P[T,T] and the |T| rows of this block's
-// 64 columns) are issued up front as cp.async copies and fly while the model is evaluated.
-// The Cholesky runs on S with nu and the identity appended as extra rows, which yields
-// y = L^-1 nu and W^T = L^-T for free; V = W G is then a register-tiled product instead
-// of a serial substitution.  Each CTA writes its block of the tiled panel (sweep.cuh), dx.
-//
-// Hazards: the kernel never writes a location another CTA reads.  P entries in the rows /
-// columns being created by this frame's augmentation (index >= n0) are never read from
-// memory (their values are known constants); P + diag(Q) is formed in registers and only
-// written back by the sweep; the state is read-only here except for CTA 0 storing new
-// landmarks, which every CTA recomputes instead of reading; dx ping-pongs between buffers.
+// Shared pieces of the single-filter front end (pipe.cuh: k_f1 / k_f2): argument block, phase stamps,
+// chunk limits, cp.async helpers and the blocked Cholesky of [S; nu^T; I] whose appended rows yield
+// y = L^-1 nu and L^-1 (EKF:124-131).  (The one-kernel front end k_front that these were written for was
+// replaced by the pipelined pair and removed in round 2.)
 #pragma once
 #include "model.cuh"
 #include "sweep.cuh"
@@ -72,33 +52,6 @@ template <int KIND> struct FrontLimits;
 template <> struct FrontLimits<0> { static constexpr int KC_MAX = 21; };   // m = 63 (<= 8 column tiles, 16 row tiles)
 template <> struct FrontLimits<1> { static constexpr int KC_MAX = 8; };    // m = 56, 212 KB
 
-template <int KIND>
-struct FrontSmem {
-    static constexpr int D = Dims<KIND>::D, R = Dims<KIND>::R, W = CAM + D;
-    static __host__ __device__ size_t region1(int kc, int m4) {   // PT, later the G slice
-        const size_t nT = CAM + D * kc, pt = nT * nT;
-        (void)m4;
-        return (pt + 1) & ~(size_t)1;   // keep 16-byte alignment behind it
-    }
-    static __host__ __device__ size_t s_rows(int kc) {            // S with nu appended, padded to even
-        const size_t m = R * kc;
-        return (size_t)128 * (m | 1);   // rows 0..m: [S; nu^T], rows 64..127: G^T of the block
-    }
-    static __host__ __device__ size_t gt_rows(int kc) {           // GT = H PT, row stride nT|1
-        const size_t m = R * kc, nT = CAM + D * kc;
-        return (m * (nT | 1) + 1) & ~(size_t)1;
-    }
-    static __host__ __device__ size_t region3(int kc, int m4) {   // staged rows, later the V slice
-        (void)m4;
-        return (size_t)(CAM + D * kc) * V_BLK;
-    }
-    static __host__ __device__ size_t bytes(int kc, int m4) {
-        const int m = R * kc, nT = CAM + D * kc, lds = m | 1;
-        size_t dbl = region1(kc, m4) + s_rows(kc) + gt_rows(kc) + region3(kc, m4) + (size_t)kc * R * W +
-                     (size_t)kc * D + 2 * (size_t)m4 + 16;
-        return dbl * sizeof(double) + (size_t)(nT + 2 * kc + 8) * sizeof(int);
-    }
-};
 
 __device__ __forceinline__ void cp_async8(void* smem, const void* gmem) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(smem)), "l"(gmem) : "memory");
@@ -246,261 +199,6 @@ __device__ __forceinline__ bool front_cholesky(double* s_S, int lds, int m, int 
     }
     __syncthreads();
     return bad;
-}
-
-template <int KIND>
-__global__ void __launch_bounds__(FRONT_THREADS, 1)
-k_front(FrontArgs p) {
-    constexpr int D = Dims<KIND>::D, R = Dims<KIND>::R, W = CAM + D, NB = R;
-    constexpr int NT = FRONT_THREADS;
-    extern __shared__ __align__(16) unsigned char fsm[];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int kc = p.kc, m = R * kc, m4 = p.m4, nT = CAM + D * kc;
-    const int lds = m | 1;
-    const int ld = p.ld, n0 = p.n0, n1 = p.n1;
-    const int j0 = blockIdx.x * V_BLK;
-
-    // ---- shared memory carve-up ---------------------------------------------------------
-    double* s_PT = reinterpret_cast<double*>(fsm);                       // nT x nT (dense)
-    double* s_S = s_PT + FrontSmem<KIND>::region1(kc, m4);               // 128 x lds: [S; nu^T] and G^T at row 64
-    double* s_GT = s_S + FrontSmem<KIND>::s_rows(kc);                    // m x ldt
-    double* s_stage = s_GT + FrontSmem<KIND>::gt_rows(kc);                           // nT x 64: P_eff[T, this block's columns]
-    double* s_blk = s_stage + FrontSmem<KIND>::region3(kc, m4);          // kc x R x W
-    double* s_lm = s_blk + (size_t)kc * R * W;                           // kc x D
-    double* s_dinv = s_lm + (size_t)kc * D;                              // m4
-    double* s_y = s_dinv + m4;                                           // m4
-    double* s_cam = s_y + m4;                                            // 10 (+6 pad)
-    int* s_T = reinterpret_cast<int*>(s_cam + 16);                       // nT touched state indices
-    int* s_idx = s_T + nT;                                               // kc
-    int* s_new = s_idx + kc;                                             // kc
-
-    front_stamp(p, 0);
-    // ---- phase 0: touched index set T ------------------------------------------------------
-    if (tid < CAM) { s_cam[tid] = p.state[tid]; s_T[tid] = tid; }
-    for (int e = tid; e < D * kc; e += NT) {
-        const int o = e / D, c = e - o * D;
-        const int ix = p.idx[o];
-        s_T[CAM + e] = CAM + D * ix + c;
-        if (c == 0) { s_idx[o] = ix; s_new[o] = p.isnew ? p.isnew[o] : 0; }
-    }
-    __syncthreads();
-
-    // ---- phase 1: every HBM read of the kernel, asynchronously -----------------------------
-    // P entries in rows / columns >= n0 (this frame's augmentation) are known constants and
-    // are never read from memory.  diag(Q) is added after the copies land (phase 3).
-    for (int a = warp; a < nT; a += NT / 32) {
-        const int i = s_T[a];
-        const double* prow = p.P + (long long)i * ld;
-        for (int b = lane; b < nT; b += 32) {  // PT[a][b] = P[T[a]][T[b]]
-            const int j = s_T[b];
-            if (i < n0 && j < n0) cp_async8(s_PT + a * nT + b, prow + j);
-            else s_PT[a * nT + b] = (i == j) ? p.nz.init_lm : 0.0;
-        }
-        const int j = j0 + 2 * lane;          // stage[a][0..64) = P[T[a]][j0..j0+64)
-        double* dst = s_stage + a * V_BLK + 2 * lane;
-        if (i < n0 && j + 1 < n0) {
-            cp_async16(dst, prow + j);
-        } else {
-#pragma unroll
-            for (int q = 0; q < 2; ++q) {
-                if (i < n0 && j + q < n0) cp_async8(dst + q, prow + j + q);
-                else dst[q] = (i == j + q && i < n1) ? p.nz.init_lm : 0.0;
-            }
-        }
-    }
-    asm volatile("cp.async.commit_group;" ::: "memory");
-    front_stamp(p, 1);
-
-    // ---- phase 2 (while the copies fly): measurement model, 
-    for (int o = tid; o < kc; o += NT) {
-        double lm[D];
-        const int li = CAM + D * s_idx[o];
-        if (s_new[o]) {
-            new_landmark<KIND>(s_cam, p.poses + 6 * o, lm);
-            if (blockIdx.x == 0) {
-#pragma unroll
-                for (int c = 0; c < D; ++c) p.state[li + c] = lm[c];
-            }
-        } else {
-#pragma unroll
-            for (int c = 0; c < D; ++c) lm[c] = p.state[li + c];
-        }
-#pragma unroll
-        for (int c = 0; c < D; ++c) s_lm[o * D + c] = lm[c];
-    }
-    __syncthreads();
-    for (int o = tid; o < kc; o += NT) {
-        double lm[D];
-        int src = o;
-        if (!s_new[o])  // a repeated id whose landmark was created earlier in this same chunk
-            for (int o2 = 0; o2 < kc; ++o2)
-                if (s_new[o2] && s_idx[o2] == s_idx[o]) { src = o2; break; }
-#pragma unroll
-        for (int c = 0; c < D; ++c) lm[c] = s_lm[src * D + c];
-        double lnu[R], blk[R * W];
-        observation_model<KIND>(s_cam, lm, p.poses + 6 * o, lnu, blk);
-        if (blockIdx.x == 0 && p.nu_out) {
-#pragma unroll
-            for (int r = 0; r < R; ++r) p.nu_out[R * o + r] = lnu[r];
-#pragma unroll
-            for (int c = 0; c < R * W; ++c) p.blocks_out[(size_t)o * R * W + c] = blk[c];
-        }
-        if (p.use_delta) {  // chunked update: nu' = nu - H delta
-            const int li = CAM + D * s_idx[o];
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                double s = lnu[r];
-#pragma unroll
-                for (int c = 0; c < CAM; ++c) s -= blk[r * W + c] * p.dx_in[c];
-#pragma unroll
-                for (int c = 0; c < D; ++c) s -= blk[r * W + CAM + c] * p.dx_in[li + c];
-                lnu[r] = s;
-            }
-        }
-#pragma unroll
-        for (int r = 0; r < R; ++r) s_S[m * lds + R * o + r] = lnu[r];
-#pragma unroll
-        for (int c = 0; c < R * W; ++c) s_blk[o * R * W + c] = blk[c];
-    }
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-    __syncthreads();
-    front_stamp(p, 2);
-
-    // ---- phase 3: predict folded in — diag(Q) on the staged copies --------------------------
-    if (p.add_q) {
-        for (int a = tid; a < nT; a += NT) {
-            const int i = s_T[a];
-            const double q = process_noise(p.nz, i);
-            s_PT[a * nT + a] += q;
-            if (i >= j0 && i < j0 + V_BLK) s_stage[a * V_BLK + (i - j0)] += q;
-        }
-        for (int e = tid; e < kc * kc; e += NT) {   // a repeated id: the same state index twice in T
-            const int o1 = e / kc, o2 = e - o1 * kc;
-            if (o1 != o2 && s_idx[o1] == s_idx[o2]) {
-#pragma unroll
-                for (int c = 0; c < D; ++c)
-                    s_PT[(CAM + D * o1 + c) * nT + CAM + D * o2 + c] += p.nz.q_lm;
-            }
-        }
-        __syncthreads();
-    }
-
-    // ---- phase 4: S = H PT H^T + R in two small products with warp-uniform observations, so
-    //      the Jacobian block of the observation sits in registers and lanes read consecutive
-    //      columns (stage a) / rows (stage b) of shared memory.
-    const int ldt = nT | 1;
-    for (int o = warp; o < kc; o += NT / 32) {   // (a) GT[rows of o][tb] = H_o PT[T_o, tb]
-        double hb[R * W];
-#pragma unroll
-        for (int c = 0; c < R * W; ++c) hb[c] = s_blk[(size_t)o * R * W + c];
-        for (int tb = lane; tb < nT; tb += 32) {
-            double acc[R];
-#pragma unroll
-            for (int r = 0; r < R; ++r) acc[r] = 0.0;
-#pragma unroll
-            for (int c = 0; c < W; ++c) {
-                const double pv = s_PT[(c < CAM ? c : CAM + D * o + (c - CAM)) * nT + tb];
-#pragma unroll
-                for (int r = 0; r < R; ++r) acc[r] += hb[r * W + c] * pv;
-            }
-#pragma unroll
-            for (int r = 0; r < R; ++r) s_GT[(R * o + r) * ldt + tb] = acc[r];
-        }
-    }
-    __syncthreads();
-    for (int ob = warp; ob < kc; ob += NT / 32) {   // (b) S[a][rows of ob] = GT[a][T_ob] H_ob^T, a >= R ob
-        double hb[R * W];
-#pragma unroll
-        for (int c = 0; c < R * W; ++c) hb[c] = s_blk[(size_t)ob * R * W + c];
-        for (int a = R * ob + lane; a < m; a += 32) {
-            const double* g = s_GT + a * ldt;
-            double gv[W];
-#pragma unroll
-            for (int c = 0; c < W; ++c) gv[c] = g[c < CAM ? c : CAM + D * ob + (c - CAM)];
-#pragma unroll
-            for (int r2 = 0; r2 < R; ++r2) {
-                const int b = R * ob + r2;
-                double sv = (a == b) ? p.nz.r : 0.0;
-#pragma unroll
-                for (int c = 0; c < W; ++c) sv += gv[c] * hb[r2 * W + c];
-                if (b <= a) s_S[a * lds + b] = sv;
-            }
-        }
-    }
-    __syncthreads();
-    front_stamp(p, 3);
-
-    // ---- phase 5: G^T for this block's 64 columns (G = H P_eff[T, block]) appended to S as rows
-    //      GROW..GROW+63: the appended-row trick of the Cholesky below turns row GROW+jj into
-    //      (L^-1 G[:, jj])^T = V[:, jj]^T, so V needs no triangular solve of its own.
-    for (int e = tid; e < kc * V_BLK; e += NT) {
-        const int o = e / V_BLK, jj = e - o * V_BLK;
-        const double* blk = s_blk + (size_t)o * R * W;
-        const double* sl = s_stage + (size_t)(CAM + D * o) * V_BLK + jj;
-        double acc[R];
-#pragma unroll
-        for (int r = 0; r < R; ++r) acc[r] = 0.0;
-#pragma unroll
-        for (int c = 0; c < W; ++c) {
-            const double pv = c < CAM ? s_stage[c * V_BLK + jj] : sl[(c - CAM) * V_BLK];
-#pragma unroll
-            for (int r = 0; r < R; ++r) acc[r] += blk[r * W + c] * pv;
-        }
-#pragma unroll
-        for (int r = 0; r < R; ++r) s_S[(GROW + jj) * lds + R * o + r] = acc[r];
-    }
-    __syncthreads();
-    front_stamp(p, 4);
-
-    // ---- phase 6: Cholesky of [S; nu^T; G^T] (front_cholesky above)
-    const bool bad = front_cholesky<NB>(s_S, lds, m, p.dbg);
-    if (bad && blockIdx.x == 0 && tid == 0) atomicExch(p.status, ASB_ERR_NOT_SPD);
-    front_stamp(p, 5);
-    front_stamp(p, 6);
-    // dx (+)= V^T y, and this CTA's block of the tiled panel (sweep.cuh): m4 rows x V_LDB.
-    // V[a][jj] = s_S[(GROW + jj) * lds + a], y[a] = s_S[m * lds + a]
-    if (tid < V_BLK) {
-        double dsum = 0.0;
-        const double* vrow = s_S + (size_t)(GROW + tid) * lds;
-        const double* yrow = s_S + (size_t)m * lds;
-        for (int a = 0; a < m; ++a) dsum += vrow[a] * yrow[a];
-        const int j = j0 + tid;
-        if (j < n1) p.dx_out[j] = (p.use_delta ? p.dx_in[j] : 0.0) + dsum;
-    }
-    {
-        // both column orders of the block (sweep.cuh): position of column jj is v_pos_row / v_pos_col
-        double* vr = p.Vr + (size_t)blockIdx.x * m4 * V_LDB;
-        double* vc = p.Vc + (size_t)blockIdx.x * m4 * V_LDB;
-        for (int e = tid; e < m4 * V_BLK; e += NT) {
-            const int a = e / V_BLK, pos = e - a * V_BLK;
-            // inverse maps: which column lands at `pos`
-            const int cr = (pos & ~31) + 4 * (pos & 7) + ((pos & 31) >> 3);
-            const int cc = (pos & ~15) + 4 * ((pos & 7) >> 1) + 2 * ((pos & 15) >> 3) + (pos & 1);
-            vr[a * V_LDB + pos] = a < m ? s_S[(GROW + cr) * lds + a] : 0.0;   // rows m..m4: identity padding of L
-            vc[a * V_LDB + pos] = a < m ? s_S[(GROW + cc) * lds + a] : 0.0;
-        }
-    }
-
-    // ---- phase 8: covariance growth for this block's columns (first chunk only) ----------
-    if (p.first_chunk && n1 > n0) {
-        const int ja = j0, jb = min(j0 + V_BLK, n1);
-        if (ja < jb) {
-            const int wcols = jb - ja;  // new rows [n0, n1) x [ja, jb)
-            for (int e = tid; e < (n1 - n0) * wcols; e += NT) {
-                const int i = n0 + e / wcols, j = ja + e % wcols;
-                p.P[(long long)i * ld + j] = (i == j) ? p.nz.init_lm : 0.0;
-            }
-            const int jc = max(ja, n0);  // old rows [0, n0) x ([ja, jb) ∩ [n0, n1))
-            if (jc < jb) {
-                const int w2 = jb - jc;
-                for (int e = tid; e < n0 * w2; e += NT) {
-                    const int i = e / w2, j = jc + e % w2;
-                    p.P[(long long)i * ld + j] = 0.0;
-                }
-            }
-        }
-    }
-    front_stamp(p, 7);
 }
 
 }  // namespace asb

@@ -214,7 +214,6 @@ struct SweepCfg {
 };
 using SweepBig = SweepCfg<4, 2, 4, 4, 1>;    // 128 x 64 tile, 1 CTA / SM (large m4)
 using SweepDual = SweepCfg<2, 4, 4, 2, 2>;   // 64 x 64 tile, 2 CTAs / SM: one computes while the other drains
-using SweepTri = SweepCfg<2, 4, 4, 2, 3, true, 1>;   // 64 x 64 tile, 3 CTAs / SM (<= 85 registers, 2 panel buffers)
 
 // Persistent kernel.  Each CTA walks a contiguous chunk of the tile list (row-block major),
 // so the TI-column panel VI stays in shared memory while the TJ-column panel VJ is
@@ -494,249 +493,4 @@ k_sweep(const double* Pin, double* P, int ld, const double* __restrict__ Vr, con
 
 
 // =========================================================================================
-// k_sweep_ws: warp-specialised version of the sweep (default).  One CTA per SM, 16 warps:
-//   warps 0-7   MMA: 64 x 64 tile as 2 x 4 warps of 32 x 16 (4 x 2 DMMA tiles); they only ever
-//               wait on the V panels and on a free accumulator slot, so the FP64 tensor pipe
-//               is fed continuously; results (V_I^T V_J fragments) go to a per-warp slot in
-//               shared memory (two slots, 512-byte conflict-free rows)
-//   warps 8-15  epilogue: warp 8+w owns the same 32 x 16 sub-tile as MMA warp w: prefetches its
-//               P fragment of the NEXT tile into registers, then out = P (+ Q) - acc, direct
-//               store and mirror store
-//   (lane 0 of warp 8 is also the producer: TMA bulk copies of the V panels, VI and VJ both
-//   double-buffered, issued two tiles ahead)
-// Hand-off through mbarriers only (no CTA-wide barrier inside the tile loop).
-// =========================================================================================
-namespace ws {
-constexpr int TI = 64, TJ = 64, RM = 4, RN = 2, WN = 4;
-constexpr int MMA_WARPS = 8, THREADS = 2 * MMA_WARPS * 32;   // 512 threads: 128 registers each
-constexpr int ACC_SLOT_BYTES = RM * RN * 32 * 16;  // one warp's fragments: 8 x 512 B
-__host__ __device__ inline size_t smem_bytes(int m4) {
-    return (size_t)4 * m4 * V_LDB * sizeof(double) + (size_t)2 * MMA_WARPS * ACC_SLOT_BYTES;
-}
-__host__ __device__ inline int num_tiles(int n) {
-    const int nI = (n + TI - 1) / TI;
-    return nI * (nI + 1) / 2;
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void tile_of(int t, int& I, int& J) {  // t = I (I + 1) / 2 + J, J <= I
-    I = (int)((sqrt(8.0 * t + 1.0) - 1.0) * 0.5);
-    while ((I + 1) * (I + 2) / 2 <= t) ++I;
-    while (I * (I + 1) / 2 > t) --I;
-    J = t - I * (I + 1) / 2;
-}
-}  // namespace ws
-
-static __global__ void __launch_bounds__(ws::THREADS, 1)
-k_sweep_ws(double* __restrict__ P, int ld, const double* __restrict__ Vr, const double* __restrict__ Vc, int m4,
-           int ntiles, int dbg, SweepExtra ex) {
-    using namespace ws;
-    extern __shared__ __align__(128) unsigned char smraw[];
-    const int blk = m4 * V_LDB;                          // doubles per 64-column block of V
-    double* VIb = reinterpret_cast<double*>(smraw);      // 2 blocks
-    double* VJb = VIb + 2 * (size_t)blk;                 // 2 blocks
-    unsigned char* accb = reinterpret_cast<unsigned char*>(VJb + 2 * (size_t)blk);  // [2][8] slots
-    __shared__ __align__(8) uint64_t vi_full[2], vi_empty[2], vj_full[2], vj_empty[2];
-    __shared__ __align__(8) uint64_t acc_full[2][MMA_WARPS], acc_empty[2][MMA_WARPS];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int g = lane >> 2, t4 = lane & 3;
-
-    if (blockIdx.x == 0 && ex.apply_kind >= 0 && warp >= MMA_WARPS && warp < 2 * MMA_WARPS) {
-        // state update (k_apply folded in), done by the epilogue warps of CTA 0
-        const int et = tid - MMA_WARPS * 32, ent = MMA_WARPS * 32;
-        if (et == 0) {
-            double cam[CAM], d[CAM];
-#pragma unroll
-            for (int c = 0; c < CAM; ++c) { cam[c] = ex.state[c]; d[c] = ex.dx[c]; }
-            camera_reset(cam, d, ex.as_written);
-#pragma unroll
-            for (int c = 0; c < CAM; ++c) ex.state[c] = cam[c];
-        }
-        if (ex.apply_kind == 0) {
-            for (int e = et; e < 3 * ex.nlm; e += ent) ex.state[CAM + e] += ex.dx[CAM + e];
-        } else {
-            for (int t = et; t < ex.nlm; t += ent) {
-                double lm[10], d[10];
-#pragma unroll
-                for (int c = 0; c < 10; ++c) { lm[c] = ex.state[CAM + 10 * t + c]; d[c] = ex.dx[CAM + 10 * t + c]; }
-                landmark_update<1>(lm, d);
-#pragma unroll
-                for (int c = 0; c < 10; ++c) ex.state[CAM + 10 * t + c] = lm[c];
-            }
-        }
-    }
-    if (tid == 0) {
-        for (int b = 0; b < 2; ++b) {
-            mbar_init(&vi_full[b], 1); mbar_init(&vj_full[b], 1);
-            mbar_init(&vi_empty[b], MMA_WARPS); mbar_init(&vj_empty[b], MMA_WARPS);
-            for (int w = 0; w < MMA_WARPS; ++w) { mbar_init(&acc_full[b][w], 1); mbar_init(&acc_empty[b][w], 1); }
-        }
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncthreads();
-    const int t_begin = (int)((long long)ntiles * blockIdx.x / gridDim.x);
-    const int t_end = (int)((long long)ntiles * (blockIdx.x + 1) / gridDim.x);
-    if (t_begin >= t_end) return;
-    int I, J;
-    tile_of(t_begin, I, J);
-    const uint32_t blk_bytes = (uint32_t)(blk * sizeof(double));
-
-    if (warp < MMA_WARPS) {
-        // ---------------- MMA warps ----------------------------------------------------------
-        const int wi = warp / WN, wj = warp % WN;
-        int vi_n = 0, prevI = -1, vis = 0;
-        for (int t = t_begin, n = 0; t < t_end; ++t, ++n) {
-            if (I != prevI) {
-                vis = vi_n & 1;
-                mbar_wait(&vi_full[vis], (vi_n >> 1) & 1);
-                ++vi_n;
-                prevI = I;
-            }
-            const int s = n & 1;
-            mbar_wait(&vj_full[s], (n >> 1) & 1);
-            double acc[RM][RN][2];
-#pragma unroll
-            for (int rm = 0; rm < RM; ++rm)
-#pragma unroll
-                for (int rn = 0; rn < RN; ++rn) acc[rm][rn][0] = acc[rm][rn][1] = 0.0;
-            const double* va = VIb + (size_t)vis * blk + t4 * V_LDB + 32 * wi + g;
-            const double* vb = VJb + (size_t)s * blk + t4 * V_LDB + 16 * wj + g;
-#pragma unroll 3
-            for (int kk = 0; kk < ((dbg & 1) ? 4 : m4); kk += 4) {
-                double a[RM], b[RN];
-#pragma unroll
-                for (int r = 0; r < RM; ++r) a[r] = va[kk * V_LDB + 8 * r];
-#pragma unroll
-                for (int r = 0; r < RN; ++r) b[r] = vb[kk * V_LDB + 8 * r];
-#pragma unroll
-                for (int rm = 0; rm < RM; ++rm)
-#pragma unroll
-                    for (int rn = 0; rn < RN; ++rn) dmma884(acc[rm][rn][0], acc[rm][rn][1], a[rm], b[rn]);
-            }
-            int In = I, Jn = J + 1;
-            if (Jn > I) { In = I + 1; Jn = 0; }
-            __syncwarp();
-            if (lane == 0) {
-                mbar_arrive(&vj_empty[s]);
-                if (In != I) mbar_arrive(&vi_empty[vis]);
-            }
-            if (n >= 2) mbar_wait(&acc_empty[s][warp], ((n >> 1) - 1) & 1);
-            double2* slot = reinterpret_cast<double2*>(accb + ((size_t)s * MMA_WARPS + warp) * ACC_SLOT_BYTES) + lane;
-#pragma unroll
-            for (int rm = 0; rm < RM; ++rm)
-#pragma unroll
-                for (int rn = 0; rn < RN; ++rn) slot[(rm * RN + rn) * 32] = make_double2(acc[rm][rn][0], acc[rm][rn][1]);
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&acc_full[s][warp]);
-            I = In;
-            J = Jn;
-        }
-    } else {
-        // ---------------- epilogue warps ---------------------------------------------------
-        const int w = warp - MMA_WARPS, wi = w / WN, wj = w % WN;
-        auto load_p = [&](double (&pf)[RM][RN][2], int Ix, int Jx) {
-            if (dbg & 8) {
-#pragma unroll
-                for (int rm = 0; rm < RM; ++rm)
-#pragma unroll
-                    for (int rn = 0; rn < RN; ++rn) pf[rm][rn][0] = pf[rm][rn][1] = 0.0;
-            } else {
-                tile_load<RM, RN>(P + (long long)(Ix * TI + 32 * wi + 4 * g) * ld + Jx * TJ + 16 * wj + 4 * t4, ld, pf, (dbg >> 4) & 3);
-            }
-        };
-        // producer state (lane 0 of epilogue warp 0): cursor over this CTA's tile sequence
-        int qI = I, qJ = J, q = 0, vi_n = 0, prevI = -1;
-        const int nt = t_end - t_begin;
-        auto produce = [&]() {  // V panels of the q-th tile; its slots were released by tile q - 2
-            if (q >= nt) return;
-            if (qI != prevI) {
-                const int s = vi_n & 1;
-                if (vi_n >= 2) mbar_wait(&vi_empty[s], ((vi_n >> 1) - 1) & 1);
-                mbar_expect_tx(&vi_full[s], blk_bytes);
-                bulk_g2s(VIb + (size_t)s * blk, Vr + (size_t)qI * blk, blk_bytes, &vi_full[s]);
-                ++vi_n;
-                prevI = qI;
-            }
-            const int s = q & 1;
-            if (q >= 2) mbar_wait(&vj_empty[s], ((q >> 1) - 1) & 1);
-            mbar_expect_tx(&vj_full[s], blk_bytes);
-            bulk_g2s(VJb + (size_t)s * blk, Vc + (size_t)qJ * blk, blk_bytes, &vj_full[s]);
-            if (++qJ > qI) { ++qI; qJ = 0; }
-            ++q;
-        };
-        const bool is_producer = (w == 0 && lane == 0);
-        if (is_producer) { produce(); produce(); }
-        // L2 prefetch cursor, PD tiles ahead of the register prefetch: under load the HBM read
-        // latency (reads queue behind twice their volume of writes) exceeds one tile time, so
-        // the lines are pulled into L2 early and the 256-bit loads one tile ahead hit L2.
-        // Each lane prefetches one 128-byte line: row 32 wi + lane of its warp's sub-tile.
-        constexpr int PD = 3;
-        int fI = I, fJ = J, fq = 0;
-        auto l2_prefetch = [&]() {
-            if (fq < nt && !(dbg & 8)) {
-                const double* a = P + (long long)(fI * TI + 32 * wi + lane) * ld + fJ * TJ + 16 * wj;
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(a));
-            }
-            if (++fJ > fI) { ++fI; fJ = 0; }
-            ++fq;
-        };
-        if (!(dbg & 256))
-            for (int i = 0; i < PD + 1; ++i) l2_prefetch();
-        double pf[RM][RN][2], pn[RM][RN][2];
-        load_p(pf, I, J);
-        for (int t = t_begin, n = 0; t < t_end; ++t, ++n) {
-            int In = I, Jn = J + 1;
-            if (Jn > I) { In = I + 1; Jn = 0; }
-            if (t + 1 < t_end) load_p(pn, In, Jn);   // next tile's P flies during this tile's epilogue
-            if (!(dbg & 256)) l2_prefetch();
-            const int s = n & 1;
-            mbar_wait(&acc_full[s][w], (n >> 1) & 1);
-            if (is_producer) produce();              // tile n + 2: the MMA warps are done with tile n's panels
-            __syncwarp();
-            const double2* slot = reinterpret_cast<const double2*>(accb + ((size_t)s * MMA_WARPS + w) * ACC_SLOT_BYTES) + lane;
-            double2 ac[RM][RN];
-#pragma unroll
-            for (int rm = 0; rm < RM; ++rm)
-#pragma unroll
-                for (int rn = 0; rn < RN; ++rn) ac[rm][rn] = slot[(rm * RN + rn) * 32];
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&acc_empty[s][w]);
-            const int r0 = I * TI + 32 * wi + 4 * g, c0 = J * TJ + 16 * wj + 4 * t4;
-#pragma unroll
-            for (int rm = 0; rm < RM; ++rm)
-#pragma unroll
-                for (int rn = 0; rn < RN; ++rn) {
-                    pf[rm][rn][0] -= ac[rm][rn].x;
-                    pf[rm][rn][1] -= ac[rm][rn].y;
-                }
-            if (I != J) {  // strictly below the diagonal
-                if (!(dbg & 4)) tile_store<RM, RN>(P + (long long)r0 * ld + c0, ld, pf, (dbg >> 6) & 3);
-                if (!(dbg & 2)) tile_store_mirror<RM, RN>(P + (long long)c0 * ld + r0, ld, pf, (dbg >> 6) & 3);
-            } else {
-#pragma unroll
-                for (int rm = 0; rm < RM; ++rm)
-#pragma unroll
-                    for (int rn = 0; rn < RN; ++rn)
-#pragma unroll
-                        for (int e = 0; e < 2; ++e) {
-                            const int i = r0 + rm, j = c0 + 16 * (rn >> 1) + 2 * (rn & 1) + e;
-                            if (i >= j) {
-                                double o = pf[rm][rn][e];
-                                if (i == j && ex.add_q && i < ex.n) o += process_noise(ex.nz, i);
-                                P[(long long)i * ld + j] = o;
-                                if (i > j) P[(long long)j * ld + i] = o;
-                            }
-                        }
-            }
-#pragma unroll
-            for (int rm = 0; rm < RM; ++rm)
-#pragma unroll
-                for (int rn = 0; rn < RN; ++rn) { pf[rm][rn][0] = pn[rm][rn][0]; pf[rm][rn][1] = pn[rm][rn][1]; }
-            I = In;
-            J = Jn;
-        }
-    }
-}
-
 }  // namespace asb

@@ -256,3 +256,41 @@ def test_process_detections_fused_equals_separate_calls(calibration, kind):
         assert np.array_equal(cam_a, cam_b) and np.array_equal(lm_a, lm_b)
     assert order_of(a.landmarks) == order_of(b.landmarks)
     assert np.array_equal(a.uncertainty, b.uncertainty)
+
+
+def test_stream_run_refuses_a_stale_upload(calibration):
+    """asb_stream_upload bakes landmark indices against the map as it was: a map mutation in between
+    (observe / add_marker / set_landmarks) must be refused, not run on stale indices."""
+    from aruco_slam_b200 import synth
+    from aruco_slam_b200._lib import ERR_NO_STREAM, AsbError
+    s = synth.make_stream(5, 8, 10, 0.7, "ekf")
+    ids, poses, off = s.packed()
+    f = make_gpu("ekf", "scalar_first", calibration, 16)
+    f.stream_upload(ids, poses, off)
+    f.stream_run(0, 4)
+    f.observe([777], np.array([[0.1, 0.2, 3.0, 0, 0, 0]]))       # a new landmark outside the stream
+    with pytest.raises(AsbError) as err:
+        f.stream_run(4, 10)
+    assert err.value.code == ERR_NO_STREAM
+    f.stream_upload(ids, poses, off)                               # a fresh upload is accepted again
+    f.stream_run(0, 10)
+    assert np.isfinite(f.state).all()
+    # a failed upload (more landmarks than the capacity) leaves no half-built stream behind
+    g = make_gpu("ekf", "scalar_first", calibration, 4)
+    with pytest.raises(AsbError):
+        g.stream_upload(ids, poses, off)
+    with pytest.raises(AsbError) as err:
+        g.stream_run(0, 1)
+    assert err.value.code == ERR_NO_STREAM
+
+
+def test_sweep_kernel_configurations(calibration):
+    """asb_bench_sweep (measurement helper): both tile configurations of k_sweep launch and time."""
+    import ctypes as C
+    from aruco_slam_b200 import _lib
+    f = make_gpu("ekf", "scalar_first", calibration, 300)
+    f.set_landmarks(np.arange(300))
+    for cfg in (0, 1):
+        us = C.c_double()
+        _lib.check(_lib.lib().asb_bench_sweep(f._h, 60, cfg, 0, 3, C.byref(us)))
+        assert us.value > 0.0

@@ -16,8 +16,10 @@ KEYS = [
     "sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active",
     "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_elapsed",
     "sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active",
-    "sm__inst_executed_pipe_tensor_op_dmma.avg.pct_of_peak_sustained_active",
-    "sm__pipe_tensor_op_dmma_cycles_active.avg.pct_of_peak_sustained_active",
+    # FP64 tensor pipe (DMMA): sm__pipe_fp64_cycles_active does NOT count DMMA (it read 1.2 % for k_sweep in round 1)
+    "sm__pipe_tensor_subpipe_dmma_cycles_active.avg.pct_of_peak_sustained_active",
+    "sm__inst_executed_pipe_tensor_subpipe_dmma.avg.pct_of_peak_sustained_active",
+    "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed",
     "smsp__sass_thread_inst_executed_op_dfma_pred_on.sum", "smsp__sass_thread_inst_executed_op_dmul_pred_on.sum",
     "smsp__sass_thread_inst_executed_op_dadd_pred_on.sum", "smsp__inst_executed.sum",
     "sm__inst_executed_pipe_tensor.sum", "smsp__inst_executed_pipe_fp64.sum",
