@@ -86,6 +86,9 @@ SIGNATURES = {
     "asb_batch_get_state": (C.c_int, [_vp, C.c_int, _dp, C.c_int]),
     "asb_batch_get_cov": (C.c_int, [_vp, C.c_int, _dp, C.c_int]),
     "asb_batch_get_landmark_ids": (C.c_int, [_vp, C.c_int, _ip, C.c_int]),
+    "asb_batch_set_landmarks": (C.c_int, [_vp, C.c_int, _ip, C.c_int]),
+    "asb_batch_set_state": (C.c_int, [_vp, C.c_int, _dp, C.c_int]),
+    "asb_batch_set_cov": (C.c_int, [_vp, C.c_int, _dp, C.c_int]),
     "asb_batch_get_cameras": (C.c_int, [_vp, _dp, _ip]),
     "asb_batch_device_views": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp), _intp, _intp]),
     "asb_batch_profile": (C.c_int, [_vp, _dp]),

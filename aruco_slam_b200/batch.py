@@ -113,6 +113,16 @@ class FilterBatch:
         _lib.check(self._lib.asb_batch_get_cov(self._h, int(seq), _lib.dptr(out), n))
         return out
 
+    def load_checkpoint(self, seq: int, state, uncertainty, ids_in_index_order) -> None:
+        """Replace one sequence's filter (id map, state, covariance): checkpoint restore / per-frame
+        re-synchronisation in the parity tests, the batch counterpart of ``_CudaFilter.load_checkpoint``."""
+        ids = _lib.as_i32(ids_in_index_order)
+        st = _lib.as_f64(state).reshape(-1)
+        cov = _lib.as_f64(uncertainty)
+        _lib.check(self._lib.asb_batch_set_landmarks(self._h, int(seq), _lib.iptr(ids), ids.size))
+        _lib.check(self._lib.asb_batch_set_state(self._h, int(seq), _lib.dptr(st), st.size))
+        _lib.check(self._lib.asb_batch_set_cov(self._h, int(seq), _lib.dptr(cov), cov.shape[0]))
+
     def landmark_ids(self, seq: int) -> np.ndarray:
         nl, _ = self.dims(seq)
         out = np.empty(max(nl, 1), dtype=np.int32)

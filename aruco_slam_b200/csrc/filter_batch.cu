@@ -546,6 +546,53 @@ int asb_batch_get_cov(asb_batch* b, int seq, double* out, int n_state) {
     return seq_status(b, seq);
 }
 
+// ---- checkpoint / re-synchronisation setters (SURVEY 8c ii: the as-written EKF is compared one step at a time
+//      with the prior state copied from the oracle; the headline workload runs that mode) --------------------
+int asb_batch_set_landmarks(asb_batch* b, int seq, const int32_t* ids_in_index_order, int n) {
+    ASB_CHECK_BATCH(b);
+    if (seq < 0 || seq >= b->n_seq) return fail(ASB_ERR_BAD_ARG, "seq %d", seq);
+    if (n < 0 || n > b->max_lm || (n > 0 && !ids_in_index_order)) return fail(ASB_ERR_CAPACITY, "%d landmarks > max_landmarks %d", n, b->max_lm);
+    ASB_CUDA(cudaStreamSynchronize(b->stream));
+    if (n) ASB_CUDA(cudaMemcpy(b->d_tab + (size_t)seq * b->max_lm, ids_in_index_order, (size_t)n * sizeof(int), cudaMemcpyHostToDevice));
+    ASB_CUDA(cudaMemcpy(b->d_nlm + seq, &n, sizeof(int), cudaMemcpyHostToDevice));
+    const int zero = 0;
+    ASB_CUDA(cudaMemcpy(b->d_status + seq, &zero, sizeof(int), cudaMemcpyHostToDevice));
+    return ASB_OK;
+}
+
+int asb_batch_set_state(asb_batch* b, int seq, const double* in, int n_state) {
+    ASB_CHECK_BATCH(b);
+    int nlm, n;
+    int rc = asb_batch_get_dims(b, seq, &nlm, &n);
+    if (rc != ASB_OK) return rc;
+    if (!in || n_state != n) return fail(ASB_ERR_BAD_ARG, "n_state %d != %d", n_state, n);
+    ASB_CUDA(cudaMemcpy(b->d_states + (size_t)seq * b->state_stride, in, (size_t)n * sizeof(double), cudaMemcpyHostToDevice));
+    return ASB_OK;
+}
+
+int asb_batch_set_cov(asb_batch* b, int seq, const double* in, int n_state) {
+    ASB_CHECK_BATCH(b);
+    int nlm, n;
+    int rc = asb_batch_get_dims(b, seq, &nlm, &n);
+    if (rc != ASB_OK) return rc;
+    if (!in || n_state != n) return fail(ASB_ERR_BAD_ARG, "n_state %d != %d", n_state, n);
+    // dense row-major n x n (the lower triangle is taken) -> the engine's layout: packed lower triangle
+    // (resident) or 8 x 8 tiles with full diagonal tiles (wide); entries outside the live block stay zero
+    std::vector<double> buf((size_t)b->cov_stride, 0.0);
+    for (int i = 0; i < n; ++i)
+        for (int j = 0; j <= i; ++j) {
+            const double v = in[(size_t)i * n + j];
+            if (b->wide) {
+                buf[((size_t)(tri(i >> 3) + (j >> 3)) << 6) + ((i & 7) << 3) + (j & 7)] = v;
+                if ((i >> 3) == (j >> 3)) buf[((size_t)(tri(i >> 3) + (j >> 3)) << 6) + ((j & 7) << 3) + (i & 7)] = v;
+            } else {
+                buf[(size_t)tri(i) + j] = v;
+            }
+        }
+    ASB_CUDA(cudaMemcpy(b->d_covs + (size_t)seq * b->cov_stride, buf.data(), buf.size() * sizeof(double), cudaMemcpyHostToDevice));
+    return ASB_OK;
+}
+
 int asb_batch_get_landmark_ids(asb_batch* b, int seq, int32_t* ids, int capacity) {
     ASB_CHECK_BATCH(b);
     int nlm, n;

@@ -243,8 +243,10 @@ static int ippe_host(const float* corners, int64_t n, const double camera_matrix
     // (BaseFilter.estimate_pose_of_markers, a few dozen markers) must not pay cudaMalloc /
     // cudaFree round trips per frame.
     struct Cache { float* dc = nullptr; double* dout = nullptr; double* dout2 = nullptr; float* derr = nullptr; int64_t cap = 0;
-                   cudaStream_t st[2] = {nullptr, nullptr}; };
+                   cudaStream_t st[3] = {nullptr, nullptr, nullptr};
+                   cudaEvent_t ev_in[64] = {}, ev_k[64] = {}; };
     constexpr int64_t IPPE_CHUNK = 65536;
+    constexpr int IPPE_EVENTS = 64;
     static std::mutex mu;
     static Cache cache[64];
     std::lock_guard<std::mutex> lock(mu);
@@ -260,28 +262,36 @@ static int ippe_host(const float* corners, int64_t n, const double camera_matrix
         c.cap = cap;
     }
     if (n >= 4 * IPPE_CHUNK) {
-        // Large batches (BASELINE config C4, 1M sets = 32 MB in + 48 MB out): slices alternate between two
-        // streams, so the H2D copy of slice i+1, the kernel of slice i and the D2H copy of slice i-1 overlap
-        // (separate copy engines per direction).  One cudaMemcpyAsync per slice and buffer; with pageable
-        // host memory the copies stage through the driver and the overlap is partial.
+        // Large batches (BASELINE config C4, 1M sets = 32 MB in + 48 MB out) go in slices: the H2D copy of slice
+        // i+1, the kernel of slice i and the D2H copy of slice i-1 overlap (separate copy engines per direction).
+        // One cudaMemcpyAsync per slice and buffer; with pageable host memory the copies stage through the driver
+        // and the overlap is partial.
         if (!c.st[0]) {
-            ASB_CUDA(cudaStreamCreateWithFlags(&c.st[0], cudaStreamNonBlocking));
-            ASB_CUDA(cudaStreamCreateWithFlags(&c.st[1], cudaStreamNonBlocking));
+            for (auto& st : c.st) ASB_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+            for (auto& e : c.ev_in) ASB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            for (auto& e : c.ev_k) ASB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         }
+        // three streams: copy-in, kernels, copy-out.  With a copy and its kernel on ONE stream the H2D copy of
+        // slice i+2 queues behind the D2H copy of slice i and the two directions alternate instead of overlapping.
+        cudaStream_t s_in = c.st[0], s_k = c.st[1], s_out = c.st[2];
         int i = 0;
         for (int64_t o = 0; o < n; o += IPPE_CHUNK, ++i) {
             const int64_t cn = std::min<int64_t>(IPPE_CHUNK, n - o);
-            cudaStream_t st = c.st[i & 1];
-            ASB_CUDA(cudaMemcpyAsync(c.dc + 8 * o, corners + 8 * o, (size_t)cn * 8 * sizeof(float), cudaMemcpyHostToDevice, st));
+            const int e = i % IPPE_EVENTS;
+            ASB_CUDA(cudaMemcpyAsync(c.dc + 8 * o, corners + 8 * o, (size_t)cn * 8 * sizeof(float), cudaMemcpyHostToDevice, s_in));
+            ASB_CUDA(cudaEventRecord(c.ev_in[e], s_in));
+            ASB_CUDA(cudaStreamWaitEvent(s_k, c.ev_in[e], 0));
             int rc = asb_ippe_square_device(c.dc + 8 * o, cn, camera_matrix, dist_coeffs, marker_size, c.dout + 6 * o,
-                                            out2 ? c.dout2 + 6 * o : nullptr, errs ? c.derr + 2 * o : nullptr, st);
+                                            out2 ? c.dout2 + 6 * o : nullptr, errs ? c.derr + 2 * o : nullptr, s_k);
             if (rc != ASB_OK) return rc;
-            ASB_CUDA(cudaMemcpyAsync(out + 6 * o, c.dout + 6 * o, (size_t)cn * 6 * sizeof(double), cudaMemcpyDeviceToHost, st));
-            if (out2) ASB_CUDA(cudaMemcpyAsync(out2 + 6 * o, c.dout2 + 6 * o, (size_t)cn * 6 * sizeof(double), cudaMemcpyDeviceToHost, st));
-            if (errs) ASB_CUDA(cudaMemcpyAsync(errs + 2 * o, c.derr + 2 * o, (size_t)cn * 2 * sizeof(float), cudaMemcpyDeviceToHost, st));
+            ASB_CUDA(cudaEventRecord(c.ev_k[e], s_k));
+            ASB_CUDA(cudaStreamWaitEvent(s_out, c.ev_k[e], 0));
+            ASB_CUDA(cudaMemcpyAsync(out + 6 * o, c.dout + 6 * o, (size_t)cn * 6 * sizeof(double), cudaMemcpyDeviceToHost, s_out));
+            if (out2) ASB_CUDA(cudaMemcpyAsync(out2 + 6 * o, c.dout2 + 6 * o, (size_t)cn * 6 * sizeof(double), cudaMemcpyDeviceToHost, s_out));
+            if (errs) ASB_CUDA(cudaMemcpyAsync(errs + 2 * o, c.derr + 2 * o, (size_t)cn * 2 * sizeof(float), cudaMemcpyDeviceToHost, s_out));
         }
-        ASB_CUDA(cudaStreamSynchronize(c.st[0]));
-        ASB_CUDA(cudaStreamSynchronize(c.st[1]));
+        ASB_CUDA(cudaStreamSynchronize(s_out));   // every copy-out waits for its kernel, every kernel for its copy-in
+        ASB_CUDA(cudaStreamSynchronize(s_in));
         return ASB_OK;
     }
     ASB_CUDA(cudaMemcpy(c.dc, corners, (size_t)n * 8 * sizeof(float), cudaMemcpyHostToDevice));

@@ -177,6 +177,12 @@ ASB_API int asb_batch_get_dims(asb_batch* b, int seq, int* n_landmarks, int* n_s
 ASB_API int asb_batch_get_state(asb_batch* b, int seq, double* out, int n_state);
 ASB_API int asb_batch_get_cov(asb_batch* b, int seq, double* out, int n_state);
 ASB_API int asb_batch_get_landmark_ids(asb_batch* b, int seq, int32_t* ids_in_index_order, int capacity);
+/* Checkpoint / re-synchronisation of one sequence (the batch counterpart of asb_set_landmarks / _set_state / _set_cov;
+ * SURVEY 8c ii): landmarks first (sets the dimension), then state (n_state) and covariance (dense n x n, lower
+ * triangle taken).  Synchronous. */
+ASB_API int asb_batch_set_landmarks(asb_batch* b, int seq, const int32_t* ids_in_index_order, int n);
+ASB_API int asb_batch_set_state(asb_batch* b, int seq, const double* in, int n_state);
+ASB_API int asb_batch_set_cov(asb_batch* b, int seq, const double* in, int n_state);
 /* camera pose (10) of every sequence, (n_seq,10) row-major, + per-sequence status. */
 ASB_API int asb_batch_get_cameras(asb_batch* b, double* out, int32_t* status_or_null);
 ASB_API int asb_batch_device_views(asb_batch* b, void** d_states, void** d_covs, int* state_stride,

@@ -107,6 +107,35 @@ def test_batch_full_size_c2_properties():
                       o.uncertainty, TOL, floor=floor)
 
 
+@pytest.mark.parametrize("engine", ["resident", "wide"])
+def test_batch_as_written_resynchronised_every_frame(engine):
+    """SURVEY.md 8c(ii) for the batched engines (the headline C2 workload runs `as_written`): the as-written EKF
+    is chaotic, so every frame is compared one step at a time with (state, P, id map) of every sequence
+    re-synchronised from the oracle through asb_batch_set_landmarks / _set_state / _set_cov."""
+    from aruco_slam_b200 import FilterBatch, synth
+    n_seq, n_markers, n_frames = 3, 12, 120
+    streams = [synth.make_stream(90 + s, n_markers, n_frames, 0.7, "ekf") for s in range(n_seq)]
+    ids, poses, off = pack(streams, n_frames)
+    b = FilterBatch("ekf", n_seq, n_markers, n_markers, quat_mode="as_written", engine=engine)
+    b.upload(ids, poses, off)
+    oracles = [ekf_oracle.make("ekf", "as_written") for _ in range(n_seq)]
+    worst = 0.0
+    for t in range(n_frames):
+        if t > 0:
+            for s, o in enumerate(oracles):
+                order = [k for k, _ in sorted(o.landmarks.items(), key=lambda kv: kv[1])]
+                b.load_checkpoint(s, o.state, np.asarray(o.uncertainty), order)
+        b.run(t, t + 1)
+        for s, o in enumerate(oracles):
+            o.observe([int(i) for i in streams[s].ids[t]], streams[s].poses[t])
+            es, ep = rel_err(b.state(s), o.state), rel_err(b.uncertainty(s), o.uncertainty)
+            worst = max(worst, es, ep)
+            if t in (1, n_frames // 2, n_frames - 1) and s == 0:
+                assert_parity(f"batch {engine} as-written EKF re-synchronised, frame {t}", b.state(s), b.uncertainty(s),
+                              o.state, o.uncertainty, TOL)
+    assert worst < TOL, worst
+
+
 def test_batch_equals_single_filter(calibration):
     """The two engines are independent implementations of the same update."""
     from aruco_slam_b200 import EKF, FilterBatch, synth
