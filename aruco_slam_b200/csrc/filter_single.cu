@@ -82,7 +82,8 @@ struct asb_filter {
         const double* pin = nullptr;
         double* pout = nullptr;
     } pending;
-    unsigned int* d_tail = nullptr;   // two tile counters used alternately by successive sweeps (sweep.cuh)
+    unsigned int* d_tail = nullptr;   // [0,1] tile counters, [2,3] range counters, used alternately by successive sweeps (sweep.cuh)
+    int reserve_sm = -1, reserve_ctas = 2;   // per-frame mode: the SM kept free for k_f1 (the highest %smid seen at creation)
     unsigned int sweep_seq = 0;
     int tail_tiles = 2;        // tiles per CTA handed out dynamically (ASB_TAIL)
     int use_vt = 0;            // ASB_VT=1: k_f2 also writes the panel by state column for k_f1 (bulk copies instead of a gather)
@@ -150,17 +151,36 @@ static void launch_k(void (*kern)(KA...), int grid, int block, size_t smem, cuda
     cudaLaunchKernelEx(&cfg, kern, static_cast<KA>(args)...);
 }
 
+// highest %smid of the device (SM ids need not be 0 .. count-1): the SM the per-frame sweeps keep free
+__global__ void k_smid_probe(unsigned int* out) {
+    unsigned int sm;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
+    if (threadIdx.x == 0) atomicMax(out, sm);
+}
+
 static void launch_sweep(asb_filter* f, int n1, int m4, int dbg, const SweepExtra& ex_in, int config = -1,
                          const double* pin = nullptr, double* pout = nullptr, int spare_ctas = 0, bool pdl = false,
-                         bool dynamic_tail = false) {
+                         bool dynamic_tail = false, bool reserve = false) {
     SweepExtra ex = ex_in;
+    ex.reserve_sm = -1;
     // hybrid tile schedule (sweep.cuh): all but the last tail_tiles tiles of a CTA's share are a
     // contiguous range, the rest are handed out one at a time
     auto schedule = [&](int ntiles, int grid) {
         if (!dynamic_tail || f->tail_tiles <= 0 || !f->d_tail) return;
         ex.tail = f->d_tail + (f->sweep_seq & 1);
         ex.tail_reset = f->d_tail + ((f->sweep_seq + 1) & 1);
-        ex.n_static = std::max(0, ntiles / grid - f->tail_tiles);
+        int ranges = grid;
+        // only when the sweep fills the GPU: a small grid leaves SMs free anyway, and its few CTAs must not retire
+        if (reserve && f->reserve_sm >= 0 && grid >= 2 * f->sweep_grid) {
+            // per-frame mode: the CTAs that land on SM reserve_sm retire (k_f1 of the next frame gets that SM);
+            // the other CTAs claim the static ranges from a counter (sweep.cuh)
+            ex.reserve_sm = f->reserve_sm;
+            ex.range_ctr = f->d_tail + 2 + (f->sweep_seq & 1);
+            ex.range_reset = f->d_tail + 2 + ((f->sweep_seq + 1) & 1);
+            ranges = std::max(1, grid - f->reserve_ctas);
+            ex.n_ranges = ranges;
+        }
+        ex.n_static = std::max(0, ntiles / ranges - f->tail_tiles);
         ++f->sweep_seq;
     };
     if (!pin) pin = f->d_P;
@@ -169,7 +189,7 @@ static void launch_sweep(asb_filter* f, int n1, int m4, int dbg, const SweepExtr
                                  : config == 1;
     if (dual) {
         const int ntiles = SweepDual::num_tiles(n1);
-        const int grid = std::min(ntiles, 2 * f->sweep_grid - spare_ctas);
+        const int grid = std::min(ntiles, 2 * f->sweep_grid - ((reserve && f->reserve_sm >= 0) ? 0 : spare_ctas));
         schedule(ntiles, grid);
         launch_k(k_sweep<SweepDual>, grid, SweepDual::THREADS, SweepDual::smem_bytes(m4), f->stream, pdl,
                  pin, pout, f->ld, f->d_Vr, f->d_Vc, m4, ntiles, dbg, ex);
@@ -252,7 +272,9 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
                 launch_k(k_f1<KIND, true>, 1, FRONT_THREADS, (size_t)f->smem_optin - 2048, st, true, a);
                 flush_pending(f, true);
             } else {
-                k_f1<KIND, false><<<1, FRONT_THREADS, F1Smem<KIND>::bytes(kc, m4), f->side>>>(a);
+                // the sweep of the previous frame (if one is running) keeps SM reserve_sm free: the exclusive
+                // variant asks for a whole SM's shared memory, so that is where it lands
+                k_f1<KIND, true><<<1, FRONT_THREADS, (size_t)f->smem_optin - 2048, f->side>>>(a);
                 cudaEventRecord(f->ev_f1, f->side);
                 cudaStreamWaitEvent(st, f->ev_f1, 0);
             }
@@ -286,7 +308,7 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
             } else {
                 // contiguous tile ranges here: with the dynamic tail the lone sweep CTA next to k_f1 would
                 // take MORE tiles and slow k_f1 (the critical kernel of this mode) further
-                launch_sweep(f, n1, m4, 2 << 4, ex, -1, f->d_P, f->d_P2, f->spare_ctas, false, false);
+                launch_sweep(f, n1, m4, 2 << 4, ex, -1, f->d_P, f->d_P2, f->spare_ctas, false, true, true);
             }
             std::swap(f->d_P, f->d_P2);
             f->lazy = true; f->prev_m4 = m4; f->prev_add_q = a.add_q;
@@ -457,8 +479,16 @@ static int filter_build(asb_filter* f, int kind, int quat_mode, const double pos
         }
         ASB_CUDA(cudaMemsetAsync(f->d_counter, 0, sizeof(unsigned int), f->stream));
     }
-    ASB_CUDA(dmalloc(&f->d_tail, 2));
-    ASB_CUDA(cudaMemsetAsync(f->d_tail, 0, 2 * sizeof(unsigned int), f->stream));
+    ASB_CUDA(dmalloc(&f->d_tail, 8));
+    ASB_CUDA(cudaMemsetAsync(f->d_tail, 0, 8 * sizeof(unsigned int), f->stream));
+    k_smid_probe<<<4 * f->sweep_grid, 32, 0, f->stream>>>(f->d_tail + 4);   // d_tail[4] = highest %smid
+    ASB_CUDA(cudaGetLastError());
+    {
+        unsigned int top = 0;
+        ASB_CUDA(cudaMemcpyAsync(&top, f->d_tail + 4, sizeof top, cudaMemcpyDeviceToHost, f->stream));
+        ASB_CUDA(cudaStreamSynchronize(f->stream));
+        f->reserve_sm = (int)top;
+    }
     ASB_CUDA(dmalloc(&f->d_Vr, (size_t)M_MAX * V_LDB * (ld / V_BLK)));
     ASB_CUDA(dmalloc(&f->d_Vc, (size_t)M_MAX * V_LDB * (ld / V_BLK)));
     ASB_CUDA(cudaMemsetAsync(f->d_Vr, 0, (size_t)M_MAX * V_LDB * (ld / V_BLK) * sizeof(double), f->stream));

@@ -48,6 +48,14 @@ struct SweepExtra {
     // instead of 12 N^2 bytes of DRAM traffic per sweep.  The readers of the pipelined engine
     // (k_f1, k_f2, asb_get_cov) take P[i][j], i < j, from P[j][i].
     int lower_only;
+    // reserve_sm >= 0 (per-frame observe(), filter_single.cu): CTAs that land on that SM retire at once, so the SM
+    // stays free for k_f1 of the NEXT frame, which then has an FP64 pipe to itself instead of sharing one with a
+    // sweep CTA.  The static ranges are then not tied to blockIdx: a live CTA claims range after range from
+    // *range_ctr (n_ranges of them) until none is left, then joins the dynamic tail - correct for any number of
+    // live CTAs.
+    int reserve_sm, n_ranges;
+    unsigned int* range_ctr;   // zero on entry
+    unsigned int* range_reset; // the NEXT launch's range counter: zeroed by CTA 0
     unsigned int* tail;        // counter of this launch (zero on entry)
     unsigned int* tail_reset;  // counter of the NEXT launch: zeroed by CTA 0
     int n_static;
@@ -259,20 +267,33 @@ k_sweep(const double* Pin, double* P, int ld, const double* __restrict__ Vr, con
     // instead of spreading over the GPU (measured: k_f2 11 -> 15 us).
     if (blockIdx.x == 0 && ex.apply_kind >= 0)   // state update (k_apply folded in)
         apply_state(ex.state, ex.dx, ex.apply_kind, ex.as_written, ex.nlm, tid, C::THREADS);
+    const bool dyn = ex.tail != nullptr;
+    const bool reserve = dyn && ex.reserve_sm >= 0;
+    if (dyn && blockIdx.x == 0 && tid == 0) {
+        *ex.tail_reset = 0u;
+        if (reserve) *ex.range_reset = 0u;
+    }
+    if (reserve) {
+        unsigned int sm;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
+        if ((int)sm == ex.reserve_sm) { pdl_trigger(); pdl_wait(); return; }   // the whole CTA: %smid is CTA-uniform
+    }
     if (tid == 0) {
         mbar_init(&bar[0], 1);
         mbar_init(&bar[1], 1);
         mbar_init(&bar[2], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    __shared__ int s_next[2], s_nij[2], s_range;
+    if (reserve && tid == 0) s_range = (int)atomicAdd(ex.range_ctr, 1u);
     __syncthreads();
-    __shared__ int s_next[2], s_nij[2];
-    const bool dyn = ex.tail != nullptr;
-    const int t_begin = dyn ? (int)blockIdx.x * ex.n_static : (int)((long long)ntiles * blockIdx.x / gridDim.x);
-    const int t_end = dyn ? t_begin + ex.n_static : (int)((long long)ntiles * (blockIdx.x + 1) / gridDim.x);
-    const int dyn_base = (int)gridDim.x * ex.n_static;
+    // virtual block index: blockIdx, or the claimed range in reserve mode (>= n_ranges: no static range)
+    int vb = reserve ? s_range : (int)blockIdx.x;
+    const int nvb = reserve ? ex.n_ranges : (int)gridDim.x;
+    int t_begin = dyn ? (vb < nvb ? vb * ex.n_static : 0) : (int)((long long)ntiles * blockIdx.x / gridDim.x);
+    int t_end = dyn ? (vb < nvb ? t_begin + ex.n_static : 0) : (int)((long long)ntiles * (blockIdx.x + 1) / gridDim.x);
+    const int dyn_base = nvb * ex.n_static;
     const bool rev = ex.reverse != 0;
-    if (dyn && blockIdx.x == 0 && tid == 0) *ex.tail_reset = 0u;
     if (t_begin >= t_end && !dyn) { pdl_trigger(); pdl_wait(); return; }
     const int pol_ld = ex.pol ? (ex.pol & 7) : ((dbg >> 4) & 3);
     const int pol_st = ex.pol ? ((ex.pol >> 3) & 7) : ((dbg >> 6) & 3);
@@ -423,7 +444,8 @@ k_sweep(const double* Pin, double* P, int ld, const double* __restrict__ Vr, con
 
     int buf = 0;
     int Ivi = -1;   // row block whose VI panel is (being) loaded
-    if (t_begin < t_end) {
+    bool drew = false;   // the first tail tile has been drawn (by the last tile of a static range)
+    while (t_begin < t_end) {
         // ---- contiguous range: tile indices follow arithmetically, everything stays warp-uniform ----
         const int t_first = rev ? t_end - 1 : t_begin;
         int I = (int)((sqrt(8.0 * t_first / C::RATIO + 1.0) - 1.0) * 0.5);
@@ -436,8 +458,9 @@ k_sweep(const double* Pin, double* P, int ld, const double* __restrict__ Vr, con
         }
         if (tid == 0) {
             load_vi(I * TI);
-            load_vj(0, J * TJ);
+            load_vj(buf, J * TJ);
         }
+        vi_pending = true;
         for (int t = t_begin; t < t_end; ++t, buf ^= 1) {
             int In = I, Jn = rev ? J - 1 : J + 1;
             if (rev) {
@@ -445,7 +468,8 @@ k_sweep(const double* Pin, double* P, int ld, const double* __restrict__ Vr, con
             } else if (Jn == (ex.rect ? ex.nJ : C::RATIO * (I + 1))) { In = I + 1; Jn = 0; }
             const bool has_next = t + 1 < t_end;
             if (C::NBUF == 2 && tid == 0 && has_next) load_vj(buf ^ 1, Jn * TJ);  // buffer freed by the last __syncthreads
-            do_tile(I, J, buf, (!has_next && dyn) ? 0 : -1, has_next ? Jn * TJ : -1);
+            do_tile(I, J, buf, (!has_next && dyn && !reserve) ? 0 : -1, has_next ? Jn * TJ : -1);
+            if (!has_next && dyn && !reserve) drew = true;
             __syncthreads();  // every warp is done with VJ[buf] (and VI) before they are overwritten
             Ivi = I;
             if (has_next && In != I) {
@@ -456,9 +480,19 @@ k_sweep(const double* Pin, double* P, int ld, const double* __restrict__ Vr, con
             I = In;
             J = Jn;
         }
-    } else {
+        // reserve mode: another static range may be unclaimed (fewer live CTAs than ranges)
+        t_begin = t_end = 0;
+        if (reserve) {
+            if (tid == 0) s_range = (int)atomicAdd(ex.range_ctr, 1u);
+            __syncthreads();
+            vb = s_range;
+            if (vb < nvb) { t_begin = vb * ex.n_static; t_end = t_begin + ex.n_static; }
+            __syncthreads();   // s_range is read by everyone before a later claim overwrites it
+        }
+    }
+    if (dyn && !drew) {
         if (tid == 0) {
-            draw(0, 0);
+            draw(0, buf);
             if (C::NBUF == 1 && s_next[0] >= 0) load_vj(0, (s_nij[0] & 0xffff) * TJ);
         }
         __syncthreads();

@@ -200,6 +200,17 @@ def test_full_size_c3_single_steps(calibration):
         q = np.full(6010, 0.01)
         q[0:3], q[3:7], q[7:10] = 0.3, 0.0, 0.5
         assert np.all(np.diagonal(p_after) <= np.diagonal(p_before) + q + 1e-12)
+    # the per-frame path at full size (main.run_slam's path): k_f1 on the side stream on the SM that the previous
+    # frame's sweep keeps free (sweep.cuh reserve mode: CTAs on that SM retire, static ranges are claimed).  Two
+    # back-to-back observe() calls so that the second front end overlaps the first sweep, then compare.
+    extra, _ = synth.make_map_build_stream(2000, 20, 4, seed=99)
+    o.state = f.state
+    o.uncertainty = f.uncertainty
+    for t in range(n_build, n_build + 4):
+        f.observe(extra.ids[t], extra.poses[t])
+        o.observe([int(i) for i in extra.ids[t]], extra.poses[t])
+    assert_parity("single C3 full size (N = 6010), 4 per-frame observe() calls back to back", f.state, f.uncertainty,
+                  o.state, o.uncertainty, TOL)
 
 
 def test_api_errors_and_accessors(calibration):
