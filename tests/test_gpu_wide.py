@@ -97,3 +97,28 @@ def test_wide_capacity_flag_and_reset():
     b.reset()
     cams, status = b.cameras()
     assert status[0] == 0 and np.array_equal(cams[0], [0, 0, 0, 1, 0, 0, 0, 0, 0, 0])
+
+
+def test_wide_full_size_c2_rot_properties():
+    """BASELINE configs[1] with EKF_Rotations at full size (4096 sequences x 32 markers x 1000 frames, N = 330; 64
+    distinct streams read through asb_batch_upload_tiled as in bench.py's C5 legs): every sequence finite and
+    status 0; the 64 copies of one stream bit-identical (deterministic, sequences do not interact: a race between
+    CTAs or stream groups would break it); first and last sequence within 1e-9 of the free-running oracle over all
+    1000 frames, with the sensitivity floor beside it."""
+    from aruco_slam_b200 import FilterBatch, synth
+    n_seq, n_markers, n_frames, unique = 4096, 32, 1000, 64
+    ids, poses, off = synth.make_batch(unique, n_markers, n_frames, 0.5, "rot", unique=unique)
+    b = FilterBatch("rot", n_seq, n_markers, n_markers)
+    assert b.engine == "wide"
+    b.upload(ids, poses, off, n_streams=unique)
+    b.run()
+    cams, status = b.cameras()
+    assert not status.any() and np.isfinite(cams).all()
+    for s in range(unique):
+        assert np.array_equal(cams[s::unique], np.broadcast_to(cams[s], cams[s::unique].shape)), s
+    for s in (0, n_seq - 1):
+        stream = synth.make_stream(s % unique, n_markers, n_frames, 0.5, "rot")
+        o = run_oracle("rot", "scalar_first", stream, n_frames)
+        floor = sensitivity_floor("rot", "scalar_first", stream.ids, stream.poses)
+        assert_parity(f"batch wide C2-ROT full size (4096 x 32 x 1000) seq {s}", b.state(s), b.uncertainty(s), o.state,
+                      o.uncertainty, TOL, floor=floor)
