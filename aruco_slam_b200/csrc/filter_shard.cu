@@ -457,6 +457,7 @@ static int shard_chunks(asb_shard* s, const std::vector<ShChunk>& chunks) {
         ex.n = c.n1; ex.add_q = c.first ? 1 : 0; ex.nz = s->nz;
         ex.apply_kind = -1;
         ex.rect = 1; ex.row0 = pt.row0; ex.nJ = std::max(nJ, 1);
+        ex.reserve_sm = -1;   // no SM reservation here (sweep.cuh)
         const int grid = std::max(1, std::min(ntiles, 2 * (s->sm_count - (next ? 1 : 0))));
         if (s->tail_tiles > 0 && ntiles > grid) {   // contiguous range + dynamic tail (sweep.cuh)
             ex.tail = s->d_tail + (s->sweep_seq & 1);

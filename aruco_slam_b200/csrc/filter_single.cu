@@ -191,8 +191,12 @@ static void launch_sweep(asb_filter* f, int n1, int m4, int dbg, const SweepExtr
         const int ntiles = SweepDual::num_tiles(n1);
         const int grid = std::min(ntiles, 2 * f->sweep_grid - ((reserve && f->reserve_sm >= 0) ? 0 : spare_ctas));
         schedule(ntiles, grid);
-        launch_k(k_sweep<SweepDual>, grid, SweepDual::THREADS, SweepDual::smem_bytes(m4), f->stream, pdl,
-                 pin, pout, f->ld, f->d_Vr, f->d_Vc, m4, ntiles, dbg, ex);
+        if (ex.reserve_sm >= 0)
+            launch_k(k_sweep<SweepDual, true>, grid, SweepDual::THREADS, SweepDual::smem_bytes(m4), f->stream, pdl,
+                     pin, pout, f->ld, f->d_Vr, f->d_Vc, m4, ntiles, dbg, ex);
+        else
+            launch_k(k_sweep<SweepDual>, grid, SweepDual::THREADS, SweepDual::smem_bytes(m4), f->stream, pdl,
+                     pin, pout, f->ld, f->d_Vr, f->d_Vc, m4, ntiles, dbg, ex);
     } else {
         const int ntiles = SweepBig::num_tiles(n1);
         const int grid = std::min(ntiles, f->sweep_grid - (spare_ctas ? 1 : 0));
@@ -529,6 +533,7 @@ static int filter_build(asb_filter* f, int kind, int quat_mode, const double pos
     const int big = (int)prop.sharedMemPerBlockOptin - 2048;  // static smem (mbarriers) counts too
     ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepBig>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepDual>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepDual, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_f1<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_f1<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ASB_CUDA(cudaFuncSetAttribute(k_f1<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
@@ -541,6 +546,7 @@ static int filter_build(asb_filter* f, int kind, int quat_mode, const double pos
     {
     ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepBig>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepDual>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    ASB_CUDA(cudaFuncSetAttribute(k_sweep<SweepDual, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     ASB_CUDA(cudaFuncSetAttribute(k_f1<0, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     ASB_CUDA(cudaFuncSetAttribute(k_f1<0, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     ASB_CUDA(cudaFuncSetAttribute(k_f1<1, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));

@@ -231,7 +231,9 @@ using SweepDual = SweepCfg<2, 4, 4, 2, 2>;   // 64 x 64 tile, 2 CTAs / SM: one c
 // latency hides behind the tile's own math.  Pin is read (lower triangle), P is written (both
 // triangles): the same buffer for an in-place update, or the two halves of the pipelined
 // engine's ping-pong pair (filter_single.cu), where the next frame's k_f1 still reads Pin.
-template <class C>
+// RESERVE: the per-frame instantiation (reserve_sm mode, see SweepExtra); the stream-mode / sharded instantiation
+// compiles without it so that its tuned register allocation and control flow stay as they were.
+template <class C, bool RESERVE = false>
 __global__ void __launch_bounds__(C::THREADS, C::MINB)
 k_sweep(const double* Pin, double* P, int ld, const double* __restrict__ Vr, const double* __restrict__ Vc, int m4,
         int ntiles, int dbg, SweepExtra ex) {
@@ -268,7 +270,7 @@ k_sweep(const double* Pin, double* P, int ld, const double* __restrict__ Vr, con
     if (blockIdx.x == 0 && ex.apply_kind >= 0)   // state update (k_apply folded in)
         apply_state(ex.state, ex.dx, ex.apply_kind, ex.as_written, ex.nlm, tid, C::THREADS);
     const bool dyn = ex.tail != nullptr;
-    const bool reserve = dyn && ex.reserve_sm >= 0;
+    const bool reserve = RESERVE && dyn && ex.range_ctr != nullptr && ex.reserve_sm >= 0;   // a zero-initialised SweepExtra is 'off'
     if (dyn && blockIdx.x == 0 && tid == 0) {
         *ex.tail_reset = 0u;
         if (reserve) *ex.range_reset = 0u;
