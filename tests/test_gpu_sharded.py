@@ -53,6 +53,26 @@ def test_world1_map_build_equals_single_gpu_engine(calibration):
     assert rel_err(a.uncertainty, b.uncertainty) < TOL
 
 
+def test_world1_full_size_equals_single_gpu_engine(calibration):
+    """C3 at full size (2000 markers, N = 6010) on the row-sharded engine at world 1: the rectangular sweep then has
+    more tiles than CTAs and takes its contiguous-range + dynamic-tail schedule (the path the `c3_sharded` bench
+    leg runs; small maps never reach it)."""
+    from aruco_slam_b200 import EKF, synth
+    from aruco_slam_b200.sharded import ShardedFilter
+    km, dist = calibration
+    stream, n_build = synth.make_map_build_stream(2000, 20, 6)
+    ids, poses, off = stream.packed()
+    a = ShardedFilter("ekf", POSE0, 2000, quat_mode="scalar_first")
+    a.stream_upload(ids, poses, off)
+    a.stream_run(0, n_build + 6)
+    b = EKF(POSE0, camera_matrix=km, dist_coeffs=dist, quat_mode="scalar_first", max_landmarks=2000)
+    b.stream_upload(ids, poses, off)
+    b.stream_run(0, n_build + 6)
+    assert_parity("row-sharded world 1 at full size (N = 6010) vs the single-GPU engine", a.state, a.uncertainty,
+                  b.state, b.uncertainty, TOL)
+    a.close()
+
+
 def _worker(rank, world, port, q):
     import torch
     import torch.distributed as dist
