@@ -43,6 +43,8 @@ struct asb_filter {
     int* d_status = nullptr;
     unsigned long long* d_prof = nullptr;
     double* d_gate = nullptr; int* d_gate_i = nullptr; int gate_cap = 0;   // asb_correct_poses staging
+    // opt-in moving-average motion model (README.md:55-56; absent from the reference code)
+    int motion_window = 0; long long motion_frames = 0; double* d_hist = nullptr;
     // staging ring (host pinned + device)
     int* h_idx = nullptr; double* h_pose = nullptr; unsigned char* h_new = nullptr;
     int* d_idx = nullptr; double* d_pose = nullptr; unsigned char* d_new = nullptr;
@@ -149,6 +151,22 @@ static void launch_k(void (*kern)(KA...), int grid, int block, size_t smem, cuda
     cfg.attrs = at;
     cfg.numAttrs = pdl ? 1 : 0;
     cudaLaunchKernelEx(&cfg, kern, static_cast<KA>(args)...);
+}
+
+// Moving-average motion model (README.md:55-56: X_k|k-1 = X_k-1 + (X_k-1 - X_k-n) / n on the camera position), opt-in.
+// hist is a ring of the last `window` posterior camera positions; frame = number of positions pushed so far.
+__global__ void k_motion(double* __restrict__ state, double* __restrict__ hist, long long frame, int window) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const double cur[3] = {state[0], state[1], state[2]};
+    double* slot = hist + 3 * (frame % window);
+    const long long have = frame + 1 < window ? frame + 1 : window;     // positions available including this one
+    if (have >= 2) {
+        // X_{k-n} with n = have: the oldest of the `have` positions held once this one is pushed
+        const double* old = frame + 1 >= window ? hist + 3 * ((frame + 1) % window) : hist;
+        const double o[3] = {old[0], old[1], old[2]};
+        for (int c = 0; c < 3; ++c) state[c] = cur[c] + (cur[c] - o[c]) / (double)have;
+    }
+    slot[0] = cur[0]; slot[1] = cur[1]; slot[2] = cur[2];
 }
 
 // highest %smid of the device (SM ids need not be 0 .. count-1): the SM the per-frame sweeps keep free
@@ -594,7 +612,7 @@ int asb_filter_destroy(asb_filter* f) {
     cudaFree(f->d_state); cudaFree(f->d_P); cudaFree(f->d_Vr); cudaFree(f->d_Vc); cudaFree(f->d_blocks); cudaFree(f->d_nu);
     cudaFree(f->d_dx[0]); cudaFree(f->d_dx[1]); cudaFree(f->d_unc);
     cudaFree(f->d_status); cudaFree(f->d_prof); cudaFree(f->d_idx); cudaFree(f->d_pose); cudaFree(f->d_new);
-    cudaFree(f->s_idx); cudaFree(f->s_pose); cudaFree(f->s_new); cudaFree(f->d_gate); cudaFree(f->d_gate_i);
+    cudaFree(f->s_idx); cudaFree(f->s_pose); cudaFree(f->s_new); cudaFree(f->d_gate); cudaFree(f->d_gate_i); cudaFree(f->d_hist);
     cudaFreeHost(f->h_idx); cudaFreeHost(f->h_pose); cudaFreeHost(f->h_new);
     cudaFreeHost(f->h_corner); cudaFree(f->d_corner);
     if (f->ev_pose) cudaEventDestroy(f->ev_pose);
@@ -660,6 +678,9 @@ static int observe_impl(asb_filter* f, const int32_t* ids, const double* poses, 
         // a pipelined update reads its observations in k_f1 on the side stream
         const bool piped = true;
         if (piped) pipe_wait(f);
+        if (do_predict && f->motion_window > 0) {   // on the side stream, ahead of this frame's k_f1
+            k_motion<<<1, 32, 0, f->side>>>(f->d_state, f->d_hist, f->motion_frames++, f->motion_window);
+        }
         double* h_slot = nullptr;
         int rc = stage(f, idx, poses, isnew, k, &d_idx, &d_pose, &d_new, piped ? f->side : f->stream, feed, &h_slot);
         if (rc != ASB_OK) return rc;
@@ -779,6 +800,7 @@ int asb_stream_upload(asb_filter* f, const int32_t* ids, const double* poses, co
 
 int asb_stream_run(asb_filter* f, int t0, int t1) {
     ASB_CHECK_HANDLE(f);
+    if (f->motion_window > 0) return fail(ASB_ERR_BAD_ARG, "the moving-average motion model runs with per-frame observe() only");
     if (f->frames.empty()) return fail(ASB_ERR_NO_STREAM, "stream_run before stream_upload");
     if (f->stream_gen != f->map_gen)
         return fail(ASB_ERR_NO_STREAM, "the landmark map changed since stream_upload (observe / add_marker / set_landmarks): upload again");
@@ -1035,6 +1057,22 @@ int asb_correct_poses(asb_filter* f, const int32_t* ids, const double* poses, co
     ASB_CUDA(cudaGetLastError());
     ASB_CUDA(cudaMemcpyAsync(choice_out, d_choice, (size_t)k * sizeof(int), cudaMemcpyDeviceToHost, f->stream));
     ASB_CUDA(cudaStreamSynchronize(f->stream));   // idx (host vector) and choice_out are done with
+    return ASB_OK;
+}
+
+int asb_set_motion_model(asb_filter* f, int window) {
+    ASB_CHECK_HANDLE(f);
+    if (window < 0 || window > 4096) return fail(ASB_ERR_BAD_ARG, "window %d", window);
+    ASB_CUDA(cudaStreamSynchronize(f->stream));
+    if (f->side) ASB_CUDA(cudaStreamSynchronize(f->side));
+    cudaFree(f->d_hist);
+    f->d_hist = nullptr;
+    f->motion_window = window;
+    f->motion_frames = 0;
+    if (window > 0) {
+        ASB_CUDA(cudaMalloc(&f->d_hist, (size_t)window * 3 * sizeof(double)));
+        ASB_CUDA(cudaMemset(f->d_hist, 0, (size_t)window * 3 * sizeof(double)));
+    }
     return ASB_OK;
 }
 

@@ -221,6 +221,8 @@ class _CudaFilter(BaseFilter):
         self.max_landmarks = new_cap
         if self._stream:
             _lib.check(self._lib.asb_filter_set_stream(self._h, C.c_void_p(self._stream)))
+        if getattr(self, "_motion_window", 0):
+            _lib.check(self._lib.asb_set_motion_model(self._h, self._motion_window))   # its history restarts
         if ids.size:
             self.load_checkpoint(state, cov, ids)
         else:
@@ -351,6 +353,13 @@ class _CudaFilter(BaseFilter):
         out_ids = [int(i) for i, c in zip(ids, choice) if c]
         out_poses = [poses[o] if c == 1 else alt[o] for o, c in enumerate(choice) if c]
         return out_ids, out_poses
+
+    def set_motion_model(self, window: int = 10) -> None:
+        """Opt-in moving-average motion model of the reference's README (README.md:55-56; MOVING_AVG_WINDOW = 10,
+        extended_kalman_filter.py:19, never read there): before each ``observe`` the camera position moves by
+        ``(X_k-1 - X_k-n) / n``.  ``window=0`` (default) is the reference code's behaviour: predict leaves the state."""
+        _lib.check(self._lib.asb_set_motion_model(self._h, int(window)))
+        self._motion_window = int(window)
 
     def predict(self) -> None:
         _lib.check(self._lib.asb_predict(self._h))

@@ -131,6 +131,14 @@ ASB_API int asb_set_landmarks(asb_filter* f, const int32_t* ids_in_index_order, 
  * kept up to date by the update kernels - asb_get_cov returns the full symmetric matrix). */
 ASB_API int asb_device_views(asb_filter* f, void** d_state, void** d_cov, int* ld);
 
+/* Opt-in moving-average motion model.  The reference's README (README.md:55-56) describes
+ * X_k|k-1 = X_k-1 + (X_k-1 - X_k-n) / n on the camera position with n = MOVING_AVG_WINDOW = 10 (EKF:19), but the
+ * constant is never read and predict() leaves the state alone (EKF:95-105) - so window = 0 (the default)
+ * IS the reference's behaviour and there is nothing to check parity of window > 0 against.  With window > 0 every
+ * observe() first moves the camera position by that step (n = the positions held so far, at most `window`), before
+ * augmentation and update.  Per-frame observe() only (asb_stream_run refuses); not in the batched engines. */
+ASB_API int asb_set_motion_model(asb_filter* f, int window);
+
 /* correct_poses (BASE:274-325, the orientation-ambiguity gate the reference defines and never calls; SURVEY 8f
  * row 3), EKF_Rotations only: observation o is kept (choice[o] = 1) when the angle between R(q_cam) *
  * from_euler('xyz', pose[3:6]) and the landmark's orientation in the state is below threshold_deg

@@ -174,3 +174,33 @@ def test_landmarks_grow_past_the_initial_capacity(calibration):
         assert dict(f.get_lm_estimates()) == o.landmarks
         assert rel_err(f.state, o.state) < TOL
         assert rel_err(f.uncertainty, o.uncertainty) < TOL
+
+
+def test_moving_average_motion_model_is_opt_in(calibration):
+    """README.md:55-56 describes a moving-average motion model that the reference code does not
+    contain (F4).  Off by default (the goldens pin that); switched on, every observe() first moves the camera
+    position by (X_k-1 - X_k-n) / n - checked against the same step applied to the oracle's state by hand."""
+    from aruco_slam_b200 import synth
+    from aruco_slam_b200._lib import AsbError
+    window = 4
+    s = synth.make_stream(17, 8, 40, 0.8, "ekf")
+    f = _gpu("ekf", calibration, quat_mode="scalar_first")
+    f.set_motion_model(window)
+    o = ekf_oracle.make("ekf", "scalar_first")
+    hist = []
+    for t in range(s.n_frames):
+        cur = o.state[:3].copy()
+        hist.append(cur)
+        held = hist[-window:]
+        if len(held) >= 2:
+            o.state[:3] = cur + (cur - held[0]) / len(held)
+        o.observe([int(i) for i in s.ids[t]], s.poses[t])
+        f.observe(s.ids[t], s.poses[t])
+        if t in (1, 5, s.n_frames - 1):
+            assert rel_err(f.state, o.state) < TOL, t
+    assert rel_err(f.uncertainty, o.uncertainty) < TOL
+    ids, poses, off = s.packed()
+    f.stream_upload(ids, poses, off)
+    with pytest.raises(AsbError):
+        f.stream_run(0, 1)               # per-frame only
+    f.set_motion_model(0)                # off again: the reference's predict
