@@ -51,3 +51,26 @@ def test_committed_goldens_reproduce_bit_for_bit():
             ref.observe(s.ids[t], s.poses[t])
             if t in frames:
                 assert rel_err(np.asarray(ref.state), g[f"{mode}/f{t}/post_state"]) == 0.0, (mode, t)
+
+
+def test_gate_oracle_matches_reference_correct_poses():
+    """oracle/gate_oracle.py (the checker of asb_correct_poses) against the reference's own, never-called
+    BaseFilter.correct_poses (base_filter.py:274-325) on a live EKF_Rotations instance."""
+    from aruco_slam_b200 import synth
+    from oracle import gate_oracle
+    s = synth.make_stream(31, 8, 12, 1.0, "rot")
+    ref = ref_import.make_rot()
+    for t in range(s.n_frames - 1):
+        ref.observe(s.ids[t], s.poses[t])
+    state = np.asarray(ref.state, dtype=float)
+    landmarks = {int(k): int(v) for k, v in ref.landmarks.items()}
+    ids = np.concatenate([s.ids[-1], [9001]])
+    good = np.vstack([s.poses[-1], s.poses[-1][:1]])
+    rng = np.random.default_rng(3)
+    for spread in (0.0, 0.3, 0.6, 1.5):
+        poses = good.copy()
+        poses[:, 3:] += rng.normal(0.0, spread, size=(len(ids), 3)) if spread else 0.0
+        ref_ids, ref_poses = ref.correct_poses([int(i) for i in ids], list(poses))
+        got_ids, got_poses, _ = gate_oracle.correct_poses(state, landmarks, ids, poses)
+        assert got_ids == [int(i) for i in ref_ids], spread
+        assert all(np.array_equal(a, b) for a, b in zip(got_poses, ref_poses))
