@@ -413,7 +413,8 @@ static int batch_upload(asb_batch* b, const int32_t* ids, const double* poses, c
         ASB_CUDA(cudaEventRecord(b->ev_group[g], b->copy_stream));
     }
     b->fresh_upload = true;
-    if (b->wide) {   // rounds per frame = ceil(max_s k(s, t) / WCK): the frame-synchronous launches need it on the host
+    {   // rounds per frame = ceil(max_s k(s, t) / WCK): the wide engine's frame-synchronous launches need it on the
+        // host (kept for the resident engine too: asb_batch_set_engine may switch after the upload)
         b->kmax.assign(n_frames, 0);
         for (long long q = 0; q < obs_seqs; ++q) {
             const int64_t* o = offsets + q * n_frames;
@@ -443,6 +444,7 @@ int asb_batch_run(asb_batch* b, int t0, int t1) {
     if (!b->d_off) return fail(ASB_ERR_NO_STREAM, "batch_run before batch_upload");
     if (t0 < 0 || t1 < t0 || t1 > b->n_frames) return fail(ASB_ERR_BAD_ARG, "bad frame range [%d,%d)", t0, t1);
     if (b->wide) {
+        if ((int)b->kmax.size() != b->n_frames) return fail(ASB_ERR_NO_STREAM, "batch_run before batch_upload");
         if (b->fresh_upload) {
             for (int g = 0; g < b->up_groups; ++g) ASB_CUDA(cudaStreamWaitEvent(b->stream, b->ev_group[g], 0));
             b->fresh_upload = false;

@@ -82,6 +82,17 @@ def test_wide_equals_resident_engine():
     for (s1, p1), (s2, p2) in zip(out["resident"], out["wide"]):
         assert rel_err(s1, s2) < 1e-10
         assert rel_err(p1, p2) < 1e-10
+    # switching the engine AFTER the upload (C ABI order): the filters restart, the uploaded stream stays
+    from aruco_slam_b200 import _lib
+    _lib.check(b._lib.asb_batch_set_engine(b._h, 1))
+    assert b.engine == "resident"
+    b.run()
+    for s, (s1, p1) in enumerate(out["resident"]):
+        assert np.array_equal(b.state(s), s1) and np.array_equal(b.uncertainty(s), p1)
+    _lib.check(b._lib.asb_batch_set_engine(b._h, 2))
+    b.run()
+    for s, (s2, p2) in enumerate(out["wide"]):
+        assert np.array_equal(b.state(s), s2) and np.array_equal(b.uncertainty(s), p2)
 
 
 def test_wide_capacity_flag_and_reset():
