@@ -131,6 +131,15 @@ def flops_batch_form(n_state: int, k: int, rows: int, width: int) -> float:
         + 2.0 * width * m * m + 2.0 * n * m
 
 
+def flops_executed(n_state: int, k: int, rows: int, width: int) -> float:
+    """FP64 flops the kernels actually execute for one frame: the covariance update on the TRIANGLE (N^2 m instead
+    of the contract's dense 2 N^2 m) and the triangular gain solve (N m^2 instead of 2 N m^2); the rest as in
+    flops_batch_form.  Reported beside the contract figure so that `frac` cannot be read as pipe utilisation."""
+    m = rows * k
+    n = n_state
+    return float(n) * n * m + float(n) * m * m + m ** 3 / 3.0 + 2.0 * width * n * m + 2.0 * width * m * m + 2.0 * n * m
+
+
 def pinned_like(a: np.ndarray):
     import torch
     t = torch.empty(a.shape, dtype=torch.from_numpy(np.empty(0, a.dtype)).dtype, pin_memory=True)
@@ -504,15 +513,17 @@ def leg_batch(torch, dist, world, rank, local, stream_ptr, args, name, kind, seq
     cams, status = b.cameras()
     rep = n_seq // u
     upd = float(counts[:, :done].sum()) * rep
-    flops = float(sum(flops_batch_form(n_state, int(k), rows, width) * c
-                      for k, c in zip(*np.unique(counts[:, :done], return_counts=True)))) * rep
-    tot = torch.tensor([upd, flops], dtype=torch.float64, device="cuda")
+    kc_hist = list(zip(*np.unique(counts[:, :done], return_counts=True)))
+    flops = float(sum(flops_batch_form(n_state, int(k), rows, width) * c for k, c in kc_hist)) * rep
+    flops_x = float(sum(flops_executed(n_state, int(k), rows, width) * c for k, c in kc_hist)) * rep
+    tot = torch.tensor([upd, flops, flops_x], dtype=torch.float64, device="cuda")
     mx = torch.tensor([ms, -float(done)], dtype=torch.float64, device="cuda")
     if dist is not None:
         dist.all_reduce(tot)
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)
     upd_all, flops_all, ms_max, frames_min = float(tot[0]), float(tot[1]), float(mx[0]), int(-float(mx[1]))
     tf = flops_all / (ms_max * 1e-3) / 1e12
+    tf_x = float(tot[2]) / (ms_max * 1e-3) / 1e12
     leg = {"workload": name, "value": upd_all / (ms_max * 1e-3), "unit": UNIT, "n_gpus": world,
            "sequences_total": n_seq * world, "sequences_per_gpu": n_seq, "markers": markers, "frames": frames,
            "frames_run": frames_min, "p_visible": p_vis, "n_state": n_state, "engine": b.engine,
@@ -520,6 +531,9 @@ def leg_batch(torch, dist, world, rank, local, stream_ptr, args, name, kind, seq
            "distinct_streams_per_gpu": u, "scaling": "strong (total sequences fixed, sharded over the ranks)",
            "roofline": {"bound": "fp64", "achieved": tf, "peak": fp64_peak * world, "unit": "TFLOP/s",
                         "frac": tf / (fp64_peak * world), "traffic": None, "peak_source": fp64_src,
+                        "executed": {"achieved": tf_x, "frac": tf_x / (fp64_peak * world),
+                                     "note": "flops the kernels execute (triangle update N^2 m, triangular solve "
+                                             "N m^2): the FP64-pipe utilisation to compare with ncu"},
                         "note": "algorithmic batch-form flops F(N,m,k) of SURVEY.md 8d / time against world x the "
                                 "FP64 peak measured live; the covariance update counts 2 N^2 m although the "
                                 "kernels compute its triangle (N^2 m)"},
@@ -615,6 +629,8 @@ def run_b200(args):
     counts = np.diff(off)
     flops = float(sum(flops_batch_form(n_state, int(k), rows, width) * c
                       for k, c in zip(*np.unique(counts, return_counts=True))))
+    flops_x = float(sum(flops_executed(n_state, int(k), rows, width) * c
+                        for k, c in zip(*np.unique(counts, return_counts=True))))
     gen_s = time.perf_counter() - t_gen
     keep_i, h_ids = pinned_like(ids)
     keep_p, h_poses = pinned_like(poses)
@@ -679,6 +695,10 @@ def run_b200(args):
         "clocks": clk.summary(),
         "roofline": {"bound": "fp64", "achieved": ach_tf, "peak": fp64_peak, "unit": "TFLOP/s",
                      "frac": ach_tf / fp64_peak, "traffic": None, "peak_source": fp64_src,
+                     "executed": {"achieved": flops_x / (ms_step * 1e-3) / 1e12,
+                                  "frac": flops_x / (ms_step * 1e-3) / 1e12 / fp64_peak,
+                                  "note": "flops k_batch executes (triangle update, triangular solve): compare with "
+                                          "ncu sm__pipe_fp64_cycles_active (profiles/r02_k_batch.txt: 25.9 %)"},
                      "note": "k_batch keeps each filter in shared memory; HBM traffic is the observation "
                              "stream only, so the FP64 FMA pipe bounds it. achieved = algorithmic "
                              "batch-form flops F(N,m,k) of SURVEY.md 8d / time; peak = DFMA peak measured "
