@@ -47,7 +47,7 @@ struct asb_batch {
     bool wide = false;
     int engine_req = 0;            // 0 auto, 1 resident, 2 wide
     int *w_meta = nullptr, *w_idx = nullptr;
-    double *w_delta = nullptr, *w_H = nullptr, *w_L = nullptr, *w_Dinv = nullptr, *w_y = nullptr, *w_V = nullptr;
+    double *w_delta = nullptr, *w_H = nullptr, *w_Hp = nullptr, *w_L = nullptr, *w_Dinv = nullptr, *w_y = nullptr, *w_V = nullptr;
     long long w_vstride = 0;
     int w_nb64 = 0;
     static constexpr int W_MAX_GROUPS = 4;
@@ -113,7 +113,7 @@ static int launch_batch_dyn(asb_batch* b, const BatchParams& p, size_t smem, int
 template <int KIND> static size_t wide_model_smem(int max_lm, int max_obs) {
     using WD = WideDims<KIND>;
     const int cap_obs = std::max(max_obs, (int)WCK);
-    return ((size_t)CAM * WD::TW + (size_t)WCK * 8 * WD::HLS + (size_t)cap_obs * 6) * 8 + ((size_t)cap_obs * 3 + max_lm + 4) * 4;
+    return ((size_t)CAM * WD::TW + (size_t)cap_obs * 6) * 8 + ((size_t)cap_obs * 3 + max_lm + 4) * 4;
 }
 template <int KIND> static size_t wide_chol_smem() {
     using WD = WideDims<KIND>;
@@ -133,7 +133,8 @@ static int resident_fits(const asb_batch* b) {
 }
 
 static void wide_free(asb_batch* b) {
-    cudaFree(b->w_meta); cudaFree(b->w_idx); cudaFree(b->w_delta); cudaFree(b->w_H);
+    cudaFree(b->w_meta); cudaFree(b->w_idx); cudaFree(b->w_delta); cudaFree(b->w_H); cudaFree(b->w_Hp);
+    b->w_Hp = nullptr;
     cudaFree(b->w_L); cudaFree(b->w_Dinv); cudaFree(b->w_y); cudaFree(b->w_V);
     b->w_meta = b->w_idx = nullptr;
     b->w_delta = b->w_H = b->w_L = b->w_Dinv = b->w_y = b->w_V = nullptr;
@@ -148,6 +149,7 @@ template <int KIND> static int wide_alloc_kind(asb_batch* b) {
     ASB_CUDA(dmalloc(&b->w_idx, ns * b->max_obs));
     ASB_CUDA(dmalloc(&b->w_delta, ns * b->state_stride));
     ASB_CUDA(dmalloc(&b->w_H, ns * WCK * WD::R * WD::W));
+    ASB_CUDA(dmalloc(&b->w_Hp, ns * WCK * 8 * WD::HLS));
     ASB_CUDA(dmalloc(&b->w_L, ns * tri(WD::NB) * 64));
     ASB_CUDA(dmalloc(&b->w_Dinv, ns * WD::NB * 64));
     ASB_CUDA(dmalloc(&b->w_y, ns * WD::M8));
@@ -181,7 +183,7 @@ template <int KIND> static int wide_run(asb_batch* b, int t0, int t1) {
     p.obs_seqs = b->obs_seqs;
     p.as_written = (b->kind == ASB_KIND_EKF && b->quat_mode == ASB_QUAT_AS_WRITTEN) ? 1 : 0;
     p.nz = b->nz;
-    p.meta = b->w_meta; p.idx = b->w_idx; p.delta = b->w_delta; p.H = b->w_H; p.L = b->w_L; p.Dinv = b->w_Dinv;
+    p.meta = b->w_meta; p.idx = b->w_idx; p.delta = b->w_delta; p.H = b->w_H; p.Hp = b->w_Hp; p.L = b->w_L; p.Dinv = b->w_Dinv;
     p.y = b->w_y; p.V = b->w_V; p.v_stride = b->w_vstride; p.nb64 = b->w_nb64;
     const size_t sm_model = wide_model_smem<KIND>(b->max_lm, b->max_obs), sm_chol = wide_chol_smem<KIND>(),
                  sm_panel = wide_panel_smem<KIND>(), sm_sweep = wide_sweep_smem<KIND>();

@@ -64,6 +64,7 @@ struct WideParams {
     int* idx;                  // max_obs landmark indices of the current frame
     double* delta;             // state_stride
     double* H;                 // WCK * R * W   measurement blocks of the current chunk
+    double* Hp;                // WCK * 8 * HLS the same blocks zero-padded to fragment order (k_wide_model's S assembly)
     double* L;                 // tri(NB) * 64  Cholesky factor, 8 x 8 tiles
     double* Dinv;              // NB * 64       inverse diagonal blocks
     double* y;                 // M8
@@ -82,14 +83,13 @@ __device__ __forceinline__ double wt_sym(const double* __restrict__ P, int i, in
 // ---- k_wide_model: association, augmentation, measurement model, S -> HBM (high occupancy: the serial
 //      model evaluation and the ragged S assembly of one sequence hide behind five other CTAs) --------
 template <int KIND>
-__global__ void __launch_bounds__(128, 5) k_wide_model(WideParams p) {
+__global__ void __launch_bounds__(128, 6) k_wide_model(WideParams p) {
     using WD = WideDims<KIND>;
     constexpr int D = WD::D, R = WD::R, W = WD::W, M8 = WD::M8, NB = WD::NB, NT = 128;
     extern __shared__ __align__(16) unsigned char smraw[];
     constexpr int HLS = WD::HLS;
     double* s_Pc = reinterpret_cast<double*>(smraw);          // CAM x TW: P[cam, touched columns]
-    double* s_H = s_Pc + CAM * WD::TW;                        // WCK x 8 x HLS padded measurement blocks
-    double* s_pose = s_H + WCK * 8 * HLS;                     // max(max_obs, WCK) x 6
+    double* s_pose = s_Pc + CAM * WD::TW;                     // max(max_obs, WCK) x 6
     const int cap_obs = max(p.max_obs, WCK);
     int* s_ids = reinterpret_cast<int*>(s_pose + (size_t)cap_obs * 6);
     int* s_idx = s_ids + cap_obs;
@@ -248,7 +248,9 @@ __global__ void __launch_bounds__(128, 5) k_wide_model(WideParams p) {
     }
     __syncthreads();   // the blocks in gH (written by this CTA's model threads) are complete
     // measurement blocks in fragment-friendly padded form: s_H[o][g < 8][HLS], columns 0..9 camera, 16..16+D-1
-    // landmark, everything else (rows >= R included) zero
+    // landmark, everything else (rows >= R included) zero.  Kept in HBM scratch (read back through L1), not in
+    // shared memory: 37 KB less per CTA is two more CTAs per SM for this latency-bound kernel
+    double* s_H = p.Hp + (long long)seq * (WCK * 8 * HLS);
     for (int e = tid; e < kc * 8 * HLS; e += NT) {
         const int o = e / (8 * HLS), rem = e - o * (8 * HLS), gg = rem / HLS, c = rem - gg * HLS;
         double v = 0.0;
