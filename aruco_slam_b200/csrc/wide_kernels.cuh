@@ -32,8 +32,14 @@ namespace asb {
 
 constexpr int WCK = 16;         // markers per update chunk
 constexpr int W_VLD = 68;       // doubles per V panel row of a 64-column block (= 4 mod 16: conflict-free fragments)
-constexpr int W_SLAB = 16;      // V rows per pipeline stage of the sweep
-constexpr int W_NST = 4;        // stages
+// measured at the C2-ROT / C5-ROT shapes (slab rows, stages): (16,4) 654.6 / 399.3 ms, (8,8) 685, (24,3) 645.9,
+// (32,2) 641.1 / 390.7, (40,2) 637.9 / 388.4: fewer, larger slabs (less mbarrier traffic per k-step) win
+#ifndef W_SLAB_ROWS
+#define W_SLAB_ROWS 40
+#define W_STAGES 2
+#endif
+constexpr int W_SLAB = W_SLAB_ROWS;   // V rows per pipeline stage of the sweep
+constexpr int W_NST = W_STAGES;       // stages
 
 template <int KIND> struct WideDims {
     static constexpr int R = Dims<KIND>::R, D = Dims<KIND>::D, W = CAM + D;
