@@ -683,7 +683,7 @@ __global__ void __launch_bounds__(W_SWEEP_THREADS, 2) k_wide_sweep(WideParams p)
         bool valid[4][2];
         double2 pv[4][2];
         double acc[4][2][2];
-        bool anyv = false;
+        bool anyv = false, allv = true;
 #pragma unroll
         for (int rm = 0; rm < 4; ++rm)
 #pragma unroll
@@ -691,6 +691,7 @@ __global__ void __launch_bounds__(W_SWEEP_THREADS, 2) k_wide_sweep(WideParams p)
                 const int i8 = 8 * I + 4 * wi + rm, j8 = 8 * J + 2 * wj + rn;
                 valid[rm][rn] = i8 < nt8 && j8 <= i8;
                 anyv = anyv || valid[rm][rn];
+                allv = allv && valid[rm][rn];
                 acc[rm][rn][0] = acc[rm][rn][1] = 0.0;
                 pv[rm][rn] = make_double2(0.0, 0.0);
                 if (valid[rm][rn])
@@ -700,7 +701,23 @@ __global__ void __launch_bounds__(W_SWEEP_THREADS, 2) k_wide_sweep(WideParams p)
             const int st = cnt % W_NST;
             if (J == 0) mbar_wait(&bar_vi[s], 0);
             mbar_wait(&bar_full[st], (uint32_t)((cnt / W_NST) & 1));
-            if (anyv) {
+            if (allv) {   // interior warp tile: no per-MMA predicate (each costs a WARPSYNC in SASS)
+                const double* vj = ring + (size_t)st * SLAB_D + 16 * wj + g;
+                const double* via = vi + (size_t)s * SLAB_D;
+                const int ksteps = min(W_SLAB, m8 - s * W_SLAB) >> 2;
+#pragma unroll 2
+                for (int kk = 0; kk < ksteps; ++kk) {
+                    double a[4], b[2];
+#pragma unroll
+                    for (int rm = 0; rm < 4; ++rm) a[rm] = via[(4 * kk + t4) * W_VLD + 8 * rm];
+#pragma unroll
+                    for (int rn = 0; rn < 2; ++rn) b[rn] = vj[(4 * kk + t4) * W_VLD + 8 * rn];
+#pragma unroll
+                    for (int rm = 0; rm < 4; ++rm)
+#pragma unroll
+                        for (int rn = 0; rn < 2; ++rn) dmma884(acc[rm][rn][0], acc[rm][rn][1], a[rm], b[rn]);
+                }
+            } else if (anyv) {
                 const double* vj = ring + (size_t)st * SLAB_D + 16 * wj + g;
                 const double* via = vi + (size_t)s * SLAB_D;
                 const int ksteps = min(W_SLAB, m8 - s * W_SLAB) >> 2;
