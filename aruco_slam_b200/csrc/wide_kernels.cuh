@@ -470,7 +470,22 @@ __global__ void __launch_bounds__(128, 4) k_wide_chol(WideParams p) {
         }
         __syncthreads();
     }
-    for (int e = tid; e < tri(nb) * 64; e += NT) gL[e] = s_S[e];
+    // Output for k_wide_panel's forward substitution V_b = Dinv_b G_b - sum_{b' < b} (Dinv_b L_bb') V_b': the
+    // off-diagonal tiles leave as  Lt(ib, jb) = -Dinv_ib L(ib, jb)  (two DMMAs per tile), so the panel kernel needs
+    // no multiply by Dinv AFTER its dependent chain (one shared-memory round trip and two serial MMAs per block row less)
+    for (int t = warp; t < tri(nb); t += NW) {
+        int ib = (int)((sqrtf(8.0f * t + 1.0f) - 1.0f) * 0.5f);
+        while (tri(ib + 1) <= t) ++ib;
+        while (tri(ib) > t) --ib;
+        const int jb = t - tri(ib);
+        if (ib == jb) continue;   // diagonal blocks are not read downstream (Dinv carries them)
+        const double* lt = s_S + t * 64;
+        double c0v = 0.0, c1v = 0.0;
+#pragma unroll
+        for (int kk = 0; kk < 2; ++kk)
+            dmma884(c0v, c1v, -__ldcg(gD + ib * 64 + g * 8 + 4 * kk + t4), lt[(4 * kk + t4) * 8 + g]);
+        *reinterpret_cast<double2*>(gL + t * 64 + g * 8 + 2 * t4) = make_double2(c0v, c1v);
+    }
     for (int a = tid; a < m8; a += NT) gy[a] = s_nu[a];
     if (tid == 0 && s_bad) p.status[seq] = ASB_ERR_NOT_SPD;
 }
@@ -557,46 +572,43 @@ __global__ void __launch_bounds__(256, 3) k_wide_panel(WideParams p) {
     double* gV = p.V + (long long)seq * p.v_stride + (long long)jb64 * (M8 * W_VLD) + 8 * warp;
     double dx0 = 0.0, dx1 = 0.0;
     for (int b = 0; b < nb; ++b) {
+        // V_b = Dinv_b G_b + sum_{b' < b} Lt(b, b') V_b'   (Lt = -Dinv L from k_wide_chol): every product takes its B
+        // operand straight from shared memory (G_b as written by phase 1, V_b' as written by the rows before), four
+        // independent accumulator chains, one shared-memory store per block row
         const double d0 = __ldg(gD + b * 64 + g * 8 + t4), d1 = __ldg(gD + b * 64 + g * 8 + 4 + t4);
         const double yv = s_y[8 * b + g];
-        double2 acc = *reinterpret_cast<double2*>(gs + (8 * b + g) * W_VLD + 2 * t4);
-        double e0 = 0.0, e1 = 0.0, f0 = 0.0, f1 = 0.0, h0 = 0.0, h1 = 0.0;
+        double v0 = 0.0, v1 = 0.0, e0 = 0.0, e1 = 0.0, f0 = 0.0, f1 = 0.0, h0 = 0.0, h1 = 0.0;
         const double* lrow = gL + (long long)tri(b) * 64 + g * 8 + t4;
-        // L fragments are fetched one trip (two 8 x 8 tiles, four k-steps) ahead of the MMAs that use them
         int tb = 0;
         double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-        if (b >= 2) { a0 = -__ldg(lrow); a1 = -__ldg(lrow + 4); a2 = -__ldg(lrow + 64); a3 = -__ldg(lrow + 68); }
-        for (; tb + 2 <= b; tb += 2) {   // four independent accumulator chains
+        if (b >= 2) { a0 = __ldg(lrow); a1 = __ldg(lrow + 4); a2 = __ldg(lrow + 64); a3 = __ldg(lrow + 68); }
+        dmma884(f0, f1, d0, gs[(8 * b + t4) * W_VLD + g]);
+        dmma884(h0, h1, d1, gs[(8 * b + 4 + t4) * W_VLD + g]);
+        for (; tb + 2 <= b; tb += 2) {
             double n0 = 0.0, n1 = 0.0, n2 = 0.0, n3 = 0.0;
             if (tb + 4 <= b) {
-                n0 = -__ldg(lrow + (tb + 2) * 64); n1 = -__ldg(lrow + (tb + 2) * 64 + 4);
-                n2 = -__ldg(lrow + (tb + 3) * 64); n3 = -__ldg(lrow + (tb + 3) * 64 + 4);
+                n0 = __ldg(lrow + (tb + 2) * 64); n1 = __ldg(lrow + (tb + 2) * 64 + 4);
+                n2 = __ldg(lrow + (tb + 3) * 64); n3 = __ldg(lrow + (tb + 3) * 64 + 4);
             }
             const double* gk = gs + (8 * tb + t4) * W_VLD + g;
-            dmma884(acc.x, acc.y, a0, gk[0]);
+            dmma884(v0, v1, a0, gk[0]);
             dmma884(e0, e1, a1, gk[4 * W_VLD]);
             dmma884(f0, f1, a2, gk[8 * W_VLD]);
             dmma884(h0, h1, a3, gk[12 * W_VLD]);
             a0 = n0; a1 = n1; a2 = n2; a3 = n3;
         }
         if (tb < b) {
-            const double l0 = -__ldg(lrow + tb * 64), l1 = -__ldg(lrow + tb * 64 + 4);
+            const double l0 = __ldg(lrow + tb * 64), l1 = __ldg(lrow + tb * 64 + 4);
             const double* gk = gs + (8 * tb + t4) * W_VLD + g;
-            dmma884(acc.x, acc.y, l0, gk[0]);
+            dmma884(v0, v1, l0, gk[0]);
             dmma884(e0, e1, l1, gk[4 * W_VLD]);
         }
-        acc.x += (e0 + f0) + h0; acc.y += (e1 + f1) + h1;
-        __syncwarp();
-        *reinterpret_cast<double2*>(gs + (8 * b + g) * W_VLD + 2 * t4) = acc;
-        __syncwarp();
-        double v0 = 0.0, v1 = 0.0;
-        dmma884(v0, v1, d0, gs[(8 * b + t4) * W_VLD + g]);
-        dmma884(v0, v1, d1, gs[(8 * b + 4 + t4) * W_VLD + g]);
-        __syncwarp();
+        v0 += (e0 + f0) + h0; v1 += (e1 + f1) + h1;
+        __syncwarp();   // every lane has read G_b before it is overwritten by V_b
         *reinterpret_cast<double2*>(gs + (8 * b + g) * W_VLD + 2 * t4) = make_double2(v0, v1);
         *reinterpret_cast<double2*>(gV + (8 * b + g) * W_VLD + 2 * t4) = make_double2(v0, v1);
         dx0 += v0 * yv; dx1 += v1 * yv;
-        __syncwarp();
+        __syncwarp();   // V_b visible to the warp before the next block row reads it
     }
 #pragma unroll
     for (int sh = 4; sh < 32; sh <<= 1) {
