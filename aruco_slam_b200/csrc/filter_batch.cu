@@ -121,7 +121,7 @@ template <int KIND> static size_t wide_chol_smem() {
 }
 template <int KIND> static size_t wide_panel_smem() {
     using WD = WideDims<KIND>;
-    return ((size_t)WD::M8 * W_VLD + 12 * W_VLD + WD::M8) * 8 + WCK * 4;
+    return ((size_t)WD::M8 * W_VLD + 2 * (size_t)WD::LROW) * 8 + WCK * 4;
 }
 template <int KIND> static size_t wide_sweep_smem() {
     return ((size_t)WideDims<KIND>::M8 * W_VLD + (size_t)W_NST * W_SLAB * W_VLD) * 8;

@@ -47,6 +47,7 @@ template <int KIND> struct WideDims {
     static constexpr int M8 = (MC + 7) & ~7;           // padded to whole 8-row blocks
     static constexpr int NB = M8 / 8;
     static constexpr int TW = CAM + D * WCK;           // touched state columns per chunk
+    static constexpr int LROW = (NB - 1) * 64 > 12 * 68 ? (NB - 1) * 64 : 12 * 68;   // k_wide_panel's L row buffer
     static constexpr int HLS = 16 + 8 * ((D + 7) / 8) + 4;   // padded block row: [cam 16 | lm 8 ceil(D/8)] + 4 (= 4 mod 16)
 };
 
@@ -79,6 +80,9 @@ struct WideParams {
     int nb64;                  // 64-column blocks at capacity
 };
 
+__device__ __forceinline__ void w_cp_async16(void* smem, const void* gmem) {   // 16-byte LDGSTS, L2 only
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem)), "l"(gmem) : "memory");
+}
 __device__ __forceinline__ long long wt_off(int i, int j) {   // (i >> 3) >= (j >> 3)
     return ((long long)(tri(i >> 3) + (j >> 3)) << 6) + ((i & 7) << 3) + (j & 7);
 }
@@ -504,10 +508,14 @@ __global__ void __launch_bounds__(256, 3) k_wide_panel(WideParams p) {
     const int col0 = 64 * jb64;
     if (col0 >= n) return;
     const int kc = meta[6], c0 = meta[7], m = R * kc, nb = m8 >> 3;
+    // L rows for phase 2 come through two shared-memory buffers of one block row ((NB - 1) tiles) each: all 8
+    // warps of the CTA walk the same Lt row at the same time, and fetched per warp from L2 the factor alone is
+    // 8 x 54 KB per CTA - the kernel was L2-bandwidth-bound on it.  Buffer 0 aliases s_Pc (dead after phase 1).
+    constexpr int LROW = WD::LROW;                            // doubles per row buffer (>= s_Pc's 12 x W_VLD)
     double* Gs = reinterpret_cast<double*>(smraw);            // m8 x W_VLD
-    double* s_Pc = Gs + M8 * W_VLD;                           // 12 x W_VLD: P[cam, cols], rows 10, 11 zero
-    double* s_y = s_Pc + 12 * W_VLD;                          // M8
-    int* s_li = reinterpret_cast<int*>(s_y + M8);             // WCK
+    double* s_L = Gs + M8 * W_VLD;                            // 2 x LROW
+    double* s_Pc = s_L;                                       // 12 x W_VLD: P[cam, cols], rows 10, 11 zero (phase 1)
+    int* s_li = reinterpret_cast<int*>(s_L + 2 * LROW);       // WCK
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, t4 = lane & 3;
     const double* P = p.covs + (long long)seq * p.cov_stride;
@@ -516,7 +524,7 @@ __global__ void __launch_bounds__(256, 3) k_wide_panel(WideParams p) {
     const double* gD = p.Dinv + (long long)seq * (NB * 64);
     const bool add_q = p.round == 0;
     for (int o = tid; o < kc; o += NT) s_li[o] = CAM + D * p.idx[(long long)seq * p.max_obs + c0 + o];
-    for (int a = tid; a < m8; a += NT) s_y[a] = p.y[(long long)seq * M8 + a];
+    const double* gy = p.y + (long long)seq * M8;
     for (int e = tid; e < 12 * 64; e += NT) {
         const int c = e >> 6, col = col0 + (e & 63);
         double v = 0.0;
@@ -571,37 +579,42 @@ __global__ void __launch_bounds__(256, 3) k_wide_panel(WideParams p) {
     double* gs = Gs + 8 * warp;
     double* gV = p.V + (long long)seq * p.v_stride + (long long)jb64 * (M8 * W_VLD) + 8 * warp;
     double dx0 = 0.0, dx1 = 0.0;
+    // row b of Lt (tiles (b, 0 .. b-1), contiguous in HBM) -> buffer b & 1, 16 bytes per cp.async
+    auto fetch_row = [&](int b) {
+        const double* src = gL + (long long)tri(b) * 64;
+        double* dst = s_L + (b & 1) * LROW;
+        for (int e = tid; e < b * 32; e += NT) w_cp_async16(dst + 2 * e, src + 2 * e);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    if (nb > 1) fetch_row(1);      // buffer 1; buffer 0 (= s_Pc) is free as of the barrier above
     for (int b = 0; b < nb; ++b) {
         // V_b = Dinv_b G_b + sum_{b' < b} Lt(b, b') V_b'   (Lt = -Dinv L from k_wide_chol): every product takes its B
         // operand straight from shared memory (G_b as written by phase 1, V_b' as written by the rows before), four
         // independent accumulator chains, one shared-memory store per block row
+        if (b >= 1) {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+            __syncthreads();       // row b has landed for everyone; everyone is done with the other buffer (row b - 1)
+            if (b + 1 < nb) fetch_row(b + 1);
+        }
         const double d0 = __ldg(gD + b * 64 + g * 8 + t4), d1 = __ldg(gD + b * 64 + g * 8 + 4 + t4);
-        const double yv = s_y[8 * b + g];
+        const double yv = __ldg(gy + 8 * b + g);
         double v0 = 0.0, v1 = 0.0, e0 = 0.0, e1 = 0.0, f0 = 0.0, f1 = 0.0, h0 = 0.0, h1 = 0.0;
-        const double* lrow = gL + (long long)tri(b) * 64 + g * 8 + t4;
-        int tb = 0;
-        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-        if (b >= 2) { a0 = __ldg(lrow); a1 = __ldg(lrow + 4); a2 = __ldg(lrow + 64); a3 = __ldg(lrow + 68); }
+        const double* lrow = s_L + (b & 1) * LROW + g * 8 + t4;
         dmma884(f0, f1, d0, gs[(8 * b + t4) * W_VLD + g]);
         dmma884(h0, h1, d1, gs[(8 * b + 4 + t4) * W_VLD + g]);
+        int tb = 0;
+#pragma unroll 2
         for (; tb + 2 <= b; tb += 2) {
-            double n0 = 0.0, n1 = 0.0, n2 = 0.0, n3 = 0.0;
-            if (tb + 4 <= b) {
-                n0 = __ldg(lrow + (tb + 2) * 64); n1 = __ldg(lrow + (tb + 2) * 64 + 4);
-                n2 = __ldg(lrow + (tb + 3) * 64); n3 = __ldg(lrow + (tb + 3) * 64 + 4);
-            }
             const double* gk = gs + (8 * tb + t4) * W_VLD + g;
-            dmma884(v0, v1, a0, gk[0]);
-            dmma884(e0, e1, a1, gk[4 * W_VLD]);
-            dmma884(f0, f1, a2, gk[8 * W_VLD]);
-            dmma884(h0, h1, a3, gk[12 * W_VLD]);
-            a0 = n0; a1 = n1; a2 = n2; a3 = n3;
+            dmma884(v0, v1, lrow[tb * 64], gk[0]);
+            dmma884(e0, e1, lrow[tb * 64 + 4], gk[4 * W_VLD]);
+            dmma884(f0, f1, lrow[tb * 64 + 64], gk[8 * W_VLD]);
+            dmma884(h0, h1, lrow[tb * 64 + 68], gk[12 * W_VLD]);
         }
         if (tb < b) {
-            const double l0 = __ldg(lrow + tb * 64), l1 = __ldg(lrow + tb * 64 + 4);
             const double* gk = gs + (8 * tb + t4) * W_VLD + g;
-            dmma884(v0, v1, l0, gk[0]);
-            dmma884(e0, e1, l1, gk[4 * W_VLD]);
+            dmma884(v0, v1, lrow[tb * 64], gk[0]);
+            dmma884(e0, e1, lrow[tb * 64 + 4], gk[4 * W_VLD]);
         }
         v0 += (e0 + f0) + h0; v1 += (e1 + f1) + h1;
         __syncwarp();   // every lane has read G_b before it is overwritten by V_b
