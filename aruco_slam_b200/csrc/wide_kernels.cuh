@@ -540,13 +540,12 @@ __global__ void __launch_bounds__(256, 3) k_wide_panel(WideParams p) {
     //      A = the observation's dense block (rows >= R zero), B = the 10 camera rows of P (shared) and
     //      the D landmark rows (straight from HBM in fragment order: H is never materialised) ----------
     constexpr int KL = (D + 3) / 4;
-    for (int it = warp; it < 4 * kc; it += 8) {      // item = (observation, 16 of the 64 columns)
+    // the landmark rows of an item come from HBM in B-fragment order, fetched one item ahead of the MMAs
+    auto load_item = [&](int it, double (&blk)[2][KL]) {
         const int o = it >> 2, q = it & 3;
         const int li = s_li[o];
-        const double* hb = gH + o * R * W;
-        double ac[3], al[KL], bl[2][KL];
 #pragma unroll
-        for (int nb8 = 0; nb8 < 2; ++nb8) {           // all landmark-row loads of the item first
+        for (int nb8 = 0; nb8 < 2; ++nb8) {
             const int col = col0 + 16 * q + 8 * nb8 + g;
 #pragma unroll
             for (int kk = 0; kk < KL; ++kk) {
@@ -556,9 +555,21 @@ __global__ void __launch_bounds__(256, 3) k_wide_panel(WideParams p) {
                     v = wt_sym(P, li + c, col);
                     if (add_q && li + c == col) v += p.nz.q_lm;
                 }
-                bl[nb8][kk] = v;
+                blk[nb8][kk] = v;
             }
         }
+    };
+    double bnext[2][KL];
+    if (warp < 4 * kc) load_item(warp, bnext);
+    for (int it = warp; it < 4 * kc; it += 8) {      // item = (observation, 16 of the 64 columns)
+        const int o = it >> 2, q = it & 3;
+        const double* hb = gH + o * R * W;
+        double ac[3], al[KL], bl[2][KL];
+#pragma unroll
+        for (int nb8 = 0; nb8 < 2; ++nb8)
+#pragma unroll
+            for (int kk = 0; kk < KL; ++kk) bl[nb8][kk] = bnext[nb8][kk];
+        if (it + 8 < 4 * kc) load_item(it + 8, bnext);
 #pragma unroll
         for (int kk = 0; kk < 3; ++kk) ac[kk] = (g < R && 4 * kk + t4 < CAM) ? __ldg(hb + g * W + 4 * kk + t4) : 0.0;
 #pragma unroll
@@ -587,6 +598,7 @@ __global__ void __launch_bounds__(256, 3) k_wide_panel(WideParams p) {
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
     if (nb > 1) fetch_row(1);      // buffer 1; buffer 0 (= s_Pc) is free as of the barrier above
+    double nd0 = __ldg(gD + g * 8 + t4), nd1 = __ldg(gD + g * 8 + 4 + t4), ny = __ldg(gy + g);
     for (int b = 0; b < nb; ++b) {
         // V_b = Dinv_b G_b + sum_{b' < b} Lt(b, b') V_b'   (Lt = -Dinv L from k_wide_chol): every product takes its B
         // operand straight from shared memory (G_b as written by phase 1, V_b' as written by the rows before), four
@@ -596,8 +608,11 @@ __global__ void __launch_bounds__(256, 3) k_wide_panel(WideParams p) {
             __syncthreads();       // row b has landed for everyone; everyone is done with the other buffer (row b - 1)
             if (b + 1 < nb) fetch_row(b + 1);
         }
-        const double d0 = __ldg(gD + b * 64 + g * 8 + t4), d1 = __ldg(gD + b * 64 + g * 8 + 4 + t4);
-        const double yv = __ldg(gy + 8 * b + g);
+        const double d0 = nd0, d1 = nd1, yv = ny;
+        if (b + 1 < nb) {   // Dinv fragments and y of the next block row: fetched a row ahead of their use
+            nd0 = __ldg(gD + (b + 1) * 64 + g * 8 + t4); nd1 = __ldg(gD + (b + 1) * 64 + g * 8 + 4 + t4);
+            ny = __ldg(gy + 8 * (b + 1) + g);
+        }
         double v0 = 0.0, v1 = 0.0, e0 = 0.0, e1 = 0.0, f0 = 0.0, f1 = 0.0, h0 = 0.0, h1 = 0.0;
         const double* lrow = s_L + (b & 1) * LROW + g * 8 + t4;
         dmma884(f0, f1, d0, gs[(8 * b + t4) * W_VLD + g]);
