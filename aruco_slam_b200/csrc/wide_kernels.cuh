@@ -277,12 +277,41 @@ __global__ void __launch_bounds__(128, 6) k_wide_model(WideParams p) {
     {
         const int lane = tid & 31, warp = tid >> 5, g = lane >> 2, t4 = lane & 3;
         constexpr int LK = (D + 3) / 4, LN = (D + 7) / 8, NTL = 2 + LN;
-        for (int pr = warp; pr < tri(kc); pr += NT / 32) {
-            int o1 = (int)((sqrtf(8.0f * pr + 1.0f) - 1.0f) * 0.5f);
+        // the D x D landmark block P[l1.., l2..] of a pair comes from HBM in B-fragment order, one pair ahead
+        auto pair_of = [&](int pr, int& o1, int& o2) {
+            o1 = (int)((sqrtf(8.0f * pr + 1.0f) - 1.0f) * 0.5f);
             while (tri(o1 + 1) <= pr) ++o1;
             while (tri(o1) > pr) --o1;
-            const int o2 = pr - tri(o1);
+            o2 = pr - tri(o1);
+        };
+        auto load_lm = [&](int pr, double (&blk)[LK][LN]) {
+            int o1, o2;
+            pair_of(pr, o1, o2);
             const int l1 = CAM + D * s_idx[c0 + o1], l2 = CAM + D * s_idx[c0 + o2];
+#pragma unroll
+            for (int kk = 0; kk < LK; ++kk)
+#pragma unroll
+                for (int nt = 0; nt < LN; ++nt) {
+                    const int k = 4 * kk + t4, nn = 8 * nt + g;
+                    double v = 0.0;
+                    if (k < D && nn < D) {
+                        v = wt_sym(P, l1 + k, l2 + nn);
+                        if (add_q && l1 + k == l2 + nn) v += p.nz.q_lm;
+                    }
+                    blk[kk][nt] = v;
+                }
+        };
+        double nxt[LK][LN];
+        if (warp < tri(kc)) load_lm(warp, nxt);
+        for (int pr = warp; pr < tri(kc); pr += NT / 32) {
+            double cur[LK][LN];
+#pragma unroll
+            for (int kk = 0; kk < LK; ++kk)
+#pragma unroll
+                for (int nt = 0; nt < LN; ++nt) cur[kk][nt] = nxt[kk][nt];
+            if (pr + NT / 32 < tri(kc)) load_lm(pr + NT / 32, nxt);
+            int o1, o2;
+            pair_of(pr, o1, o2);
             const int sl1 = CAM + D * o1, sl2 = CAM + D * o2;
             const double* h1 = s_H + o1 * 8 * HLS + g * HLS;
             const double* h2 = s_H + o2 * 8 * HLS + g * HLS;
@@ -317,15 +346,7 @@ __global__ void __launch_bounds__(128, 6) k_wide_model(WideParams p) {
                     dmma884(mc[nt][0], mc[nt][1], a, (k < D && nn < CAM) ? s_Pc[nn * WD::TW + sl1 + k] : 0.0);
                 }
 #pragma unroll
-                for (int nt = 0; nt < LN; ++nt) {
-                    const int nn = 8 * nt + g;
-                    double v = 0.0;
-                    if (k < D && nn < D) {
-                        v = wt_sym(P, l1 + k, l2 + nn);
-                        if (add_q && l1 + k == l2 + nn) v += p.nz.q_lm;
-                    }
-                    dmma884(mc[2 + nt][0], mc[2 + nt][1], a, v);
-                }
+                for (int nt = 0; nt < LN; ++nt) dmma884(mc[2 + nt][0], mc[2 + nt][1], a, cur[kk][nt]);
             }
             // S_blk = M H2^T: M from accumulator to A-fragment layout with shuffles; k over the columns of M
             double s0 = 0.0, s1 = 0.0;
