@@ -693,13 +693,8 @@ __global__ void __launch_bounds__(W_SWEEP_THREADS, 2) k_wide_sweep(WideParams p)
     constexpr int NSL = (M8 + W_SLAB - 1) / W_SLAB;             // slabs of a full panel
     __shared__ __align__(8) uint64_t bar_full[W_NST], bar_empty[W_NST], bar_vi[NSL];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    // barrier set-up first: the init fence waits for the thread's outstanding memory operations, so it goes
-    // before the first global load of the kernel
-    if (tid == 0) {
-        for (int s = 0; s < W_NST; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 8); }
-        for (int s = 0; s < NSL; ++s) mbar_init(&bar_vi[s], 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
+    // idle work items leave before the barrier set-up (its init fence costs about a microsecond, and in a later
+    // chunk round more than half of the CTAs are idle)
     const int seq = p.seq0 + blockIdx.y;
     const int* meta = p.meta + (long long)seq * 8;
     const int m8 = meta[5];
@@ -707,6 +702,11 @@ __global__ void __launch_bounds__(W_SWEEP_THREADS, 2) k_wide_sweep(WideParams p)
     const int n = meta[3], nt8 = (n + 7) >> 3, nb64 = (n + 63) >> 6;
     const int I = (int)gridDim.x - 1 - (int)blockIdx.x;        // heavy strips first
     if (I >= nb64) return;
+    if (tid == 0) {
+        for (int s = 0; s < W_NST; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 8); }
+        for (int s = 0; s < NSL; ++s) mbar_init(&bar_vi[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     constexpr int SLAB_D = W_SLAB * W_VLD;
     double* VI = reinterpret_cast<double*>(smraw);               // M8 x W_VLD
     double* ring = VI + M8 * W_VLD;                              // W_NST x W_SLAB x W_VLD
