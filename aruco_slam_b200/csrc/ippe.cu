@@ -245,7 +245,17 @@ static int ippe_host(const float* corners, int64_t n, const double camera_matrix
     struct Cache { float* dc = nullptr; double* dout = nullptr; double* dout2 = nullptr; float* derr = nullptr; int64_t cap = 0;
                    cudaStream_t st[3] = {nullptr, nullptr, nullptr};
                    cudaEvent_t ev_in[64] = {}, ev_k[64] = {}; };
-    constexpr int64_t IPPE_CHUNK = 65536;
+#ifndef ASB_IPPE_CHUNK
+#define ASB_IPPE_CHUNK 32768
+#endif
+#ifndef ASB_IPPE_CHUNK_MAX
+#define ASB_IPPE_CHUNK_MAX 32768
+#endif
+    // slice sizes of the large-batch path (first slice, doubling up to the maximum).  Measured on the B200 box for
+    // 1M sets with page-locked buffers (tools/ippe_e2e_exp.py; both copies alone, concurrently: 1.01-1.04 ms):
+    // 32768 fixed 1.16-1.20 ms, 16384 doubling to 131072 / 262144 1.20-1.23 ms, 65536 fixed 1.38 ms (3 MB copy-outs
+    // alternate with the 2 MB copy-ins instead of overlapping)
+    constexpr int64_t IPPE_CHUNK = ASB_IPPE_CHUNK, IPPE_CHUNK_MAX = ASB_IPPE_CHUNK_MAX;
     constexpr int IPPE_EVENTS = 64;
     static std::mutex mu;
     static Cache cache[64];
@@ -261,7 +271,7 @@ static int ippe_host(const float* corners, int64_t n, const double camera_matrix
         ASB_CUDA(cudaMalloc(&c.derr, (size_t)cap * 2 * sizeof(float)));
         c.cap = cap;
     }
-    if (n >= 4 * IPPE_CHUNK) {
+    if (n >= 4 * 65536) {
         // Large batches (BASELINE config C4, 1M sets = 32 MB in + 48 MB out) go in slices: the H2D copy of slice
         // i+1, the kernel of slice i and the D2H copy of slice i-1 overlap (separate copy engines per direction).
         // One cudaMemcpyAsync per slice and buffer; with pageable host memory the copies stage through the driver
@@ -275,8 +285,10 @@ static int ippe_host(const float* corners, int64_t n, const double camera_matrix
         // slice i+2 queues behind the D2H copy of slice i and the two directions alternate instead of overlapping.
         cudaStream_t s_in = c.st[0], s_k = c.st[1], s_out = c.st[2];
         int i = 0;
-        for (int64_t o = 0; o < n; o += IPPE_CHUNK, ++i) {
-            const int64_t cn = std::min<int64_t>(IPPE_CHUNK, n - o);
+        int64_t cn = 0, chunk = IPPE_CHUNK;
+        for (int64_t o = 0; o < n; o += cn, ++i) {
+            cn = std::min<int64_t>(chunk, n - o);
+            if (i > 0) chunk = std::min<int64_t>(2 * chunk, IPPE_CHUNK_MAX);
             const int e = i % IPPE_EVENTS;
             ASB_CUDA(cudaMemcpyAsync(c.dc + 8 * o, corners + 8 * o, (size_t)cn * 8 * sizeof(float), cudaMemcpyHostToDevice, s_in));
             ASB_CUDA(cudaEventRecord(c.ev_in[e], s_in));
