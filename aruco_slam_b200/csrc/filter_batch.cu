@@ -30,7 +30,10 @@ struct asb_batch {
     int obs_seqs = 0;          // distinct observation streams on the device (n_seq, or fewer after an upload_tiled)
     long long n_obs = 0;
     int sm_count = 0, smem_optin = 0;
-    int ck = 4;       // markers per chunk
+#ifndef ASB_BATCH_CK
+#define ASB_BATCH_CK 4
+#endif
+    int ck = ASB_BATCH_CK;       // markers per chunk
     int threads = 128;
     // Pipelined host path: asb_batch_upload copies the observations in N_GROUPS sequence groups on a
     // copy stream; the asb_batch_run that follows launches one kernel per group as soon as that
@@ -105,7 +108,7 @@ static int launch_batch_nt(asb_batch* b, const BatchParams& p, size_t smem, int 
 }
 
 static int launch_batch_dyn(asb_batch* b, const BatchParams& p, size_t smem, int grid, cudaStream_t st) {
-    if (b->kind == ASB_KIND_EKF) return launch_batch_nt<0, 4>(b, p, smem, grid, st);
+    if (b->kind == ASB_KIND_EKF) return launch_batch_nt<0, ASB_BATCH_CK>(b, p, smem, grid, st);
     return launch_batch_nt<1, 4>(b, p, smem, grid, st);
 }
 
@@ -243,6 +246,7 @@ static int batch_build(asb_batch* b, int kind, int quat_mode, const double pose0
     b->kind = kind; b->quat_mode = quat_mode; b->device = device;
     b->D = kind == ASB_KIND_EKF ? 3 : 10;
     b->R = kind == ASB_KIND_EKF ? 3 : 7;
+    b->ck = kind == ASB_KIND_EKF ? ASB_BATCH_CK : 4;   // rows per chunk R * ck <= 31 (single-warp Cholesky)
     b->nz = to_noise(kind, cfg);
     b->n_seq = n_seq; b->max_lm = max_landmarks; b->max_obs = max_obs_per_frame;
     b->ncap = CAM + b->D * max_landmarks;
