@@ -215,6 +215,28 @@ def test_ippe_large_batch_vs_oracle(calibration):
     assert np.median(err) < 0.5 and err.max() < 8.0  # pixel noise is N(0, 0.3^2)
 
 
+def test_ippe_sliced_host_path_equals_single_shot(calibration):
+    """Batches of >= 262144 sets go through the three-stream slice pipeline of ippe_host (32768-set slices, a ring of
+    64 events): 2.3 M sets = 71 slices, so the ring wraps and the last slice is ragged.  Bit-exact against the same
+    sets sent in single-shot pieces of 200 000, for the one-solution and the two-solution entry points."""
+    from aruco_slam_b200 import estimate_pose_of_markers, synth
+    from aruco_slam_b200.ippe import estimate_both_poses
+    km, dist = calibration
+    base = synth.make_corner_sets(230_000, km, dist, seed=11)
+    corners = np.concatenate([base + np.float32(0.25 * i) for i in range(10)])
+    n = len(corners)
+    assert n == 2_300_000 and n % 32768 != 0
+    out = estimate_pose_of_markers(corners, km, dist, 0.16)
+    piece = 200_000
+    ref = np.concatenate([estimate_pose_of_markers(corners[o:o + piece], km, dist, 0.16) for o in range(0, n, piece)])
+    assert np.array_equal(out, ref)
+    m = 600_000
+    both, errs = estimate_both_poses(corners[:m], km, dist, 0.16)
+    rb, re = zip(*[estimate_both_poses(corners[o:o + piece], km, dist, 0.16) for o in range(0, m, piece)])
+    assert np.array_equal(both, np.concatenate(rb)) and np.array_equal(errs, np.concatenate(re))
+    assert np.array_equal(both[:, 0], out[:m])
+
+
 def test_ippe_accepts_detector_layout(calibration):
     """detectMarkers returns a tuple of (1,4,2) float32 arrays (base_filter.py:194)."""
     from aruco_slam_b200 import estimate_pose_of_markers, synth
