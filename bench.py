@@ -402,9 +402,12 @@ def leg_c4(torch, stream_ptr, hbm_peak, fp64_peak):
     keep_c, h_corners = pinned_like(corners)
     keep_o, h_out = pinned_like(np.zeros((n, 6)))
     estimate_pose_of_markers(h_corners, km, dist, 0.16, out=h_out)   # warm (buffers of the call grow once)
-    t0 = time.perf_counter()
-    out = estimate_pose_of_markers(h_corners, km, dist, 0.16, out=h_out)
-    wall = time.perf_counter() - t0
+    walls = []
+    for _ in range(5):   # median of five calls (each: 32 MB in, kernels, 48 MB out, synchronous return)
+        t0 = time.perf_counter()
+        out = estimate_pose_of_markers(h_corners, km, dist, 0.16, out=h_out)
+        walls.append(time.perf_counter() - t0)
+    wall = sorted(walls)[2]
     ach = 80.0 * n / (ms * 1e-3) / 1e9
     return {"workload": "C4: batched IPPE square-marker pose, 1M corner sets", "value": n / (ms * 1e-3),
             "unit": "poses/s", "ms_per_batch": ms,
