@@ -199,23 +199,32 @@ template <int KIND> static int wide_run(asb_batch* b, int t0, int t1) {
     // tensor-pipe-bound ones (panel, sweep) of the others.  Frames stay ordered inside a group (stream order).
     const int ngroups = b->w_groups;
     ASB_CUDA(cudaEventRecord(b->ev_main, b->stream));
-    for (int gidx = 0; gidx < ngroups; ++gidx) {
-        cudaStream_t st = ngroups == 1 ? b->stream : b->w_streams[gidx];
-        if (ngroups > 1) ASB_CUDA(cudaStreamWaitEvent(st, b->ev_main, 0));
-        const int s0 = (int)((long long)b->n_seq * gidx / ngroups), s1 = (int)((long long)b->n_seq * (gidx + 1) / ngroups);
-        if (s1 == s0) continue;
-        p.seq0 = s0;
-        const dim3 g_panel(b->w_nb64, s1 - s0), g_sweep(b->w_nb64, s1 - s0);
-        for (int t = t0; t < t1; ++t) {
-            const int rounds = (b->kmax[t] + WCK - 1) / WCK;
-            for (int r = 0; r < rounds; ++r) {
-                p.t = t; p.round = r;
+    auto group_stream = [&](int gidx) { return ngroups == 1 ? b->stream : b->w_streams[gidx]; };
+    auto group_first = [&](int gidx) { return (int)((long long)b->n_seq * gidx / ngroups); };
+    if (ngroups > 1)
+        for (int gidx = 0; gidx < ngroups; ++gidx) ASB_CUDA(cudaStreamWaitEvent(group_stream(gidx), b->ev_main, 0));
+    // frames outermost, groups inside: a long run queues thousands of launches, and issued group by group the
+    // first group's backlog would fill the launch queue before the second stream gets anything to overlap with
+    for (int t = t0; t < t1; ++t) {
+        const int rounds = (b->kmax[t] + WCK - 1) / WCK;
+        for (int r = 0; r < rounds; ++r)
+            for (int gidx = 0; gidx < ngroups; ++gidx) {
+                const int s0 = group_first(gidx), s1 = group_first(gidx + 1);
+                if (s1 == s0) continue;
+                cudaStream_t st = group_stream(gidx);
+                p.seq0 = s0; p.t = t; p.round = r;
+                const dim3 g_strips(b->w_nb64, s1 - s0);
                 k_wide_model<KIND><<<s1 - s0, 128, sm_model, st>>>(p);
                 k_wide_chol<KIND><<<s1 - s0, 128, sm_chol, st>>>(p);
-                k_wide_panel<KIND><<<g_panel, 256, sm_panel, st>>>(p);
-                k_wide_sweep<KIND><<<g_sweep, W_SWEEP_THREADS, sm_sweep, st>>>(p);
+                k_wide_panel<KIND><<<g_strips, 256, sm_panel, st>>>(p);
+                k_wide_sweep<KIND><<<g_strips, W_SWEEP_THREADS, sm_sweep, st>>>(p);
             }
-        }
+    }
+    for (int gidx = 0; gidx < ngroups; ++gidx) {
+        const int s0 = group_first(gidx), s1 = group_first(gidx + 1);
+        if (s1 == s0) continue;
+        cudaStream_t st = group_stream(gidx);
+        p.seq0 = s0;
         k_wide_apply<KIND><<<s1 - s0, 64, 0, st>>>(p);
         if (ngroups > 1) {
             ASB_CUDA(cudaEventRecord(b->w_done[gidx], st));

@@ -217,7 +217,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(json.dumps(line))
 
 
 def workload_config(args):
@@ -617,7 +617,7 @@ def run_b200(args):
     if args.only:
         leg = extra_leg(args.only)
         if rank == 0:
-            print(json.dumps(leg), flush=True)
+            emit(json.dumps(leg))
         if dist is not None:
             dist.destroy_process_group()
         return
@@ -775,13 +775,30 @@ def run_b200(args):
                       f"oracle/ekf_oracle.py (numpy restatement of the reference algorithm), "
                       f"{wall_cpu:.1f} s on {os.cpu_count()} host cores (1 used)"}
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()
 
 
+_RESULT_FD = None
+
+
+def emit(text):
+    """The result line goes to the process's ORIGINAL stdout; everything else printed while the run is going on
+    (NCCL's version banner, library chatter) lands on stderr, so stdout carries the one JSON line only."""
+    sys.stderr.flush()
+    if _RESULT_FD is None:
+        print(text, flush=True)
+    else:
+        os.write(_RESULT_FD, (text + "\n").encode())
+
+
 def main():
+    global _RESULT_FD
     args = parse_args()
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:
