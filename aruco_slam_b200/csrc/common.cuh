@@ -59,5 +59,6 @@ inline Noise to_noise(int kind, const asb_noise* cfg) {
 }
 
 inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
+inline size_t round_up16(size_t v) { return (v + 15) & ~size_t(15); }
 
 }  // namespace asb

@@ -46,8 +46,9 @@ struct asb_filter {
     // opt-in moving-average motion model (README.md:55-56; absent from the reference code)
     int motion_window = 0; long long motion_frames = 0; double* d_hist = nullptr;
     // staging ring (host pinned + device)
-    int* h_idx = nullptr; double* h_pose = nullptr; unsigned char* h_new = nullptr;
-    int* d_idx = nullptr; double* d_pose = nullptr; unsigned char* d_new = nullptr;
+    // per-frame staging, N_SLOTS slots of stage_stride bytes: [poses k x 6 f64 | idx k x i32 | isnew k x u8], each part
+    // 16-byte aligned, so that one frame's observations go to the device in ONE copy
+    unsigned char* h_stage = nullptr; unsigned char* d_stage = nullptr; size_t stage_stride = 0;
     cudaEvent_t slot_ev[N_SLOTS]{};
     float* h_corner = nullptr; float* d_corner = nullptr;   // asb_observe_corners: (slot, max_obs, 4, 2) float32
     cudaEvent_t ev_pose = nullptr;                            // the IPPE poses of that call are back on the host
@@ -376,31 +377,33 @@ static int stage(asb_filter* f, const std::vector<int>& idx, const double* poses
     const int s = f->slot;
     f->slot = (f->slot + 1) % N_SLOTS;
     ASB_CUDA(cudaEventSynchronize(f->slot_ev[s]));
-    const size_t o = (size_t)s * f->max_obs;
-    std::memcpy(f->h_idx + o, idx.data(), k * sizeof(int));
-    std::memcpy(f->h_new + o, isnew.data(), k);
-    ASB_CUDA(cudaMemcpyAsync(f->d_idx + o, f->h_idx + o, k * sizeof(int), cudaMemcpyHostToDevice, st));
+    // slot layout, compact in k: poses at 0, idx at off_idx, isnew at off_new (one contiguous copy)
+    const size_t off_idx = round_up16((size_t)k * 48), off_new = off_idx + round_up16((size_t)k * 4);
+    const size_t bytes = off_new + (size_t)k;
+    unsigned char* hs = f->h_stage + (size_t)s * f->stage_stride;
+    unsigned char* ds = f->d_stage + (size_t)s * f->stage_stride;
+    std::memcpy(hs + off_idx, idx.data(), k * sizeof(int));
+    std::memcpy(hs + off_new, isnew.data(), k);
     if (feed) {
+        const size_t o = (size_t)s * f->max_obs;
         std::memcpy(f->h_corner + 8 * o, feed->corners, (size_t)k * 8 * sizeof(float));
         ASB_CUDA(cudaMemcpyAsync(f->d_corner + 8 * o, f->h_corner + 8 * o, (size_t)k * 8 * sizeof(float),
                                  cudaMemcpyHostToDevice, st));
+        ASB_CUDA(cudaMemcpyAsync(ds + off_idx, hs + off_idx, bytes - off_idx, cudaMemcpyHostToDevice, st));
         int rc = asb_ippe_square_device(f->d_corner + 8 * o, k, feed->camera_matrix, feed->dist_coeffs,
-                                        feed->marker_size, f->d_pose + 6 * o, nullptr, nullptr, st);
+                                        feed->marker_size, reinterpret_cast<double*>(ds), nullptr, nullptr, st);
         if (rc != ASB_OK) return rc;
-        ASB_CUDA(cudaMemcpyAsync(f->h_pose + 6 * o, f->d_pose + 6 * o, (size_t)k * 6 * sizeof(double),
-                                 cudaMemcpyDeviceToHost, st));
+        ASB_CUDA(cudaMemcpyAsync(hs, ds, (size_t)k * 6 * sizeof(double), cudaMemcpyDeviceToHost, st));
         ASB_CUDA(cudaEventRecord(f->ev_pose, st));
-        if (h_pose_slot) *h_pose_slot = f->h_pose + 6 * o;
+        if (h_pose_slot) *h_pose_slot = reinterpret_cast<double*>(hs);
     } else {
-        std::memcpy(f->h_pose + 6 * o, poses, (size_t)k * 6 * sizeof(double));
-        ASB_CUDA(cudaMemcpyAsync(f->d_pose + 6 * o, f->h_pose + 6 * o, (size_t)k * 6 * sizeof(double),
-                                 cudaMemcpyHostToDevice, st));
+        std::memcpy(hs, poses, (size_t)k * 6 * sizeof(double));
+        ASB_CUDA(cudaMemcpyAsync(ds, hs, bytes, cudaMemcpyHostToDevice, st));
     }
-    ASB_CUDA(cudaMemcpyAsync(f->d_new + o, f->h_new + o, k, cudaMemcpyHostToDevice, st));
     ASB_CUDA(cudaEventRecord(f->slot_ev[s], st));
-    *d_idx = f->d_idx + o;
-    *d_pose = f->d_pose + 6 * o;
-    *d_new = f->d_new + o;
+    *d_idx = reinterpret_cast<int*>(ds + off_idx);
+    *d_pose = reinterpret_cast<double*>(ds);
+    *d_new = ds + off_new;
     return ASB_OK;
 }
 
@@ -524,12 +527,9 @@ static int filter_build(asb_filter* f, int kind, int quat_mode, const double pos
     ASB_CUDA(dmalloc(&f->d_status, 1));
     ASB_CUDA(dmalloc(&f->d_prof, 32));
     ASB_CUDA(cudaMemsetAsync(f->d_prof, 0, 32 * sizeof(unsigned long long), f->stream));
-    ASB_CUDA(dmalloc(&f->d_idx, (size_t)N_SLOTS * f->max_obs));
-    ASB_CUDA(dmalloc(&f->d_pose, (size_t)N_SLOTS * f->max_obs * 6));
-    ASB_CUDA(dmalloc(&f->d_new, (size_t)N_SLOTS * f->max_obs));
-    ASB_CUDA(cudaMallocHost(&f->h_idx, (size_t)N_SLOTS * f->max_obs * sizeof(int)));
-    ASB_CUDA(cudaMallocHost(&f->h_pose, (size_t)N_SLOTS * f->max_obs * 6 * sizeof(double)));
-    ASB_CUDA(cudaMallocHost(&f->h_new, (size_t)N_SLOTS * f->max_obs));
+    f->stage_stride = round_up16((size_t)f->max_obs * 48) + round_up16((size_t)f->max_obs * 4) + round_up16((size_t)f->max_obs);
+    ASB_CUDA(dmalloc(&f->d_stage, (size_t)N_SLOTS * f->stage_stride));
+    ASB_CUDA(cudaMallocHost(&f->h_stage, (size_t)N_SLOTS * f->stage_stride));
     ASB_CUDA(cudaMallocHost(&f->h_corner, (size_t)N_SLOTS * f->max_obs * 8 * sizeof(float)));
     ASB_CUDA(dmalloc(&f->d_corner, (size_t)N_SLOTS * f->max_obs * 8));
     ASB_CUDA(cudaEventCreateWithFlags(&f->ev_pose, cudaEventDisableTiming));
@@ -611,9 +611,9 @@ int asb_filter_destroy(asb_filter* f) {
     cudaFree(f->d_tail); cudaFree(f->d_P2); cudaFree(f->d_At); cudaFree(f->d_y); cudaFree(f->d_T); cudaFree(f->d_counter); cudaFree(f->d_ctaprof); cudaFree(f->d_Vt);
     cudaFree(f->d_state); cudaFree(f->d_P); cudaFree(f->d_Vr); cudaFree(f->d_Vc); cudaFree(f->d_blocks); cudaFree(f->d_nu);
     cudaFree(f->d_dx[0]); cudaFree(f->d_dx[1]); cudaFree(f->d_unc);
-    cudaFree(f->d_status); cudaFree(f->d_prof); cudaFree(f->d_idx); cudaFree(f->d_pose); cudaFree(f->d_new);
+    cudaFree(f->d_status); cudaFree(f->d_prof); cudaFree(f->d_stage);
     cudaFree(f->s_idx); cudaFree(f->s_pose); cudaFree(f->s_new); cudaFree(f->d_gate); cudaFree(f->d_gate_i); cudaFree(f->d_hist);
-    cudaFreeHost(f->h_idx); cudaFreeHost(f->h_pose); cudaFreeHost(f->h_new);
+    cudaFreeHost(f->h_stage);
     cudaFreeHost(f->h_corner); cudaFree(f->d_corner);
     if (f->ev_pose) cudaEventDestroy(f->ev_pose);
     for (auto& e : f->slot_ev) cudaEventDestroy(e);
