@@ -174,7 +174,10 @@ k_f1(F1Args p) {
                 if (s_new[o2] && s_idx[o2] == s_idx[o]) { src = o2; break; }
 #pragma unroll
         for (int c = 0; c < D; ++c) lm[c] = s_lm[src * D + c];
-        double lnu[R], blk[R * W];
+        // the dense block goes straight to shared memory: as a local array its R x W values (140 for
+        // EKF_Rotations) do not fit the register file and the model ran out of local memory
+        double lnu[R];
+        double* blk = s_blk + (size_t)o * R * W;
         observation_model<KIND>(s_cam, lm, p.poses + 6 * o, lnu, blk);
         if (p.nu_out) {
 #pragma unroll
@@ -196,8 +199,6 @@ k_f1(F1Args p) {
         }
 #pragma unroll
         for (int r = 0; r < R; ++r) s_nu[R * o + r] = lnu[r];
-#pragma unroll
-        for (int c = 0; c < R * W; ++c) s_blk[o * R * W + c] = blk[c];
     }
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();

@@ -29,3 +29,17 @@ for cls, kind in ((EKF, "ekf"), (EKF_Rotations, "rot")):
         if t >= 50: t_lib += b - a
     print(f"{kind}: asb_observe alone (asynchronous return) {t_lib/n*1e6:.1f} us per frame")
     f2.get_poses()
+
+# k_f1 / k_f2 phase times of the last update (globaltimer stamps, asb_front_profile)
+import ctypes as C
+for cls, kind in ((EKF, "ekf"), (EKF_Rotations, "rot")):
+    st = synth.make_stream(1234, 10, 300, 0.8, kind)
+    f = cls(pose0, camera_matrix=km, dist_coeffs=dist)
+    acc = np.zeros(12); cnt = 0
+    for t in range(300):
+        f.observe(st.ids[t], st.poses[t])
+        if t >= 50 and len(st.ids[t]) <= 8:
+            us = (C.c_double * 12)()
+            _lib.check(_lib.lib().asb_front_profile(f._h, us)); acc += np.array(us[:]); cnt += 1
+    names = ["f1 index set + copy issue", "f1 model + copy wait", "f1 lazy operand + Q + S", "f1 cholesky", "f1 outputs (A = L^-1 H)", "f1 total", "f1 start->f2 start", "f1 start->f2 end", "f2 loads", "f2 product", "f2 stores", "-"]
+    print(kind, "single-chunk frames:", ", ".join(f"{n} {v:.1f}" for n, v in zip(names, acc / max(cnt, 1))))
