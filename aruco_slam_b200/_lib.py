@@ -70,6 +70,7 @@ SIGNATURES = {
     "asb_set_landmarks": (C.c_int, [_vp, _ip, C.c_int]),
     "asb_device_views": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp), _intp]),
     "asb_set_motion_model": (C.c_int, [_vp, C.c_int]),
+    "asb_set_small_map_limit": (C.c_int, [_vp, C.c_int]),
     "asb_correct_poses": (C.c_int, [_vp, _ip, _dp, _dp, C.c_int, C.c_double, _ip]),
     "asb_get_last_update": (C.c_int, [_vp, _dp, _dp, _dp, _intp]),
     "asb_batch_create": (C.c_int, [C.c_int, C.c_int, _dp, C.POINTER(Noise), C.c_int, C.c_int,

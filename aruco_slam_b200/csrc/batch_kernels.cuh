@@ -33,6 +33,14 @@ struct BatchParams {
     int obs_seqs;          // distinct observation streams: sequence s reads stream s % obs_seqs (= n_seq unless tiled)
     Noise nz;
     unsigned long long* prof;   // 10 phase accumulators (clocks) of CTA 0, may be null
+    // SINGLE instantiation (one frame of ONE asb_filter whose map is small enough for an SM, filter_single.cu):
+    // the covariance is that filter's dense array (lower triangle valid, leading dimension ld), the host has
+    // already associated the ids (landmark index + first-sighting flag per observation), the frame's k poses
+    // are at `poses`; raw innovations / measurement blocks / dx are left for asb_get_last_update
+    const int* one_idx; const unsigned char* one_new;
+    int one_k, one_nlm0, one_nlm1, ld;
+    double *nu_out, *blocks_out, *dx_out;
+    double* one_state_host; int* one_status_host;   // page-locked host mirror of the posterior state + status (may be null)
 };
 
 __host__ __device__ __forceinline__ int tri(int i) { return (i * (i + 1)) >> 1; }
@@ -63,8 +71,8 @@ __device__ __forceinline__ double psym(const double* P, int i, int j) {
     return j <= i ? P[tri(i) + j] : P[tri(j) + i];
 }
 
-template <int KIND, int CK, int NT>
-__global__ void __launch_bounds__(NT, (NT <= 128 && KIND == 0) ? 3 : 1)
+template <int KIND, int CK, int NT, bool SINGLE = false>
+__global__ void __launch_bounds__(NT, (NT <= 128 && KIND == 0 && !SINGLE) ? 3 : 1)
 k_batch(BatchParams p) {
     constexpr int D = Dims<KIND>::D, R = Dims<KIND>::R, W = CAM + D;
     constexpr int MC = R * CK;           // max rows per chunk
@@ -118,56 +126,85 @@ k_batch(BatchParams p) {
             P[tidx(i, j)] = v;
             if ((i >> 3) == (j >> 3)) P[tchunk(tri(i >> 3) + (j >> 3), ((j & 7) << 2) + ((i & 7) >> 1)) + (i & 1)] = v;
         };
-        int nlm = p.nlm[seq];
+        int nlm = SINGLE ? p.one_nlm0 : p.nlm[seq];
         int n = CAM + D * nlm;
         for (int i = tid; i < n; i += NT) s_state[i] = g_state[i];
-        for (int i = tid; i < nlm; i += NT) s_tab[i] = g_tab[i];
+        if constexpr (!SINGLE)
+            for (int i = tid; i < nlm; i += NT) s_tab[i] = g_tab[i];
         {
             for (int e = tid; e < tiled_doubles(ncap); e += NT) s_P[e] = 0.0;
             __syncthreads();
-            for (int i = tid; i < n; i += NT)
-                for (int j = 0; j <= i; ++j) pset(i, j, g_P[tri(i) + j]);
+            if constexpr (SINGLE) {
+                // dense rows; eight independent loads per thread in flight (a load -> store -> next-load chain
+                // costs an L2 round trip per element: 28 us for N = 110)
+                const int nn = n * n;
+                for (int base = 0; base < nn; base += 8 * NT) {
+                    double v[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
+                        const int e = base + u * NT + tid, i = e / n, j = e - i * n;
+                        v[u] = (e < nn && j <= i) ? __ldcg(g_P + (long long)i * p.ld + j) : 0.0;
+                    }
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
+                        const int e = base + u * NT + tid, i = e / n, j = e - i * n;
+                        if (e < nn && j <= i) pset(i, j, v[u]);
+                    }
+                }
+            } else {
+                for (int i = tid; i < n; i += NT)
+                    for (int j = 0; j <= i; ++j) pset(i, j, g_P[tri(i) + j]);
+            }
         }
         if (tid == 0) s_misc[1] = 0;
         __syncthreads();
 
         for (int t = p.t0; t < p.t1; ++t) {
-            const long long orec = (long long)(seq % p.obs_seqs) * p.n_frames + t;
-            const long long ob = p.offsets[orec];
-            const int k = (int)(p.offsets[orec + 1] - ob);
+            long long ob = 0;
+            int k = p.one_k;
+            if constexpr (!SINGLE) {
+                const long long orec = (long long)(seq % p.obs_seqs) * p.n_frames + t;
+                ob = p.offsets[orec];
+                k = (int)(p.offsets[orec + 1] - ob);
+            }
             if (k == 0) continue;  // no detection: no predict either (base_filter.py:197-204)
             if (k > p.max_obs) {
                 if (tid == 0) s_misc[1] = ASB_ERR_CAPACITY;
                 break;
             }
             // ---- load the frame, associate ids ---------------------------------------
-            for (int o = tid; o < k; o += NT) s_ids[o] = p.ids[ob + o];
             for (int e = tid; e < 6 * k; e += NT) s_pose[e] = p.poses[6 * ob + e];
-            __syncthreads();
-            for (int o = tid; o < k; o += NT) {
-                const int id = s_ids[o];
-                int found = -1;
-                for (int i = 0; i < nlm; ++i)
-                    if (s_tab[i] == id) { found = i; break; }
-                s_idx[o] = found;
-                s_new[o] = 0;
-            }
-            __syncthreads();
-            if (tid == 0) {  // unseen ids, in frame order; duplicates bind to the first
-                int cur = nlm;
-                for (int o = 0; o < k; ++o) {
-                    if (s_idx[o] >= 0) continue;
+            if constexpr (SINGLE) {   // associated on the host (first-seen order, the same rule as below)
+                for (int o = tid; o < k; o += NT) { s_idx[o] = p.one_idx[o]; s_new[o] = p.one_new[o]; }
+                if (tid == 0) s_misc[0] = p.one_nlm1;
+            } else {
+                for (int o = tid; o < k; o += NT) s_ids[o] = p.ids[ob + o];
+                __syncthreads();
+                for (int o = tid; o < k; o += NT) {
                     const int id = s_ids[o];
                     int found = -1;
-                    for (int i = nlm; i < cur; ++i)
+                    for (int i = 0; i < nlm; ++i)
                         if (s_tab[i] == id) { found = i; break; }
-                    if (found < 0) {
-                        if (cur >= p.max_lm) { s_misc[1] = ASB_ERR_CAPACITY; found = 0; }
-                        else { s_tab[cur] = id; found = cur++; s_new[o] = 1; }
-                    }
                     s_idx[o] = found;
+                    s_new[o] = 0;
                 }
-                s_misc[0] = cur;
+                __syncthreads();
+                if (tid == 0) {  // unseen ids, in frame order; duplicates bind to the first
+                    int cur = nlm;
+                    for (int o = 0; o < k; ++o) {
+                        if (s_idx[o] >= 0) continue;
+                        const int id = s_ids[o];
+                        int found = -1;
+                        for (int i = nlm; i < cur; ++i)
+                            if (s_tab[i] == id) { found = i; break; }
+                        if (found < 0) {
+                            if (cur >= p.max_lm) { s_misc[1] = ASB_ERR_CAPACITY; found = 0; }
+                            else { s_tab[cur] = id; found = cur++; s_new[o] = 1; }
+                        }
+                        s_idx[o] = found;
+                    }
+                    s_misc[0] = cur;
+                }
             }
             __syncthreads();
             BPROF(0);
@@ -218,6 +255,12 @@ k_batch(BatchParams p) {
                 observation_model<KIND>(s_state, lm, s_pose + 6 * (c0m + o), lnu, s_blk0 + (which * CK + o) * R * W);
 #pragma unroll
                 for (int r = 0; r < R; ++r) s_nu0[which * NU_LD + R * o + r] = lnu[r];
+                if constexpr (SINGLE) {
+                    const double* blk = s_blk0 + (which * CK + o) * R * W;
+#pragma unroll
+                    for (int r = 0; r < R; ++r) p.nu_out[R * (c0m + o) + r] = lnu[r];
+                    for (int c = 0; c < R * W; ++c) p.blocks_out[(size_t)(c0m + o) * R * W + c] = blk[c];
+                }
             };
             for (int o = tid; o < min(CK, k); o += NT) eval_model(0, 0, o);
             __syncthreads();
@@ -422,6 +465,8 @@ k_batch(BatchParams p) {
             }  // chunks
 
             // ---- state update + quaternion reset --------------------------------------
+            if constexpr (SINGLE)
+                for (int i = tid; i < n; i += NT) p.dx_out[i] = s_delta[i];
             if (tid == 0) camera_reset(s_state, s_delta, p.as_written);
             for (int l = tid; l < nlm; l += NT)
                 landmark_update<KIND>(s_state + CAM + D * l, s_delta + CAM + D * l);
@@ -431,12 +476,22 @@ k_batch(BatchParams p) {
 
         // ---- write back -----------------------------------------------------------------
         for (int i = tid; i < n; i += NT) g_state[i] = s_state[i];
-        for (int i = tid; i < nlm; i += NT) g_tab[i] = s_tab[i];
-        for (int i = tid; i < n; i += NT)
+        if constexpr (SINGLE) {
+            if (p.one_state_host) {   // the caller reads the pose from here after an event wait: no copy operation
+                for (int i = tid; i < n; i += NT) p.one_state_host[i] = s_state[i];
+                if (tid == 0) *p.one_status_host = s_misc[1];
+            }
+            for (int i = tid >> 5; i < n; i += NT / 32)
+                for (int j = tid & 31; j <= i; j += 32) g_P[(long long)i * p.ld + j] = s_P[tidx(i, j)];
+            if (tid == 0 && s_misc[1] != 0) p.status[0] = s_misc[1];
+        } else {
+            for (int i = tid; i < nlm; i += NT) g_tab[i] = s_tab[i];
+            for (int i = tid; i < n; i += NT)
                 for (int j = 0; j <= i; ++j) g_P[tri(i) + j] = s_P[tidx(i, j)];
-        if (tid == 0) {
-            p.nlm[seq] = nlm;
-            if (s_misc[1] != 0) p.status[seq] = s_misc[1];
+            if (tid == 0) {
+                p.nlm[seq] = nlm;
+                if (s_misc[1] != 0) p.status[seq] = s_misc[1];
+            }
         }
         __syncthreads();
     }

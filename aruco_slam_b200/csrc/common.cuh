@@ -58,6 +58,21 @@ inline Noise to_noise(int kind, const asb_noise* cfg) {
     return n;
 }
 
+// One observe() of a single filter whose whole covariance fits an SM's shared memory: ONE launch of the resident
+// batched kernel's SINGLE instantiation (batch_kernels.cuh) instead of the pipelined k_f1 / k_f2 / k_sweep.
+// Defined in filter_batch.cu (the translation unit that instantiates k_batch), used by filter_single.cu.
+struct SmallFrame {
+    int kind, as_written;
+    double* state; double* P; int ld;           // the filter's dense covariance (lower triangle valid)
+    const int* idx; const unsigned char* isnew; const double* poses; int k;   // this frame, on the device
+    int nlm0, nlm1;                              // landmarks before / after this frame's first sightings
+    Noise nz;
+    int* status; double* nu_out; double* blocks_out; double* dx_out;
+    double* host_state; int* host_status;        // page-locked mirror the kernel writes the posterior state into (or null)
+};
+size_t small_frame_smem(int kind, int nlm1, int k);     // dynamic shared memory the launch needs
+int small_frame_launch(const SmallFrame& a, cudaStream_t st);
+
 inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
 inline size_t round_up16(size_t v) { return (v + 15) & ~size_t(15); }
 

@@ -235,6 +235,49 @@ template <int KIND> static int wide_run(asb_batch* b, int t0, int t1) {
     return ASB_OK;
 }
 
+// ---- one frame of a single small-map filter on the resident kernel (declared in common.cuh) ----------------
+namespace asb {
+
+size_t small_frame_smem(int kind, int nlm1, int k) {
+    const int D = kind == ASB_KIND_EKF ? 3 : 10, R = kind == ASB_KIND_EKF ? 3 : 7;
+    return batch_smem_base(D, R, 4, nlm1, k) + (size_t)tiled_doubles(CAM + D * nlm1) * sizeof(double);
+}
+
+template <int KIND, int NT>
+static int small_launch(const BatchParams& p, size_t smem, cudaStream_t st) {
+    auto kern = k_batch<KIND, 4, NT, true>;
+    static size_t granted[64] = {};   // per device: the largest dynamic shared-memory size asked for so far
+    int dev = 0;
+    ASB_CUDA(cudaGetDevice(&dev));
+    if (smem > granted[dev & 63]) {
+        ASB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        granted[dev & 63] = smem;
+    }
+    kern<<<1, NT, smem, st>>>(p);
+    ASB_CUDA(cudaGetLastError());
+    return ASB_OK;
+}
+
+int small_frame_launch(const SmallFrame& a, cudaStream_t st) {
+    BatchParams p{};
+    p.states = a.state; p.covs = a.P; p.ld = a.ld;
+    p.status = a.status;
+    p.poses = a.poses;
+    p.n_seq = 1; p.n_frames = 1; p.t0 = 0; p.t1 = 1; p.seq0 = 0; p.seq1 = 1; p.obs_seqs = 1;
+    p.max_lm = a.nlm1; p.max_obs = a.k;
+    p.as_written = a.as_written;
+    p.nz = a.nz;
+    p.one_idx = a.idx; p.one_new = a.isnew; p.one_k = a.k; p.one_nlm0 = a.nlm0; p.one_nlm1 = a.nlm1;
+    p.nu_out = a.nu_out; p.blocks_out = a.blocks_out; p.dx_out = a.dx_out;
+    p.one_state_host = a.host_state; p.one_status_host = a.host_status;
+    const size_t smem = small_frame_smem(a.kind, a.nlm1, a.k);
+    // 256 threads at every size: the CTA has its SM to itself, and measured against 128 threads it is faster from
+    // N = 40 (41.4 vs 42.6 us per frame) to N = 150 (99.6 vs 125.8 us, EKF_Rotations) - tools/small_map_exp.py
+    return a.kind == ASB_KIND_EKF ? small_launch<0, 256>(p, smem, st) : small_launch<1, 256>(p, smem, st);
+}
+
+}  // namespace asb
+
 extern "C" {
 
 int asb_batch_reset(asb_batch* b) {

@@ -16,6 +16,10 @@
 
 using namespace asb;
 
+#ifndef ASB_SMALL_MAP_DEFAULT
+#define ASB_SMALL_MAP_DEFAULT 192
+#endif
+
 namespace {
 constexpr uint32_t FILTER_MAGIC = 0x41534246;  // "ASBF"
 constexpr int N_SLOTS = 8;                     // staging ring depth
@@ -49,6 +53,9 @@ struct asb_filter {
     // per-frame staging, N_SLOTS slots of stage_stride bytes: [poses k x 6 f64 | idx k x i32 | isnew k x u8], each part
     // 16-byte aligned, so that one frame's observations go to the device in ONE copy
     unsigned char* h_stage = nullptr; unsigned char* d_stage = nullptr; size_t stage_stride = 0;
+    // one-launch frames: the kernel reads the staged observations straight from the page-locked slot and writes the
+    // posterior state + status into this page-locked mirror (ncap doubles, then the status int)
+    double* h_mirror = nullptr;
     cudaEvent_t slot_ev[N_SLOTS]{};
     float* h_corner = nullptr; float* d_corner = nullptr;   // asb_observe_corners: (slot, max_obs, 4, 2) float32
     cudaEvent_t ev_pose = nullptr;                            // the IPPE poses of that call are back on the host
@@ -69,6 +76,7 @@ struct asb_filter {
     unsigned int* d_counter = nullptr;
     cudaStream_t side = nullptr;
     cudaEvent_t ev_ready = nullptr, ev_f1 = nullptr;
+    bool state_on_main = false;    // ... and nothing is queued behind it on the main stream (one-launch frame)
     bool state_at_ready = false;   // the state vector is final at ev_ready (only a sweep is queued behind it):
                                    // asb_get_state need not wait for that sweep
     bool lazy = false;         // d_P2 holds the input of the sweep launched last, d_Vr its panel
@@ -93,6 +101,10 @@ struct asb_filter {
     int lower_only = 0;        // pipelined engine: the sweeps keep only the lower triangle of P up to date (ASB_FULL_P=1: both)
     bool defer = false;        // set by asb_stream_run around its frame loop
     int pdl = 1;               // ASB_PDL=0: stream mode uses the side-stream engine as well
+
+    // observe() on a map of at most small_n_max state dims runs as ONE launch of the resident batched kernel
+    // (common.cuh SmallFrame); larger maps take the pipelined k_f1 / k_f2 / k_sweep engine.  0 = never.
+    int small_n_max = ASB_SMALL_MAP_DEFAULT;
 
     int n_state() const { return CAM + D * nlm; }
 };
@@ -337,11 +349,13 @@ static int launch_frame(asb_filter* f, const int* idx, const double* pose, const
             f->lazy = true; f->prev_m4 = m4; f->prev_add_q = a.add_q;
         }
         f->dx_last = f->d_dx[cur];
+        f->state_on_main = false;
         f->state_at_ready = !(f->defer && f->pdl);   // per-frame mode: ev_ready was recorded right after the last k_f2
     } else if (!do_update || k == 0) {
         flush_pending(f, false);
         f->lazy = false;
         f->state_at_ready = false;
+        f->state_on_main = false;
         // predict() / add_marker() on their own: diagonal add, covariance growth, new states
         long long work = (long long)n0 + (long long)(n1 - n0) * (n1 + n0);
         int grid = (int)std::min<long long>(1 + work / 1024, 592);
@@ -530,6 +544,7 @@ static int filter_build(asb_filter* f, int kind, int quat_mode, const double pos
     f->stage_stride = round_up16((size_t)f->max_obs * 48) + round_up16((size_t)f->max_obs * 4) + round_up16((size_t)f->max_obs);
     ASB_CUDA(dmalloc(&f->d_stage, (size_t)N_SLOTS * f->stage_stride));
     ASB_CUDA(cudaMallocHost(&f->h_stage, (size_t)N_SLOTS * f->stage_stride));
+    ASB_CUDA(cudaMallocHost(&f->h_mirror, ((size_t)f->ncap + 2) * sizeof(double)));
     ASB_CUDA(cudaMallocHost(&f->h_corner, (size_t)N_SLOTS * f->max_obs * 8 * sizeof(float)));
     ASB_CUDA(dmalloc(&f->d_corner, (size_t)N_SLOTS * f->max_obs * 8));
     ASB_CUDA(cudaEventCreateWithFlags(&f->ev_pose, cudaEventDisableTiming));
@@ -613,7 +628,7 @@ int asb_filter_destroy(asb_filter* f) {
     cudaFree(f->d_dx[0]); cudaFree(f->d_dx[1]); cudaFree(f->d_unc);
     cudaFree(f->d_status); cudaFree(f->d_prof); cudaFree(f->d_stage);
     cudaFree(f->s_idx); cudaFree(f->s_pose); cudaFree(f->s_new); cudaFree(f->d_gate); cudaFree(f->d_gate_i); cudaFree(f->d_hist);
-    cudaFreeHost(f->h_stage);
+    cudaFreeHost(f->h_stage); cudaFreeHost(f->h_mirror);
     cudaFreeHost(f->h_corner); cudaFree(f->d_corner);
     if (f->ev_pose) cudaEventDestroy(f->ev_pose);
     for (auto& e : f->slot_ev) cudaEventDestroy(e);
@@ -674,6 +689,59 @@ static int observe_impl(asb_filter* f, const int32_t* ids, const double* poses, 
     }
     const int n1 = f->n_state();
     int* d_idx = nullptr; double* d_pose = nullptr; unsigned char* d_new = nullptr;
+    if (k > 0 && add_new && do_predict && f->side && n1 <= f->small_n_max &&
+        small_frame_smem(f->kind, f->nlm, k) <= (size_t)f->smem_optin) {
+        // small map: the whole frame in one launch on the main stream (no side stream, no ping-pong)
+        flush_pending(f, false);
+        if (f->motion_window > 0)
+            k_motion<<<1, 32, 0, f->stream>>>(f->d_state, f->d_hist, f->motion_frames++, f->motion_window);
+        double* h_slot = nullptr;
+        int rc = ASB_OK;
+        int mapped_slot = -1;
+        if (feed) {
+            rc = stage(f, idx, poses, isnew, k, &d_idx, &d_pose, &d_new, f->stream, feed, &h_slot);
+            if (rc != ASB_OK) return rc;
+        } else {
+            // no copy operation: the kernel reads the k observations from the page-locked slot itself (pinned host
+            // memory is device-addressable under unified addressing); the slot is free again when the kernel is done
+            const int s = f->slot;
+            f->slot = (f->slot + 1) % N_SLOTS;
+            ASB_CUDA(cudaEventSynchronize(f->slot_ev[s]));
+            const size_t off_idx = round_up16((size_t)k * 48), off_new = off_idx + round_up16((size_t)k * 4);
+            unsigned char* hs = f->h_stage + (size_t)s * f->stage_stride;
+            std::memcpy(hs, poses, (size_t)k * 6 * sizeof(double));
+            std::memcpy(hs + off_idx, idx.data(), k * sizeof(int));
+            std::memcpy(hs + off_new, isnew.data(), k);
+            d_pose = reinterpret_cast<double*>(hs);
+            d_idx = reinterpret_cast<int*>(hs + off_idx);
+            d_new = hs + off_new;
+            mapped_slot = s;
+        }
+        SmallFrame a{};
+        a.kind = f->kind; a.as_written = (f->kind == ASB_KIND_EKF && f->quat_mode == ASB_QUAT_AS_WRITTEN) ? 1 : 0;
+        a.state = f->d_state; a.P = f->d_P; a.ld = f->ld;
+        a.idx = d_idx; a.isnew = d_new; a.poses = d_pose; a.k = k;
+        a.nlm0 = (n0 - CAM) / f->D; a.nlm1 = f->nlm;
+        a.nz = f->nz;
+        a.status = f->d_status; a.nu_out = f->d_nu; a.blocks_out = f->d_blocks; a.dx_out = f->d_dx[0];
+        a.host_state = f->h_mirror; a.host_status = reinterpret_cast<int*>(f->h_mirror + f->ncap);
+        rc = small_frame_launch(a, f->stream);
+        if (rc != ASB_OK) return rc;
+        if (mapped_slot >= 0) ASB_CUDA(cudaEventRecord(f->slot_ev[mapped_slot], f->stream));
+        ASB_CUDA(cudaEventRecord(f->ev_ready, f->stream));
+        f->state_at_ready = true;    // asb_get_state waits for this kernel only
+        f->state_on_main = true;
+        f->lazy = false;             // the next pipelined update reads d_P as it is
+        f->side_waited = false;
+        f->dx_last = f->d_dx[0];
+        f->last_k = k;
+        f->last_idx = d_idx;
+        if (feed && poses_out) {
+            ASB_CUDA(cudaEventSynchronize(f->ev_pose));
+            std::memcpy(poses_out, h_slot, (size_t)k * 6 * sizeof(double));
+        }
+        return ASB_OK;
+    }
     if (k > 0) {
         // a pipelined update reads its observations in k_f1 on the side stream
         const bool piped = true;
@@ -713,6 +781,13 @@ int asb_observe_corners(asb_filter* f, const int32_t* ids, const float* corners,
     if (k <= 0 || !ids || !corners || !camera_matrix || !dist_coeffs) return fail(ASB_ERR_BAD_ARG, "bad ids/corners/k/intrinsics");
     CornerFeed feed{corners, camera_matrix, dist_coeffs, marker_size};
     return observe_impl(f, ids, nullptr, k, true, true, &feed, poses_out);
+}
+
+int asb_set_small_map_limit(asb_filter* f, int n_state_max) {
+    ASB_CHECK_HANDLE(f);
+    if (n_state_max < 0) return fail(ASB_ERR_BAD_ARG, "n_state_max must be >= 0");
+    f->small_n_max = n_state_max;
+    return ASB_OK;
 }
 
 int asb_predict(asb_filter* f) {
@@ -844,11 +919,19 @@ int asb_get_state(asb_filter* f, double* out, int n_state) {
     if (f->side && f->state_at_ready) {
         // The state (and the status flag) are final once the last k_f2 is done; the covariance sweep
         // queued behind it keeps running while the host reads the pose and prepares the next frame.
+        // (After a one-launch small-map frame nothing is queued behind: the copies stay on the main stream.)
         int st = 0;
-        ASB_CUDA(cudaStreamWaitEvent(f->side, f->ev_ready, 0));
-        ASB_CUDA(cudaMemcpyAsync(&st, f->d_status, sizeof(int), cudaMemcpyDeviceToHost, f->side));
-        ASB_CUDA(cudaMemcpyAsync(out, f->d_state, n_state * sizeof(double), cudaMemcpyDeviceToHost, f->side));
-        ASB_CUDA(cudaStreamSynchronize(f->side));
+        if (f->state_on_main) {
+            // the kernel left the posterior state and the status in the page-locked mirror
+            ASB_CUDA(cudaEventSynchronize(f->ev_ready));
+            st = *reinterpret_cast<const int*>(f->h_mirror + f->ncap);
+            std::memcpy(out, f->h_mirror, (size_t)n_state * sizeof(double));
+        } else {
+            ASB_CUDA(cudaStreamWaitEvent(f->side, f->ev_ready, 0));
+            ASB_CUDA(cudaMemcpyAsync(&st, f->d_status, sizeof(int), cudaMemcpyDeviceToHost, f->side));
+            ASB_CUDA(cudaMemcpyAsync(out, f->d_state, n_state * sizeof(double), cudaMemcpyDeviceToHost, f->side));
+            ASB_CUDA(cudaStreamSynchronize(f->side));
+        }
         if (st != 0) {
             ASB_CUDA(cudaMemsetAsync(f->d_status, 0, sizeof(int), f->stream));
             return fail(st, "innovation covariance S was not positive definite / finite");

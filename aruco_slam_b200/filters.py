@@ -223,6 +223,8 @@ class _CudaFilter(BaseFilter):
             _lib.check(self._lib.asb_filter_set_stream(self._h, C.c_void_p(self._stream)))
         if getattr(self, "_motion_window", 0):
             _lib.check(self._lib.asb_set_motion_model(self._h, self._motion_window))   # its history restarts
+        if getattr(self, "_small_map_limit", None) is not None:
+            _lib.check(self._lib.asb_set_small_map_limit(self._h, self._small_map_limit))
         if ids.size:
             self.load_checkpoint(state, cov, ids)
         else:
@@ -360,6 +362,12 @@ class _CudaFilter(BaseFilter):
         ``(X_k-1 - X_k-n) / n``.  ``window=0`` (default) is the reference code's behaviour: predict leaves the state."""
         _lib.check(self._lib.asb_set_motion_model(self._h, int(window)))
         self._motion_window = int(window)
+
+    def set_small_map_limit(self, n_state_max: int) -> None:
+        """``observe`` on a map of at most ``n_state_max`` state dimensions runs as one kernel launch per frame
+        (default 192); larger maps, or ``0``, use the pipelined multi-SM engine."""
+        _lib.check(self._lib.asb_set_small_map_limit(self._h, int(n_state_max)))
+        self._small_map_limit = int(n_state_max)
 
     def predict(self) -> None:
         _lib.check(self._lib.asb_predict(self._h))

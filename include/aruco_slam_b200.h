@@ -139,6 +139,14 @@ ASB_API int asb_device_views(asb_filter* f, void** d_state, void** d_cov, int* l
  * augmentation and update.  Per-frame observe() only (asb_stream_run refuses); not in the batched engines. */
 ASB_API int asb_set_motion_model(asb_filter* f, int window);
 
+/* Engine choice of asb_observe / asb_observe_corners (no counterpart in the reference: EKF.observe, EKF:58-82, is one
+ * code path).  A map of at most n_state_max state dimensions whose covariance fits one SM's shared memory is updated
+ * by ONE kernel launch per frame (the resident batched kernel on a single sequence: the reference's own use case,
+ * main/run_slam.py with a few dozen markers); larger maps run the pipelined k_f1 / k_f2 / k_sweep engine over the
+ * whole GPU.  Default 192 (per-frame latency of the two engines crosses near N = 190 on a B200,
+ * tools/small_map_exp.py); 0 = always the pipelined engine.  Both are checked against the same goldens. */
+ASB_API int asb_set_small_map_limit(asb_filter* f, int n_state_max);
+
 /* correct_poses (BASE:274-325, the orientation-ambiguity gate the reference defines and never calls; SURVEY 8f
  * row 3), EKF_Rotations only: observation o is kept (choice[o] = 1) when the angle between R(q_cam) *
  * from_euler('xyz', pose[3:6]) and the landmark's orientation in the state is below threshold_deg

@@ -14,25 +14,34 @@ MODES = {"ekf_as_written": ("ekf", "as_written"), "ekf_scalar_first": ("ekf", "s
 STEP_FRAMES = (0, 1, 2, 29, 30, 31, 40, 41, 80, 119)
 
 
-def make_gpu(kind, quat_mode, calibration, max_landmarks=64):
+ENGINES = ("one_launch", "pipelined")
+
+
+def make_gpu(kind, quat_mode, calibration, max_landmarks=64, engine="one_launch"):
+    """engine: per-frame observe() on a small map is ONE launch of the resident kernel by default
+    (asb_set_small_map_limit); "pipelined" forces the k_f1 / k_f2 / k_sweep engine that large maps use."""
     from aruco_slam_b200 import EKF, EKF_Rotations
     km, dist = calibration
     pose = np.array([0, 0, 0, 1, 0, 0, 0, 0, 0, 0], dtype=float)
     if kind == "ekf":
-        return EKF(pose, camera_matrix=km, dist_coeffs=dist, quat_mode=quat_mode,
-                   max_landmarks=max_landmarks)
-    return EKF_Rotations(pose, camera_matrix=km, dist_coeffs=dist, max_landmarks=max_landmarks)
+        f = EKF(pose, camera_matrix=km, dist_coeffs=dist, quat_mode=quat_mode, max_landmarks=max_landmarks)
+    else:
+        f = EKF_Rotations(pose, camera_matrix=km, dist_coeffs=dist, max_landmarks=max_landmarks)
+    if engine == "pipelined":
+        f.set_small_map_limit(0)
+    return f
 
 
 def order_of(landmarks):
     return [k for k, _ in sorted(landmarks.items(), key=lambda kv: kv[1])]
 
 
+@pytest.mark.parametrize("engine", ENGINES)
 @pytest.mark.parametrize("mode", list(MODES))
-def test_one_step_goldens(golden_steps, calibration, mode):
+def test_one_step_goldens(golden_steps, calibration, mode, engine):
     g = golden_steps
     kind, qm = MODES[mode]
-    f = make_gpu(kind, qm, calibration)
+    f = make_gpu(kind, qm, calibration, engine=engine)
     r = 3 if kind == "ekf" else 7
     d = 3 if kind == "ekf" else 10
     for frame in STEP_FRAMES:
@@ -52,15 +61,16 @@ def test_one_step_goldens(golden_steps, calibration, mode):
             hd[r * o:r * o + r, 0:10] = blocks[o][:, 0:10]
             hd[r * o:r * o + r, s:s + d] = blocks[o][:, 10:]
         assert rel_err(hd, g[f"{key}/H"]) < TOL, key
-        assert_parity(f"single one-step vs reference golden {key}", f.state, f.uncertainty,
+        assert_parity(f"single [{engine}] one-step vs reference golden {key}", f.state, f.uncertainty,
                       g[f"{key}/post_state"], g[f"{key}/post_P"], TOL)
 
 
+@pytest.mark.parametrize("engine", ENGINES)
 @pytest.mark.parametrize("mode", list(MODES))
-def test_free_running_stream(calibration, mode):
+def test_free_running_stream(calibration, mode, engine):
     g = np.load(GOLDEN / f"stream_{mode}.npz")
     kind, qm = MODES[mode]
-    f = make_gpu(kind, qm, calibration, 16)
+    f = make_gpu(kind, qm, calibration, 16, engine=engine)
     off, cam = g["offsets"], g["cam"]
     n_frames = 40 if mode == "ekf_as_written" else len(cam)
     worst = 0.0
@@ -73,18 +83,19 @@ def test_free_running_stream(calibration, mode):
     if mode != "ekf_as_written":
         frames = [(g["ids"][off[t]:off[t + 1]], g["poses"][off[t]:off[t + 1]]) for t in range(n_frames)]
         floor = sensitivity_floor(kind, qm, [f_[0] for f_ in frames], [f_[1] for f_ in frames])
-        assert_parity(f"single free-running {n_frames} frames vs reference stream golden [{mode}]", f.state,
+        assert_parity(f"single [{engine}] free-running {n_frames} frames vs reference stream golden [{mode}]", f.state,
                       f.uncertainty, g["final_state"], g["final_P"], TOL, floor=floor)
         assert order_of(f.landmarks) == [int(i) for i in g["lm"]]
 
 
-def test_as_written_resynchronised_every_frame(calibration):
+@pytest.mark.parametrize("engine", ENGINES)
+def test_as_written_resynchronised_every_frame(calibration, engine):
     """as-written EKF is chaotic, so every frame is compared one-step
     with (state, P) re-synchronised from the oracle (itself pinned to the reference)."""
     from aruco_slam_b200 import synth
     s = synth.make_stream(3, 10, 300, 0.8, "ekf")
     o = ekf_oracle.make("ekf", "as_written")
-    f = make_gpu("ekf", "as_written", calibration, 16)
+    f = make_gpu("ekf", "as_written", calibration, 16, engine=engine)
     worst = 0.0
     for t in range(s.n_frames):
         if t > 0:
@@ -93,7 +104,7 @@ def test_as_written_resynchronised_every_frame(calibration):
         f.observe(s.ids[t], s.poses[t])
         worst = max(worst, rel_err(f.state, o.state), rel_err(f.uncertainty, o.uncertainty))
         if t in (1, 150, s.n_frames - 1):
-            assert_parity(f"single as-written EKF re-synchronised, frame {t}", f.state, f.uncertainty, o.state,
+            assert_parity(f"single [{engine}] as-written EKF re-synchronised, frame {t}", f.state, f.uncertainty, o.state,
                           o.uncertainty, TOL)
     assert worst < TOL, worst
 
@@ -103,10 +114,14 @@ def test_stream_mode_equals_per_frame_calls(calibration):
     from aruco_slam_b200 import synth
     s = synth.make_stream(5, 12, 60, 0.6, "ekf")
     ids, poses, off = s.packed()
-    a = make_gpu("ekf", "scalar_first", calibration, 16)
+    a = make_gpu("ekf", "scalar_first", calibration, 16, engine="pipelined")
     b = make_gpu("ekf", "scalar_first", calibration, 16)
+    c = make_gpu("ekf", "scalar_first", calibration, 16)     # one launch per frame (small map)
     for t in range(s.n_frames):
         a.observe(s.ids[t], s.poses[t])
+        c.observe(s.ids[t], s.poses[t])
+    assert rel_err(a.state, c.state) < 1e-11 and rel_err(a.uncertainty, c.uncertainty) < 1e-11
+    assert order_of(a.landmarks) == order_of(c.landmarks)
     b.stream_upload(ids, poses, off)
     b.stream_run(0, 30)
     b.stream_run(30, 60)
@@ -117,19 +132,20 @@ def test_stream_mode_equals_per_frame_calls(calibration):
     assert order_of(dict(b.get_lm_estimates())) == order_of(a.landmarks)
 
 
+@pytest.mark.parametrize("engine", ENGINES)
 @pytest.mark.parametrize("kind", ["ekf", "rot"])
-def test_chunked_update_many_observations(calibration, kind):
+def test_chunked_update_many_observations(calibration, kind, engine):
     """More rows than one Cholesky chunk holds (m > 126): chunk-sequential conditioning
-    must equal the reference's single batch update."""
+    must equal the reference's single batch update.  (EKF: N = 190, the largest map the one-launch engine takes by default; EKF_Rotations: N = 250, pipelined either way.)"""
     from aruco_slam_b200 import synth
     n = 60 if kind == "ekf" else 24
     s = synth.make_stream(11, n, 6, 1.0, kind)
     o = ekf_oracle.make(kind, "scalar_first")
-    f = make_gpu(kind, "scalar_first", calibration, 64)
+    f = make_gpu(kind, "scalar_first", calibration, 64, engine=engine)
     for t in range(s.n_frames):
         o.observe([int(i) for i in s.ids[t]], s.poses[t])
         f.observe(s.ids[t], s.poses[t])
-        assert_parity(f"single chunked update {kind} frame {t}", f.state, f.uncertainty, o.state, o.uncertainty, TOL)
+        assert_parity(f"single [{engine}] chunked update {kind} frame {t}", f.state, f.uncertainty, o.state, o.uncertainty, TOL)
 
 
 def test_map_build_reduced_c3(calibration):
@@ -245,14 +261,15 @@ def test_missing_calibration_raises(tmp_path, monkeypatch):
         EKF(np.array([0, 0, 0, 1, 0, 0, 0, 0, 0, 0.0]))
 
 
+@pytest.mark.parametrize("engine", ENGINES)
 @pytest.mark.parametrize("kind", ["ekf", "rot"])
-def test_process_detections_fused_equals_separate_calls(calibration, kind):
+def test_process_detections_fused_equals_separate_calls(calibration, kind, engine):
     """BASE:196-212: process_detections (IPPE + observe in one library call, poses kept on the
     device) gives exactly what estimate_pose_of_markers followed by observe gives."""
     from aruco_slam_b200 import synth
     km, dist = calibration
-    a = make_gpu(kind, "as_written", calibration)
-    b = make_gpu(kind, "as_written", calibration)
+    a = make_gpu(kind, "as_written", calibration, engine=engine)
+    b = make_gpu(kind, "as_written", calibration, engine=engine)
     rng = np.random.default_rng(5)
     corners_all = synth.make_corner_sets(400, km, dist, seed=3)
     for frame in range(12):
