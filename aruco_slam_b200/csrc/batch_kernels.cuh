@@ -77,6 +77,7 @@ k_batch(BatchParams p) {
     constexpr int D = Dims<KIND>::D, R = Dims<KIND>::R, W = CAM + D;
     constexpr int MC = R * CK;           // max rows per chunk
     constexpr int LDS_S = (MC + 1) | 1;  // leading dim of S (+ appended nu row)
+    __shared__ __align__(16) double s_col[64];   // single-warp Cholesky: column j of L, two buffers
     extern __shared__ __align__(16) unsigned char smraw[];
     const int tid = threadIdx.x;
     const int ncap = CAM + D * p.max_lm;
@@ -356,9 +357,9 @@ k_batch(BatchParams p) {
                 bool bad = false;
                 static_assert(MC + 1 <= 32, "the single-warp Cholesky holds one row of [S; nu^T] per lane");
                 {
-                    // Cholesky of [S; nu^T] by ONE warp, lane i holding row i in registers; column j
-                    // of L is broadcast with shuffles (no shared-memory round trips, no CTA barrier
-                    // inside the factorisation)
+                    // Cholesky of [S; nu^T] by ONE warp, lane i holding row i in registers; the pivot is
+                    // broadcast with a shuffle, column j of L through a 32-double shared buffer (no CTA
+                    // barrier inside the factorisation)
                     if (tid < 32) {
                         const int i = tid;
                         double a[MC], dv[MC];
@@ -374,10 +375,16 @@ k_batch(BatchParams p) {
                                 dv[j] = rs;
                                 const double lij = a[j] * rs;
                                 a[j] = lij;
+                                // column j of L to every lane through shared memory: one store and ceil((MC - j) / 2)
+                                // 128-bit broadcast loads instead of 2 (MC - 1 - j) shuffle instructions per pivot
+                                double* col = s_col + 32 * (j & 1);
+                                col[i] = lij;
+                                __syncwarp();
 #pragma unroll
-                                for (int c = j + 1; c < MC; ++c) {
-                                    const double lcj = __shfl_sync(0xffffffffu, lij, c);
-                                    a[c] -= lij * lcj;
+                                for (int c = (j + 1) & ~1; c < MC; c += 2) {
+                                    const double2 l2 = *reinterpret_cast<const double2*>(col + c);
+                                    if (c > j) a[c] -= lij * l2.x;
+                                    if (c + 1 < MC) a[c + 1] -= lij * l2.y;
                                 }
                             }
                         }
