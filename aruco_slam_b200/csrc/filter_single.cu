@@ -96,11 +96,11 @@ struct asb_filter {
     unsigned int* d_tail = nullptr;   // [0,1] tile counters, [2,3] range counters, used alternately by successive sweeps (sweep.cuh)
     int reserve_sm = -1, reserve_ctas = 2;   // per-frame mode: the SM kept free for k_f1 (the highest %smid seen at creation)
     unsigned int sweep_seq = 0;
-    int tail_tiles = 2;        // tiles per CTA handed out dynamically (ASB_TAIL)
-    int use_vt = 0;            // ASB_VT=1: k_f2 also writes the panel by state column for k_f1 (bulk copies instead of a gather)
-    int lower_only = 0;        // pipelined engine: the sweeps keep only the lower triangle of P up to date (ASB_FULL_P=1: both)
+    int tail_tiles = 2;        // tiles per CTA handed out dynamically at the end of a sweep
+    int use_vt = 0;            // 1: k_f2 also writes the panel by state column for k_f1 (bulk copies instead of a gather); measured slower, kept off
+    int lower_only = 0;        // pipelined engine: the sweeps keep only the lower triangle of P up to date
     bool defer = false;        // set by asb_stream_run around its frame loop
-    int pdl = 1;               // ASB_PDL=0: stream mode uses the side-stream engine as well
+    int pdl = 1;               // stream mode launches its kernels as programmatic dependents of each other
 
     // observe() on a map of at most small_n_max state dims runs as ONE launch of the resident batched kernel
     // (common.cuh SmallFrame); larger maps take the pipelined k_f1 / k_f2 / k_sweep engine.  0 = never.
