@@ -148,6 +148,32 @@ def test_chunked_update_many_observations(calibration, kind, engine):
         assert_parity(f"single [{engine}] chunked update {kind} frame {t}", f.state, f.uncertainty, o.state, o.uncertainty, TOL)
 
 
+@pytest.mark.parametrize("kind", ["ekf", "rot"])
+def test_engines_hand_over_to_each_other(calibration, kind):
+    """One filter, the per-frame engine switched back and forth (asb_set_small_map_limit): the one-launch kernel
+    must find the covariance the pipelined engine left (ping-pong buffers, lazy operand) and the other way round;
+    update() / predict() on their own always take the pipelined kernels."""
+    from aruco_slam_b200 import synth
+    s = synth.make_stream(21, 9, 60, 0.7, kind)
+    o = ekf_oracle.make(kind, "scalar_first")
+    f = make_gpu(kind, "scalar_first", calibration, 16)
+    pattern = (4096, 0, 0, 4096, 4096, 0, 4096)
+    for t in range(s.n_frames):
+        f.set_small_map_limit(pattern[t % len(pattern)])
+        ids, poses = [int(i) for i in s.ids[t]], s.poses[t]
+        if t % 11 == 5 and all(i in o.landmarks for i in ids):
+            o.predict(); o.update(ids, poses)
+            f.predict(); f.update(s.ids[t], poses)
+        else:
+            o.observe(ids, poses)
+            f.observe(s.ids[t], poses)
+        if t % 7 == 0 or t == s.n_frames - 1:
+            assert rel_err(f.state, o.state) < TOL, t
+    assert_parity(f"single {kind}, engines alternating per frame, 60 frames", f.state, f.uncertainty, o.state,
+                  o.uncertainty, TOL)
+    assert order_of(f.landmarks) == order_of(o.landmarks)
+
+
 def test_map_build_reduced_c3(calibration):
     """C3 at reduced size: 200 markers added 20 per frame, then updates
     of 20 known markers; full build + run parity against the oracle."""
