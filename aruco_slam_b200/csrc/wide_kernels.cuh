@@ -678,7 +678,7 @@ __global__ void __launch_bounds__(256, 3) k_wide_panel(WideParams p) {
 // (TMA bulk copies, full / empty mbarriers) by a dedicated producer warp, so the ring never drains between
 // tiles.  8 consumer warps of 32 x 16 (4 x 2 DMMA tiles); the P sub-tiles go HBM -> registers in the
 // accumulator-fragment layout at the start of a tile and are consumed after its k-loop.
-constexpr int W_SWEEP_THREADS = 288;
+constexpr int W_SWEEP_THREADS = 320;   // 8 consumer warps, a producer warp, a prefetch warp (9 warps are allocated as 10 anyway)
 // "empty" arrival of a consumer warp.  .relaxed: the default .release semantics make the arrive wait for the
 // warp's outstanding global loads (the P sub-tiles prefetched for the end of the tile), which serialises what
 // the prefetch is there to overlap; the stage's shared-memory reads have already been consumed by issued MMAs.
@@ -732,6 +732,16 @@ __global__ void __launch_bounds__(W_SWEEP_THREADS, 2) k_wide_sweep(WideParams p)
                     bulk_g2s(ring + (size_t)st * SLAB_D, VJg + (long long)s * SLAB_D, bytes, &bar_full[st]);
                 }
             }
+        }
+        return;
+    }
+    if (warp == 9) {   // ---- L2 prefetch of the strip's P tiles: row i8 of 8 x 8 tiles is one contiguous run ----
+        if (lane < 8) {
+            const int i8 = 8 * I + lane;
+            if (i8 < nt8)
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(P + ((long long)tri(i8) << 6)),
+                             "r"((uint32_t)((i8 + 1) * 512))
+                             : "memory");
         }
         return;
     }
