@@ -545,6 +545,18 @@ __global__ void __launch_bounds__(256, 3) k_wide_panel(WideParams p) {
     const double* gD = p.Dinv + (long long)seq * (NB * 64);
     const bool add_q = p.round == 0;
     for (int o = tid; o < kc; o += NT) s_li[o] = CAM + D * p.idx[(long long)seq * p.max_obs + c0 + o];
+    {   // L2 prefetch of the landmark rows of P this CTA will gather in phase 1: observation tid / 16, its (up to) two
+        // row tiles x the eight column tiles of this 64-column block, one 512-byte tile per thread
+        const int o = tid >> 4, r = (tid >> 3) & 1, c = tid & 7;
+        if (o < kc) {
+            const int li = CAM + D * __ldg(p.idx + (long long)seq * p.max_obs + c0 + o);
+            const int i8 = (li >> 3) + r, j8 = 8 * jb64 + c;
+            if (i8 <= ((li + D - 1) >> 3) && 8 * j8 < n) {
+                const long long off = i8 >= j8 ? ((long long)(tri(i8) + j8) << 6) : ((long long)(tri(j8) + i8) << 6);
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], 512;" ::"l"(P + off) : "memory");
+            }
+        }
+    }
     const double* gy = p.y + (long long)seq * M8;
     for (int e = tid; e < 12 * 64; e += NT) {
         const int c = e >> 6, col = col0 + (e & 63);
