@@ -166,7 +166,21 @@ k_batch(BatchParams p) {
             if constexpr (!SINGLE) {
                 const long long orec = (long long)(seq % p.obs_seqs) * p.n_frames + t;
                 ob = p.offsets[orec];
-                k = (int)(p.offsets[orec + 1] - ob);
+                const long long ob1 = p.offsets[orec + 1];
+                k = (int)(ob1 - ob);
+                // next frame's observations towards L2 now (its count is not known yet: a window of max_obs, clipped
+                // to the stream): by the time this frame's update is done they are an L2 hit, not a DRAM round trip
+                if (tid == 0 && t + 1 < p.t1) {
+                    const long long last = p.offsets[(long long)p.obs_seqs * p.n_frames];
+                    const long long w = min((long long)p.max_obs, last - ob1);
+                    if (w > 0) {
+                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p.poses + 6 * ob1),
+                                     "r"((uint32_t)(w * 48)) : "memory");
+                        const long long i0 = ob1 & ~3ll;
+                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p.ids + i0),
+                                     "r"((uint32_t)(((ob1 + w - i0) * 4 + 15) & ~15ll)) : "memory");
+                    }
+                }
             }
             if (k == 0) continue;  // no detection: no predict either (base_filter.py:197-204)
             if (k > p.max_obs) {
@@ -181,13 +195,19 @@ k_batch(BatchParams p) {
             } else {
                 for (int o = tid; o < k; o += NT) s_ids[o] = p.ids[ob + o];
                 __syncthreads();
-                for (int o = tid; o < k; o += NT) {
-                    const int id = s_ids[o];
+                // eight lanes per observation walk the id table with stride 8 (ids are unique in the table: at most one
+                // lane finds it), combined with three shuffles - a quarter of the serial probes of one thread per id
+                for (int o0 = 0; o0 < k; o0 += NT / 8) {
+                    const int o = o0 + (tid >> 3);
+                    const int id = o < k ? s_ids[o] : -1;
                     int found = -1;
-                    for (int i = 0; i < nlm; ++i)
-                        if (s_tab[i] == id) { found = i; break; }
-                    s_idx[o] = found;
-                    s_new[o] = 0;
+                    if (o < k)
+                        for (int i = tid & 7; i < nlm; i += 8)
+                            if (s_tab[i] == id) found = i;
+                    found = max(found, __shfl_xor_sync(0xffffffffu, found, 1));
+                    found = max(found, __shfl_xor_sync(0xffffffffu, found, 2));
+                    found = max(found, __shfl_xor_sync(0xffffffffu, found, 4));
+                    if (o < k && (tid & 7) == 0) { s_idx[o] = found; s_new[o] = 0; }
                 }
                 __syncthreads();
                 if (tid == 0) {  // unseen ids, in frame order; duplicates bind to the first
