@@ -189,12 +189,14 @@ k_batch(BatchParams p) {
             }
             // ---- load the frame, associate ids ---------------------------------------
             for (int e = tid; e < 6 * k; e += NT) s_pose[e] = p.poses[6 * ob + e];
+            int any_unseen = 1;
             if constexpr (SINGLE) {   // associated on the host (first-seen order, the same rule as below)
                 for (int o = tid; o < k; o += NT) { s_idx[o] = p.one_idx[o]; s_new[o] = p.one_new[o]; }
                 if (tid == 0) s_misc[0] = p.one_nlm1;
             } else {
                 for (int o = tid; o < k; o += NT) s_ids[o] = p.ids[ob + o];
                 __syncthreads();
+                int unseen = 0;
                 // eight lanes per observation walk the id table with stride 8 (ids are unique in the table: at most one
                 // lane finds it), combined with three shuffles - a quarter of the serial probes of one thread per id
                 for (int o0 = 0; o0 < k; o0 += NT / 8) {
@@ -208,9 +210,11 @@ k_batch(BatchParams p) {
                     found = max(found, __shfl_xor_sync(0xffffffffu, found, 2));
                     found = max(found, __shfl_xor_sync(0xffffffffu, found, 4));
                     if (o < k && (tid & 7) == 0) { s_idx[o] = found; s_new[o] = 0; }
+                    unseen |= (o < k && found < 0);
                 }
-                __syncthreads();
-                if (tid == 0) {  // unseen ids, in frame order; duplicates bind to the first
+                // (the common frame sees known markers only: then the serial pass below and its barrier are skipped)
+                any_unseen = __syncthreads_or(unseen);
+                if (any_unseen && tid == 0) {  // unseen ids, in frame order; duplicates bind to the first
                     int cur = nlm;
                     for (int o = 0; o < k; ++o) {
                         if (s_idx[o] >= 0) continue;
@@ -227,9 +231,9 @@ k_batch(BatchParams p) {
                     s_misc[0] = cur;
                 }
             }
-            __syncthreads();
+            if (SINGLE || any_unseen) __syncthreads();
             BPROF(0);
-            const int nlm1 = s_misc[0];
+            const int nlm1 = (SINGLE || any_unseen) ? s_misc[0] : nlm;
             if (s_misc[1] == ASB_ERR_CAPACITY) break;
             const int n1 = CAM + D * nlm1;
             // ---- augmentation: new landmark states, block-diagonal covariance growth -
