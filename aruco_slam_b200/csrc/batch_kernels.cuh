@@ -76,6 +76,7 @@ __global__ void __launch_bounds__(NT, (NT <= 128 && KIND == 0 && !SINGLE) ? 3 : 
 k_batch(BatchParams p) {
     constexpr int D = Dims<KIND>::D, R = Dims<KIND>::R, W = CAM + D;
     constexpr int MC = R * CK;           // max rows per chunk
+    constexpr int BLK = (R * W + 1) & ~1;   // doubles per observation block in shared memory (even: 16-byte aligned)
     constexpr int LDS_S = (MC + 1) | 1;  // leading dim of S (+ appended nu row)
     __shared__ __align__(16) double s_col[64];   // single-warp Cholesky: column j of L, two buffers
     extern __shared__ __align__(16) unsigned char smraw[];
@@ -90,7 +91,7 @@ k_batch(BatchParams p) {
     // measurement-model blocks and raw innovations of TWO chunks: the next chunk's model is evaluated by
     // the idle warps while warp 0 factors S (the state it is evaluated at does not change inside a frame)
     double* s_blk0 = s_G + (size_t)MC * npad;                 // 2 x (CK x R x W)
-    double* s_nu0 = s_blk0 + 2 * CK * R * W;                  // 2 x MC (padded)
+    double* s_nu0 = s_blk0 + 2 * CK * BLK;                    // 2 x MC (padded)
     constexpr int NU_LD = (MC + 3) & ~3;
     double* s_S = s_nu0 + 2 * NU_LD;                          // (MC+1) x LDS_S
     double* s_dinv = s_S + (MC + 1) * LDS_S;                  // MC
@@ -277,11 +278,11 @@ k_batch(BatchParams p) {
                 const int li = CAM + D * s_idx[c0m + o];
 #pragma unroll
                 for (int c = 0; c < D; ++c) lm[c] = s_state[li + c];
-                observation_model<KIND>(s_state, lm, s_pose + 6 * (c0m + o), lnu, s_blk0 + (which * CK + o) * R * W);
+                observation_model<KIND>(s_state, lm, s_pose + 6 * (c0m + o), lnu, s_blk0 + (which * CK + o) * BLK);
 #pragma unroll
                 for (int r = 0; r < R; ++r) s_nu0[which * NU_LD + R * o + r] = lnu[r];
                 if constexpr (SINGLE) {
-                    const double* blk = s_blk0 + (which * CK + o) * R * W;
+                    const double* blk = s_blk0 + (which * CK + o) * BLK;
 #pragma unroll
                     for (int r = 0; r < R; ++r) p.nu_out[R * (c0m + o) + r] = lnu[r];
                     for (int c = 0; c < R * W; ++c) p.blocks_out[(size_t)(c0m + o) * R * W + c] = blk[c];
@@ -294,7 +295,7 @@ k_batch(BatchParams p) {
                 const int kc = min(CK, k - c0);
                 const int mc = R * kc;
                 const int which = (c0 / CK) & 1;
-                const double* s_blk = s_blk0 + which * CK * R * W;
+                const double* s_blk = s_blk0 + which * CK * BLK;
                 const double* s_nu = s_nu0 + which * NU_LD;
                 const int kc_next = min(CK, k - c0 - CK);   // <= 0: this is the last chunk
                 // G = H P  (mc x n): one thread per state column; the 10 camera rows of P are
@@ -317,19 +318,40 @@ k_batch(BatchParams p) {
                         for (int c = 0; c < CAM; ++c) pc[c] = pget(c, j);
                     }
                     for (int o = 0; o < kc; ++o) {
-                        const double* blk = s_blk + o * R * W;
                         const int li = CAM + D * s_idx[c0 + o];
                         double pl[D], acc[R];
 #pragma unroll
                         for (int c = 0; c < D; ++c) pl[c] = pget(li + c, j);
+                        // the observation's R x W block as 128-bit broadcast loads (blocks start 16-byte aligned:
+                        // stride BLK), half the shared-memory instructions of one 64-bit load per coefficient
+                        if constexpr (BLK <= 40) {
+                            double hb[BLK];
+                            const double2* blk2 = reinterpret_cast<const double2*>(s_blk + o * BLK);
 #pragma unroll
-                        for (int r = 0; r < R; ++r) {
-                            double sv = 0.0;
+                            for (int e = 0; e < BLK / 2; ++e) {
+                                const double2 v = blk2[e];
+                                hb[2 * e] = v.x; hb[2 * e + 1] = v.y;
+                            }
 #pragma unroll
-                            for (int c = 0; c < CAM; ++c) sv += blk[r * W + c] * pc[c];
+                            for (int r = 0; r < R; ++r) {
+                                double sv = 0.0;
 #pragma unroll
-                            for (int c = 0; c < D; ++c) sv += blk[r * W + CAM + c] * pl[c];
-                            acc[r] = sv;
+                                for (int c = 0; c < CAM; ++c) sv += hb[r * W + c] * pc[c];
+#pragma unroll
+                                for (int c = 0; c < D; ++c) sv += hb[r * W + CAM + c] * pl[c];
+                                acc[r] = sv;
+                            }
+                        } else {   // EKF_Rotations: 140 coefficients do not fit in registers
+                            const double* blk = s_blk + o * BLK;
+#pragma unroll
+                            for (int r = 0; r < R; ++r) {
+                                double sv = 0.0;
+#pragma unroll
+                                for (int c = 0; c < CAM; ++c) sv += blk[r * W + c] * pc[c];
+#pragma unroll
+                                for (int c = 0; c < D; ++c) sv += blk[r * W + CAM + c] * pl[c];
+                                acc[r] = sv;
+                            }
                         }
 #pragma unroll
                         for (int r = 0; r < R; ++r) s_G[(R * o + r) * npad + gcol(j)] = acc[r];
@@ -354,7 +376,7 @@ k_batch(BatchParams p) {
                     double s;
                     if (a < mc) {
                         const int o2 = b / R, ib = b - o2 * R;
-                        const double* hb = s_blk + o2 * R * W + ib * W;
+                        const double* hb = s_blk + o2 * BLK + ib * W;
                         const double* g = s_G + a * npad;
                         const int li = CAM + D * s_idx[c0 + o2];
                         s = (a == b) ? p.nz.r : 0.0;
@@ -366,7 +388,7 @@ k_batch(BatchParams p) {
                         s = s_nu[b];
                         if (c0 > 0) {   // nu' = nu - H delta (delta = the correction accumulated by the chunks before)
                             const int o2 = b / R, ib = b - o2 * R;
-                            const double* hb = s_blk + o2 * R * W + ib * W;
+                            const double* hb = s_blk + o2 * BLK + ib * W;
                             const int li = CAM + D * s_idx[c0 + o2];
 #pragma unroll
                             for (int c = 0; c < CAM; ++c) s -= hb[c] * s_delta[c];

@@ -80,7 +80,7 @@ static cudaError_t dmalloc(T** p, size_t count) {
 static size_t batch_smem_base(int D, int R, int CK, int max_lm, int max_obs) {
     const int W = CAM + D, MC = R * CK, LDS_S = (MC + 1) | 1;
     const int ncap = CAM + D * max_lm, npad = batch_npad(ncap);
-    size_t dbl = (size_t)npad * 2 + (size_t)MC * npad + (size_t)2 * CK * R * W + 2 * ((MC + 3) & ~3) +
+    size_t dbl = (size_t)npad * 2 + (size_t)MC * npad + (size_t)2 * CK * ((R * W + 1) & ~1) + 2 * ((MC + 3) & ~3) +
                  (size_t)(MC + 1) * LDS_S + ((MC + 3) & ~3) + (size_t)max_obs * 6;
     size_t ints = (size_t)max_obs * 3 + max_lm + 4;
     return dbl * 8 + ints * 4 + 16;
