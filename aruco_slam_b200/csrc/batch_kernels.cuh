@@ -520,12 +520,15 @@ k_batch(BatchParams p) {
             // ---- state update + quaternion reset --------------------------------------
             if constexpr (SINGLE)
                 for (int i = tid; i < n; i += NT) p.dx_out[i] = s_delta[i];
-            if (tid == 0) camera_reset(s_state, s_delta, p.as_written);
+            // No barrier here: the serial camera reset (two normalisations) runs on the last thread while the others
+            // already fetch and associate the next frame's observations (neither touches the state or delta); the
+            // barrier after the association orders it before the next model evaluation / predict.
+            if (tid == NT - 1) camera_reset(s_state, s_delta, p.as_written);
             for (int l = tid; l < nlm; l += NT)
                 landmark_update<KIND>(s_state + CAM + D * l, s_delta + CAM + D * l);
-            __syncthreads();
             BPROF(9);
         }  // frames
+        __syncthreads();
 
         // ---- write back -----------------------------------------------------------------
         for (int i = tid; i < n; i += NT) g_state[i] = s_state[i];
