@@ -267,7 +267,8 @@ k_batch(BatchParams p) {
                 const int npadc = 8 * ((n + 7) >> 3) - n;
                 for (int e = tid; e < MC * npadc; e += NT) s_G[(e / npadc) * npad + gcol(n + e % npadc)] = 0.0;
             }
-            __syncthreads();
+            // (no barrier: the first chunk's model evaluation below touches neither P, delta nor the panel; the barrier
+            // after it covers both)
 
             BPROF(1);
             // ---- update, CK markers at a time -----------------------------------------
