@@ -8,8 +8,12 @@
 //   processed in chunks of CK markers: with R = r I block-diagonal and H evaluated once
 //   at the pre-update state, chunk-sequential conditioning with the innovation corrected
 //   by H delta is algebraically the batch update (DESIGN.md "chunked update").
-//   Each chunk: G = H P, S = G H^T + R, blocked Cholesky (3x3 / 7x7 diagonal blocks
-//   factored redundantly in registers), V = L^-1 G, delta += V^T y, P -= V^T V.
+//   Each chunk: G = H P (one thread per state column), S = G H^T + R, Cholesky of [S; nu^T] by ONE
+//   warp (a row per lane in registers, the column of L exchanged through shared memory) while the other
+//   warps evaluate the next chunk's measurement model, V = L^-1 G and delta += V^T y (one thread per
+//   column), P -= V^T V on the tile-blocked lower triangle (one thread per 4 x 8 register tile).
+// The SINGLE instantiation runs the same frame for ONE asb_filter with a small map (filter_single.cu,
+// common.cuh SmallFrame): its dense covariance in, the same phases, its dense covariance out.
 #pragma once
 #include <cstdint>
 
