@@ -303,14 +303,14 @@ def leg_c3(torch, stream_ptr, hbm_peak, fp64_peak):
         "value": 20.0 * timed_frames / (ms * 1e-3), "unit": UNIT, "us_per_frame": 1e3 * ms / timed_frames,
         "frames": timed_frames, "gpu_launches_per_frame": 3,
         "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": ach / hbm_peak, "traffic": 257.5e6,
+                     "frac": ach / hbm_peak, "traffic": 256.3e6,
                      "dense_equivalent": {"achieved": dense_eq, "frac": dense_eq / hbm_peak,
                                           "note": "16 N^2 B per frame (SURVEY.md 8d contract figure: one read + one "
                                                   "write of a DENSE P) / whole-frame time"},
                      "note": "achieved = 8 N^2 B per frame (lower triangle read + write, what k_sweep moves) / "
                              "whole-frame time (k_f2 + k_sweep on the critical path, k_f1 of the next frame "
                              "overlapped); traffic = dram read + write bytes of one k_sweep launch, ncu --set full "
-                             "(profiles/r01c_k_sweep.txt).  The kernel is bound by the FP64 tensor pipe, see "
+                             "(profiles/r02_k_sweep.txt: 154.35 MB read + 101.95 MB written).  The kernel is bound by the FP64 tensor pipe, see "
                              "roofline_fp64"},
         "roofline_fp64": {"bound": "tensor", "achieved": tf, "peak": fp64_peak, "unit": "TFLOP/s",
                           "frac": tf / fp64_peak, "peak_source": "asb_fp64_peak(which=1): mma.sync m8n8k4 f64 (DMMA) "
