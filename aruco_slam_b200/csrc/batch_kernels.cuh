@@ -75,7 +75,7 @@ __device__ __forceinline__ double psym(const double* P, int i, int j) {
     return j <= i ? P[tri(i) + j] : P[tri(j) + i];
 }
 
-template <int KIND, int CK, int NT, bool SINGLE = false>
+template <int KIND, int CK, int NT, bool SINGLE = false, bool PROF = false>
 __global__ void __launch_bounds__(NT, (NT <= 128 && KIND == 0 && !SINGLE) ? 3 : 1)
 k_batch(BatchParams p) {
     constexpr int D = Dims<KIND>::D, R = Dims<KIND>::R, W = CAM + D;
@@ -109,11 +109,13 @@ k_batch(BatchParams p) {
         (reinterpret_cast<uintptr_t>(s_misc + 4) + 15) & ~uintptr_t(15));  // packed, if it fits
 
     // phase profile of CTA 0 (clock64 deltas accumulated per phase in registers), measurement aid
-    long long prof_t = clock64(), prof_acc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
-    const bool prof_on = p.prof && blockIdx.x == 0 && tid == 0;
+    // (PROF instantiation only - asb_batch_profile switches a handle to it: the ten 64-bit accumulators cost the
+    // production kernel, which sits at its register cap, twenty registers and a spill slot each)
+    [[maybe_unused]] long long prof_t = PROF ? clock64() : 0, prof_acc[PROF ? 10 : 1] = {};
+    const bool prof_on = PROF && p.prof && blockIdx.x == 0 && tid == 0;
 #define BPROF(slot)                                  \
     do {                                             \
-        if (prof_on) {                               \
+        if constexpr (PROF) if (prof_on) {           \
             const long long now_ = clock64();        \
             prof_acc[slot] += now_ - prof_t;         \
             prof_t = now_;                           \
@@ -556,8 +558,9 @@ k_batch(BatchParams p) {
         }
         __syncthreads();
     }
-    if (prof_on)
-        for (int i = 0; i < 10; ++i) p.prof[i] += (unsigned long long)prof_acc[i];
+    if constexpr (PROF)
+        if (prof_on)
+            for (int i = 0; i < 10; ++i) p.prof[i] += (unsigned long long)prof_acc[i];
 #undef BPROF
 }
 

@@ -26,6 +26,7 @@ struct asb_batch {
     int *d_nlm = nullptr, *d_tab = nullptr, *d_status = nullptr, *d_ids = nullptr;
     long long* d_off = nullptr;
     unsigned long long* d_prof = nullptr;
+    bool profiling = false;   // asb_batch_profile was called: later runs use the instrumented instantiation of k_batch
     int n_frames = 0;
     int obs_seqs = 0;          // distinct observation streams on the device (n_seq, or fewer after an upload_tiled)
     long long n_obs = 0;
@@ -86,9 +87,9 @@ static size_t batch_smem_base(int D, int R, int CK, int max_lm, int max_obs) {
     return dbl * 8 + ints * 4 + 16;
 }
 
-template <int KIND, int CK, int NT>
+template <int KIND, int CK, int NT, bool PROF = false>
 static int launch_batch(asb_batch* b, const BatchParams& p, size_t smem, int grid, cudaStream_t st) {
-    auto kern = k_batch<KIND, CK, NT>;
+    auto kern = k_batch<KIND, CK, NT, false, PROF>;
     ASB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     ASB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     // persistent grid: exactly the CTAs that are co-resident (registers can bind before shared memory)
@@ -103,6 +104,10 @@ static int launch_batch(asb_batch* b, const BatchParams& p, size_t smem, int gri
 
 template <int KIND, int CK>
 static int launch_batch_nt(asb_batch* b, const BatchParams& p, size_t smem, int grid, cudaStream_t st) {
+    if (b->profiling) {   // phase-profile instantiation (asb_batch_profile has been called on this handle)
+        if (b->threads >= 256) return launch_batch<KIND, CK, 256, true>(b, p, smem, grid, st);
+        return launch_batch<KIND, CK, 128, true>(b, p, smem, grid, st);
+    }
     if (b->threads >= 256) return launch_batch<KIND, CK, 256>(b, p, smem, grid, st);
     return launch_batch<KIND, CK, 128>(b, p, smem, grid, st);
 }
@@ -555,6 +560,7 @@ int asb_batch_profile(asb_batch* b, double clocks[10]) {
     if (!clocks) return fail(ASB_ERR_BAD_ARG, "clocks is NULL");
     unsigned long long t[16];
     ASB_CUDA(cudaStreamSynchronize(b->stream));
+    b->profiling = true;
     ASB_CUDA(cudaMemcpy(t, b->d_prof, sizeof t, cudaMemcpyDeviceToHost));
     ASB_CUDA(cudaMemset(b->d_prof, 0, sizeof t));
     for (int i = 0; i < 10; ++i) clocks[i] = (double)t[i];
